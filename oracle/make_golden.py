@@ -1,0 +1,105 @@
+"""TEST INFRASTRUCTURE ONLY -- generate tests/golden/*.npz from the LIVE reference.
+
+Run in the build container (where /root/reference exists):
+
+    python -m oracle.make_golden            # writes tests/golden/<case>.npz and prints the
+                                            # reference-vs-restatement agreement for every key
+
+Each case runs the unmodified reference `MapAnything.infer(views, use_amp=False)` on CPU/fp32 with
+the deterministic synthetic checkpoint of oracle/weights.py and stores the prediction dicts
+(sub-sampled for the full-resolution case so the fixture stays small; masks are bit-packed in
+full).  tests/test_oracle_golden.py re-runs the restatement (oracle/mapanything_oracle.py) on the
+same inputs anywhere (no /root/reference needed) and compares against these files; the `-m gpu`
+tests compare the CUDA path against the same files.
+"""
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if _ROOT not in sys.path:
+    sys.path.insert(0, _ROOT)
+
+from oracle import weights  # noqa: E402
+
+GOLDEN_DIR = os.path.join(_ROOT, "tests", "golden")
+
+DENSE_KEYS = ["pts3d", "pts3d_cam", "ray_directions", "depth_along_ray", "depth_z", "conf",
+              "non_ambiguous_mask_logits", "img_no_norm"]
+SMALL_KEYS = ["cam_trans", "cam_quats", "camera_poses", "intrinsics", "metric_scaling_factor"]
+MASK_KEYS = ["non_ambiguous_mask", "mask"]
+
+# name -> (num_views, H, W, multimodal, subsample stride, infer kwargs)
+CASES = {
+    "c1_n2_392x518": (2, 392, 518, False, 7, {}),
+    "c1_loose_n2_392x518": (2, 392, 518, False, 7, dict(edge_depth_threshold=0.1, edge_normal_threshold=30.0)),
+    "small_n3_70x98": (3, 70, 98, False, 1, {}),
+    "small_mm_n3_70x98": (3, 70, 98, True, 1, {}),
+    "small_conf_n2_56x84": (2, 56, 84, False, 1, dict(apply_confidence_mask=True, confidence_percentile=25)),
+}
+
+
+def case_views(name):
+    n, H, W, mm, _, _ = CASES[name]
+    views = weights.synthetic_views(n, H, W, seed=1)
+    if mm:
+        views = weights.add_multimodal_inputs(views, seed=2)
+    return views
+
+
+def pack_outputs(preds, stride):
+    out = {}
+    for i, p in enumerate(preds):
+        for k in DENSE_KEYS:
+            t = p[k].detach().cpu().numpy()
+            out[f"v{i}.{k}"] = np.ascontiguousarray(t[:, ::stride, ::stride]).astype(np.float32)
+        for k in SMALL_KEYS:
+            out[f"v{i}.{k}"] = p[k].detach().cpu().numpy().astype(np.float32)
+        for k in MASK_KEYS:
+            m = p[k].detach().cpu().numpy().astype(bool)
+            out[f"v{i}.{k}.shape"] = np.array(m.shape, np.int64)
+            out[f"v{i}.{k}.bits"] = np.packbits(m.reshape(-1))
+    return out
+
+
+def main(only=None):
+    from oracle import mapanything_oracle as orc
+    from oracle import ref_shim
+
+    os.makedirs(GOLDEN_DIR, exist_ok=True)
+    sd = weights.synthetic_state_dict()
+    model = ref_shim.build_reference_model(sd)
+    for name, (n, H, W, mm, stride, kw) in CASES.items():
+        if only and name not in only:
+            continue
+        views = case_views(name)
+        t0 = time.time()
+        ref = model.infer([dict(v) for v in views], use_amp=False, amp_dtype="fp32", **kw)
+        t_ref = time.time() - t0
+        gold = pack_outputs(ref, stride)
+        np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"), **gold)
+        t0 = time.time()
+        mine = pack_outputs(orc.infer(sd, [dict(v) for v in views], **kw), stride)
+        t_orc = time.time() - t0
+        print(f"== {name}: reference {t_ref:.1f}s, restatement {t_orc:.1f}s")
+        worst = 0.0
+        for k in sorted(gold):
+            a, b = gold[k], mine[k]
+            if k.endswith(".bits"):
+                nd = int(np.unpackbits(a ^ b).sum())
+                print(f"   {k:44s} differing bits {nd}")
+            elif k.endswith(".shape"):
+                assert (a == b).all(), k
+            else:
+                rel = float(np.linalg.norm(a - b) / (np.linalg.norm(a) + 1e-30))
+                worst = max(worst, rel)
+                if rel > 1e-5:
+                    print(f"   {k:44s} rel-L2 {rel:.3e}")
+        print(f"   worst rel-L2 over float keys: {worst:.3e}")
+
+
+if __name__ == "__main__":
+    main(sys.argv[1:] or None)

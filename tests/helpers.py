@@ -1,0 +1,85 @@
+"""Shared comparison helpers for the parity tests (golden fixtures <-> oracle <-> CUDA path)."""
+import math
+import os
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+
+MASKED_KEYS = ("pts3d", "pts3d_cam", "depth_along_ray", "depth_z")
+
+
+def load_golden(name):
+    return dict(np.load(os.path.join(GOLDEN_DIR, name + ".npz")))
+
+
+def unpack_mask(g, key):
+    shape = tuple(int(x) for x in g[key + ".shape"])
+    return np.unpackbits(g[key + ".bits"])[: int(np.prod(shape))].astype(bool).reshape(shape)
+
+
+def rel_l2(a, b):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / (np.linalg.norm(b) + 1e-30))
+
+
+def quat_angle_deg(q, q_ref):
+    """Angular error between unit quaternions, 4*asin(|q - q_ref|/2) after sign alignment
+    (mapanything/utils/metrics.py:18-34)."""
+    q = np.asarray(q, np.float64).reshape(-1, 4)
+    r = np.asarray(q_ref, np.float64).reshape(-1, 4)
+    q = q / np.linalg.norm(q, axis=1, keepdims=True)
+    r = r / np.linalg.norm(r, axis=1, keepdims=True)
+    sign = np.where((q * r).sum(1, keepdims=True) < 0, -1.0, 1.0)
+    d = np.linalg.norm(q * sign - r, axis=1)
+    return float(np.degrees(4 * np.arcsin(np.clip(d / 2, 0, 1))).max())
+
+
+def compare_with_golden(preds, g, stride, tol_dense, tol_pose_deg, tol_small=None, min_mask_agree=0.0):
+    """preds: list of per-view dicts (torch tensors, any device).  Returns a report dict and asserts.
+
+    Dense float keys are compared by relative L2 on the golden's sub-sampled grid; keys that
+    `infer` multiplies by the final mask are compared where both masks are True (the mask itself is
+    compared by agreement rate: it thresholds floats produced by different arithmetic)."""
+    report = {}
+    nviews = len(preds)
+    for i in range(nviews):
+        p = {k: (v.detach().float().cpu().numpy() if torch.is_tensor(v) and v.dtype != torch.bool
+                 else (v.detach().cpu().numpy() if torch.is_tensor(v) else v)) for k, v in preds[i].items()}
+        gm = unpack_mask(g, f"v{i}.mask")
+        pm = p["mask"].astype(bool)
+        assert pm.shape == gm.shape, (pm.shape, gm.shape)
+        report[f"v{i}.mask_agree"] = float((pm == gm).mean())
+        gn = unpack_mask(g, f"v{i}.non_ambiguous_mask")
+        report[f"v{i}.non_ambiguous_mask_agree"] = float((p["non_ambiguous_mask"].astype(bool) == gn).mean())
+        both = (pm & gm)[:, ::stride, ::stride]
+        for k in ("pts3d", "pts3d_cam", "ray_directions", "depth_along_ray", "depth_z", "conf",
+                  "non_ambiguous_mask_logits", "img_no_norm"):
+            a = p[k][:, ::stride, ::stride]
+            b = g[f"v{i}.{k}"]
+            assert a.shape == b.shape, (k, a.shape, b.shape)
+            if k in MASKED_KEYS:
+                a, b = a * both, b * both
+            report[f"v{i}.{k}"] = rel_l2(a, b)
+        for k in ("cam_trans", "camera_poses", "intrinsics", "metric_scaling_factor"):
+            assert p[k].shape == g[f"v{i}.{k}"].shape, k
+            report[f"v{i}.{k}"] = rel_l2(p[k], g[f"v{i}.{k}"])
+        report[f"v{i}.cam_quats_deg"] = quat_angle_deg(p["cam_quats"], g[f"v{i}.cam_quats"])
+    bad = []
+    for k, v in report.items():
+        if k.endswith("_agree"):
+            if v < min_mask_agree:
+                bad.append((k, v))
+        elif k.endswith("_deg"):
+            if v > tol_pose_deg:
+                bad.append((k, v))
+        elif k.split(".")[1] in ("cam_trans", "camera_poses", "intrinsics", "metric_scaling_factor"):
+            if v > (tol_small if tol_small is not None else tol_dense):
+                bad.append((k, v))
+        elif v > tol_dense:
+            bad.append((k, v))
+    assert not bad, f"out of tolerance: {bad}\nfull report: {report}"
+    return report
