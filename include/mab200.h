@@ -1,0 +1,154 @@
+/* libmab200 -- C ABI of the B200-native MapAnything inference hot path.
+ *
+ * The reference has no native boundary on this path (its only native entry point is cuRoPE's
+ * pybind `rope_2d`, uniception/models/libs/croco/curope/curope.cpp:49-69, which the default model
+ * never calls).  These entry points are what a ctypes/cffi binding inside the reference's
+ * `MapAnything.forward` (mapanything/models/mapanything/model.py:1657-2152) and
+ * `postprocess_model_outputs_for_inference` (mapanything/utils/inference.py:314-506) would bind;
+ * see INTEGRATION.md for the stub.
+ *
+ * Conventions: plain pointers and sizes, no torch types.  Every pointer is a DEVICE pointer unless
+ * the name ends in _host.  Every call is asynchronous on the caller's `stream` (a cudaStream_t
+ * passed as void*), never synchronises the device and returns 0 on success, a negative value for
+ * an argument error, or a positive cudaError_t.  mab_last_error() returns a static description.
+ * A handle may be used by one host thread at a time.
+ */
+#ifndef MAB200_H
+#define MAB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mab_handle mab_handle;
+
+enum { MAB_F32 = 0, MAB_BF16 = 1 };
+enum { MAB_ACT_NONE = 0, MAB_ACT_GELU = 1, MAB_ACT_RELU = 2 };
+
+/* Architecture of the production model (configs/model/mapanything.yaml and SURVEY.md section 0). */
+typedef struct {
+  int patch;          /* 14 */
+  int enc_dim;        /* 1024 */
+  int enc_depth;      /* 24 */
+  int enc_heads;      /* 16 */
+  int enc_pos_grid;   /* 37 (pos_embed is 1 + 37*37 rows) */
+  int aat_dim;        /* 768 */
+  int aat_depth;      /* 24 */
+  int aat_heads;      /* 12 */
+  int aat_tap0;       /* 11 */
+  int aat_tap1;       /* 17 */
+  int head_chunk;     /* views per dense-head pass (workspace knob; outputs do not depend on it) */
+} mab_config;
+
+/* One scene, `views` views of H x W pixels held by this rank. */
+typedef struct {
+  int views;             /* views held by this rank */
+  int H, W;              /* multiples of 14 */
+  const float* images;   /* [views,3,H,W] fp32, already normalised (model.py:2229-2232) */
+  /* optional geometric inputs (multi-modal, model.py:1377-1436); NULL = absent for every view */
+  const float* ray_dirs;        /* [views,H,W,3] unit rays in the camera frame */
+  const float* depth_along_ray; /* [views,H,W]   0 = missing */
+  const float* cam_quats;       /* [views,4] xyzw cam2world, already relative to view 0 */
+  const float* cam_trans;       /* [views,3] already relative to view 0 */
+  const unsigned char* ray_mask;    /* [views] per-view availability flags (0/1) */
+  const unsigned char* depth_mask;  /* [views] */
+  const unsigned char* cam_mask;    /* [views] */
+  const unsigned char* depth_metric_mask; /* [views] is_metric_scale & use_depth_scale */
+  const unsigned char* pose_metric_mask;  /* [views] is_metric_scale & use_pose_scale */
+  float pose_trans_norm;  /* mean non-zero |t| over ALL views of the scene (geometry.py:1629-1666) */
+} mab_inputs;
+
+/* Raw forward outputs (model.py:1907-1923, 2117-2150), all fp32 unless noted. */
+typedef struct {
+  float* pts3d;            /* [views,H,W,3] */
+  float* pts3d_cam;        /* [views,H,W,3] */
+  float* ray_directions;   /* [views,H,W,3] */
+  float* depth_along_ray;  /* [views,H,W]   */
+  float* conf;             /* [views,H,W]   */
+  float* mask_logits;      /* [views,H,W]   */
+  unsigned char* non_ambiguous_mask; /* [views,H,W] 0/1 */
+  float* pose;             /* [views,8]: unscaled t(3), unit q(4), pad */
+  float* metric_scale;     /* [1] */
+  float* logits6;          /* optional [views,H,W,6] raw regressor output, may be NULL */
+} mab_outputs;
+
+/* Post-processed extras (inference.py:314-506). */
+typedef struct {
+  float* img_no_norm;      /* [views,H,W,3] */
+  float* depth_z;          /* [views,H,W] */
+  float* intrinsics;       /* [views,3,3] */
+  float* camera_poses;     /* [views,4,4] */
+  float* cam_trans;        /* [views,3] (x metric scale) */
+  float* cam_quats;        /* [views,4] */
+  unsigned char* mask;     /* [views,H,W] 0/1 */
+} mab_post_outputs;
+
+typedef struct {
+  int apply_mask, mask_edges;
+  float edge_normal_threshold_deg, edge_depth_threshold;
+  int apply_confidence_mask;
+  float confidence_percentile;
+} mab_post_options;
+
+const char* mab_last_error(void);
+int mab_version(void);
+
+int mab_create(const mab_config* cfg, int device, mab_handle** out);
+int mab_destroy(mab_handle* h);
+/* Upload one tensor of the reference state dict (reference key names, fp32, host or device). */
+int mab_set_weight(mab_handle* h, const char* ref_key, const void* ptr, int dtype, int ndim,
+                   const int64_t* shape);
+/* Pack bf16 GEMM/conv operands, merge aliases, drop the fp32 staging copies that are not needed. */
+int mab_finalize_weights(mab_handle* h, void* stream);
+
+size_t mab_workspace_bytes(mab_handle* h, int views_local, int views_total, int H, int W);
+/* Whole forward on one GPU (views_total == views). */
+int mab_forward(mab_handle* h, const mab_inputs* in, mab_outputs* out, void* workspace,
+                size_t workspace_bytes, void* stream);
+int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs* raw, mab_post_outputs* post,
+                    const mab_post_options* opt, void* workspace, size_t workspace_bytes,
+                    void* stream);
+
+/* ---- staged forward (view-sharded multi-GPU: the caller exchanges K/V between the stages) ---- */
+int mab_stage_encode(mab_handle* h, const mab_inputs* in, void* workspace, size_t workspace_bytes,
+                     int has_scale_token, void* stream);
+/* LN1 + qkv projection of info-sharing block `layer`; returns the device pointer of this rank's
+ * packed [rows, 3*aat_dim] bf16 qkv buffer and its row count. */
+int mab_stage_aat_qkv(mab_handle* h, int layer, void* workspace, void** qkv_out, int* rows_out,
+                      void* stream);
+/* Attention + proj + MLP of block `layer`.  For global (even) layers kv points to a
+ * [kv_rows, 3*aat_dim] bf16 buffer holding every rank's qkv rows (NULL = use the local buffer). */
+int mab_stage_aat_block(mab_handle* h, int layer, void* workspace, const void* kv, int kv_rows,
+                        void* stream);
+int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out, void* workspace,
+                    const float* metric_scale_in, void* stream);
+
+/* ---- per-kernel entry points (parity tests call these through the same ABI) ---- */
+int mab_layernorm(const float* x, int rows, int C, const float* w, const float* b, float eps,
+                  void* out_bf16, float* out_f32, void* stream);
+/* C = act(A[M,K] * B[N,K]^T + bias) * gamma + res ; A,B bf16 row-major; outputs optional */
+int mab_gemm(const void* A, const void* B, int M, int N, int K, const float* bias,
+             const float* gamma, const float* res_f32, int act, float* out_f32, void* out_bf16,
+             void* stream);
+/* qkv: [rows, 3*heads*64] bf16 packed q|k|v ; out: [rows, heads*64] bf16 */
+int mab_attention(const void* q_src, int q_rows_total, const void* kv_src, int kv_rows_total,
+                  int heads, int num_seqs, int q_len, int kv_len, int q_seq_stride,
+                  int kv_seq_stride, float scale, void* out, float* lse, void* stream);
+/* 3x3/s1/p1 conv over NHWC bf16; weight packed [Cout, 9, Cpad] bf16 (mab_pack_conv3_weight) */
+int mab_conv3x3(const void* x, int batch, int H, int W, int C, const void* w_packed, int Cout,
+                const float* bias, const void* res1, const void* res2, int act, void* out_bf16,
+                void* out_relu, void* stream);
+int mab_pack_conv3_weight(const float* w_oihw, int Cout, int Cin, void* out_packed, void* stream);
+int mab_resize_bilinear(const void* x, int batch, int Hi, int Wi, int C, int Hv, int Wv, int Ho,
+                        int Wo, void* out, void* out_relu, void* stream);
+int mab_posembed_resize(const float* pos, int grid, int C, int h, int w, float* out, void* stream);
+int mab_edge_mask(const float* pts3d, float* pts3d_cam, const unsigned char* fmask, int views, int H,
+                  int W, float normal_tol_deg, float depth_rtol, void* workspace,
+                  unsigned char* mask_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,94 @@
+"""ctypes binding of libmab200.so (include/mab200.h).  No CPU fallback: a missing library raises."""
+import ctypes as C
+import os
+
+from . import build as _build
+
+c_float_p = C.POINTER(C.c_float)
+c_ubyte_p = C.POINTER(C.c_ubyte)
+
+
+class MabConfig(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("patch", "enc_dim", "enc_depth", "enc_heads", "enc_pos_grid",
+                                       "aat_dim", "aat_depth", "aat_heads", "aat_tap0", "aat_tap1",
+                                       "head_chunk")]
+
+
+class MabInputs(C.Structure):
+    _fields_ = [("views", C.c_int), ("H", C.c_int), ("W", C.c_int), ("images", C.c_void_p),
+                ("ray_dirs", C.c_void_p), ("depth_along_ray", C.c_void_p), ("cam_quats", C.c_void_p),
+                ("cam_trans", C.c_void_p), ("ray_mask", C.c_void_p), ("depth_mask", C.c_void_p),
+                ("cam_mask", C.c_void_p), ("depth_metric_mask", C.c_void_p),
+                ("pose_metric_mask", C.c_void_p), ("pose_trans_norm", C.c_float)]
+
+
+class MabOutputs(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("pts3d", "pts3d_cam", "ray_directions", "depth_along_ray",
+                                          "conf", "mask_logits", "non_ambiguous_mask", "pose",
+                                          "metric_scale", "logits6")]
+
+
+class MabPostOutputs(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("img_no_norm", "depth_z", "intrinsics", "camera_poses",
+                                          "cam_trans", "cam_quats", "mask")]
+
+
+class MabPostOptions(C.Structure):
+    _fields_ = [("apply_mask", C.c_int), ("mask_edges", C.c_int),
+                ("edge_normal_threshold_deg", C.c_float), ("edge_depth_threshold", C.c_float),
+                ("apply_confidence_mask", C.c_int), ("confidence_percentile", C.c_float)]
+
+
+# every symbol include/mab200.h declares: (name, restype, argtypes)
+_vp, _i, _f = C.c_void_p, C.c_int, C.c_float
+SYMBOLS = {
+    "mab_last_error": (C.c_char_p, []),
+    "mab_version": (_i, []),
+    "mab_create": (_i, [C.POINTER(MabConfig), _i, C.POINTER(_vp)]),
+    "mab_destroy": (_i, [_vp]),
+    "mab_set_weight": (_i, [_vp, C.c_char_p, _vp, _i, _i, C.POINTER(C.c_int64)]),
+    "mab_finalize_weights": (_i, [_vp, _vp]),
+    "mab_workspace_bytes": (C.c_size_t, [_vp, _i, _i, _i, _i]),
+    "mab_forward": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), _vp, C.c_size_t, _vp]),
+    "mab_postprocess": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), C.POINTER(MabPostOutputs),
+                             C.POINTER(MabPostOptions), _vp, C.c_size_t, _vp]),
+    "mab_stage_encode": (_i, [_vp, C.POINTER(MabInputs), _vp, C.c_size_t, _i, _vp]),
+    "mab_stage_aat_qkv": (_i, [_vp, _i, _vp, C.POINTER(_vp), C.POINTER(_i), _vp]),
+    "mab_stage_aat_block": (_i, [_vp, _i, _vp, _vp, _i, _vp]),
+    "mab_stage_heads": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), _vp, _vp, _vp]),
+    "mab_layernorm": (_i, [_vp, _i, _i, _vp, _vp, _f, _vp, _vp, _vp]),
+    "mab_gemm": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
+    "mab_attention": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp]),
+    "mab_conv3x3": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
+    "mab_pack_conv3_weight": (_i, [_vp, _i, _i, _vp, _vp]),
+    "mab_resize_bilinear": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "mab_posembed_resize": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "mab_edge_mask": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp, _vp]),
+}
+
+_lib = None
+
+
+def load(allow_build=True):
+    """Load libmab200.so, building it in-tree first when it is missing and nvcc is present."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if not os.path.exists(path):
+        if not allow_build:
+            raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        _build.build()
+    lib = C.CDLL(path)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)  # AttributeError if the ABI and the header ever diverge
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(status, what=""):
+    if status != 0:
+        msg = load().mab_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"libmab200 {what} failed with status {status}: {msg}")

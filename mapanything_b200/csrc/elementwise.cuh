@@ -1,0 +1,329 @@
+// Bandwidth-bound kernels of libmab200: LayerNorm, patch im2col, token assembly, bicubic
+// pos-embed resize, bilinear (align_corners) resize, pixel shuffle, strided im2col, pooling and
+// the small fp32 head linears.  All are coalesced + vectorised; roofline = HBM GB/s.
+#pragma once
+#include "common.cuh"
+
+namespace mab {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ----------------------------------------------------------------------------------------------
+// LayerNorm over the last dim (C = 32*4*VPL), fp32 in, bf16 and/or fp32 out.  One warp per row.
+// Row gather: output row o reads input row (o / group_out) * group_in + skip + o % group_out
+// (drops the cls token of each view: vision_transformer.py:305-312).
+// Optional second LayerNorm applied to the result of the first (image-only fusion norm,
+// model.py:1423-1431 directly after the encoder norm).
+// ----------------------------------------------------------------------------------------------
+template <int VPL>  // float4 per lane: C = 128 * VPL
+__global__ void layernorm_kernel(const float* __restrict__ x, int rows_out, int group_out,
+                                 int group_in, int skip, const float* __restrict__ w,
+                                 const float* __restrict__ b, const float* __restrict__ w2,
+                                 const float* __restrict__ b2, float eps,
+                                 __nv_bfloat16* __restrict__ out_bf16, float* __restrict__ out_f32,
+                                 float* __restrict__ out_mid_f32) {
+  constexpr int C = 128 * VPL;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= rows_out) return;
+  const long long in_row = (long long)(warp / group_out) * group_in + skip + warp % group_out;
+  const float4* xr = reinterpret_cast<const float4*>(x + in_row * C);
+  float4 v[VPL];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    v[i] = xr[lane + 32 * i];
+    s += v[i].x + v[i].y + v[i].z + v[i].w;
+  }
+  auto normalise = [&](const float* ww, const float* bb) {
+    const float mean = warp_sum(s) * (1.0f / C);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const float a = v[i].x - mean, b_ = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+      q += a * a + b_ * b_ + c * c + d * d;
+    }
+    const float rstd = rsqrtf(warp_sum(q) * (1.0f / C) + eps);
+    s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(ww) + lane + 32 * i);
+      const float4 h = __ldg(reinterpret_cast<const float4*>(bb) + lane + 32 * i);
+      v[i].x = (v[i].x - mean) * rstd * g.x + h.x;
+      v[i].y = (v[i].y - mean) * rstd * g.y + h.y;
+      v[i].z = (v[i].z - mean) * rstd * g.z + h.z;
+      v[i].w = (v[i].w - mean) * rstd * g.w + h.w;
+      s += v[i].x + v[i].y + v[i].z + v[i].w;
+    }
+  };
+  normalise(w, b);
+  if (out_mid_f32) {
+#pragma unroll
+    for (int i = 0; i < VPL; ++i)
+      reinterpret_cast<float4*>(out_mid_f32 + (long long)warp * C)[lane + 32 * i] = v[i];
+  }
+  if (w2) normalise(w2, b2);
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    if (out_f32) reinterpret_cast<float4*>(out_f32 + (long long)warp * C)[lane + 32 * i] = v[i];
+    if (out_bf16)
+      reinterpret_cast<uint2*>(out_bf16 + (long long)warp * C)[lane + 32 * i] =
+          make_uint2(pack_bf16(v[i].x, v[i].y), pack_bf16(v[i].z, v[i].w));
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Patch im2col for the 14x14/s14 patch-embed conv (patch_embed.py:65-80): fp32 NCHW image ->
+// bf16 [views*h*w, KP] with k = c*196 + ky*14 + kx (the flattening of the conv weight), zero pad
+// to KP.
+// ----------------------------------------------------------------------------------------------
+__global__ void patch_im2col_kernel(const float* __restrict__ img, int views, int H, int W, int KP,
+                                    __nv_bfloat16* __restrict__ out) {
+  const int h = H / 14, w = W / 14;
+  const long long total = (long long)views * h * w * KP;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = i % KP;
+    const long long row = i / KP;
+    float val = 0.f;
+    if (k < 588) {
+      const int c = k / 196, ky = (k % 196) / 14, kx = k % 14;
+      const int px = row % w, py = (row / w) % h, v = row / (w * h);
+      val = img[(((long long)v * 3 + c) * H + py * 14 + ky) * W + px * 14 + kx];
+    }
+    out[i] = __float2bfloat16(val);
+  }
+}
+
+// tokens[v, 0] = cls + pos[0]; tokens[v, 1+t] = patch[v*T + t] + pos[1+t]
+// (vision_transformer.py:244-251; patch already contains the conv bias)
+__global__ void assemble_tokens_kernel(const float* __restrict__ patch, const float* __restrict__ cls,
+                                       const float* __restrict__ pos, int views, int T, int C,
+                                       float* __restrict__ tokens) {
+  const long long total = (long long)views * (T + 1) * (C / 4);
+  const int c4n = C / 4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c4 = i % c4n;
+    const int t = (i / c4n) % (T + 1);
+    const int v = i / ((long long)c4n * (T + 1));
+    float4 a = (t == 0) ? reinterpret_cast<const float4*>(cls)[c4]
+                        : reinterpret_cast<const float4*>(patch)[((long long)v * T + t - 1) * c4n + c4];
+    const float4 p = reinterpret_cast<const float4*>(pos)[(long long)t * c4n + c4];
+    a.x += p.x; a.y += p.y; a.z += p.z; a.w += p.w;
+    reinterpret_cast<float4*>(tokens)[i] = a;
+  }
+}
+
+// Bicubic (A = -0.75, align_corners = False, explicit scale factor) resize of the DINOv2 position
+// embedding grid, bit-compatible in structure with ATen's upsample_bicubic2d as called from
+// vision_transformer.py:208-242: src = (dst + 0.5) / scale_factor - 0.5, border-clamped taps.
+// pos_in [1 + M*M, C] -> pos_out [1 + h*w, C] (row 0 = class position, copied).
+__device__ __forceinline__ void cubic_coeffs(float t, float* c) {
+  const float A = -0.75f;
+  auto cc1 = [&](float x) { return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f; };
+  auto cc2 = [&](float x) { return ((A * x - 5.f * A) * x + 8.f * A) * x - 4.f * A; };
+  c[0] = cc2(t + 1.f);
+  c[1] = cc1(t);
+  c[2] = cc1(1.f - t);
+  c[3] = cc2(2.f - t);
+}
+__global__ void posembed_bicubic_kernel(const float* __restrict__ pos_in, int M, int C, int h, int w,
+                                        float inv_sy, float inv_sx, float* __restrict__ pos_out) {
+  const long long total = (long long)(1 + h * w) * C;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = i % C;
+    const int t = i / C;
+    if (t == 0) { pos_out[i] = pos_in[c]; continue; }
+    const int oy = (t - 1) / w, ox = (t - 1) % w;
+    const float sy = inv_sy * (oy + 0.5f) - 0.5f, sx = inv_sx * (ox + 0.5f) - 0.5f;
+    const int iy = (int)floorf(sy), ix = (int)floorf(sx);
+    float cy[4], cx[4];
+    cubic_coeffs(sy - iy, cy);
+    cubic_coeffs(sx - ix, cx);
+    float acc = 0.f;
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      const int yy = min(max(iy - 1 + a, 0), M - 1);
+      float rowv = 0.f;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int xx = min(max(ix - 1 + b, 0), M - 1);
+        rowv += pos_in[(long long)(1 + yy * M + xx) * C + c] * cx[b];
+      }
+      acc += rowv * cy[a];
+    }
+    pos_out[i] = acc;
+  }
+}
+
+// x[r, :] += pe[:] for r < rows  (reference-view positional encoding, aat.py:618-626)
+__global__ void add_row_vector_kernel(float* __restrict__ x, const float* __restrict__ pe, int rows,
+                                      int C) {
+  const long long total = (long long)rows * C;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x)
+    x[i] += pe[i % C];
+}
+
+__global__ void f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                   long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    y[i] = __float2bfloat16(x[i]);
+}
+
+// ----------------------------------------------------------------------------------------------
+// Bilinear resize, align_corners=True, NHWC bf16, 8 channels per thread.
+// Computes the (Hv x Wv) virtual output grid from (Hi x Wi) but stores only the top-left
+// (Ho x Wo) crop (dpt.py:213 crops refinenet4's 2x up-sampled 28x38 to 28x37).
+// dpt_block.py:251-253 (x2) and dpt.py:304 (224x296 -> 392x518).  Optional second output relu(x).
+// ----------------------------------------------------------------------------------------------
+__global__ void resize_bilinear_ac_kernel(const __nv_bfloat16* __restrict__ in, int views, int Hi,
+                                          int Wi, int C, int Hv, int Wv, int Ho, int Wo,
+                                          __nv_bfloat16* __restrict__ out,
+                                          __nv_bfloat16* __restrict__ out_relu) {
+  const int c8n = C / 8;
+  const long long total = (long long)views * Ho * Wo * c8n;
+  const float ry = Hv > 1 ? float(Hi - 1) / float(Hv - 1) : 0.f;
+  const float rx = Wv > 1 ? float(Wi - 1) / float(Wv - 1) : 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c8 = i % c8n;
+    const int ox = (i / c8n) % Wo;
+    const int oy = (i / ((long long)c8n * Wo)) % Ho;
+    const int v = i / ((long long)c8n * Wo * Ho);
+    const float sy = ry * oy, sx = rx * ox;
+    const int y0 = min((int)sy, Hi - 1), x0 = min((int)sx, Wi - 1);
+    const int y1 = min(y0 + 1, Hi - 1), x1 = min(x0 + 1, Wi - 1);
+    const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
+    const uint4* base = reinterpret_cast<const uint4*>(in) + (long long)v * Hi * Wi * c8n + c8;
+    const uint4 a = base[((long long)y0 * Wi + x0) * c8n], b = base[((long long)y0 * Wi + x1) * c8n];
+    const uint4 c = base[((long long)y1 * Wi + x0) * c8n], d = base[((long long)y1 * Wi + x1) * c8n];
+    const uint32_t* pa = &a.x; const uint32_t* pb = &b.x; const uint32_t* pc = &c.x; const uint32_t* pd = &d.x;
+    uint32_t o[4], orl[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      // ATen: hy*(hx*a + lx*b) + ly*(hx*c + lx*d)
+      const float lo = hy * (hx * bf16_lo(pa[k]) + lx * bf16_lo(pb[k])) +
+                       ly * (hx * bf16_lo(pc[k]) + lx * bf16_lo(pd[k]));
+      const float hi = hy * (hx * bf16_hi(pa[k]) + lx * bf16_hi(pb[k])) +
+                       ly * (hx * bf16_hi(pc[k]) + lx * bf16_hi(pd[k]));
+      o[k] = pack_bf16(lo, hi);
+      orl[k] = pack_bf16(fmaxf(lo, 0.f), fmaxf(hi, 0.f));
+    }
+    if (out) reinterpret_cast<uint4*>(out)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+    if (out_relu) reinterpret_cast<uint4*>(out_relu)[i] = make_uint4(orl[0], orl[1], orl[2], orl[3]);
+  }
+}
+
+// ConvTranspose2d with kernel == stride (dpt.py:117-127,139-149) = GEMM + pixel shuffle.
+// in: GEMM output [views*h*w, k*k*C] with column (i*k + j)*C + c  ->  NHWC [views, h*k, w*k, C]
+__global__ void pixel_shuffle_kernel(const __nv_bfloat16* __restrict__ in, int views, int h, int w,
+                                     int k, int C, __nv_bfloat16* __restrict__ out) {
+  const int c8n = C / 8;
+  const long long total = (long long)views * h * k * w * k * c8n;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c8 = i % c8n;
+    const int ox = (i / c8n) % (w * k);
+    const int oy = (i / ((long long)c8n * w * k)) % (h * k);
+    const int v = i / ((long long)c8n * w * k * h * k);
+    const int y = oy / k, ii = oy % k, x = ox / k, jj = ox % k;
+    const long long src = (((long long)v * h + y) * w + x) * (k * k * c8n) + (ii * k + jj) * c8n + c8;
+    reinterpret_cast<uint4*>(out)[i] = reinterpret_cast<const uint4*>(in)[src];
+  }
+}
+
+// im2col for the 3x3 / stride 2 / pad 1 conv of act_4_postprocess (dpt.py:160-166):
+// NHWC [views,H,W,C] -> [views*Ho*Wo, 9*C], column tap*C + c
+__global__ void im2col3x3_s2_kernel(const __nv_bfloat16* __restrict__ in, int views, int H, int W,
+                                    int C, int Ho, int Wo, __nv_bfloat16* __restrict__ out) {
+  const int c8n = C / 8;
+  const long long total = (long long)views * Ho * Wo * 9 * c8n;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c8 = i % c8n;
+    const int tap = (i / c8n) % 9;
+    const int ox = (i / ((long long)c8n * 9)) % Wo;
+    const int oy = (i / ((long long)c8n * 9 * Wo)) % Ho;
+    const int v = i / ((long long)c8n * 9 * Wo * Ho);
+    const int y = oy * 2 - 1 + tap / 3, x = ox * 2 - 1 + tap % 3;
+    uint4 val = make_uint4(0, 0, 0, 0);
+    if (y >= 0 && y < H && x >= 0 && x < W)
+      val = reinterpret_cast<const uint4*>(in)[(((long long)v * H + y) * W + x) * c8n + c8];
+    reinterpret_cast<uint4*>(out)[i] = val;
+  }
+}
+
+// mean over the T tokens of each view: bf16 [views*T, C] -> fp32 [views, C]  (pose_head.py:150)
+__global__ void token_mean_kernel(const __nv_bfloat16* __restrict__ x, int T, int C,
+                                  float* __restrict__ out) {
+  const int v = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim.x channels, blockDim.y row lanes
+  __shared__ float part[8][128];
+  float s = 0.f;
+  if (c < C)
+    for (int t = threadIdx.y; t < T; t += blockDim.y)
+      s += __bfloat162float(x[((long long)v * T + t) * C + c]);
+  part[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    float tot = 0.f;
+    for (int k = 0; k < blockDim.y; ++k) tot += part[k][threadIdx.x];
+    out[(long long)v * C + c] = tot / T;
+  }
+}
+
+// y[r, n] = act(sum_k x[r,k] * w[n,k] + b[n]) in fp32 for the tiny head MLPs
+// (pose_head.py:152-157, mlp_head.py:80-90, global_rep_encoder.py:83-105).  One warp per (n, 8 rows).
+// act: 0 none, 1 gelu (exact), 2 relu
+__global__ void small_linear_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                    const float* __restrict__ b, int rows, int K, int N, int act,
+                                    float* __restrict__ y, int ldx, int ldy) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int n = warp % N, rblk = warp / N;
+  const int r0 = rblk * 8;
+  if (r0 >= rows) return;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  for (int k = lane; k < K; k += 32) {
+    const float wv = __ldg(w + (long long)n * K + k);
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (r0 + i < rows) acc[i] = fmaf(x[(long long)(r0 + i) * ldx + k], wv, acc[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float v = warp_sum(acc[i]);
+    if (lane == 0 && r0 + i < rows) {
+      v += b ? b[n] : 0.f;
+      if (act == 1) v = 0.5f * v * (1.0f + erff(v * 0.70710678118654752f));
+      else if (act == 2) v = fmaxf(v, 0.f);
+      y[(long long)(r0 + i) * ldy + n] = v;
+    }
+  }
+}
+
+// pose adaptor (adaptors.py:714-732): raw [views, 7] (t | q) -> pose [views, 8] (t | q/|q| | 0)
+__global__ void pose_finalize_kernel(const float* __restrict__ raw, int views, float* __restrict__ pose) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= views) return;
+  const float* r = raw + v * 7;
+  const float n = fmaxf(sqrtf(r[3] * r[3] + r[4] * r[4] + r[5] * r[5] + r[6] * r[6]), 1e-8f);
+  float* p = pose + v * 8;
+  p[0] = r[0]; p[1] = r[1]; p[2] = r[2];
+  p[3] = r[3] / n; p[4] = r[4] / n; p[5] = r[5] / n; p[6] = r[6] / n; p[7] = 0.f;
+}
+
+// scale adaptor (adaptors.py:190-212): exp then clip to >= 1e-8
+__global__ void scale_finalize_kernel(const float* __restrict__ raw, float* __restrict__ scale) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) scale[0] = fmaxf(expf(raw[0]), 1e-8f);
+}
+
+}  // namespace mab

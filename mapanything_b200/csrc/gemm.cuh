@@ -1,0 +1,367 @@
+// tcgen05 / TMEM / TMA GEMM family of libmab200 (sm_100a).
+//
+//   C[M,N] = A[M,K] * B[N,K]^T     bf16 operands (K-major, 128B-swizzled smem tiles), fp32 TMEM accum
+//
+// Two A-operand producers share one kernel:
+//   MODE_GEMM : A is a row-major [M,K] bf16 matrix (every nn.Linear and 1x1 conv of the path:
+//               transformer_blocks.py:75-78,146-154, dinov2 layers/attention.py:48-50, mlp.py:29-31)
+//   MODE_CONV3: implicit-GEMM 3x3 / stride 1 / pad 1 convolution over an NHWC bf16 activation
+//               (dpt_block.py:34-69,128-146, dpt.py:271-277).  A-tile = 8x16 output pixels; for
+//               each of the 9 taps the TMA box is shifted by (dy-1, dx-1) and out-of-image
+//               coordinates are zero-filled by the TMA unit, so no im2col buffer ever exists.
+//
+// Persistent, warp-specialised: warp0 = TMA producer, warp1 = MMA issuer (+TMEM owner),
+// warps 2..5 = epilogue.  smem ring of STAGES {A 128x64, B BNx64}; TMEM holds two BN-column fp32
+// accumulators so the epilogue of tile i overlaps the main loop of tile i+1.
+#pragma once
+#include "common.cuh"
+
+namespace mab {
+
+constexpr int GEMM_BM = 128;
+constexpr int GEMM_BK = 64;
+constexpr int GEMM_THREADS = 192;
+constexpr int CONV_TH = 8;   // conv tile: 8 rows x 16 cols of output pixels = 128 GEMM rows
+constexpr int CONV_TW = 16;
+
+enum { MODE_GEMM = 0, MODE_CONV3 = 1 };
+enum { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2 };
+enum { EPI_GENERIC = 0, EPI_REGRESS = 1 };
+
+struct GemmEpilogue {
+  const float* bias;             // [N] or null
+  const float* gamma;            // [N] LayerScale or null
+  const float* res_f32;          // fp32 residual, same indexing as out (may alias out_f32)
+  const __nv_bfloat16* res1;     // bf16 residuals (RCU skip / fusion add), same indexing as out
+  const __nv_bfloat16* res2;
+  float* out_f32;                // any subset of the three outputs
+  __nv_bfloat16* out_bf16;
+  __nv_bfloat16* out_relu;       // relu(value) (input of the next ResidualConvUnit)
+  int ldo;                       // output row pitch in elements
+  int act;                       // ACT_*
+};
+
+// Fused tail of the dense head: ReLU -> 1x1 conv 128->6 -> adaptor -> pointmap (EPI_REGRESS)
+struct RegressEpilogue {
+  const float* bias2;        // [128]   dpt_regressor_head.conv2.0.bias
+  const float* w3;           // [6,128] dpt_regressor_head.conv2.2.weight
+  const float* b3;           // [6]
+  const float* pose;         // [views,8]: t(3) q(4, unit) pad  (pose head output after adaptor)
+  const float* scale;        // [1] metric scale
+  float* pts3d;              // [views,H,W,3]
+  float* pts3d_cam;          // [views,H,W,3]
+  float* rays;               // [views,H,W,3]
+  float* depth;              // [views,H,W]   (depth_along_ray, x scale)
+  float* conf;               // [views,H,W]
+  float* mask_logits;        // [views,H,W]
+  unsigned char* mask;       // [views,H,W]   non_ambiguous_mask (0/1)
+  float* logits6;            // optional [views,H,W,6] raw regressor output (tests) or null
+};
+
+struct GemmShape {
+  int M, N, K;          // MODE_GEMM: A is [M,K].  MODE_CONV3: K = 9*Cpad, M unused
+  int batch, H, W;      // MODE_CONV3: activation is [batch,H,W,C]
+  int cblocks;          // MODE_CONV3: Cpad/64
+};
+
+__device__ __forceinline__ float gelu_erf(float x) {
+  // exact-erf GELU (nn.GELU default, transformer_blocks.py:68).  erf via Abramowitz-Stegun
+  // 7.1.26 (|err| < 1.5e-7, far below the bf16 rounding of the stored activation).
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+  float p = fmaf(1.061405429f, t, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  const float e = 1.0f - p * t * __expf(-z * z);
+  const float erfv = copysignf(e, x);
+  return 0.5f * x * (1.0f + erfv);
+}
+
+template <int BN, int STAGES>
+struct GemmSmem {
+  static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
+  static constexpr int B_BYTES = BN * GEMM_BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int EPI_PITCH = 36;  // floats; conflict-free 32x32 transpose (see below)
+  static constexpr int EPI_BYTES = 4 * 32 * EPI_PITCH * 4;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +align slack
+};
+
+template <int BN, int STAGES, int MODE, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            GemmShape shp, GemmEpilogue ep, RegressEpilogue rg) {
+  using SM = GemmSmem<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* epi_smem = smem + STAGES * SM::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + SM::EPI_BYTES);
+  uint64_t* full_bar = bars;                 // [STAGES]
+  uint64_t* empty_bar = bars + STAGES;       // [STAGES]
+  uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
+  uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // ---- tile bookkeeping -------------------------------------------------------------------
+  int tiles_x = 0, tiles_y = 0, num_m;
+  if (MODE == MODE_CONV3) {
+    tiles_x = (shp.W + CONV_TW - 1) / CONV_TW;
+    tiles_y = (shp.H + CONV_TH - 1) / CONV_TH;
+    num_m = shp.batch * tiles_x * tiles_y;
+  } else {
+    num_m = (shp.M + GEMM_BM - 1) / GEMM_BM;
+  }
+  const int num_n = (shp.N + BN - 1) / BN;
+  const int num_tiles = num_m * num_n;
+  const int num_kb = (MODE == MODE_CONV3) ? 9 * shp.cblocks : (shp.K + GEMM_BK - 1) / GEMM_BK;
+  constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128
+                                 : (2 * BN <= 256) ? 256 : 512;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 4);  // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================ TMA producer ==========================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile % num_m, n_blk = tile / num_m;
+        int cn = 0, cy = 0, cx = 0;
+        if (MODE == MODE_CONV3) {
+          cx = (m_blk % tiles_x) * CONV_TW;
+          cy = ((m_blk / tiles_x) % tiles_y) * CONV_TH;
+          cn = m_blk / (tiles_x * tiles_y);
+        }
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * SM::STAGE_BYTES;
+          uint8_t* sb = sa + SM::A_BYTES;
+          mbar_arrive_expect_tx(&full_bar[stage], SM::STAGE_BYTES);
+          if (MODE == MODE_CONV3) {
+            const int tap = kb / shp.cblocks, cb = kb - tap * shp.cblocks;
+            const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+            tma_load_4d(sa, &tmA, &full_bar[stage], cb * GEMM_BK, cx + dx, cy + dy, cn);
+          } else {
+            tma_load_2d(sa, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * GEMM_BM);
+          }
+          tma_load_2d(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer =============================================
+    constexpr uint32_t IDESC = make_idesc_bf16(GEMM_BM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tempty_bar[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + stage * SM::STAGE_BYTES);
+          const uint32_t sb = sa + SM::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < GEMM_BK / 16; ++k) {
+            // +32 bytes per UMMA_K=16 step inside the 128B swizzle atom
+            umma_ss(d_tmem, make_sw128_desc(sa + k * 32), make_sw128_desc(sb + k * 32), IDESC,
+                    (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);                      // frees the smem slot
+          if (kb == num_kb - 1) umma_commit(&tfull_bar[acc]);  // accumulator complete
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ================================ epilogue (warps 2..5) ==================================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    float* stg = reinterpret_cast<float*>(epi_smem) + q * 32 * SM::EPI_PITCH;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      const int m_blk = tile % num_m, n_blk = tile / num_m;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (uint32_t(q * 32) << 16) + acc * BN;
+
+      int cn = 0, cy = 0, cx = 0;
+      if (MODE == MODE_CONV3) {
+        cx = (m_blk % tiles_x) * CONV_TW;
+        cy = ((m_blk / tiles_x) % tiles_y) * CONV_TH;
+        cn = m_blk / (tiles_x * tiles_y);
+      }
+      // row (0..127 within the tile) -> element offset of the output row, or -1 if out of range
+      auto row_offset = [&](int r) -> long long {
+        if (MODE == MODE_CONV3) {
+          const int y = cy + r / CONV_TW, x = cx + r % CONV_TW;
+          if (y >= shp.H || x >= shp.W) return -1;
+          return ((long long)(cn * shp.H + y) * shp.W + x);
+        } else {
+          const int m = m_blk * GEMM_BM + r;
+          return m < shp.M ? (long long)m : -1;
+        }
+      };
+
+      if (EPI == EPI_REGRESS) {
+        // thread = one output pixel holding all BN(=128) channels of conv2.0
+        float lg[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) lg[k] = __ldg(rg.b3 + k);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          uint32_t v[32];
+          MAB_TMEM_LD_32(t_row + c0, v);
+          tmem_wait_ld();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float a = fmaxf(__uint_as_float(v[j]) + __ldg(rg.bias2 + c0 + j), 0.f);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) lg[k] = fmaf(a, __ldg(rg.w3 + k * BN + c0 + j), lg[k]);
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        const long long pix = row_offset(q * 32 + lane);
+        if (pix >= 0) {
+          // adaptors.py:432-466 (unit-sphere rays), :256-280 (exp depth), :1044-1073 (1+exp conf),
+          // :1126-1131 (sigmoid mask) ; geometry.py:855-907 ; model.py:1907-1923
+          const float* ps = rg.pose + cn * 8;
+          const float s = __ldg(rg.scale);
+          const float nrm = fmaxf(sqrtf(lg[0] * lg[0] + lg[1] * lg[1] + lg[2] * lg[2]), 1e-8f);
+          const float rx = lg[0] / nrm, ry = lg[1] / nrm, rz = lg[2] / nrm;
+          const float d = expf(lg[3]);
+          const float cf = 1.0f + expf(lg[4]);
+          const float qx = ps[3], qy = ps[4], qz = ps[5], qw = ps[6];
+          const float px = d * rx, py = d * ry, pz = d * rz;
+          const float r00 = 1 - 2 * (qy * qy + qz * qz), r01 = 2 * (qx * qy - qw * qz),
+                      r02 = 2 * (qx * qz + qw * qy);
+          const float r10 = 2 * (qx * qy + qw * qz), r11 = 1 - 2 * (qx * qx + qz * qz),
+                      r12 = 2 * (qy * qz - qw * qx);
+          const float r20 = 2 * (qx * qz - qw * qy), r21 = 2 * (qy * qz + qw * qx),
+                      r22 = 1 - 2 * (qx * qx + qy * qy);
+          const float wx = r00 * px + r01 * py + r02 * pz + ps[0];
+          const float wy = r10 * px + r11 * py + r12 * pz + ps[1];
+          const float wz = r20 * px + r21 * py + r22 * pz + ps[2];
+          rg.pts3d[pix * 3 + 0] = wx * s; rg.pts3d[pix * 3 + 1] = wy * s; rg.pts3d[pix * 3 + 2] = wz * s;
+          rg.pts3d_cam[pix * 3 + 0] = px * s; rg.pts3d_cam[pix * 3 + 1] = py * s; rg.pts3d_cam[pix * 3 + 2] = pz * s;
+          rg.rays[pix * 3 + 0] = rx; rg.rays[pix * 3 + 1] = ry; rg.rays[pix * 3 + 2] = rz;
+          rg.depth[pix] = d * s;
+          rg.conf[pix] = cf;
+          rg.mask_logits[pix] = lg[5];
+          // sigmoid(x) > 0.5 evaluated exactly as the reference does in fp32
+          rg.mask[pix] = (1.0f / (1.0f + expf(-lg[5])) > 0.5f) ? 1 : 0;
+          if (rg.logits6) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) rg.logits6[pix * 6 + k] = lg[k];
+          }
+        }
+        continue;
+      }
+
+      // ---- generic epilogue: TMEM -> regs -> smem transpose -> coalesced global ------------
+      // pass 1 thread = row `lane` of this warp's 32-row slab, 32 columns per chunk
+      // pass 2 thread = (row 4*i + lane/8, columns 4*(lane%8)..+3): 8 lanes cover 128 contiguous B
+      const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        const int ncol0 = n_blk * BN + c0;
+        if (ncol0 >= shp.N) break;
+        uint32_t v[32];
+        MAB_TMEM_LD_32(t_row + c0, v);
+        tmem_wait_ld();
+        __syncwarp();  // previous chunk's readers are done with stg
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(stg + lane * SM::EPI_PITCH + 4 * j) =
+              make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                          __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+        __syncwarp();
+        const int col = ncol0 + sub_c;
+        const bool col_ok = col < shp.N;  // N is a multiple of 4 for every layer of the path
+        float4 b4 = make_float4(0, 0, 0, 0), g4 = make_float4(1, 1, 1, 1);
+        if (col_ok && ep.bias) b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
+        if (col_ok && ep.gamma) g4 = __ldg(reinterpret_cast<const float4*>(ep.gamma + col));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = 4 * i + sub_r;
+          const long long ro = row_offset(q * 32 + r);
+          if (ro < 0 || !col_ok) continue;
+          float4 a = *reinterpret_cast<const float4*>(stg + r * SM::EPI_PITCH + sub_c);
+          a.x += b4.x; a.y += b4.y; a.z += b4.z; a.w += b4.w;
+          if (ep.act == ACT_GELU) {
+            a.x = gelu_erf(a.x); a.y = gelu_erf(a.y); a.z = gelu_erf(a.z); a.w = gelu_erf(a.w);
+          } else if (ep.act == ACT_RELU) {
+            a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); a.z = fmaxf(a.z, 0.f); a.w = fmaxf(a.w, 0.f);
+          }
+          a.x *= g4.x; a.y *= g4.y; a.z *= g4.z; a.w *= g4.w;
+          const long long off = ro * ep.ldo + col;
+          if (ep.res_f32) {
+            const float4 r4 = *reinterpret_cast<const float4*>(ep.res_f32 + off);
+            a.x += r4.x; a.y += r4.y; a.z += r4.z; a.w += r4.w;
+          }
+          if (ep.res1) {
+            const uint2 r2 = *reinterpret_cast<const uint2*>(ep.res1 + off);
+            a.x += bf16_lo(r2.x); a.y += bf16_hi(r2.x); a.z += bf16_lo(r2.y); a.w += bf16_hi(r2.y);
+          }
+          if (ep.res2) {
+            const uint2 r2 = *reinterpret_cast<const uint2*>(ep.res2 + off);
+            a.x += bf16_lo(r2.x); a.y += bf16_hi(r2.x); a.z += bf16_lo(r2.y); a.w += bf16_hi(r2.y);
+          }
+          if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + off) = a;
+          if (ep.out_bf16)
+            *reinterpret_cast<uint2*>(ep.out_bf16 + off) =
+                make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
+          if (ep.out_relu)
+            *reinterpret_cast<uint2*>(ep.out_relu + off) =
+                make_uint2(pack_bf16(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f)),
+                           pack_bf16(fmaxf(a.z, 0.f), fmaxf(a.w, 0.f)));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+}  // namespace mab

@@ -1,0 +1,236 @@
+// Host-side helpers: error handling, TMA tensor-map encoding, kernel launchers.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "attention.cuh"
+#include "elementwise.cuh"
+#include "gemm.cuh"
+#include "postprocess.cuh"
+
+namespace mab {
+
+inline char* err_buf() {
+  static thread_local char buf[512] = "";
+  return buf;
+}
+inline int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(err_buf(), 512, fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define MAB_CUDA(expr)                                                                    \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess)                                                                \
+      return ::mab::fail((int)_e, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                         __FILE__, __LINE__);                                             \
+  } while (0)
+#define MAB_TRY(expr)         \
+  do {                        \
+    int _r = (expr);          \
+    if (_r != 0) return _r;   \
+  } while (0)
+#define MAB_ARG(cond, msg) \
+  do {                     \
+    if (!(cond)) return ::mab::fail(-1, "argument error: %s (%s)", msg, #cond); \
+  } while (0)
+
+// ---- cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda link dependency)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 row-major [rows, cols] (row pitch ld elements), box = [box_rows, 64 cols], 128B swizzle
+inline int make_tmap_2d(CUtensorMap* m, const void* ptr, long long rows, long long cols,
+                        long long ld, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return fail(-2, "cuTensorMapEncodeTiled entry point not available");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * 2) & 15))
+    return fail(-1, "TMA operand must be 16B aligned with a 16B-multiple row pitch (ld=%lld)", ld);
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(-3, "cuTensorMapEncodeTiled(2d) failed: %d", (int)r);
+  return 0;
+}
+
+// bf16 NHWC [batch,H,W,C], box = [1, CONV_TH, CONV_TW, 64], 128B swizzle
+inline int make_tmap_nhwc(CUtensorMap* m, const void* ptr, int batch, int H, int W, int C) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return fail(-2, "cuTensorMapEncodeTiled entry point not available");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((C * 2) & 15))
+    return fail(-1, "NHWC TMA operand must be 16B aligned with C a multiple of 8 (C=%d)", C);
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)batch};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {64, CONV_TW, CONV_TH, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(-3, "cuTensorMapEncodeTiled(4d) failed: %d", (int)r);
+  return 0;
+}
+
+inline int sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+inline int ew_grid(long long total, int block = 256) {
+  long long g = (total + block - 1) / block;
+  const long long cap = (long long)sm_count() * 16;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+// ---- GEMM / conv launchers ---------------------------------------------------------------------
+template <int BN, int STAGES, int MODE, int EPI>
+inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const GemmShape& shp,
+                         const GemmEpilogue& ep, const RegressEpilogue& rg, cudaStream_t st) {
+  using SM = GemmSmem<BN, STAGES>;
+  auto kern = gemm_kernel<BN, STAGES, MODE, EPI>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    MAB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::TOTAL));
+    attr_done = true;
+  }
+  int num_m;
+  if (MODE == MODE_CONV3)
+    num_m = shp.batch * ((shp.W + CONV_TW - 1) / CONV_TW) * ((shp.H + CONV_TH - 1) / CONV_TH);
+  else
+    num_m = (shp.M + GEMM_BM - 1) / GEMM_BM;
+  const int tiles = num_m * ((shp.N + BN - 1) / BN);
+  if (tiles <= 0) return 0;
+  const int grid = tiles < sm_count() ? tiles : sm_count();
+  kern<<<grid, GEMM_THREADS, SM::TOTAL, st>>>(tA, tB, shp, ep, rg);
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// C[M,N] = epilogue(A[M,K] B[N,K]^T); lda/ldb row pitches in elements
+inline int launch_gemm(const void* A, long long lda, const void* B, long long ldb, int M, int N,
+                       int K, const GemmEpilogue& ep, cudaStream_t st) {
+  MAB_ARG(M > 0 && N > 0 && K > 0, "empty GEMM");
+  MAB_ARG(N % 4 == 0, "N must be a multiple of 4");
+  CUtensorMap tA, tB;
+  GemmShape shp{M, N, K, 0, 0, 0, 0};
+  RegressEpilogue rg{};
+  MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM));
+  if (N > 128) {
+    MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 256));
+    return launch_gemm_t<256, 4, MODE_GEMM, EPI_GENERIC>(tA, tB, shp, ep, rg, st);
+  }
+  MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 128));
+  return launch_gemm_t<128, 6, MODE_GEMM, EPI_GENERIC>(tA, tB, shp, ep, rg, st);
+}
+
+// 3x3/s1/p1 conv, x NHWC bf16 [batch,H,W,C], w packed [Cout, 9*Cpad] (Cpad = ceil64(C))
+inline int launch_conv3(const void* x, int batch, int H, int W, int C, const void* w, int Cout,
+                        const GemmEpilogue& ep, cudaStream_t st) {
+  const int cblocks = (C + 63) / 64;
+  CUtensorMap tA, tB;
+  GemmShape shp{0, Cout, 9 * cblocks * 64, batch, H, W, cblocks};
+  RegressEpilogue rg{};
+  MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, C));
+  if (Cout > 128) {
+    MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 256));
+    return launch_gemm_t<256, 4, MODE_CONV3, EPI_GENERIC>(tA, tB, shp, ep, rg, st);
+  }
+  MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 128));
+  return launch_gemm_t<128, 6, MODE_CONV3, EPI_GENERIC>(tA, tB, shp, ep, rg, st);
+}
+
+// last conv of the dense head with the fused 1x1 + adaptor + pointmap epilogue (C = Cout = 128)
+inline int launch_conv3_regress(const void* x, int batch, int H, int W, const void* w,
+                                const RegressEpilogue& rg, cudaStream_t st) {
+  CUtensorMap tA, tB;
+  GemmShape shp{0, 128, 9 * 2 * 64, batch, H, W, 2};
+  GemmEpilogue ep{};
+  MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, 128));
+  MAB_TRY(make_tmap_2d(&tB, w, 128, 9LL * 128, 9LL * 128, 128));
+  return launch_gemm_t<128, 6, MODE_CONV3, EPI_REGRESS>(tA, tB, shp, ep, rg, st);
+}
+
+// ---- attention launcher ------------------------------------------------------------------------
+// q_src / kv_src: packed [rows, 3*heads*64] bf16 buffers (q | k | v)
+inline int launch_attention(const void* q_src, long long q_rows_total, const void* kv_src,
+                            long long kv_rows_total, int heads, int num_seqs, int q_len, int kv_len,
+                            int q_seq_stride, int kv_seq_stride, float scale, void* out, float* lse,
+                            cudaStream_t st) {
+  MAB_ARG(heads > 0 && num_seqs > 0 && q_len > 0 && kv_len > 0, "empty attention");
+  const int D = heads * 64;
+  CUtensorMap tQ, tKV;
+  MAB_TRY(make_tmap_2d(&tQ, q_src, q_rows_total, 3LL * D, 3LL * D, ATT_BQ));
+  MAB_TRY(make_tmap_2d(&tKV, kv_src, kv_rows_total, 3LL * D, 3LL * D, ATT_BKV));
+  AttnParams p;
+  p.num_seqs = num_seqs; p.heads = heads; p.q_len = q_len; p.kv_len = kv_len;
+  p.q_seq_stride = q_seq_stride; p.kv_seq_stride = kv_seq_stride;
+  p.q_col0 = 0; p.k_col0 = D; p.v_col0 = 2 * D;
+  p.out = reinterpret_cast<__nv_bfloat16*>(out); p.ldo = D;
+  p.scale_log2e = scale * 1.4426950408889634f;
+  p.lse = lse;
+  static bool attr_done = false;
+  if (!attr_done) {
+    MAB_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  ATT_SMEM_BYTES));
+    attr_done = true;
+  }
+  dim3 grid((q_len + ATT_BQ - 1) / ATT_BQ, heads, num_seqs);
+  attention_kernel<<<grid, ATT_THREADS, ATT_SMEM_BYTES, st>>>(tQ, tKV, tKV, p);
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+inline int launch_layernorm(const float* x, int rows_out, int C, int group_out, int group_in,
+                            int skip, const float* w, const float* b, const float* w2,
+                            const float* b2, float eps, void* out_bf16, float* out_f32,
+                            float* out_mid, cudaStream_t st) {
+  if (rows_out <= 0) return 0;
+  const int block = 256, rows_per_block = block / 32;
+  const int grid = (rows_out + rows_per_block - 1) / rows_per_block;
+  auto ob = reinterpret_cast<__nv_bfloat16*>(out_bf16);
+  if (C == 768)
+    layernorm_kernel<6><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
+                                                 b2, eps, ob, out_f32, out_mid);
+  else if (C == 1024)
+    layernorm_kernel<8><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
+                                                 b2, eps, ob, out_f32, out_mid);
+  else if (C == 128)
+    layernorm_kernel<1><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
+                                                 b2, eps, ob, out_f32, out_mid);
+  else
+    return fail(-1, "layernorm: unsupported width %d (supported 128, 768, 1024)", C);
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace mab

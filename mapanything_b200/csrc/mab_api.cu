@@ -1,0 +1,805 @@
+// libmab200: C ABI (include/mab200.h) + host runtime that sequences the sm_100a kernels of the
+// MapAnything inference hot path.  Part 1: weight packing kernels and the per-kernel entry points.
+#include "../../include/mab200.h"
+
+#include <map>
+#include <vector>
+
+#include "host_util.cuh"
+
+using namespace mab;
+typedef __nv_bfloat16 bf16;
+
+// ------------------------------------------------------------------------------------------------
+// weight packing kernels (run once in mab_finalize_weights)
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+// fp32 [rows, cols] -> bf16 [rows, ldo] zero padded
+__global__ void pack_matrix_kernel(const float* __restrict__ w, int rows, int cols, int ldo,
+                                   bf16* __restrict__ out) {
+  const long long total = (long long)rows * ldo;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = i % ldo;
+    const long long r = i / ldo;
+    out[i] = __float2bfloat16(c < cols ? w[r * cols + c] : 0.f);
+  }
+}
+
+// conv weight [Cout, Cin, 3, 3] fp32 -> [Cout, 9, Cpad] bf16 (tap = ky*3+kx), zero padded channels
+__global__ void pack_conv3_kernel(const float* __restrict__ w, int Cout, int Cin, int Cpad,
+                                  bf16* __restrict__ out) {
+  const long long total = (long long)Cout * 9 * Cpad;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = i % Cpad;
+    const int tap = (i / Cpad) % 9;
+    const int co = i / ((long long)Cpad * 9);
+    out[i] = __float2bfloat16(c < Cin ? w[((long long)co * Cin + c) * 9 + tap] : 0.f);
+  }
+}
+
+// ConvTranspose2d weight [Cin, Cout, k, k] -> GEMM B [k*k*Cout, Cin] with row (i*k+j)*Cout + co
+__global__ void pack_convT_kernel(const float* __restrict__ w, int Cin, int Cout, int k,
+                                  bf16* __restrict__ out) {
+  const long long total = (long long)k * k * Cout * Cin;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int ci = idx % Cin;
+    const int row = idx / Cin;
+    const int co = row % Cout, ij = row / Cout;
+    out[idx] = __float2bfloat16(w[((long long)ci * Cout + co) * k * k + ij]);
+  }
+}
+
+// bias [Cout] -> [k*k*Cout] repeated
+__global__ void tile_bias_kernel(const float* __restrict__ b, int Cout, int reps, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < Cout * reps) out[i] = b[i % Cout];
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// per-kernel C entry points
+// ------------------------------------------------------------------------------------------------
+extern "C" const char* mab_last_error(void) { return err_buf(); }
+extern "C" int mab_version(void) { return 100; }
+
+extern "C" int mab_layernorm(const float* x, int rows, int C, const float* w, const float* b,
+                             float eps, void* out_bf16, float* out_f32, void* stream) {
+  return launch_layernorm(x, rows, C, rows > 0 ? rows : 1, rows > 0 ? rows : 1, 0, w, b, nullptr,
+                          nullptr, eps, out_bf16, out_f32, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int mab_gemm(const void* A, const void* B, int M, int N, int K, const float* bias,
+                        const float* gamma, const float* res_f32, int act, float* out_f32,
+                        void* out_bf16, void* stream) {
+  GemmEpilogue ep{};
+  ep.bias = bias; ep.gamma = gamma; ep.res_f32 = res_f32; ep.out_f32 = out_f32;
+  ep.out_bf16 = reinterpret_cast<bf16*>(out_bf16); ep.ldo = N; ep.act = act;
+  return launch_gemm(A, K, B, K, M, N, K, ep, (cudaStream_t)stream);
+}
+
+extern "C" int mab_attention(const void* q_src, int q_rows_total, const void* kv_src,
+                             int kv_rows_total, int heads, int num_seqs, int q_len, int kv_len,
+                             int q_seq_stride, int kv_seq_stride, float scale, void* out, float* lse,
+                             void* stream) {
+  return launch_attention(q_src, q_rows_total, kv_src, kv_rows_total, heads, num_seqs, q_len, kv_len,
+                          q_seq_stride, kv_seq_stride, scale, out, lse, (cudaStream_t)stream);
+}
+
+extern "C" int mab_pack_conv3_weight(const float* w, int Cout, int Cin, void* out, void* stream) {
+  const int Cpad = (Cin + 63) / 64 * 64;
+  pack_conv3_kernel<<<ew_grid((long long)Cout * 9 * Cpad), 256, 0, (cudaStream_t)stream>>>(
+      w, Cout, Cin, Cpad, reinterpret_cast<bf16*>(out));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mab_conv3x3(const void* x, int batch, int H, int W, int C, const void* w_packed,
+                           int Cout, const float* bias, const void* res1, const void* res2, int act,
+                           void* out_bf16, void* out_relu, void* stream) {
+  GemmEpilogue ep{};
+  ep.bias = bias; ep.res1 = reinterpret_cast<const bf16*>(res1);
+  ep.res2 = reinterpret_cast<const bf16*>(res2); ep.out_bf16 = reinterpret_cast<bf16*>(out_bf16);
+  ep.out_relu = reinterpret_cast<bf16*>(out_relu); ep.ldo = Cout; ep.act = act;
+  return launch_conv3(x, batch, H, W, C, w_packed, Cout, ep, (cudaStream_t)stream);
+}
+
+extern "C" int mab_resize_bilinear(const void* x, int batch, int Hi, int Wi, int C, int Hv, int Wv,
+                                   int Ho, int Wo, void* out, void* out_relu, void* stream) {
+  MAB_ARG(C % 8 == 0, "C must be a multiple of 8");
+  resize_bilinear_ac_kernel<<<ew_grid((long long)batch * Ho * Wo * (C / 8)), 256, 0,
+                              (cudaStream_t)stream>>>(
+      reinterpret_cast<const bf16*>(x), batch, Hi, Wi, C, Hv, Wv, Ho, Wo,
+      reinterpret_cast<bf16*>(out), reinterpret_cast<bf16*>(out_relu));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mab_posembed_resize(const float* pos, int grid, int C, int h, int w, float* out,
+                                   void* stream) {
+  // vision_transformer.py:223-228: scale_factor = ((h + 0.1)/M, (w + 0.1)/M); ATen then uses
+  // 1/scale_factor as the source step
+  const float inv_sy = 1.0f / (float)((double)(h + 0.1) / grid);
+  const float inv_sx = 1.0f / (float)((double)(w + 0.1) / grid);
+  posembed_bicubic_kernel<<<ew_grid((long long)(1 + h * w) * C), 256, 0, (cudaStream_t)stream>>>(
+      pos, grid, C, h, w, inv_sy, inv_sx, out);
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// workspace: views*H*W*(3*4 + 1 + 4) bytes  (normals fp32x3, normal mask u8, angle fp32)
+extern "C" int mab_edge_mask(const float* pts3d, float* pts3d_cam, const unsigned char* fmask,
+                             int views, int H, int W, float normal_tol_deg, float depth_rtol,
+                             void* workspace, unsigned char* mask_out, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long npix = (long long)views * H * W;
+  float* normals = reinterpret_cast<float*>(workspace);
+  float* ang = normals + npix * 3;
+  unsigned char* nmask = reinterpret_cast<unsigned char*>(ang + npix);
+  normals_kernel<<<ew_grid(npix), 256, 0, st>>>(pts3d, fmask, views, H, W, normals, nmask);
+  normal_angle_kernel<<<ew_grid(npix), 256, 0, st>>>(normals, nmask, views, H, W, ang);
+  const double tol = (double)normal_tol_deg * 3.14159265358979323846 / 180.0;
+  edge_mask_apply_kernel<<<ew_grid(npix), 256, 0, st>>>(ang, fmask, views, H, W, 1, tol, depth_rtol,
+                                                        nullptr, pts3d_cam, nullptr, nullptr, mask_out);
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ================================================================================================
+// Part 2: model handle, weights, workspace plan
+// ================================================================================================
+namespace {
+
+struct RawTensor {
+  float* p = nullptr;
+  std::vector<int64_t> shape;
+  long long numel = 0;
+};
+
+std::string canonical_key(const std::string& k) {
+  // aliases of the reference state dict (model.py:398-400, dpt_block.py:71-78, dpt.py:176-178)
+  std::string s = k;
+  auto starts = [&](const char* p) { return s.rfind(p, 0) == 0; };
+  if (starts("dense_head.0.")) s = "dpt_feature_head." + s.substr(13);
+  else if (starts("dense_head.1.")) s = "dpt_regressor_head." + s.substr(13);
+  const std::string a = "dpt_feature_head.scratch.layer_rn.";
+  const std::string b = "dpt_feature_head.input_process.";
+  if (s.rfind(a, 0) == 0 && s.size() > a.size() + 1) {
+    const int i = s[a.size()] - '0';
+    s = "dpt_feature_head.scratch.layer" + std::to_string(i + 1) + "_rn" + s.substr(a.size() + 1);
+  } else if (s.rfind(b, 0) == 0 && s.size() > b.size() + 3 && s.substr(b.size() + 1, 3) == ".1.") {
+    const int i = s[b.size()] - '0';
+    s = "dpt_feature_head.scratch.layer" + std::to_string(i + 1) + "_rn" + s.substr(b.size() + 2);
+  }
+  return s;
+}
+
+struct Bump {  // bump allocator over the caller's workspace (256-byte aligned)
+  uint8_t* base = nullptr;
+  size_t off = 0;
+  template <typename T>
+  T* take(long long count) {
+    off = (off + 255) & ~size_t(255);
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += (size_t)count * sizeof(T);
+    return p;
+  }
+};
+
+struct Plan {  // every workspace pointer of one forward
+  int V = 0, Vtot = 0, H = 0, W = 0, h = 0, w = 0, T = 0;
+  int has_scale = 0, has_ref = 0;
+  long long Lenc = 0, L = 0;  // encoder rows V*(T+1); info-sharing rows V*T (+1)
+  // encoder
+  bf16* im2col; float* patch; float* pos; float* xs; bf16* ln; bf16* qkv; bf16* att; bf16* hid;
+  float* enc_out; bf16* fused;
+  // info sharing
+  float* ys; bf16* tap[2]; bf16* fin; float* scale_tok;
+  // heads (small)
+  float* scale_tmp; float* pose_pool; float* pose_tmp; float* pose_raw; bf16* ph_a; bf16* ph_b; bf16* ph_c;
+  // dense head chunk buffers
+  int vc = 0;
+  bf16* d_a; bf16* d_s; bf16* d_u; bf16* lvl[4]; bf16* lvl_relu[4]; bf16* t0; bf16* t1; bf16* t2; bf16* t3;
+  bf16* path; bf16* feat8; bf16* r1; bf16* r2;
+  size_t total = 0;
+};
+
+}  // namespace
+
+struct mab_handle {
+  mab_config cfg;
+  int device = 0;
+  bool finalized = false;
+  std::map<std::string, RawTensor> raw;       // fp32 device copies, canonical keys
+  std::map<std::string, bf16*> packed;        // bf16 GEMM / conv operands
+  std::map<std::string, float*> extra;        // derived fp32 tensors (tiled biases)
+  std::vector<void*> owned;
+  Plan plan;
+
+  const float* F(const std::string& k) const {
+    auto it = raw.find(k);
+    return it == raw.end() ? nullptr : it->second.p;
+  }
+  const bf16* P(const std::string& k) const {
+    auto it = packed.find(k);
+    return it == packed.end() ? nullptr : it->second;
+  }
+};
+
+namespace {
+
+void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scale, int has_ref,
+               void* ws, Plan* pl) {
+  const mab_config& c = hd->cfg;
+  Plan& p = *pl;
+  p.V = V; p.Vtot = Vtot; p.H = H; p.W = W; p.h = H / c.patch; p.w = W / c.patch; p.T = p.h * p.w;
+  p.has_scale = has_scale; p.has_ref = has_ref;
+  p.Lenc = (long long)V * (p.T + 1);
+  p.L = (long long)V * p.T + (has_scale ? 1 : 0);
+  const long long VT = (long long)V * p.T;
+  const int D = c.enc_dim, A = c.aat_dim;
+  Bump b; b.base = reinterpret_cast<uint8_t*>(ws);
+  p.im2col = b.take<bf16>(VT * 640);
+  p.patch = b.take<float>(VT * D);
+  p.pos = b.take<float>((long long)(p.T + 1) * D);
+  p.xs = b.take<float>(p.Lenc * D);
+  p.ln = b.take<bf16>(p.Lenc * D);
+  p.qkv = b.take<bf16>(p.Lenc * 3 * D);
+  p.att = b.take<bf16>(p.Lenc * D);
+  p.hid = b.take<bf16>(p.Lenc * 4 * D);
+  p.enc_out = b.take<float>(VT * D);
+  p.fused = b.take<bf16>((VT + 1) * D);
+  p.ys = b.take<float>((VT + 1) * A);
+  p.tap[0] = b.take<bf16>(VT * A);
+  p.tap[1] = b.take<bf16>(VT * A);
+  p.fin = b.take<bf16>(VT * A);
+  p.scale_tok = b.take<float>(A);
+  p.scale_tmp = b.take<float>(4 * 256);
+  p.pose_pool = b.take<float>((long long)V * 784);
+  p.pose_tmp = b.take<float>((long long)V * 784 * 2);
+  p.pose_raw = b.take<float>((long long)V * 8);
+  p.ph_a = b.take<bf16>(VT * 784);
+  p.ph_b = b.take<bf16>(VT * 784);
+  p.ph_c = b.take<bf16>(VT * 784);
+  // dense head, per chunk of vc views
+  p.vc = c.head_chunk < 1 ? 1 : (c.head_chunk > V ? V : c.head_chunk);
+  const long long vc = p.vc, T = p.T;
+  const int h = p.h, w = p.w;
+  p.d_a = b.take<bf16>(vc * T * 768);
+  p.d_s = b.take<bf16>(vc * T * 6912 / 1);  // >= T*1536 (convT) and >= Ho*Wo*9*768 (im2col s2)
+  p.d_u = b.take<bf16>(vc * 16 * T * 96);   // 4h x 4w x 96 == 2h x 2w x 192 * 2
+  const long long lvl_pix[4] = {16LL * T, 4LL * T, T, (long long)((h + 1) / 2) * ((w + 1) / 2)};
+  for (int i = 0; i < 4; ++i) {
+    p.lvl[i] = b.take<bf16>(vc * lvl_pix[i] * 256);
+    p.lvl_relu[i] = b.take<bf16>(vc * lvl_pix[i] * 256);
+  }
+  const long long big = vc * 16 * T * 256;  // 4h x 4w x 256
+  p.t0 = b.take<bf16>(big); p.t1 = b.take<bf16>(big); p.t2 = b.take<bf16>(big); p.t3 = b.take<bf16>(big);
+  p.path = b.take<bf16>(big);
+  p.feat8 = b.take<bf16>(vc * 64 * T * 256);
+  p.r1 = b.take<bf16>(vc * 64 * T * 128);
+  p.r2 = b.take<bf16>(vc * (long long)H * W * 128);
+  p.total = b.off + 256;
+}
+
+}  // namespace
+
+extern "C" int mab_create(const mab_config* cfg, int device, mab_handle** out) {
+  MAB_ARG(cfg && out, "null argument");
+  MAB_ARG(cfg->patch == 14 && cfg->enc_dim == 1024 && cfg->aat_dim == 768, "unsupported architecture");
+  MAB_ARG(cfg->enc_heads * 64 == cfg->enc_dim && cfg->aat_heads * 64 == cfg->aat_dim, "head_dim must be 64");
+  MAB_CUDA(cudaSetDevice(device));
+  mab_handle* h = new mab_handle();
+  h->cfg = *cfg;
+  h->device = device;
+  *out = h;
+  return 0;
+}
+
+extern "C" int mab_destroy(mab_handle* h) {
+  if (!h) return 0;
+  for (auto& kv : h->raw) cudaFree(kv.second.p);
+  for (void* p : h->owned) cudaFree(p);
+  delete h;
+  return 0;
+}
+
+extern "C" int mab_set_weight(mab_handle* h, const char* ref_key, const void* ptr, int dtype,
+                              int ndim, const int64_t* shape) {
+  MAB_ARG(h && ref_key && ptr && shape, "null argument");
+  MAB_ARG(dtype == MAB_F32, "weights must be fp32");
+  MAB_ARG(!h->finalized, "weights are frozen after mab_finalize_weights");
+  MAB_CUDA(cudaSetDevice(h->device));
+  const std::string key = canonical_key(ref_key);
+  long long n = 1;
+  for (int i = 0; i < ndim; ++i) n *= shape[i];
+  RawTensor& t = h->raw[key];
+  if (t.p && t.numel != n) { cudaFree(t.p); t.p = nullptr; }
+  if (!t.p) MAB_CUDA(cudaMalloc(&t.p, (size_t)n * sizeof(float)));
+  t.numel = n;
+  t.shape.assign(shape, shape + ndim);
+  MAB_CUDA(cudaMemcpy(t.p, ptr, (size_t)n * sizeof(float), cudaMemcpyDefault));
+  return 0;
+}
+
+// ================================================================================================
+// Part 3: weight packing
+// ================================================================================================
+namespace {
+
+int pack_linear(mab_handle* h, const std::string& key, int ld_pad, cudaStream_t st) {
+  auto it = h->raw.find(key);
+  if (it == h->raw.end()) return fail(-4, "missing weight %s", key.c_str());
+  const RawTensor& t = it->second;
+  const int rows = (int)t.shape[0];
+  const int cols = (int)(t.numel / rows);
+  const int ld = ld_pad > 0 ? ld_pad : cols;
+  bf16* out;
+  MAB_CUDA(cudaMalloc(&out, (size_t)rows * ld * sizeof(bf16)));
+  h->owned.push_back(out);
+  pack_matrix_kernel<<<ew_grid((long long)rows * ld), 256, 0, st>>>(t.p, rows, cols, ld, out);
+  MAB_CUDA(cudaGetLastError());
+  h->packed[key] = out;
+  return 0;
+}
+
+int pack_conv3(mab_handle* h, const std::string& key, cudaStream_t st) {
+  auto it = h->raw.find(key);
+  if (it == h->raw.end()) return fail(-4, "missing weight %s", key.c_str());
+  const RawTensor& t = it->second;
+  const int Cout = (int)t.shape[0], Cin = (int)t.shape[1];
+  const int Cpad = (Cin + 63) / 64 * 64;
+  bf16* out;
+  MAB_CUDA(cudaMalloc(&out, (size_t)Cout * 9 * Cpad * sizeof(bf16)));
+  h->owned.push_back(out);
+  pack_conv3_kernel<<<ew_grid((long long)Cout * 9 * Cpad), 256, 0, st>>>(t.p, Cout, Cin, Cpad, out);
+  MAB_CUDA(cudaGetLastError());
+  h->packed[key] = out;
+  return 0;
+}
+
+int pack_convT(mab_handle* h, const std::string& wkey, const std::string& bkey, cudaStream_t st) {
+  auto it = h->raw.find(wkey);
+  auto ib = h->raw.find(bkey);
+  if (it == h->raw.end() || ib == h->raw.end()) return fail(-4, "missing weight %s", wkey.c_str());
+  const RawTensor& t = it->second;
+  const int Cin = (int)t.shape[0], Cout = (int)t.shape[1], k = (int)t.shape[2];
+  bf16* out;
+  MAB_CUDA(cudaMalloc(&out, (size_t)k * k * Cout * Cin * sizeof(bf16)));
+  h->owned.push_back(out);
+  pack_convT_kernel<<<ew_grid((long long)k * k * Cout * Cin), 256, 0, st>>>(t.p, Cin, Cout, k, out);
+  float* bt;
+  MAB_CUDA(cudaMalloc(&bt, (size_t)k * k * Cout * sizeof(float)));
+  h->owned.push_back(bt);
+  tile_bias_kernel<<<(k * k * Cout + 255) / 256, 256, 0, st>>>(ib->second.p, Cout, k * k, bt);
+  MAB_CUDA(cudaGetLastError());
+  h->packed[wkey] = out;
+  h->extra[bkey + ".tiled"] = bt;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
+  MAB_ARG(h, "null handle");
+  MAB_CUDA(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const mab_config& c = h->cfg;
+  MAB_TRY(pack_linear(h, "encoder.model.patch_embed.proj.weight", 640, st));
+  for (int i = 0; i < c.enc_depth; ++i) {
+    const std::string p = "encoder.model.blocks." + std::to_string(i);
+    for (const char* s : {".attn.qkv.weight", ".attn.proj.weight", ".mlp.fc1.weight", ".mlp.fc2.weight"})
+      MAB_TRY(pack_linear(h, p + s, 0, st));
+  }
+  MAB_TRY(pack_linear(h, "info_sharing.proj_embed.weight", 0, st));
+  for (int i = 0; i < c.aat_depth; ++i) {
+    const std::string p = "info_sharing.self_attention_blocks." + std::to_string(i);
+    for (const char* s : {".attn.qkv.weight", ".attn.proj.weight", ".mlp.fc1.weight", ".mlp.fc2.weight"})
+      MAB_TRY(pack_linear(h, p + s, 0, st));
+  }
+  const std::string ip = "dpt_feature_head.input_process.";
+  for (int i = 0; i < 4; ++i) MAB_TRY(pack_linear(h, ip + std::to_string(i) + ".0.0.weight", 0, st));
+  MAB_TRY(pack_convT(h, ip + "0.0.1.weight", ip + "0.0.1.bias", st));
+  MAB_TRY(pack_convT(h, ip + "1.0.1.weight", ip + "1.0.1.bias", st));
+  MAB_TRY(pack_conv3(h, ip + "3.0.1.weight", st));
+  const std::string sc = "dpt_feature_head.scratch.";
+  for (int i = 1; i <= 4; ++i) {
+    MAB_TRY(pack_conv3(h, sc + "layer" + std::to_string(i) + "_rn.weight", st));
+    const std::string r = sc + "refinenet" + std::to_string(i);
+    for (const char* u : {".resConfUnit1", ".resConfUnit2"}) {
+      if (i == 4 && std::string(u) == ".resConfUnit1") continue;  // dpt.py:82-83
+      MAB_TRY(pack_conv3(h, r + u + ".conv1.weight", st));
+      MAB_TRY(pack_conv3(h, r + u + ".conv2.weight", st));
+    }
+    MAB_TRY(pack_linear(h, r + ".out_conv.weight", 0, st));
+  }
+  MAB_TRY(pack_conv3(h, "dpt_regressor_head.conv1.weight", st));
+  MAB_TRY(pack_conv3(h, "dpt_regressor_head.conv2.0.weight", st));
+  MAB_TRY(pack_linear(h, "pose_head.proj.weight", 0, st));
+  for (int b = 0; b < 2; ++b)
+    for (int k = 1; k <= 3; ++k)
+      MAB_TRY(pack_linear(h, "pose_head.res_conv." + std::to_string(b) + ".res_conv" + std::to_string(k) + ".weight", 0, st));
+  // required fp32 tensors that are used as-is
+  for (const char* k : {"encoder.model.cls_token", "encoder.model.pos_embed", "encoder.model.norm.weight",
+                        "fusion_norm_layer.weight", "scale_token", "info_sharing.view_pos_table",
+                        "info_sharing.norm.weight", "dpt_regressor_head.conv2.2.weight",
+                        "pose_head.more_mlps.0.weight", "pose_head.fc_t.weight", "pose_head.fc_rot.weight",
+                        "scale_head.proj.weight", "scale_head.output_proj.weight"})
+    if (!h->F(k)) return fail(-4, "missing weight %s", k);
+  // fc_t | fc_rot fused into one [7,784] matrix + [7] bias for the pose tail
+  {
+    float* w7; float* b7;
+    MAB_CUDA(cudaMalloc(&w7, 7 * 784 * sizeof(float)));
+    MAB_CUDA(cudaMalloc(&b7, 8 * sizeof(float)));
+    h->owned.push_back(w7); h->owned.push_back(b7);
+    MAB_CUDA(cudaMemcpyAsync(w7, h->F("pose_head.fc_t.weight"), 3 * 784 * 4, cudaMemcpyDeviceToDevice, st));
+    MAB_CUDA(cudaMemcpyAsync(w7 + 3 * 784, h->F("pose_head.fc_rot.weight"), 4 * 784 * 4, cudaMemcpyDeviceToDevice, st));
+    MAB_CUDA(cudaMemcpyAsync(b7, h->F("pose_head.fc_t.bias"), 3 * 4, cudaMemcpyDeviceToDevice, st));
+    MAB_CUDA(cudaMemcpyAsync(b7 + 3, h->F("pose_head.fc_rot.bias"), 4 * 4, cudaMemcpyDeviceToDevice, st));
+    h->extra["pose_head.fc7.weight"] = w7;
+    h->extra["pose_head.fc7.bias"] = b7;
+  }
+  MAB_CUDA(cudaStreamSynchronize(st));  // one-time setup, not on the inference path
+  h->finalized = true;
+  return 0;
+}
+
+extern "C" size_t mab_workspace_bytes(mab_handle* h, int views_local, int views_total, int H, int W) {
+  if (!h || views_local <= 0 || H % h->cfg.patch || W % h->cfg.patch) return 0;
+  Plan p;
+  make_plan(h, views_local, views_total, H, W, 1, 1, nullptr, &p);
+  return p.total;
+}
+
+// ================================================================================================
+// Part 4: forward stages
+// ================================================================================================
+namespace {
+
+struct Ctx {
+  mab_handle* h;
+  cudaStream_t st;
+  // y = epilogue(A[M,K] W[N,K]^T); W, bias looked up by reference key
+  int linear(const void* A, int M, int K, long long lda, const std::string& wkey, int N,
+             const float* bias, int act, const float* gamma, const float* res_f32, float* out_f32,
+             bf16* out_bf16, const bf16* res1 = nullptr, long long ldw = 0) {
+    const bf16* W = h->P(wkey);
+    if (!W) return fail(-4, "weight %s was not packed", wkey.c_str());
+    GemmEpilogue ep{};
+    ep.bias = bias; ep.gamma = gamma; ep.res_f32 = res_f32; ep.out_f32 = out_f32;
+    ep.out_bf16 = out_bf16; ep.res1 = res1; ep.ldo = N; ep.act = act;
+    return launch_gemm(A, lda, W, ldw > 0 ? ldw : K, M, N, K, ep, st);
+  }
+  int conv3(const bf16* x, int batch, int H, int W, int C, const std::string& wkey, int Cout,
+            const float* bias, int act, const bf16* res1, const bf16* res2, bf16* out, bf16* out_relu) {
+    const bf16* Wp = h->P(wkey);
+    if (!Wp) return fail(-4, "weight %s was not packed", wkey.c_str());
+    GemmEpilogue ep{};
+    ep.bias = bias; ep.res1 = res1; ep.res2 = res2; ep.out_bf16 = out; ep.out_relu = out_relu;
+    ep.ldo = Cout; ep.act = act;
+    return launch_conv3(x, batch, H, W, C, Wp, Cout, ep, st);
+  }
+};
+
+// one pre-LN transformer block over `rows` tokens of width D (block.py:93-118,
+// transformer_blocks.py:467-468): x += g1*proj(attn(LN1 x)); x += g2*fc2(gelu(fc1(LN2 x)))
+int block_qkv(Ctx& c, const std::string& p, float* x, long long rows, int D, bf16* ln, bf16* qkv) {
+  mab_handle* h = c.h;
+  MAB_TRY(launch_layernorm(x, (int)rows, D, (int)rows, (int)rows, 0, h->F(p + ".norm1.weight"),
+                           h->F(p + ".norm1.bias"), nullptr, nullptr, 1e-6f, ln, nullptr, nullptr, c.st));
+  return c.linear(ln, (int)rows, D, D, p + ".attn.qkv.weight", 3 * D, h->F(p + ".attn.qkv.bias"),
+                  ACT_NONE, nullptr, nullptr, nullptr, qkv);
+}
+int block_tail(Ctx& c, const std::string& p, float* x, long long rows, int D, bf16* att, bf16* ln,
+               bf16* hid, const float* g1, const float* g2) {
+  mab_handle* h = c.h;
+  MAB_TRY(c.linear(att, (int)rows, D, D, p + ".attn.proj.weight", D, h->F(p + ".attn.proj.bias"),
+                   ACT_NONE, g1, x, x, nullptr));
+  MAB_TRY(launch_layernorm(x, (int)rows, D, (int)rows, (int)rows, 0, h->F(p + ".norm2.weight"),
+                           h->F(p + ".norm2.bias"), nullptr, nullptr, 1e-6f, ln, nullptr, nullptr, c.st));
+  MAB_TRY(c.linear(ln, (int)rows, D, D, p + ".mlp.fc1.weight", 4 * D, h->F(p + ".mlp.fc1.bias"),
+                   ACT_GELU, nullptr, nullptr, nullptr, hid));
+  return c.linear(hid, (int)rows, 4 * D, 4 * D, p + ".mlp.fc2.weight", D, h->F(p + ".mlp.fc2.bias"),
+                  ACT_NONE, g2, x, x, nullptr);
+}
+
+}  // namespace
+
+// a2-a7: patch embed, 24 DINOv2 blocks, encoder norm (+ fusion norm), proj_embed, ref-view PE
+extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, void* workspace,
+                                size_t workspace_bytes, int has_scale_token, void* stream) {
+  MAB_ARG(h && in && workspace && h->finalized, "handle not ready");
+  MAB_ARG(in->views > 0 && in->H % 14 == 0 && in->W % 14 == 0 && in->images, "bad inputs");
+  MAB_CUDA(cudaSetDevice(h->device));
+  const mab_config& cf = h->cfg;
+  Ctx c{h, (cudaStream_t)stream};
+  // has_scale_token bit0: this rank owns the scale token; bit1: this rank owns view 0
+  make_plan(h, in->views, in->views, in->H, in->W, has_scale_token & 1, (has_scale_token >> 1) & 1,
+            workspace, &h->plan);
+  Plan& p = h->plan;
+  if (p.total > workspace_bytes)
+    return fail(-5, "workspace too small: need %zu bytes, got %zu", p.total, workspace_bytes);
+  const int V = p.V, T = p.T, D = cf.enc_dim;
+  const long long VT = (long long)V * T;
+  const bool multimodal = in->ray_dirs || in->depth_along_ray || in->cam_quats;
+  if (multimodal) return fail(-6, "geometric inputs are not wired into this build yet");
+
+  patch_im2col_kernel<<<ew_grid(VT * 640), 256, 0, c.st>>>(in->images, V, p.H, p.W, 640, p.im2col);
+  MAB_TRY(c.linear(p.im2col, (int)VT, 640, 640, "encoder.model.patch_embed.proj.weight", D,
+                   h->F("encoder.model.patch_embed.proj.bias"), ACT_NONE, nullptr, nullptr, p.patch,
+                   nullptr, nullptr, 640));
+  MAB_TRY(mab_posembed_resize(h->F("encoder.model.pos_embed"), cf.enc_pos_grid, D, p.h, p.w, p.pos, c.st));
+  assemble_tokens_kernel<<<ew_grid(p.Lenc * D / 4), 256, 0, c.st>>>(
+      p.patch, h->F("encoder.model.cls_token"), p.pos, V, T, D, p.xs);
+  MAB_CUDA(cudaGetLastError());
+  for (int i = 0; i < cf.enc_depth; ++i) {
+    const std::string b = "encoder.model.blocks." + std::to_string(i);
+    MAB_TRY(block_qkv(c, b, p.xs, p.Lenc, D, p.ln, p.qkv));
+    MAB_TRY(launch_attention(p.qkv, p.Lenc, p.qkv, p.Lenc, cf.enc_heads, V, T + 1, T + 1, T + 1,
+                             T + 1, 0.125f, p.att, nullptr, c.st));
+    MAB_TRY(block_tail(c, b, p.xs, p.Lenc, D, p.att, p.ln, p.hid, h->F(b + ".ls1.gamma"),
+                       h->F(b + ".ls2.gamma")));
+  }
+  // encoder norm on the patch tokens only (drop cls), immediately followed by the fusion norm
+  // (image-only: the geometric features are exactly zero, model.py:931-968 / SURVEY 8a a6)
+  MAB_TRY(launch_layernorm(p.xs, (int)VT, D, T, T + 1, 1, h->F("encoder.model.norm.weight"),
+                           h->F("encoder.model.norm.bias"), h->F("fusion_norm_layer.weight"),
+                           h->F("fusion_norm_layer.bias"), 1e-6f, p.fused, nullptr, nullptr, c.st));
+  if (p.has_scale) {
+    f32_to_bf16_kernel<<<4, 256, 0, c.st>>>(h->F("scale_token"), p.fused + VT * D, D);
+    MAB_CUDA(cudaGetLastError());
+  }
+  // proj_embed (aat.py:121-124,600) + reference-view PE on view 0's tokens (aat.py:618-626)
+  MAB_TRY(c.linear(p.fused, (int)p.L, D, D, "info_sharing.proj_embed.weight", cf.aat_dim,
+                   h->F("info_sharing.proj_embed.bias"), ACT_NONE, nullptr, nullptr, p.ys, nullptr));
+  if (p.has_ref) {
+    add_row_vector_kernel<<<ew_grid((long long)T * cf.aat_dim), 256, 0, c.st>>>(
+        p.ys, h->F("info_sharing.view_pos_table"), T, cf.aat_dim);
+    MAB_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+extern "C" int mab_stage_aat_qkv(mab_handle* h, int layer, void* workspace, void** qkv_out,
+                                 int* rows_out, void* stream) {
+  MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");
+  (void)workspace;
+  Ctx c{h, (cudaStream_t)stream};
+  Plan& p = h->plan;
+  const long long rows = (layer % 2 == 0) ? p.L : (long long)p.V * p.T;  // odd: scale token skips
+  const std::string b = "info_sharing.self_attention_blocks." + std::to_string(layer);
+  MAB_TRY(block_qkv(c, b, p.ys, rows, h->cfg.aat_dim, p.ln, p.qkv));
+  if (qkv_out) *qkv_out = p.qkv;
+  if (rows_out) *rows_out = (int)rows;
+  return 0;
+}
+
+extern "C" int mab_stage_aat_block(mab_handle* h, int layer, void* workspace, const void* kv,
+                                   int kv_rows, void* stream) {
+  MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");
+  (void)workspace;
+  const mab_config& cf = h->cfg;
+  Ctx c{h, (cudaStream_t)stream};
+  Plan& p = h->plan;
+  const int A = cf.aat_dim, T = p.T, V = p.V;
+  const std::string b = "info_sharing.self_attention_blocks." + std::to_string(layer);
+  long long rows;
+  if (layer % 2 == 0) {  // global attention over every token of the scene (aat.py:657-661)
+    rows = p.L;
+    const void* kvp = kv ? kv : p.qkv;
+    const int kvr = kv ? kv_rows : (int)rows;
+    MAB_TRY(launch_attention(p.qkv, rows, kvp, kvr, cf.aat_heads, 1, (int)rows, kvr, 0, 0, 0.125f,
+                             p.att, nullptr, c.st));
+  } else {  // frame attention inside each view (aat.py:662-705)
+    rows = (long long)V * T;
+    MAB_TRY(launch_attention(p.qkv, rows, p.qkv, rows, cf.aat_heads, V, T, T, T, T, 0.125f, p.att,
+                             nullptr, c.st));
+  }
+  MAB_TRY(block_tail(c, b, p.ys, rows, A, p.att, p.ln, p.hid, nullptr, nullptr));
+  // intermediate taps + final norm (aat.py:706-716), token-major == NHWC for the dense head
+  const long long VT = (long long)V * T;
+  const float* nw = h->F("info_sharing.norm.weight");
+  const float* nb = h->F("info_sharing.norm.bias");
+  bf16* dst = nullptr;
+  if (layer == cf.aat_tap0) dst = p.tap[0];
+  else if (layer == cf.aat_tap1) dst = p.tap[1];
+  if (dst)
+    MAB_TRY(launch_layernorm(p.ys, (int)VT, A, (int)VT, (int)VT, 0, nw, nb, nullptr, nullptr, 1e-6f,
+                             dst, nullptr, nullptr, c.st));
+  if (layer == cf.aat_depth - 1) {
+    MAB_TRY(launch_layernorm(p.ys, (int)VT, A, (int)VT, (int)VT, 0, nw, nb, nullptr, nullptr, 1e-6f,
+                             p.fin, nullptr, nullptr, c.st));
+    if (p.has_scale)
+      MAB_TRY(launch_layernorm(p.ys + VT * A, 1, A, 1, 1, 0, nw, nb, nullptr, nullptr, 1e-6f, nullptr,
+                               p.scale_tok, nullptr, c.st));
+  }
+  return 0;
+}
+
+// ================================================================================================
+// Part 5: heads (a10-a14), whole forward, post-processing (a16)
+// ================================================================================================
+namespace {
+
+int small_linear(cudaStream_t st, const float* x, const float* w, const float* b, int rows, int K,
+                 int N, int act, float* y) {
+  const long long warps = (long long)N * ((rows + 7) / 8);
+  small_linear_kernel<<<(int)((warps * 32 + 255) / 256), 256, 0, st>>>(x, w, b, rows, K, N, act, y, K, N);
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ResidualConvUnit_custom (dpt_block.py:156-177) on `x` (with relu(x) precomputed in x_relu):
+//   out = conv2(relu(conv1(relu(x)) + b1)) + b2 + x (+ extra)
+int rcu(Ctx& c, const std::string& p, const bf16* x, const bf16* x_relu, const bf16* extra, int batch,
+        int H, int W, bf16* tmp_relu, bf16* out, bf16* out_relu) {
+  mab_handle* h = c.h;
+  MAB_TRY(c.conv3(x_relu, batch, H, W, 256, p + ".conv1.weight", 256, h->F(p + ".conv1.bias"), ACT_RELU,
+                  nullptr, nullptr, tmp_relu, nullptr));
+  return c.conv3(tmp_relu, batch, H, W, 256, p + ".conv2.weight", 256, h->F(p + ".conv2.bias"), ACT_NONE,
+                 x, extra, out, out_relu);
+}
+
+}  // namespace
+
+extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out, void* workspace,
+                               const float* metric_scale_in, void* stream) {
+  MAB_ARG(h && in && out && h->plan.V > 0, "mab_stage_encode must run first");
+  (void)workspace;
+  const mab_config& cf = h->cfg;
+  Ctx c{h, (cudaStream_t)stream};
+  Plan& p = h->plan;
+  const int V = p.V, T = p.T, A = cf.aat_dim, hh = p.h, ww = p.w, H = p.H, W = p.W;
+  const long long VT = (long long)V * T;
+
+  // ---- scale head (mlp_head.py:58-92, adaptors.py:190-212) ------------------------------------
+  if (p.has_scale) {
+    float* t0 = p.scale_tmp; float* t1 = p.scale_tmp + 256; float* t2 = p.scale_tmp + 512;
+    MAB_TRY(small_linear(c.st, p.scale_tok, h->F("scale_head.proj.weight"), h->F("scale_head.proj.bias"), 1, A, 196, 0, t0));
+    MAB_TRY(small_linear(c.st, t0, h->F("scale_head.mlp.0.0.weight"), h->F("scale_head.mlp.0.0.bias"), 1, 196, 196, 2, t1));
+    MAB_TRY(small_linear(c.st, t1, h->F("scale_head.mlp.1.0.weight"), h->F("scale_head.mlp.1.0.bias"), 1, 196, 196, 2, t2));
+    MAB_TRY(small_linear(c.st, t2, h->F("scale_head.output_proj.weight"), h->F("scale_head.output_proj.bias"), 1, 196, 1, 0, t0));
+    scale_finalize_kernel<<<1, 32, 0, c.st>>>(t0, out->metric_scale);
+  } else {
+    MAB_ARG(metric_scale_in, "rank without the scale token needs metric_scale_in");
+    MAB_CUDA(cudaMemcpyAsync(out->metric_scale, metric_scale_in, sizeof(float), cudaMemcpyDeviceToDevice, c.st));
+  }
+
+  // ---- pose head (pose_head.py:115-159, adaptors.py:714-732) -----------------------------------
+  {
+    const std::string ph = "pose_head.";
+    MAB_TRY(c.linear(p.fin, (int)VT, A, A, ph + "proj.weight", 784, h->F(ph + "proj.bias"), ACT_NONE,
+                     nullptr, nullptr, nullptr, p.ph_a));
+    bf16* feat = p.ph_a; bf16* other = p.att;  // p.att is free after the transformer
+    for (int b = 0; b < 2; ++b) {
+      const std::string r = ph + "res_conv." + std::to_string(b) + ".res_conv";
+      MAB_TRY(c.linear(feat, (int)VT, 784, 784, r + "1.weight", 784, h->F(r + "1.bias"), ACT_RELU, nullptr, nullptr, nullptr, p.ph_b));
+      MAB_TRY(c.linear(p.ph_b, (int)VT, 784, 784, r + "2.weight", 784, h->F(r + "2.bias"), ACT_RELU, nullptr, nullptr, nullptr, p.ph_c));
+      MAB_TRY(c.linear(p.ph_c, (int)VT, 784, 784, r + "3.weight", 784, h->F(r + "3.bias"), ACT_RELU, nullptr, nullptr, nullptr, other, feat));
+      bf16* t = feat; feat = other; other = t;
+    }
+    dim3 blk(128, 8), grd((784 + 127) / 128, V);
+    token_mean_kernel<<<grd, blk, 0, c.st>>>(feat, T, 784, p.pose_pool);
+    MAB_CUDA(cudaGetLastError());
+    float* m0 = p.pose_tmp; float* m1 = p.pose_tmp + (long long)V * 784;
+    MAB_TRY(small_linear(c.st, p.pose_pool, h->F(ph + "more_mlps.0.weight"), h->F(ph + "more_mlps.0.bias"), V, 784, 784, 2, m0));
+    MAB_TRY(small_linear(c.st, m0, h->F(ph + "more_mlps.2.weight"), h->F(ph + "more_mlps.2.bias"), V, 784, 784, 2, m1));
+    small_linear_kernel<<<(int)(((long long)7 * ((V + 7) / 8) * 32 + 255) / 256), 256, 0, c.st>>>(
+        m1, h->extra["pose_head.fc7.weight"], h->extra["pose_head.fc7.bias"], V, 784, 7, 0, p.pose_raw, 784, 7);
+    pose_finalize_kernel<<<(V + 127) / 128, 128, 0, c.st>>>(p.pose_raw, V, out->pose);
+    MAB_CUDA(cudaGetLastError());
+  }
+
+  // ---- dense head: DPT feature pyramid + regressor + fused adaptor/pointmap epilogue -----------
+  const std::string ip = "dpt_feature_head.input_process.";
+  const std::string sc = "dpt_feature_head.scratch.";
+  const int h3 = (hh + 1) / 2, w3 = (ww + 1) / 2;
+  for (int v0 = 0; v0 < V; v0 += p.vc) {
+    const int vc = (V - v0 < p.vc) ? V - v0 : p.vc;
+    const int M = vc * T;
+    const bf16* f0 = p.fused + (long long)v0 * T * cf.enc_dim;
+    const bf16* f1 = p.tap[0] + (long long)v0 * T * A;
+    const bf16* f2 = p.tap[1] + (long long)v0 * T * A;
+    const bf16* f3 = p.fin + (long long)v0 * T * A;
+    // layer 0: 1x1 (1024->96) -> convT 4x4/s4 -> 3x3 (96->256, no bias)           dpt.py:107-128
+    MAB_TRY(c.linear(f0, M, cf.enc_dim, cf.enc_dim, ip + "0.0.0.weight", 96, h->F(ip + "0.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
+    MAB_TRY(c.linear(p.d_a, M, 96, 96, ip + "0.0.1.weight", 16 * 96, h->extra[ip + "0.0.1.bias.tiled"], ACT_NONE, nullptr, nullptr, nullptr, p.d_s));
+    pixel_shuffle_kernel<<<ew_grid((long long)M * 16 * 12), 256, 0, c.st>>>(p.d_s, vc, hh, ww, 4, 96, p.d_u);
+    MAB_TRY(c.conv3(p.d_u, vc, 4 * hh, 4 * ww, 96, sc + "layer1_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[0], p.lvl_relu[0]));
+    // layer 1: 1x1 (768->192) -> convT 2x2/s2 -> 3x3 (192->256)
+    MAB_TRY(c.linear(f1, M, A, A, ip + "1.0.0.weight", 192, h->F(ip + "1.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
+    MAB_TRY(c.linear(p.d_a, M, 192, 192, ip + "1.0.1.weight", 4 * 192, h->extra[ip + "1.0.1.bias.tiled"], ACT_NONE, nullptr, nullptr, nullptr, p.d_s));
+    pixel_shuffle_kernel<<<ew_grid((long long)M * 4 * 24), 256, 0, c.st>>>(p.d_s, vc, hh, ww, 2, 192, p.d_u);
+    MAB_TRY(c.conv3(p.d_u, vc, 2 * hh, 2 * ww, 192, sc + "layer2_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[1], p.lvl_relu[1]));
+    // layer 2: 1x1 (768->384) -> 3x3 (384->256)
+    MAB_TRY(c.linear(f2, M, A, A, ip + "2.0.0.weight", 384, h->F(ip + "2.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
+    MAB_TRY(c.conv3(p.d_a, vc, hh, ww, 384, sc + "layer3_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[2], p.lvl_relu[2]));
+    // layer 3: 1x1 (768->768) -> 3x3/s2 (im2col + GEMM) -> 3x3 (768->256)
+    MAB_TRY(c.linear(f3, M, A, A, ip + "3.0.0.weight", 768, h->F(ip + "3.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
+    im2col3x3_s2_kernel<<<ew_grid((long long)vc * h3 * w3 * 9 * 96), 256, 0, c.st>>>(p.d_a, vc, hh, ww, 768, h3, w3, p.d_s);
+    MAB_TRY(c.linear(p.d_s, vc * h3 * w3, 9 * 768, 9 * 768, ip + "3.0.1.weight", 768, h->F(ip + "3.0.1.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_u));
+    MAB_TRY(c.conv3(p.d_u, vc, h3, w3, 768, sc + "layer4_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[3], p.lvl_relu[3]));
+    MAB_CUDA(cudaGetLastError());
+
+    // refinenet4: RCU2 -> out_conv (1x1, commutes with the bilinear x2) -> x2 -> crop   dpt.py:213
+    MAB_TRY(rcu(c, sc + "refinenet4.resConfUnit2", p.lvl[3], p.lvl_relu[3], nullptr, vc, h3, w3, p.t0, p.t1, nullptr));
+    MAB_TRY(c.linear(p.t1, vc * h3 * w3, 256, 256, sc + "refinenet4.out_conv.weight", 256, h->F(sc + "refinenet4.out_conv.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.t2));
+    MAB_TRY(mab_resize_bilinear(p.t2, vc, h3, w3, 256, 2 * h3, 2 * w3, hh, ww, p.path, nullptr, c.st));
+    // refinenet3/2/1: x = path + RCU1(skip); x = RCU2(x); out_conv; x2                dpt_block.py:225-255
+    int lh = hh, lw = ww;
+    for (int lvl = 2; lvl >= 0; --lvl) {
+      const std::string r = sc + "refinenet" + std::to_string(lvl + 1);
+      MAB_TRY(rcu(c, r + ".resConfUnit1", p.lvl[lvl], p.lvl_relu[lvl], p.path, vc, lh, lw, p.t0, p.t1, p.t2));
+      MAB_TRY(rcu(c, r + ".resConfUnit2", p.t1, p.t2, nullptr, vc, lh, lw, p.t0, p.t3, nullptr));
+      MAB_TRY(c.linear(p.t3, vc * lh * lw, 256, 256, r + ".out_conv.weight", 256, h->F(r + ".out_conv.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.t0));
+      bf16* dst = (lvl == 0) ? p.feat8 : p.path;
+      MAB_TRY(mab_resize_bilinear(p.t0, vc, lh, lw, 256, 2 * lh, 2 * lw, 2 * lh, 2 * lw, dst, nullptr, c.st));
+      lh *= 2; lw *= 2;
+    }
+    // regressor: 3x3 (256->128) -> bilinear to HxW -> [3x3 (128->128) + ReLU + 1x1 (128->6) +
+    // adaptor + pointmap] in one kernel                                               dpt.py:285-311
+    MAB_TRY(c.conv3(p.feat8, vc, lh, lw, 256, "dpt_regressor_head.conv1.weight", 128, h->F("dpt_regressor_head.conv1.bias"), ACT_NONE, nullptr, nullptr, p.r1, nullptr));
+    MAB_TRY(mab_resize_bilinear(p.r1, vc, lh, lw, 128, H, W, H, W, p.r2, nullptr, c.st));
+    RegressEpilogue rg{};
+    const long long px0 = (long long)v0 * H * W;
+    rg.bias2 = h->F("dpt_regressor_head.conv2.0.bias");
+    rg.w3 = h->F("dpt_regressor_head.conv2.2.weight");
+    rg.b3 = h->F("dpt_regressor_head.conv2.2.bias");
+    rg.pose = out->pose + (long long)v0 * 8;
+    rg.scale = out->metric_scale;
+    rg.pts3d = out->pts3d + px0 * 3; rg.pts3d_cam = out->pts3d_cam + px0 * 3;
+    rg.rays = out->ray_directions + px0 * 3; rg.depth = out->depth_along_ray + px0;
+    rg.conf = out->conf + px0; rg.mask_logits = out->mask_logits + px0;
+    rg.mask = out->non_ambiguous_mask + px0;
+    rg.logits6 = out->logits6 ? out->logits6 + px0 * 6 : nullptr;
+    const bf16* w2 = h->P("dpt_regressor_head.conv2.0.weight");
+    MAB_TRY(launch_conv3_regress(p.r2, vc, H, W, w2, rg, c.st));
+  }
+  return 0;
+}
+
+extern "C" int mab_forward(mab_handle* h, const mab_inputs* in, mab_outputs* out, void* workspace,
+                           size_t workspace_bytes, void* stream) {
+  MAB_ARG(h && in && out, "null argument");
+  MAB_TRY(mab_stage_encode(h, in, workspace, workspace_bytes, 3, stream));
+  for (int l = 0; l < h->cfg.aat_depth; ++l) {
+    MAB_TRY(mab_stage_aat_qkv(h, l, workspace, nullptr, nullptr, stream));
+    MAB_TRY(mab_stage_aat_block(h, l, workspace, nullptr, 0, stream));
+  }
+  return mab_stage_heads(h, in, out, workspace, nullptr, stream);
+}
+
+// workspace: views*H*W*17 bytes + 256
+extern "C" int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs* raw,
+                               mab_post_outputs* post, const mab_post_options* opt, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+  MAB_ARG(h && in && raw && post && opt, "null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int V = in->views, H = in->H, W = in->W;
+  const long long npix = (long long)V * H * W;
+  MAB_ARG(workspace_bytes >= (size_t)npix * 17 + 256, "post-process workspace too small");
+  if (opt->apply_confidence_mask)
+    return fail(-6, "apply_confidence_mask is not wired into this build yet");
+  denorm_image_kernel<<<ew_grid(npix), 256, 0, st>>>(in->images, V, H, W, 0.485f, 0.456f, 0.406f,
+                                                     0.229f, 0.224f, 0.225f, post->img_no_norm);
+  intrinsics_pose_kernel<<<V, 256, 0, st>>>(raw->ray_directions, H, W, raw->pose, raw->metric_scale,
+                                            post->intrinsics, post->camera_poses, post->cam_trans,
+                                            post->cam_quats);
+  if (opt->apply_mask) {
+    if (opt->mask_edges) {
+      MAB_TRY(mab_edge_mask(raw->pts3d, raw->pts3d_cam, raw->non_ambiguous_mask, V, H, W,
+                            opt->edge_normal_threshold_deg, opt->edge_depth_threshold, workspace,
+                            post->mask, st));
+    } else {
+      MAB_CUDA(cudaMemcpyAsync(post->mask, raw->non_ambiguous_mask, npix, cudaMemcpyDeviceToDevice, st));
+    }
+  }
+  apply_mask_kernel<<<ew_grid(npix), 256, 0, st>>>(post->mask, npix, opt->apply_mask, raw->pts3d,
+                                                   raw->pts3d_cam, raw->depth_along_ray, post->depth_z);
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}

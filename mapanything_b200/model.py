@@ -1,0 +1,337 @@
+"""Host-side mirror of the reference's `MapAnything` class for the inference hot path.
+
+Same constructor / `from_pretrained` / `load_state_dict` / `infer` / `forward` surface, argument
+meaning, exception types and prediction-dict keys, shapes and dtypes as
+mapanything/models/mapanything/model.py:96-113, 1657, 2206-2355 and
+mapanything/utils/inference.py:130-506, but every tensor op runs in hand-written sm_100a kernels
+behind the C ABI of libmab200 (include/mab200.h).  PyTorch is used for device memory, streams and
+torch.distributed only.  There is no CPU path: without a CUDA device or without libmab200.so this
+module raises.
+"""
+import ctypes as C
+import json
+import os
+from typing import Any, Dict, List, Optional
+
+import torch
+
+from . import _lib
+
+# keys a view may carry (inference.py:28-46)
+REQUIRED_KEYS = {"data_norm_type"}
+CONFLICTING_KEYS = [("intrinsics", "ray_directions")]
+_PASS_THROUGH = {"instance", "idx", "true_shape", "data_norm_type"}
+
+
+def validate_input_views_for_inference(views):
+    """Same checks, order and exception type as inference.py:130-219."""
+    if not views:
+        raise ValueError("At least one view must be provided")
+    views_with_poses = []
+    for view_idx, view in enumerate(views):
+        keys = set(view.keys())
+        missing = REQUIRED_KEYS - keys
+        if missing:
+            raise ValueError(f"View {view_idx} missing required keys: {missing}")
+        for conflict in CONFLICTING_KEYS:
+            present = [k for k in conflict if k in keys]
+            if len(present) > 1:
+                raise ValueError(f"View {view_idx} contains conflicting keys: {present}. "
+                                 f"Only one of {conflict} can be provided at a time.")
+        if view_idx == 0 and "img" not in keys:
+            raise ValueError("The First View missing required keys: img")
+        if "img" not in keys:
+            if "intrinsics" not in keys and "ray_directions" not in keys:
+                raise ValueError(f"View {view_idx} without image must provide intrinsics or ray_directions")
+            if "camera_poses" not in keys:
+                raise ValueError(f"View {view_idx} without image must provide camera_poses")
+        if "depth_z" in keys and "intrinsics" not in keys and "ray_directions" not in keys:
+            raise ValueError(f"View {view_idx} depth constraint violation: If 'depth_z' is provided, "
+                             f"then 'intrinsics' or 'ray_directions' must also be provided.")
+        if "camera_poses" in keys:
+            views_with_poses.append(view_idx)
+    if views_with_poses and 0 not in views_with_poses:
+        raise ValueError(f"Camera pose constraint violation: Views {views_with_poses} have camera_poses, "
+                         f"but view 0 (reference view) does not.")
+    return views
+
+
+def default_config():
+    """Architecture of the production model (configs/model/mapanything.yaml)."""
+    return dict(patch=14, enc_dim=1024, enc_depth=24, enc_heads=16, enc_pos_grid=37, aat_dim=768,
+                aat_depth=24, aat_heads=12, aat_tap0=11, aat_tap1=17, head_chunk=8)
+
+
+class MapAnything(torch.nn.Module):
+    """Drop-in for the reference class on the inference path (no trainable state on the torch side:
+    the weights live in packed device buffers owned by libmab200)."""
+
+    def __init__(self, name: str = "mapanything", encoder_config: Optional[dict] = None,
+                 info_sharing_config: Optional[dict] = None, pred_head_config: Optional[dict] = None,
+                 geometric_input_config: Optional[dict] = None, fusion_norm_layer=None,
+                 pretrained_checkpoint_path: Optional[str] = None,
+                 load_specific_pretrained_submodules: bool = False,
+                 specific_pretrained_submodules: Optional[list] = None,
+                 torch_hub_force_reload: bool = False, device="cuda", head_chunk: int = 8):
+        super().__init__()
+        self.name = name
+        self.encoder_config = encoder_config or {"data_norm_type": "dinov2", "name": "dinov2_large"}
+        self.info_sharing_config = info_sharing_config or {}
+        self.pred_head_config = pred_head_config or {}
+        self.geometric_input_config = geometric_input_config or {}
+        self.data_norm_type = self.encoder_config.get("data_norm_type", "dinov2")
+        self._check_supported()
+        if not torch.cuda.is_available():
+            raise RuntimeError("mapanything_b200 needs a CUDA device (sm_100a); there is no CPU path")
+        self._device = torch.device(device if device != "cuda" else f"cuda:{torch.cuda.current_device()}")
+        self._lib = _lib.load()
+        cfg = default_config()
+        margs = self.info_sharing_config.get("module_args", {})
+        if "depth" in margs:
+            cfg["aat_depth"] = int(margs["depth"])
+        if "indices" in margs:
+            cfg["aat_tap0"], cfg["aat_tap1"] = [int(i) for i in margs["indices"]]
+        cfg["head_chunk"] = int(head_chunk)
+        self._cfg = _lib.MabConfig(**cfg)
+        self._handle = C.c_void_p()
+        _lib.check(self._lib.mab_create(C.byref(self._cfg), self._device.index or 0, C.byref(self._handle)),
+                   "mab_create")
+        self._finalized = False
+        self._workspace = None
+        if pretrained_checkpoint_path is not None:
+            ckpt = torch.load(pretrained_checkpoint_path, map_location="cpu", weights_only=False)
+            self.load_state_dict(ckpt["model"] if "model" in ckpt else ckpt)
+
+    # ------------------------------------------------------------------ construction helpers
+    def _check_supported(self):
+        ic = self.info_sharing_config
+        if ic and ic.get("model_type", "alternating_attention") != "alternating_attention":
+            raise NotImplementedError("only the alternating-attention info-sharing model is built")
+        if ic and ic.get("custom_positional_encoding") is not None:
+            raise NotImplementedError("custom positional encodings are not part of the default path")
+        pc = self.pred_head_config
+        if pc and pc.get("type", "dpt+pose") != "dpt+pose":
+            raise NotImplementedError("only the dpt+pose head is built")
+
+    @classmethod
+    def from_pretrained(cls, path: str, device="cuda", **kwargs):
+        """Local-directory flavour of PyTorchModelHubMixin.from_pretrained (model.py:96):
+        `config.json` -> constructor kwargs, `model.safetensors` (or `model.pth`) -> state dict."""
+        if not os.path.isdir(path):
+            raise FileNotFoundError(f"{path}: hub downloads need network access; pass a local directory "
+                                    f"holding config.json and model.safetensors")
+        with open(os.path.join(path, "config.json")) as f:
+            config = json.load(f)
+        config = {k: v for k, v in config.items() if k in (
+            "name", "encoder_config", "info_sharing_config", "pred_head_config", "geometric_input_config")}
+        model = cls(device=device, **config, **kwargs)
+        st_path = os.path.join(path, "model.safetensors")
+        if os.path.exists(st_path):
+            from safetensors.torch import load_file
+            sd = load_file(st_path)
+        else:
+            sd = torch.load(os.path.join(path, "model.pth"), map_location="cpu", weights_only=False)
+            sd = sd.get("model", sd)
+        model.load_state_dict(sd)
+        return model
+
+    @property
+    def device(self):
+        return self._device
+
+    def to(self, device=None, *a, **k):
+        if device is not None and torch.device(device).type != "cuda":
+            raise RuntimeError("mapanything_b200 runs on CUDA devices only")
+        return self
+
+    def load_state_dict(self, state_dict, strict: bool = True):
+        """Accepts the reference key space unchanged, aliases included."""
+        if self._finalized:
+            raise RuntimeError("weights are already finalized for this instance")
+        with torch.cuda.device(self._device):
+            for key, t in state_dict.items():
+                t = t.detach().to(dtype=torch.float32).contiguous()
+                shape = (C.c_int64 * max(t.dim(), 1))(*(list(t.shape) or [1]))
+                _lib.check(self._lib.mab_set_weight(self._handle, key.encode(), t.data_ptr(), 0,
+                                                    max(t.dim(), 1), shape), f"mab_set_weight({key})")
+            _lib.check(self._lib.mab_finalize_weights(self._handle, self._stream_ptr()),
+                       "mab_finalize_weights")
+        self._finalized = True
+        return torch.nn.modules.module._IncompatibleKeys([], [])
+
+    def __del__(self):
+        try:
+            if getattr(self, "_handle", None):
+                self._lib.mab_destroy(self._handle)
+                self._handle = None
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ plumbing
+    def _stream_ptr(self):
+        return C.c_void_p(torch.cuda.current_stream(self._device).cuda_stream)
+
+    def _get_workspace(self, nbytes):
+        if self._workspace is None or self._workspace.numel() < nbytes:
+            self._workspace = None
+            self._workspace = torch.empty(int(nbytes), dtype=torch.uint8, device=self._device)
+        return self._workspace
+
+    def _pack_images(self, views):
+        shapes = {tuple(v["img"].shape) for v in views}
+        assert len(shapes) == 1, "All views must have the same image shape"  # model.py:1666-1667
+        B, Cc, H, W = views[0]["img"].shape
+        assert Cc == 3, "Input must have 3 channels"
+        assert H % 14 == 0 and W % 14 == 0, "Input shape must be divisible by patch size: 14"
+        if B != 1:
+            raise NotImplementedError("batch size per view > 1 (every reference config uses 1)")
+        imgs = torch.empty((len(views), 3, H, W), dtype=torch.float32, device=self._device)
+        for i, v in enumerate(views):
+            imgs[i].copy_(v["img"][0], non_blocking=True)
+        return imgs, H, W
+
+    def _alloc_outputs(self, V, H, W, want_logits=False):
+        dev = self._device
+        o = dict(
+            pts3d=torch.empty((V, H, W, 3), dtype=torch.float32, device=dev),
+            pts3d_cam=torch.empty((V, H, W, 3), dtype=torch.float32, device=dev),
+            ray_directions=torch.empty((V, H, W, 3), dtype=torch.float32, device=dev),
+            depth_along_ray=torch.empty((V, H, W, 1), dtype=torch.float32, device=dev),
+            conf=torch.empty((V, H, W), dtype=torch.float32, device=dev),
+            mask_logits=torch.empty((V, H, W), dtype=torch.float32, device=dev),
+            non_ambiguous_mask=torch.empty((V, H, W), dtype=torch.bool, device=dev),
+            pose=torch.empty((V, 8), dtype=torch.float32, device=dev),
+            metric_scale=torch.empty((1, 1), dtype=torch.float32, device=dev),
+        )
+        if want_logits:
+            o["logits6"] = torch.empty((V, H, W, 6), dtype=torch.float32, device=dev)
+        return o
+
+    @staticmethod
+    def _out_struct(o):
+        return _lib.MabOutputs(**{k: (o[k].data_ptr() if k in o else None) for k, _ in _lib.MabOutputs._fields_})
+
+    def _run_forward(self, imgs, H, W, want_logits=False):
+        """One whole forward on this GPU: returns the raw output tensors (all views stacked)."""
+        V = imgs.shape[0]
+        with torch.cuda.device(self._device):
+            nbytes = self._lib.mab_workspace_bytes(self._handle, V, V, H, W)
+            if nbytes == 0:
+                raise RuntimeError("mab_workspace_bytes rejected the problem shape")
+            ws = self._get_workspace(nbytes)
+            outs = self._alloc_outputs(V, H, W, want_logits)
+            inp = _lib.MabInputs(views=V, H=H, W=W, images=imgs.data_ptr())
+            ost = self._out_struct(outs)
+            _lib.check(self._lib.mab_forward(self._handle, C.byref(inp), C.byref(ost), ws.data_ptr(),
+                                             ws.numel(), self._stream_ptr()), "mab_forward")
+        return outs
+
+    def _raw_dicts(self, outs, V):
+        scale = outs["metric_scale"]
+        cam_trans = outs["pose"][:, 0:3] * scale  # (V,3)
+        cam_quats = outs["pose"][:, 3:7]
+        res = []
+        for i in range(V):
+            res.append({
+                "pts3d": outs["pts3d"][i:i + 1],
+                "pts3d_cam": outs["pts3d_cam"][i:i + 1],
+                "ray_directions": outs["ray_directions"][i:i + 1],
+                "depth_along_ray": outs["depth_along_ray"][i:i + 1],
+                "cam_trans": cam_trans[i:i + 1],
+                "cam_quats": cam_quats[i:i + 1].contiguous(),
+                "metric_scaling_factor": scale,
+                "conf": outs["conf"][i:i + 1],
+                "non_ambiguous_mask": outs["non_ambiguous_mask"][i:i + 1],
+                "non_ambiguous_mask_logits": outs["mask_logits"][i:i + 1],
+            })
+        return res
+
+    # ------------------------------------------------------------------ public API
+    @torch.inference_mode()
+    def forward(self, views, memory_efficient_inference: bool = False):
+        """Raw (un-post-processed) predictions, model.py:1657-2152.  `memory_efficient_inference`
+        only changes the dense-head chunking in the reference; outputs are identical, so it is a
+        no-op here (the dense head always streams `head_chunk` views through a fixed workspace)."""
+        if not self._finalized:
+            raise RuntimeError("load_state_dict() / from_pretrained() must be called before inference")
+        if any(k in v for v in views for k in ("ray_directions_cam", "depth_along_ray", "camera_pose_quats")):
+            raise NotImplementedError("geometric inputs are not wired into this build yet")
+        imgs, H, W = self._pack_images(views)
+        outs = self._run_forward(imgs, H, W)
+        return self._raw_dicts(outs, len(views))
+
+    @torch.inference_mode()
+    def infer(self, views: List[Dict[str, Any]], memory_efficient_inference: bool = False,
+              use_amp: bool = True, amp_dtype: str = "bf16", apply_mask: bool = True,
+              mask_edges: bool = True, edge_normal_threshold: float = 5.0,
+              edge_depth_threshold: float = 0.03, apply_confidence_mask: bool = False,
+              confidence_percentile: float = 10, ignore_calibration_inputs: bool = False,
+              ignore_depth_inputs: bool = False, ignore_pose_inputs: bool = False,
+              ignore_depth_scale_inputs: bool = False, ignore_pose_scale_inputs: bool = False,
+              ) -> List[Dict[str, torch.Tensor]]:
+        """model.py:2206-2355.  The kernels always compute in bf16 with fp32 accumulation / fp32
+        residual streams (the reference's bf16-autocast semantics); `use_amp`/`amp_dtype` are
+        accepted for signature compatibility."""
+        if not self._finalized:
+            raise RuntimeError("load_state_dict() / from_pretrained() must be called before inference")
+        views = validate_input_views_for_inference(views)
+        for v in views:
+            if v["data_norm_type"][0] != self.data_norm_type:  # encoders/base.py:83-96
+                raise AssertionError(f"data_norm_type {v['data_norm_type']} != encoder's {self.data_norm_type}")
+        geo = [k for v in views for k in ("intrinsics", "ray_directions", "depth_z", "camera_poses") if k in v]
+        use_geo = geo and not (ignore_calibration_inputs and ignore_depth_inputs and ignore_pose_inputs)
+        if use_geo:
+            raise NotImplementedError("geometric inputs are not wired into this build yet")
+        # move the caller's tensors to the model device in place, like model.py:2316-2320
+        for v in views:
+            for name in list(v.keys()):
+                if name not in _PASS_THROUGH and torch.is_tensor(v[name]):
+                    v[name] = v[name].to(self._device, non_blocking=True)
+        V = len(views)
+        imgs, H, W = self._pack_images(views)
+        outs = self._run_forward(imgs, H, W)
+        dev = self._device
+        post = dict(
+            img_no_norm=torch.empty((V, H, W, 3), dtype=torch.float32, device=dev),
+            depth_z=torch.empty((V, H, W, 1), dtype=torch.float32, device=dev),
+            intrinsics=torch.empty((V, 3, 3), dtype=torch.float32, device=dev),
+            camera_poses=torch.empty((V, 4, 4), dtype=torch.float32, device=dev),
+            cam_trans=torch.empty((V, 3), dtype=torch.float32, device=dev),
+            cam_quats=torch.empty((V, 4), dtype=torch.float32, device=dev),
+            mask=torch.empty((V, H, W, 1), dtype=torch.bool, device=dev),
+        )
+        with torch.cuda.device(dev):
+            need = V * H * W * 17 + 256
+            ws = self._get_workspace(need)
+            inp = _lib.MabInputs(views=V, H=H, W=W, images=imgs.data_ptr())
+            ost = self._out_struct(outs)
+            pst = _lib.MabPostOutputs(**{k: post[k].data_ptr() for k, _ in _lib.MabPostOutputs._fields_})
+            opt = _lib.MabPostOptions(int(apply_mask), int(mask_edges), float(edge_normal_threshold),
+                                      float(edge_depth_threshold), int(apply_confidence_mask),
+                                      float(confidence_percentile))
+            _lib.check(self._lib.mab_postprocess(self._handle, C.byref(inp), C.byref(ost), C.byref(pst),
+                                                 C.byref(opt), ws.data_ptr(), ws.numel(),
+                                                 self._stream_ptr()), "mab_postprocess")
+        preds = []
+        scale = outs["metric_scale"]
+        for i in range(V):
+            d = {
+                "pts3d": outs["pts3d"][i:i + 1],
+                "pts3d_cam": outs["pts3d_cam"][i:i + 1],
+                "ray_directions": outs["ray_directions"][i:i + 1],
+                "depth_along_ray": outs["depth_along_ray"][i:i + 1],
+                "cam_trans": post["cam_trans"][i:i + 1],
+                "cam_quats": post["cam_quats"][i:i + 1],
+                "metric_scaling_factor": scale,
+                "conf": outs["conf"][i:i + 1],
+                "non_ambiguous_mask": outs["non_ambiguous_mask"][i:i + 1],
+                "non_ambiguous_mask_logits": outs["mask_logits"][i:i + 1],
+                "img_no_norm": post["img_no_norm"][i:i + 1],
+                "depth_z": post["depth_z"][i:i + 1],
+                "intrinsics": post["intrinsics"][i:i + 1],
+                "camera_poses": post["camera_poses"][i:i + 1],
+            }
+            if apply_mask:
+                d["mask"] = post["mask"][i:i + 1]
+            preds.append(d)
+        return preds

@@ -1,0 +1,47 @@
+"""CPU-side checks: the C-ABI library builds, loads and exports every symbol include/mab200.h
+declares (no compute call), and the host-side validation logic mirrors the reference."""
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    import __graft_entry__ as ge
+    from mapanything_b200 import _lib
+
+    ge.build()
+    lib = _lib.load(allow_build=False)
+    header = open(os.path.join(ROOT, "include", "mab200.h")).read()
+    declared = set(re.findall(r"\b(mab_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations found"
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in mab200.h but not exported"
+        assert name in _lib.SYMBOLS, f"{name} has no ctypes signature"
+    assert lib.mab_version() == 100
+
+
+def test_validation_mirrors_reference():
+    from mapanything_b200.model import validate_input_views_for_inference as val
+
+    v = {"img": torch.zeros(1, 3, 28, 28), "data_norm_type": ["dinov2"]}
+    assert val([v]) == [v]
+    for bad in ([], [{"img": v["img"]}],
+                [dict(v, intrinsics=torch.eye(3)[None], ray_directions=torch.zeros(1, 28, 28, 3))],
+                [dict(v, depth_z=torch.zeros(1, 28, 28))],
+                [v, dict(v, camera_poses=torch.eye(4)[None])],
+                [v, {"data_norm_type": ["dinov2"], "camera_poses": torch.eye(4)[None]}]):
+        with pytest.raises(ValueError):
+            val(bad)
+
+
+def test_product_fails_loudly_without_gpu():
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from mapanything_b200 import MapAnything
+
+    with pytest.raises(RuntimeError):
+        MapAnything()
