@@ -1,0 +1,316 @@
+#!/usr/bin/env python
+"""bench.py -- views/sec of the MapAnything inference hot path on B200 (contract: task prompt / DESIGN.md).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--views V] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step = one whole `infer()` of ONE scene (encoder -> 24 alternating-attention blocks -> DPT / pose /
+scale heads -> fused pointmap + post-processing) on synthetic views (518x392, DINOv2-normalised) with
+random-init weights of the production architecture.  N=1: BASELINE.json configs[1], 8 views on one
+B200.  N>1: one scene of 8*N views, view-sharded over N ranks with ring global attention over NCCL.
+
+JSON keys: see DESIGN.md "Measurement".  `value` times the C-ABI forward+postprocess with inputs
+resident in HBM (CUDA events, max over ranks); `e2e` times `MapAnything.infer` from pinned HOST images
+with every prediction tensor copied back to pinned host memory inside the timed region.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+H_IMG, W_IMG = 392, 518  # "518x392" is WxH (image.py:40-52)
+VIEWS_PER_GPU = 8
+METRIC = "views/sec (518px, bf16)"
+UNIT = "views/s"
+
+
+def flops_per_scene(n):
+    """image-only algorithmic FLOPs of one scene of n views."""
+    return (1369.1 * n + 39.57 * n * n) * 1e9
+
+
+class ClockSampler:
+    """nvidia-smi sampler running during the timed region (B200_PROFILING.md clocks line)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def reference_arm(args, rank, world):
+    """The reference's own CPU path for this hot path, timed on the box's host cores.  The reference
+    is pure Python and cannot travel to the GPU box, so this is the oracle port (oracle/, pinned to
+    the live reference by tests/golden); each step is a bounded sample (2 views) of the workload."""
+    if rank != 0:
+        return
+    from mapanything_b200 import synthetic
+    from oracle import mapanything_oracle as orc
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sample_views = 2
+    sd = synthetic.synthetic_state_dict()
+    views = synthetic.synthetic_views(sample_views, H_IMG, W_IMG, seed=1)
+    for _ in range(max(args.warmup, 1)):
+        orc.infer(sd, [dict(v) for v in views])
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        orc.infer(sd, [dict(v) for v in views])
+    dt = (time.perf_counter() - t0) / args.steps
+    v = sample_views / dt
+    n_views = args.views or VIEWS_PER_GPU * world
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"MapAnything image-only infer, {n_views} views 518x392, random-init weights",
+                   "sample": f"{sample_views} of those views per step (fp32, CPU)"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{sample_views} views 518x392 per step, oracle/mapanything_oracle.py (fp32 torch CPU)"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def cpu_baseline_leg(budget_s=25.0):
+    from mapanything_b200 import synthetic
+    from oracle import mapanything_oracle as orc
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = synthetic.synthetic_state_dict()
+    views = synthetic.synthetic_views(2, H_IMG, W_IMG, seed=1)
+    t0 = time.perf_counter()
+    reps = 0
+    while True:
+        orc.infer(sd, [dict(v) for v in views])
+        reps += 1
+        if time.perf_counter() - t0 > budget_s * 0.6 or reps >= 4:
+            break
+    dt = (time.perf_counter() - t0) / reps
+    return {"value": 2 / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{reps} x infer of 2 views 518x392 (fp32, oracle/mapanything_oracle.py, {cores} threads)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--views", type=int, default=0, help="views in the scene (default 8 per GPU)")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+        return
+    assert args.warmup >= 3 or os.environ.get("MAB_BENCH_ALLOW_SHORT"), "timing rules: at least 3 warm-up steps"
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: libmab200 has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
+
+    from mapanything_b200 import MapAnything, _lib, synthetic
+    from mapanything_b200.parallel import shard_views
+
+    n_views = args.views or VIEWS_PER_GPU * world
+    lo, hi = shard_views(n_views, world, rank)
+    model = MapAnything(device=dev, head_chunk=8)
+    model.load_state_dict(synthetic.synthetic_state_dict())
+    lib = model._lib
+
+    # this rank's views of the scene: pinned host copies (e2e) and a device-resident stack (value)
+    all_views = synthetic.synthetic_views(n_views, H_IMG, W_IMG, seed=1) if n_views <= 64 else None
+    if all_views is None:  # many-view scenes: tile 64 distinct views (content does not change the work)
+        base = synthetic.synthetic_views(64, H_IMG, W_IMG, seed=1)
+        all_views = [base[i % 64] for i in range(n_views)]
+    host_views = [{"img": v["img"].pin_memory(), "data_norm_type": ["dinov2"]} for v in all_views[lo:hi]]
+    dev_imgs = torch.cat([v["img"] for v in host_views], 0).to(dev)
+    V = hi - lo
+
+    def step_resident():
+        outs, post = model.run_resident(dev_imgs, H_IMG, W_IMG, view_range=(lo, hi), total_views=n_views)
+        return outs, post
+
+    host_out = {}
+
+    def step_e2e():
+        preds = model.infer([dict(v) for v in host_views], view_range=(lo, hi), total_views=n_views)
+        nbytes = 0
+        for i, p in enumerate(preds):
+            for k, t in p.items():
+                key = (i, k)
+                if key not in host_out:
+                    host_out[key] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+                host_out[key].copy_(t, non_blocking=True)
+                nbytes += t.numel() * t.element_size()
+        return nbytes
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) / steps
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = lib.mab_launch_count()
+    ms_step = timed(step_resident, args.steps, args.warmup)
+    launches = (lib.mab_launch_count() - l0) // (args.steps + args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+
+    d2h = [0]
+
+    def e2e_fn():
+        d2h[0] = step_e2e()
+
+    ms_e2e = timed(e2e_fn, max(3, args.steps // 2), 3)
+    h2d_bytes = V * 3 * H_IMG * W_IMG * 4
+
+    roof = None
+    if not args.no_roofline:
+        # per-launch CUDA events (recorded by the library on the launch stream) over K more steps
+        lib.mab_prof_enable(1)
+        barrier()
+        for _ in range(args.steps):
+            step_resident()
+        cats = {}
+        for cat, name in enumerate(["gemm", "conv3", "conv3_regress", "attention", "layernorm", "elementwise", "postprocess"]):
+            n, ms, fl, by = C.c_longlong(), C.c_double(), C.c_double(), C.c_double()
+            _lib.check(lib.mab_prof_query(cat, C.byref(n), C.byref(ms), C.byref(fl), C.byref(by)))
+            cats[name] = dict(launches=n.value // args.steps, ms=ms.value / args.steps, flops=fl.value / args.steps,
+                              bytes=by.value / args.steps)
+        lib.mab_prof_enable(0)
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except Exception:
+            pass
+        peak_tf = peaks.get("bf16_tflops_sustained", 1400.0)
+        peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained (kernel timed inside a long step)" if peaks else "fallback 1.4 PFLOP/s sustained (B200_PROFILING.md)"
+        total_ms = sum(c["ms"] for c in cats.values())
+        dom = max(("gemm", "attention", "conv3"), key=lambda k: cats[k]["ms"])
+        d = cats[dom]
+        ach = d["flops"] / (d["ms"] * 1e-3) / 1e12 if d["ms"] > 0 else 0.0
+        kernel_name = {"gemm": "gemm_kernel<MODE_GEMM> (tcgen05 linear layers)",
+                       "attention": "attention_kernel (tcgen05 flash attention)",
+                       "conv3": "gemm_kernel<MODE_CONV3> (tcgen05 implicit-GEMM 3x3 conv)"}[dom]
+        roof = {"bound": "tensor", "kernel": kernel_name, "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
+                "frac": ach / peak_tf, "traffic": None, "peak_source": peak_src,
+                "launches_per_step": d["launches"], "avg_launch_ms": d["ms"] / max(d["launches"], 1),
+                "share_of_step": d["ms"] / total_ms if total_ms else None,
+                "how": "library-recorded CUDA events around every launch on the launch stream, K extra steps after the timed region",
+                "per_kernel": {k: {"ms_per_step": round(c["ms"], 4), "launches": c["launches"],
+                                   "tflops": round(c["flops"] / (c["ms"] * 1e-3) / 1e12, 1) if c["ms"] > 0 and c["flops"] else None,
+                                   "gbs": round(c["bytes"] / (c["ms"] * 1e-3) / 1e9, 1) if c["ms"] > 0 and c["bytes"] else None}
+                               for k, c in cats.items()}}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_leg()
+
+    if rank == 0:
+        value = n_views / (ms_step * 1e-3)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"MapAnything image-only infer, {n_views} views 518x392 (WxH), one scene, random-init weights of the production architecture (DINOv2 ViT-L/14 + 24-layer alternating attention + DPT/pose/scale heads)",
+                       "views": n_views, "views_per_gpu": V, "parallelism": "single GPU" if world == 1 else f"view-sharded x{world}, ring global attention over NCCL",
+                       "l2": "working set per step (activations of all views, > 1 GB) exceeds the 126 MB L2; no explicit flush"},
+            "tflops_per_gpu": flops_per_scene(n_views) / (ms_step * 1e-3) / 1e12 / world,
+            "e2e": {"value": n_views / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h[0],
+                    "api": "MapAnything.infer(views) with pinned host images; all prediction tensors copied to pinned host memory"},
+            "gpu_launches": int(launches) * args.steps,
+            "gpu_launches_per_step": int(launches),
+            "clocks": clocks,
+        }
+        if roof is not None:
+            line["roofline"] = roof
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -111,19 +111,45 @@ int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs* raw, mab_p
                     const mab_post_options* opt, void* workspace, size_t workspace_bytes,
                     void* stream);
 
-/* ---- staged forward (view-sharded multi-GPU: the caller exchanges K/V between the stages) ---- */
-int mab_stage_encode(mab_handle* h, const mab_inputs* in, void* workspace, size_t workspace_bytes,
-                     int has_scale_token, void* stream);
+/* ---- staged forward (view-sharded multi-GPU: the caller exchanges K/V between the stages) ----
+ * Rank r holds a contiguous block of the scene's views; the rank that holds view 0 also owns the
+ * scale token.  has_scale_token: bit 0 = this rank owns the scale token, bit 1 = this rank holds
+ * view 0 (gets the reference-view positional encoding, alternating_attention_transformer.py:618-626).
+ * views_total > in->views reserves the ring-attention carry buffers in the workspace. */
+int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_total, void* workspace,
+                     size_t workspace_bytes, int has_scale_token, void* stream);
 /* LN1 + qkv projection of info-sharing block `layer`; returns the device pointer of this rank's
- * packed [rows, 3*aat_dim] bf16 qkv buffer and its row count. */
-int mab_stage_aat_qkv(mab_handle* h, int layer, void* workspace, void** qkv_out, int* rows_out,
-                      void* stream);
-/* Attention + proj + MLP of block `layer`.  For global (even) layers kv points to a
- * [kv_rows, 3*aat_dim] bf16 buffer holding every rank's qkv rows (NULL = use the local buffer). */
-int mab_stage_aat_block(mab_handle* h, int layer, void* workspace, const void* kv, int kv_rows,
-                        void* stream);
-int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out, void* workspace,
+ * packed [rows, 3*aat_dim] bf16 qkv buffer (inside the workspace) and its row count. */
+int mab_stage_aat_qkv(mab_handle* h, int layer, void** qkv_out, int* rows_out, void* stream);
+/* Attention of block `layer` against ONE K/V block: kv = [kv_rows, 3*aat_dim] bf16 qkv rows of the
+ * rank whose block is currently held (NULL = this rank's own).  A global (even) layer of a
+ * view-sharded scene takes one call per ring step, flags marking the first / last step; the
+ * online-softmax state is carried between the calls.  Everything else: one call, both flags. */
+enum { MAB_RING_FIRST = 1, MAB_RING_LAST = 2 };
+int mab_stage_aat_attend(mab_handle* h, int layer, const void* kv, int kv_rows, int flags,
+                         void* stream);
+/* proj + MLP of block `layer` (+ intermediate taps / final norm) */
+int mab_stage_aat_finish(mab_handle* h, int layer, void* stream);
+/* metric scale from the final scale token (rank owning it); broadcast the float to the others */
+int mab_stage_scale_head(mab_handle* h, float* metric_scale_out, void* stream);
+/* pose head + dense head + fused adaptor/pointmap.  metric_scale_in: device float broadcast from
+ * the scale-token rank, or NULL to compute it here (single GPU). */
+int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out,
                     const float* metric_scale_in, void* stream);
+
+/* Launch accounting for bench.py: kernels launched by this library since load, and an optional
+ * per-launch CUDA-event profiler (events recorded on the launch stream around every kernel). */
+enum { MAB_CAT_GEMM = 0, MAB_CAT_CONV3 = 1, MAB_CAT_CONV3_REGRESS = 2, MAB_CAT_ATTENTION = 3,
+       MAB_CAT_LAYERNORM = 4, MAB_CAT_ELEMENTWISE = 5, MAB_CAT_POSTPROCESS = 6, MAB_CAT_COUNT = 7 };
+long long mab_launch_count(void);
+int mab_prof_enable(int on); /* also clears the records */
+/* synchronises the device; sums device time, algorithmic FLOPs and bytes of one category */
+int mab_prof_query(int cat, long long* launches, double* ms, double* flops, double* bytes);
+
+/* Diagnostic hook for the parity tests: device pointer, element count and dtype (MAB_F32 /
+ * MAB_BF16) of a named intermediate of the last forward ("enc_tokens", "fused", "aat_stream",
+ * "tap0", "tap1", "final", "scale_token", "pose_raw", "pose_pool", "feat8"). */
+int mab_debug_buffer(mab_handle* h, const char* name, void** ptr, long long* numel, int* dtype);
 
 /* ---- per-kernel entry points (parity tests call these through the same ABI) ---- */
 int mab_layernorm(const float* x, int rows, int C, const float* w, const float* b, float eps,
@@ -136,6 +162,12 @@ int mab_gemm(const void* A, const void* B, int M, int N, int K, const float* bia
 int mab_attention(const void* q_src, int q_rows_total, const void* kv_src, int kv_rows_total,
                   int heads, int num_seqs, int q_len, int kv_len, int q_seq_stride,
                   int kv_seq_stride, float scale, void* out, float* lse, void* stream);
+/* one ring step of attention with carried online-softmax state (carry_o [rows, heads*64] fp32,
+ * carry_ml [rows, heads, 2] fp32); carry_out = 0 writes the normalised bf16 `out` */
+int mab_attention_carry(const void* q_src, int q_rows_total, const void* kv_src, int kv_rows_total,
+                        int heads, int num_seqs, int q_len, int kv_len, int q_seq_stride,
+                        int kv_seq_stride, float scale, void* out, float* carry_o, float* carry_ml,
+                        int carry_in, int carry_out, void* stream);
 /* 3x3/s1/p1 conv over NHWC bf16; weight packed [Cout, 9, Cpad] bf16 (mab_pack_conv3_weight) */
 int mab_conv3x3(const void* x, int batch, int H, int W, int C, const void* w_packed, int Cout,
                 const float* bias, const void* res1, const void* res2, int act, void* out_bf16,

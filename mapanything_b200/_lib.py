@@ -52,19 +52,29 @@ SYMBOLS = {
     "mab_forward": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), _vp, C.c_size_t, _vp]),
     "mab_postprocess": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), C.POINTER(MabPostOutputs),
                              C.POINTER(MabPostOptions), _vp, C.c_size_t, _vp]),
-    "mab_stage_encode": (_i, [_vp, C.POINTER(MabInputs), _vp, C.c_size_t, _i, _vp]),
-    "mab_stage_aat_qkv": (_i, [_vp, _i, _vp, C.POINTER(_vp), C.POINTER(_i), _vp]),
-    "mab_stage_aat_block": (_i, [_vp, _i, _vp, _vp, _i, _vp]),
-    "mab_stage_heads": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), _vp, _vp, _vp]),
+    "mab_stage_encode": (_i, [_vp, C.POINTER(MabInputs), _i, _vp, C.c_size_t, _i, _vp]),
+    "mab_stage_aat_qkv": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_i), _vp]),
+    "mab_stage_aat_attend": (_i, [_vp, _i, _vp, _i, _i, _vp]),
+    "mab_stage_aat_finish": (_i, [_vp, _i, _vp]),
+    "mab_stage_scale_head": (_i, [_vp, _vp, _vp]),
+    "mab_stage_heads": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), _vp, _vp]),
+    "mab_launch_count": (C.c_longlong, []),
+    "mab_prof_enable": (_i, [_i]),
+    "mab_prof_query": (_i, [_i, C.POINTER(C.c_longlong), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                            C.POINTER(C.c_double)]),
+    "mab_debug_buffer": (_i, [_vp, C.c_char_p, C.POINTER(_vp), C.POINTER(C.c_longlong), C.POINTER(_i)]),
     "mab_layernorm": (_i, [_vp, _i, _i, _vp, _vp, _f, _vp, _vp, _vp]),
     "mab_gemm": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
     "mab_attention": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp]),
+    "mab_attention_carry": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _i, _i, _vp]),
     "mab_conv3x3": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
     "mab_pack_conv3_weight": (_i, [_vp, _i, _i, _vp, _vp]),
     "mab_resize_bilinear": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "mab_posembed_resize": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "mab_edge_mask": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp, _vp]),
 }
+
+RING_FIRST, RING_LAST = 1, 2  # include/mab200.h MAB_RING_*
 
 _lib = None
 

@@ -33,7 +33,14 @@ struct AttnParams {
   __nv_bfloat16* out;               // [rows, ldo]
   int ldo;
   float scale_log2e;                // softmax scale * log2(e)
-  float* lse;                       // optional [rows, heads] natural-log sum-exp (ring merge) or null
+  float* lse;                       // optional [rows, heads] natural-log sum-exp or null
+  // Ring (context-parallel) attention: the online-softmax state of every query row is carried
+  // between the per-block launches.  carry_o [rows, heads*64] fp32 un-normalised O, carry_ml
+  // [rows, heads, 2] fp32 (running max of the raw scores, running sum).
+  float* carry_o;
+  float* carry_ml;
+  int carry_in;                     // 1: start from the carried state instead of (-inf, 0, 0)
+  int carry_out;                    // 1: store the state, skip the normalised bf16 output
 };
 
 __global__ void __launch_bounds__(ATT_THREADS, 1)
@@ -159,6 +166,18 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     float o_acc[ATT_D];
 #pragma unroll
     for (int d = 0; d < ATT_D; ++d) o_acc[d] = 0.f;
+    const bool row_ok = q_tile * ATT_BQ + row < p.q_len;
+    if (p.carry_in && row_ok) {
+      const long long grow = (long long)q_row0 + row;
+      const float2 ml = *reinterpret_cast<const float2*>(p.carry_ml + (grow * p.heads + head) * 2);
+      m_run = ml.x; l_run = ml.y;
+      const float4* src = reinterpret_cast<const float4*>(p.carry_o + grow * p.ldo + head * ATT_D);
+#pragma unroll
+      for (int d = 0; d < ATT_D / 4; ++d) {
+        const float4 v = src[d];
+        o_acc[4 * d] = v.x; o_acc[4 * d + 1] = v.y; o_acc[4 * d + 2] = v.z; o_acc[4 * d + 3] = v.w;
+      }
+    }
 
     auto consume_o = [&](int j, float alpha) {
       const int b = j & 1;
@@ -230,8 +249,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     }
     consume_o(nkv - 1, alpha_pending);
 
-    const int qi = q_tile * ATT_BQ + row;
-    if (qi < p.q_len) {
+    if (row_ok && p.carry_out) {
+      const long long grow = (long long)q_row0 + row;
+      *reinterpret_cast<float2*>(p.carry_ml + (grow * p.heads + head) * 2) = make_float2(m_run, l_run);
+      float4* dst = reinterpret_cast<float4*>(p.carry_o + grow * p.ldo + head * ATT_D);
+#pragma unroll
+      for (int d = 0; d < ATT_D / 4; ++d)
+        dst[d] = make_float4(o_acc[4 * d], o_acc[4 * d + 1], o_acc[4 * d + 2], o_acc[4 * d + 3]);
+    } else if (row_ok) {
       const float inv = 1.0f / l_run;
       const long long grow = (long long)q_row0 + row;
       uint4* dst = reinterpret_cast<uint4*>(p.out + grow * p.ldo + head * ATT_D);

@@ -62,6 +62,7 @@ struct GemmShape {
   int M, N, K;          // MODE_GEMM: A is [M,K].  MODE_CONV3: K = 9*Cpad, M unused
   int batch, H, W;      // MODE_CONV3: activation is [batch,H,W,C]
   int cblocks;          // MODE_CONV3: Cpad/64
+  int creal;            // MODE_CONV3: un-padded input channels (algorithmic FLOP accounting)
 };
 
 __device__ __forceinline__ float gelu_erf(float x) {

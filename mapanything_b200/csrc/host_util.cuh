@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "attention.cuh"
 #include "elementwise.cuh"
@@ -41,6 +42,57 @@ inline int fail(int code, const char* fmt, ...) {
 #define MAB_ARG(cond, msg) \
   do {                     \
     if (!(cond)) return ::mab::fail(-1, "argument error: %s (%s)", msg, #cond); \
+  } while (0)
+
+// ---- launch accounting + optional per-launch CUDA-event profiler (bench.py's roofline leg) -------
+enum { CAT_GEMM = 0, CAT_CONV3 = 1, CAT_CONV3_REGRESS = 2, CAT_ATTENTION = 3, CAT_LAYERNORM = 4,
+       CAT_ELEMENTWISE = 5, CAT_POSTPROCESS = 6, CAT_COUNT = 7 };
+struct ProfRec { int cat; double flops, bytes; cudaEvent_t e0, e1; };
+struct ProfState {
+  bool on = false;
+  long long launches = 0;             // every kernel launch of the library, profiling or not
+  std::vector<ProfRec> recs;
+  std::vector<cudaEvent_t> pool;
+  size_t used = 0;
+  cudaEvent_t get() {
+    if (used == pool.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      pool.push_back(e);
+    }
+    return pool[used++];
+  }
+};
+inline ProfState& prof() {
+  static ProfState p;
+  return p;
+}
+// RAII around ONE kernel launch: counts it; when profiling, brackets it with events on its stream.
+struct ProfScope {
+  cudaStream_t st;
+  bool rec;
+  ProfRec r;
+  ProfScope(int cat, double flops, double bytes, cudaStream_t s) : st(s) {
+    ProfState& p = prof();
+    ++p.launches;
+    rec = p.on;
+    if (rec) {
+      r.cat = cat; r.flops = flops; r.bytes = bytes;
+      r.e0 = p.get(); r.e1 = p.get();
+      cudaEventRecord(r.e0, st);
+    }
+  }
+  ~ProfScope() {
+    if (rec) {
+      cudaEventRecord(r.e1, st);
+      prof().recs.push_back(r);
+    }
+  }
+};
+#define MAB_LAUNCH(cat, flops, bytes, st, ...)       \
+  do {                                               \
+    ::mab::ProfScope _ps(cat, flops, bytes, st);     \
+    __VA_ARGS__;                                     \
   } while (0)
 
 // ---- cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda link dependency)
@@ -131,6 +183,13 @@ inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const Gem
   const int tiles = num_m * ((shp.N + BN - 1) / BN);
   if (tiles <= 0) return 0;
   const int grid = tiles < sm_count() ? tiles : sm_count();
+  double flops;
+  if (MODE == MODE_CONV3)
+    flops = 2.0 * shp.batch * shp.H * shp.W * (double)shp.N * 9.0 * shp.creal;
+  else
+    flops = 2.0 * shp.M * (double)shp.N * shp.K;
+  const int cat = MODE == MODE_CONV3 ? (EPI == EPI_REGRESS ? CAT_CONV3_REGRESS : CAT_CONV3) : CAT_GEMM;
+  ProfScope ps(cat, flops, 0.0, st);
   kern<<<grid, GEMM_THREADS, SM::TOTAL, st>>>(tA, tB, shp, ep, rg);
   MAB_CUDA(cudaGetLastError());
   return 0;
@@ -142,7 +201,7 @@ inline int launch_gemm(const void* A, long long lda, const void* B, long long ld
   MAB_ARG(M > 0 && N > 0 && K > 0, "empty GEMM");
   MAB_ARG(N % 4 == 0, "N must be a multiple of 4");
   CUtensorMap tA, tB;
-  GemmShape shp{M, N, K, 0, 0, 0, 0};
+  GemmShape shp{M, N, K, 0, 0, 0, 0, 0};
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM));
   if (N > 128) {
@@ -158,7 +217,7 @@ inline int launch_conv3(const void* x, int batch, int H, int W, int C, const voi
                         const GemmEpilogue& ep, cudaStream_t st) {
   const int cblocks = (C + 63) / 64;
   CUtensorMap tA, tB;
-  GemmShape shp{0, Cout, 9 * cblocks * 64, batch, H, W, cblocks};
+  GemmShape shp{0, Cout, 9 * cblocks * 64, batch, H, W, cblocks, C};
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, C));
   if (Cout > 128) {
@@ -173,7 +232,7 @@ inline int launch_conv3(const void* x, int batch, int H, int W, int C, const voi
 inline int launch_conv3_regress(const void* x, int batch, int H, int W, const void* w,
                                 const RegressEpilogue& rg, cudaStream_t st) {
   CUtensorMap tA, tB;
-  GemmShape shp{0, 128, 9 * 2 * 64, batch, H, W, 2};
+  GemmShape shp{0, 128, 9 * 2 * 64, batch, H, W, 2, 128};
   GemmEpilogue ep{};
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, 128));
   MAB_TRY(make_tmap_2d(&tB, w, 128, 9LL * 128, 9LL * 128, 128));
@@ -185,7 +244,9 @@ inline int launch_conv3_regress(const void* x, int batch, int H, int W, const vo
 inline int launch_attention(const void* q_src, long long q_rows_total, const void* kv_src,
                             long long kv_rows_total, int heads, int num_seqs, int q_len, int kv_len,
                             int q_seq_stride, int kv_seq_stride, float scale, void* out, float* lse,
-                            cudaStream_t st) {
+                            cudaStream_t st, float* carry_o = nullptr, float* carry_ml = nullptr,
+                            int carry_in = 0, int carry_out = 0) {
+  MAB_ARG(!(carry_in || carry_out) || (carry_o && carry_ml), "carry buffers missing");
   MAB_ARG(heads > 0 && num_seqs > 0 && q_len > 0 && kv_len > 0, "empty attention");
   const int D = heads * 64;
   CUtensorMap tQ, tKV;
@@ -198,6 +259,7 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
   p.out = reinterpret_cast<__nv_bfloat16*>(out); p.ldo = D;
   p.scale_log2e = scale * 1.4426950408889634f;
   p.lse = lse;
+  p.carry_o = carry_o; p.carry_ml = carry_ml; p.carry_in = carry_in; p.carry_out = carry_out;
   static bool attr_done = false;
   if (!attr_done) {
     MAB_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -205,6 +267,7 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
     attr_done = true;
   }
   dim3 grid((q_len + ATT_BQ - 1) / ATT_BQ, heads, num_seqs);
+  ProfScope ps(CAT_ATTENTION, 4.0 * q_len * (double)kv_len * 64.0 * heads * num_seqs, 0.0, st);
   attention_kernel<<<grid, ATT_THREADS, ATT_SMEM_BYTES, st>>>(tQ, tKV, tKV, p);
   MAB_CUDA(cudaGetLastError());
   return 0;
@@ -218,6 +281,10 @@ inline int launch_layernorm(const float* x, int rows_out, int C, int group_out, 
   const int block = 256, rows_per_block = block / 32;
   const int grid = (rows_out + rows_per_block - 1) / rows_per_block;
   auto ob = reinterpret_cast<__nv_bfloat16*>(out_bf16);
+  // algorithmic bytes: fp32 row in, bf16 and/or fp32 row(s) out
+  const double bytes = (double)rows_out * C * (4.0 + (out_bf16 ? 2.0 : 0.0) + (out_f32 ? 4.0 : 0.0) +
+                                               (out_mid ? 4.0 : 0.0));
+  ProfScope ps(CAT_LAYERNORM, 0.0, bytes, st);
   if (C == 768)
     layernorm_kernel<6><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
                                                  b2, eps, ob, out_f32, out_mid);

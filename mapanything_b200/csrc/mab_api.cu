@@ -67,6 +67,28 @@ __global__ void tile_bias_kernel(const float* __restrict__ b, int Cout, int reps
 extern "C" const char* mab_last_error(void) { return err_buf(); }
 extern "C" int mab_version(void) { return 100; }
 
+extern "C" long long mab_launch_count(void) { return prof().launches; }
+extern "C" int mab_prof_enable(int on) {
+  ProfState& p = prof();
+  p.on = on != 0;
+  p.recs.clear();
+  p.used = 0;
+  return 0;
+}
+// Synchronises the device, then sums the recorded launches of category `cat` (CAT_*; include/mab200.h).
+extern "C" int mab_prof_query(int cat, long long* launches, double* ms, double* flops, double* bytes) {
+  MAB_ARG(cat >= 0 && cat < CAT_COUNT && launches && ms && flops && bytes, "bad category");
+  MAB_CUDA(cudaDeviceSynchronize());
+  *launches = 0; *ms = 0; *flops = 0; *bytes = 0;
+  for (const ProfRec& r : prof().recs) {
+    if (r.cat != cat) continue;
+    float t = 0.f;
+    MAB_CUDA(cudaEventElapsedTime(&t, r.e0, r.e1));
+    ++*launches; *ms += t; *flops += r.flops; *bytes += r.bytes;
+  }
+  return 0;
+}
+
 extern "C" int mab_layernorm(const float* x, int rows, int C, const float* w, const float* b,
                              float eps, void* out_bf16, float* out_f32, void* stream) {
   return launch_layernorm(x, rows, C, rows > 0 ? rows : 1, rows > 0 ? rows : 1, 0, w, b, nullptr,
@@ -90,6 +112,16 @@ extern "C" int mab_attention(const void* q_src, int q_rows_total, const void* kv
                           q_seq_stride, kv_seq_stride, scale, out, lse, (cudaStream_t)stream);
 }
 
+extern "C" int mab_attention_carry(const void* q_src, int q_rows_total, const void* kv_src,
+                                   int kv_rows_total, int heads, int num_seqs, int q_len, int kv_len,
+                                   int q_seq_stride, int kv_seq_stride, float scale, void* out,
+                                   float* carry_o, float* carry_ml, int carry_in, int carry_out,
+                                   void* stream) {
+  return launch_attention(q_src, q_rows_total, kv_src, kv_rows_total, heads, num_seqs, q_len, kv_len,
+                          q_seq_stride, kv_seq_stride, scale, out, nullptr, (cudaStream_t)stream,
+                          carry_o, carry_ml, carry_in, carry_out);
+}
+
 extern "C" int mab_pack_conv3_weight(const float* w, int Cout, int Cin, void* out, void* stream) {
   const int Cpad = (Cin + 63) / 64 * 64;
   pack_conv3_kernel<<<ew_grid((long long)Cout * 9 * Cpad), 256, 0, (cudaStream_t)stream>>>(
@@ -111,10 +143,11 @@ extern "C" int mab_conv3x3(const void* x, int batch, int H, int W, int C, const 
 extern "C" int mab_resize_bilinear(const void* x, int batch, int Hi, int Wi, int C, int Hv, int Wv,
                                    int Ho, int Wo, void* out, void* out_relu, void* stream) {
   MAB_ARG(C % 8 == 0, "C must be a multiple of 8");
-  resize_bilinear_ac_kernel<<<ew_grid((long long)batch * Ho * Wo * (C / 8)), 256, 0,
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, (cudaStream_t)stream,
+             resize_bilinear_ac_kernel<<<ew_grid((long long)batch * Ho * Wo * (C / 8)), 256, 0,
                               (cudaStream_t)stream>>>(
       reinterpret_cast<const bf16*>(x), batch, Hi, Wi, C, Hv, Wv, Ho, Wo,
-      reinterpret_cast<bf16*>(out), reinterpret_cast<bf16*>(out_relu));
+      reinterpret_cast<bf16*>(out), reinterpret_cast<bf16*>(out_relu)));
   MAB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -123,10 +156,16 @@ extern "C" int mab_posembed_resize(const float* pos, int grid, int C, int h, int
                                    void* stream) {
   // vision_transformer.py:223-228: scale_factor = ((h + 0.1)/M, (w + 0.1)/M); ATen then uses
   // 1/scale_factor as the source step
+  if (h == grid && w == grid) {  // vision_transformer.py:214-215: same grid -> returned unchanged
+    MAB_CUDA(cudaMemcpyAsync(out, pos, (size_t)(1 + h * w) * C * sizeof(float),
+                             cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return 0;
+  }
   const float inv_sy = 1.0f / (float)((double)(h + 0.1) / grid);
   const float inv_sx = 1.0f / (float)((double)(w + 0.1) / grid);
-  posembed_bicubic_kernel<<<ew_grid((long long)(1 + h * w) * C), 256, 0, (cudaStream_t)stream>>>(
-      pos, grid, C, h, w, inv_sy, inv_sx, out);
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, (cudaStream_t)stream,
+             posembed_bicubic_kernel<<<ew_grid((long long)(1 + h * w) * C), 256, 0, (cudaStream_t)stream>>>(
+      pos, grid, C, h, w, inv_sy, inv_sx, out));
   MAB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -140,11 +179,14 @@ extern "C" int mab_edge_mask(const float* pts3d, float* pts3d_cam, const unsigne
   float* normals = reinterpret_cast<float*>(workspace);
   float* ang = normals + npix * 3;
   unsigned char* nmask = reinterpret_cast<unsigned char*>(ang + npix);
-  normals_kernel<<<ew_grid(npix), 256, 0, st>>>(pts3d, fmask, views, H, W, normals, nmask);
-  normal_angle_kernel<<<ew_grid(npix), 256, 0, st>>>(normals, nmask, views, H, W, ang);
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
+             normals_kernel<<<ew_grid(npix), 256, 0, st>>>(pts3d, fmask, views, H, W, normals, nmask));
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
+             normal_angle_kernel<<<ew_grid(npix), 256, 0, st>>>(normals, nmask, views, H, W, ang));
   const double tol = (double)normal_tol_deg * 3.14159265358979323846 / 180.0;
-  edge_mask_apply_kernel<<<ew_grid(npix), 256, 0, st>>>(ang, fmask, views, H, W, 1, tol, depth_rtol,
-                                                        nullptr, pts3d_cam, nullptr, nullptr, mask_out);
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
+             edge_mask_apply_kernel<<<ew_grid(npix), 256, 0, st>>>(ang, fmask, views, H, W, 1, tol, depth_rtol,
+                                                        nullptr, pts3d_cam, nullptr, nullptr, mask_out));
   MAB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -198,7 +240,7 @@ struct Plan {  // every workspace pointer of one forward
   bf16* im2col; float* patch; float* pos; float* xs; bf16* ln; bf16* qkv; bf16* att; bf16* hid;
   float* enc_out; bf16* fused;
   // info sharing
-  float* ys; bf16* tap[2]; bf16* fin; float* scale_tok;
+  float* ys; bf16* tap[2]; bf16* fin; float* scale_tok; float* carry_o; float* carry_ml;
   // heads (small)
   float* scale_tmp; float* pose_pool; float* pose_tmp; float* pose_raw; bf16* ph_a; bf16* ph_b; bf16* ph_c;
   // dense head chunk buffers
@@ -258,6 +300,8 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
   p.tap[1] = b.take<bf16>(VT * A);
   p.fin = b.take<bf16>(VT * A);
   p.scale_tok = b.take<float>(A);
+  p.carry_o = Vtot > V ? b.take<float>((VT + 1) * A) : nullptr;   // ring attention state
+  p.carry_ml = Vtot > V ? b.take<float>((VT + 1) * (A / 64) * 2) : nullptr;
   p.scale_tmp = b.take<float>(4 * 256);
   p.pose_pool = b.take<float>((long long)V * 784);
   p.pose_tmp = b.take<float>((long long)V * 784 * 2);
@@ -448,10 +492,32 @@ extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
   return 0;
 }
 
+// test/diagnostic hook: device pointer of a named intermediate of the last forward
+extern "C" int mab_debug_buffer(mab_handle* h, const char* name, void** ptr, long long* numel,
+                                int* dtype) {
+  MAB_ARG(h && name && ptr && numel && dtype && h->plan.V > 0, "no forward has run");
+  const Plan& p = h->plan;
+  const long long VT = (long long)p.V * p.T;
+  const int D = h->cfg.enc_dim, A = h->cfg.aat_dim;
+  const std::string n = name;
+  if (n == "enc_tokens") { *ptr = p.xs; *numel = p.Lenc * D; *dtype = MAB_F32; }
+  else if (n == "fused") { *ptr = p.fused; *numel = VT * D; *dtype = MAB_BF16; }
+  else if (n == "aat_stream") { *ptr = p.ys; *numel = p.L * A; *dtype = MAB_F32; }
+  else if (n == "tap0") { *ptr = p.tap[0]; *numel = VT * A; *dtype = MAB_BF16; }
+  else if (n == "tap1") { *ptr = p.tap[1]; *numel = VT * A; *dtype = MAB_BF16; }
+  else if (n == "final") { *ptr = p.fin; *numel = VT * A; *dtype = MAB_BF16; }
+  else if (n == "scale_token") { *ptr = p.scale_tok; *numel = A; *dtype = MAB_F32; }
+  else if (n == "pose_raw") { *ptr = p.pose_raw; *numel = (long long)p.V * 7; *dtype = MAB_F32; }
+  else if (n == "pose_pool") { *ptr = p.pose_pool; *numel = (long long)p.V * 784; *dtype = MAB_F32; }
+  else if (n == "feat8") { *ptr = p.feat8; *numel = (long long)p.vc * 64 * p.T * 256; *dtype = MAB_BF16; }
+  else return fail(-1, "unknown debug buffer %s", name);
+  return 0;
+}
+
 extern "C" size_t mab_workspace_bytes(mab_handle* h, int views_local, int views_total, int H, int W) {
   if (!h || views_local <= 0 || H % h->cfg.patch || W % h->cfg.patch) return 0;
   Plan p;
-  make_plan(h, views_local, views_total, H, W, 1, 1, nullptr, &p);
+  make_plan(h, views_local, views_total > views_local ? views_total : views_local, H, W, 1, 1, nullptr, &p);
   return p.total;
 }
 
@@ -510,7 +576,7 @@ int block_tail(Ctx& c, const std::string& p, float* x, long long rows, int D, bf
 }  // namespace
 
 // a2-a7: patch embed, 24 DINOv2 blocks, encoder norm (+ fusion norm), proj_embed, ref-view PE
-extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, void* workspace,
+extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_total, void* workspace,
                                 size_t workspace_bytes, int has_scale_token, void* stream) {
   MAB_ARG(h && in && workspace && h->finalized, "handle not ready");
   MAB_ARG(in->views > 0 && in->H % 14 == 0 && in->W % 14 == 0 && in->images, "bad inputs");
@@ -518,8 +584,8 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, void* works
   const mab_config& cf = h->cfg;
   Ctx c{h, (cudaStream_t)stream};
   // has_scale_token bit0: this rank owns the scale token; bit1: this rank owns view 0
-  make_plan(h, in->views, in->views, in->H, in->W, has_scale_token & 1, (has_scale_token >> 1) & 1,
-            workspace, &h->plan);
+  make_plan(h, in->views, views_total > in->views ? views_total : in->views, in->H, in->W,
+            has_scale_token & 1, (has_scale_token >> 1) & 1, workspace, &h->plan);
   Plan& p = h->plan;
   if (p.total > workspace_bytes)
     return fail(-5, "workspace too small: need %zu bytes, got %zu", p.total, workspace_bytes);
@@ -528,13 +594,15 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, void* works
   const bool multimodal = in->ray_dirs || in->depth_along_ray || in->cam_quats;
   if (multimodal) return fail(-6, "geometric inputs are not wired into this build yet");
 
-  patch_im2col_kernel<<<ew_grid(VT * 640), 256, 0, c.st>>>(in->images, V, p.H, p.W, 640, p.im2col);
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+             patch_im2col_kernel<<<ew_grid(VT * 640), 256, 0, c.st>>>(in->images, V, p.H, p.W, 640, p.im2col));
   MAB_TRY(c.linear(p.im2col, (int)VT, 640, 640, "encoder.model.patch_embed.proj.weight", D,
                    h->F("encoder.model.patch_embed.proj.bias"), ACT_NONE, nullptr, nullptr, p.patch,
                    nullptr, nullptr, 640));
   MAB_TRY(mab_posembed_resize(h->F("encoder.model.pos_embed"), cf.enc_pos_grid, D, p.h, p.w, p.pos, c.st));
-  assemble_tokens_kernel<<<ew_grid(p.Lenc * D / 4), 256, 0, c.st>>>(
-      p.patch, h->F("encoder.model.cls_token"), p.pos, V, T, D, p.xs);
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+             assemble_tokens_kernel<<<ew_grid(p.Lenc * D / 4), 256, 0, c.st>>>(
+      p.patch, h->F("encoder.model.cls_token"), p.pos, V, T, D, p.xs));
   MAB_CUDA(cudaGetLastError());
   for (int i = 0; i < cf.enc_depth; ++i) {
     const std::string b = "encoder.model.blocks." + std::to_string(i);
@@ -550,24 +618,25 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, void* works
                            h->F("encoder.model.norm.bias"), h->F("fusion_norm_layer.weight"),
                            h->F("fusion_norm_layer.bias"), 1e-6f, p.fused, nullptr, nullptr, c.st));
   if (p.has_scale) {
-    f32_to_bf16_kernel<<<4, 256, 0, c.st>>>(h->F("scale_token"), p.fused + VT * D, D);
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               f32_to_bf16_kernel<<<4, 256, 0, c.st>>>(h->F("scale_token"), p.fused + VT * D, D));
     MAB_CUDA(cudaGetLastError());
   }
   // proj_embed (aat.py:121-124,600) + reference-view PE on view 0's tokens (aat.py:618-626)
   MAB_TRY(c.linear(p.fused, (int)p.L, D, D, "info_sharing.proj_embed.weight", cf.aat_dim,
                    h->F("info_sharing.proj_embed.bias"), ACT_NONE, nullptr, nullptr, p.ys, nullptr));
   if (p.has_ref) {
-    add_row_vector_kernel<<<ew_grid((long long)T * cf.aat_dim), 256, 0, c.st>>>(
-        p.ys, h->F("info_sharing.view_pos_table"), T, cf.aat_dim);
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               add_row_vector_kernel<<<ew_grid((long long)T * cf.aat_dim), 256, 0, c.st>>>(
+        p.ys, h->F("info_sharing.view_pos_table"), T, cf.aat_dim));
     MAB_CUDA(cudaGetLastError());
   }
   return 0;
 }
 
-extern "C" int mab_stage_aat_qkv(mab_handle* h, int layer, void* workspace, void** qkv_out,
-                                 int* rows_out, void* stream) {
+extern "C" int mab_stage_aat_qkv(mab_handle* h, int layer, void** qkv_out, int* rows_out,
+                                 void* stream) {
   MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");
-  (void)workspace;
   Ctx c{h, (cudaStream_t)stream};
   Plan& p = h->plan;
   const long long rows = (layer % 2 == 0) ? p.L : (long long)p.V * p.T;  // odd: scale token skips
@@ -578,27 +647,41 @@ extern "C" int mab_stage_aat_qkv(mab_handle* h, int layer, void* workspace, void
   return 0;
 }
 
-extern "C" int mab_stage_aat_block(mab_handle* h, int layer, void* workspace, const void* kv,
-                                   int kv_rows, void* stream) {
+// Attention of block `layer` against one K/V block.  Odd (frame) layers and single-GPU global
+// layers take one call (flags = FIRST|LAST, kv = NULL).  View-sharded global layers call it once
+// per ring step with the qkv rows of the rank whose block is currently held: the online-softmax
+// state is carried in the workspace between the calls (attention.cuh).
+extern "C" int mab_stage_aat_attend(mab_handle* h, int layer, const void* kv, int kv_rows, int flags,
+                                    void* stream) {
   MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");
-  (void)workspace;
+  const mab_config& cf = h->cfg;
+  Ctx c{h, (cudaStream_t)stream};
+  Plan& p = h->plan;
+  const int T = p.T, V = p.V;
+  const int first = flags & MAB_RING_FIRST, last = flags & MAB_RING_LAST;
+  if (layer % 2 == 0) {  // global attention over every token of the scene (aat.py:657-661)
+    const long long rows = p.L;
+    const void* kvp = kv ? kv : p.qkv;
+    const int kvr = kv ? kv_rows : (int)rows;
+    MAB_ARG((first && last) || p.carry_o, "ring attention needs views_total > views at mab_stage_encode");
+    return launch_attention(p.qkv, rows, kvp, kvr, cf.aat_heads, 1, (int)rows, kvr, 0, 0, 0.125f,
+                            p.att, nullptr, c.st, p.carry_o, p.carry_ml, first ? 0 : 1, last ? 0 : 1);
+  }
+  MAB_ARG(first && last && !kv, "frame attention is local to a view: one step");
+  const long long rows = (long long)V * T;  // frame attention inside each view (aat.py:662-705)
+  return launch_attention(p.qkv, rows, p.qkv, rows, cf.aat_heads, V, T, T, T, T, 0.125f, p.att,
+                          nullptr, c.st);
+}
+
+// proj + residual, LN2, MLP + residual of block `layer`, intermediate taps and the final norm
+extern "C" int mab_stage_aat_finish(mab_handle* h, int layer, void* stream) {
+  MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");
   const mab_config& cf = h->cfg;
   Ctx c{h, (cudaStream_t)stream};
   Plan& p = h->plan;
   const int A = cf.aat_dim, T = p.T, V = p.V;
   const std::string b = "info_sharing.self_attention_blocks." + std::to_string(layer);
-  long long rows;
-  if (layer % 2 == 0) {  // global attention over every token of the scene (aat.py:657-661)
-    rows = p.L;
-    const void* kvp = kv ? kv : p.qkv;
-    const int kvr = kv ? kv_rows : (int)rows;
-    MAB_TRY(launch_attention(p.qkv, rows, kvp, kvr, cf.aat_heads, 1, (int)rows, kvr, 0, 0, 0.125f,
-                             p.att, nullptr, c.st));
-  } else {  // frame attention inside each view (aat.py:662-705)
-    rows = (long long)V * T;
-    MAB_TRY(launch_attention(p.qkv, rows, p.qkv, rows, cf.aat_heads, V, T, T, T, T, 0.125f, p.att,
-                             nullptr, c.st));
-  }
+  const long long rows = (layer % 2 == 0) ? p.L : (long long)V * T;
   MAB_TRY(block_tail(c, b, p.ys, rows, A, p.att, p.ln, p.hid, nullptr, nullptr));
   // intermediate taps + final norm (aat.py:706-716), token-major == NHWC for the dense head
   const long long VT = (long long)V * T;
@@ -628,7 +711,8 @@ namespace {
 int small_linear(cudaStream_t st, const float* x, const float* w, const float* b, int rows, int K,
                  int N, int act, float* y) {
   const long long warps = (long long)N * ((rows + 7) / 8);
-  small_linear_kernel<<<(int)((warps * 32 + 255) / 256), 256, 0, st>>>(x, w, b, rows, K, N, act, y, K, N);
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, st,
+             small_linear_kernel<<<(int)((warps * 32 + 255) / 256), 256, 0, st>>>(x, w, b, rows, K, N, act, y, K, N));
   MAB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -646,27 +730,39 @@ int rcu(Ctx& c, const std::string& p, const bf16* x, const bf16* x_relu, const b
 
 }  // namespace
 
-extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out, void* workspace,
+// scale head (mlp_head.py:58-92, adaptors.py:190-212) on the final scale token -> metric scale [1]
+extern "C" int mab_stage_scale_head(mab_handle* h, float* metric_scale_out, void* stream) {
+  MAB_ARG(h && metric_scale_out && h->plan.V > 0 && h->plan.has_scale, "this rank has no scale token");
+  Ctx c{h, (cudaStream_t)stream};
+  Plan& p = h->plan;
+  const int A = h->cfg.aat_dim;
+  float* t0 = p.scale_tmp; float* t1 = p.scale_tmp + 256; float* t2 = p.scale_tmp + 512;
+  MAB_TRY(small_linear(c.st, p.scale_tok, h->F("scale_head.proj.weight"), h->F("scale_head.proj.bias"), 1, A, 196, 0, t0));
+  MAB_TRY(small_linear(c.st, t0, h->F("scale_head.mlp.0.0.weight"), h->F("scale_head.mlp.0.0.bias"), 1, 196, 196, 2, t1));
+  MAB_TRY(small_linear(c.st, t1, h->F("scale_head.mlp.1.0.weight"), h->F("scale_head.mlp.1.0.bias"), 1, 196, 196, 2, t2));
+  MAB_TRY(small_linear(c.st, t2, h->F("scale_head.output_proj.weight"), h->F("scale_head.output_proj.bias"), 1, 196, 1, 0, t0));
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st, scale_finalize_kernel<<<1, 32, 0, c.st>>>(t0, metric_scale_out));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out,
                                const float* metric_scale_in, void* stream) {
   MAB_ARG(h && in && out && h->plan.V > 0, "mab_stage_encode must run first");
-  (void)workspace;
   const mab_config& cf = h->cfg;
   Ctx c{h, (cudaStream_t)stream};
   Plan& p = h->plan;
   const int V = p.V, T = p.T, A = cf.aat_dim, hh = p.h, ww = p.w, H = p.H, W = p.W;
   const long long VT = (long long)V * T;
 
-  // ---- scale head (mlp_head.py:58-92, adaptors.py:190-212) ------------------------------------
-  if (p.has_scale) {
-    float* t0 = p.scale_tmp; float* t1 = p.scale_tmp + 256; float* t2 = p.scale_tmp + 512;
-    MAB_TRY(small_linear(c.st, p.scale_tok, h->F("scale_head.proj.weight"), h->F("scale_head.proj.bias"), 1, A, 196, 0, t0));
-    MAB_TRY(small_linear(c.st, t0, h->F("scale_head.mlp.0.0.weight"), h->F("scale_head.mlp.0.0.bias"), 1, 196, 196, 2, t1));
-    MAB_TRY(small_linear(c.st, t1, h->F("scale_head.mlp.1.0.weight"), h->F("scale_head.mlp.1.0.bias"), 1, 196, 196, 2, t2));
-    MAB_TRY(small_linear(c.st, t2, h->F("scale_head.output_proj.weight"), h->F("scale_head.output_proj.bias"), 1, 196, 1, 0, t0));
-    scale_finalize_kernel<<<1, 32, 0, c.st>>>(t0, out->metric_scale);
+  // ---- scale head: computed here by the rank that owns the scale token, unless the caller
+  // already ran mab_stage_scale_head and broadcast its result (view-sharded run) ------------------
+  if (metric_scale_in) {
+    if (metric_scale_in != out->metric_scale)
+      MAB_CUDA(cudaMemcpyAsync(out->metric_scale, metric_scale_in, sizeof(float), cudaMemcpyDeviceToDevice, c.st));
   } else {
-    MAB_ARG(metric_scale_in, "rank without the scale token needs metric_scale_in");
-    MAB_CUDA(cudaMemcpyAsync(out->metric_scale, metric_scale_in, sizeof(float), cudaMemcpyDeviceToDevice, c.st));
+    MAB_ARG(p.has_scale, "rank without the scale token needs metric_scale_in");
+    MAB_TRY(mab_stage_scale_head(h, out->metric_scale, stream));
   }
 
   // ---- pose head (pose_head.py:115-159, adaptors.py:714-732) -----------------------------------
@@ -683,14 +779,17 @@ extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs*
       bf16* t = feat; feat = other; other = t;
     }
     dim3 blk(128, 8), grd((784 + 127) / 128, V);
-    token_mean_kernel<<<grd, blk, 0, c.st>>>(feat, T, 784, p.pose_pool);
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               token_mean_kernel<<<grd, blk, 0, c.st>>>(feat, T, 784, p.pose_pool));
     MAB_CUDA(cudaGetLastError());
     float* m0 = p.pose_tmp; float* m1 = p.pose_tmp + (long long)V * 784;
     MAB_TRY(small_linear(c.st, p.pose_pool, h->F(ph + "more_mlps.0.weight"), h->F(ph + "more_mlps.0.bias"), V, 784, 784, 2, m0));
     MAB_TRY(small_linear(c.st, m0, h->F(ph + "more_mlps.2.weight"), h->F(ph + "more_mlps.2.bias"), V, 784, 784, 2, m1));
-    small_linear_kernel<<<(int)(((long long)7 * ((V + 7) / 8) * 32 + 255) / 256), 256, 0, c.st>>>(
-        m1, h->extra["pose_head.fc7.weight"], h->extra["pose_head.fc7.bias"], V, 784, 7, 0, p.pose_raw, 784, 7);
-    pose_finalize_kernel<<<(V + 127) / 128, 128, 0, c.st>>>(p.pose_raw, V, out->pose);
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               small_linear_kernel<<<(int)(((long long)7 * ((V + 7) / 8) * 32 + 255) / 256), 256, 0, c.st>>>(
+        m1, h->extra["pose_head.fc7.weight"], h->extra["pose_head.fc7.bias"], V, 784, 7, 0, p.pose_raw, 784, 7));
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               pose_finalize_kernel<<<(V + 127) / 128, 128, 0, c.st>>>(p.pose_raw, V, out->pose));
     MAB_CUDA(cudaGetLastError());
   }
 
@@ -708,19 +807,22 @@ extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs*
     // layer 0: 1x1 (1024->96) -> convT 4x4/s4 -> 3x3 (96->256, no bias)           dpt.py:107-128
     MAB_TRY(c.linear(f0, M, cf.enc_dim, cf.enc_dim, ip + "0.0.0.weight", 96, h->F(ip + "0.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
     MAB_TRY(c.linear(p.d_a, M, 96, 96, ip + "0.0.1.weight", 16 * 96, h->extra[ip + "0.0.1.bias.tiled"], ACT_NONE, nullptr, nullptr, nullptr, p.d_s));
-    pixel_shuffle_kernel<<<ew_grid((long long)M * 16 * 12), 256, 0, c.st>>>(p.d_s, vc, hh, ww, 4, 96, p.d_u);
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               pixel_shuffle_kernel<<<ew_grid((long long)M * 16 * 12), 256, 0, c.st>>>(p.d_s, vc, hh, ww, 4, 96, p.d_u));
     MAB_TRY(c.conv3(p.d_u, vc, 4 * hh, 4 * ww, 96, sc + "layer1_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[0], p.lvl_relu[0]));
     // layer 1: 1x1 (768->192) -> convT 2x2/s2 -> 3x3 (192->256)
     MAB_TRY(c.linear(f1, M, A, A, ip + "1.0.0.weight", 192, h->F(ip + "1.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
     MAB_TRY(c.linear(p.d_a, M, 192, 192, ip + "1.0.1.weight", 4 * 192, h->extra[ip + "1.0.1.bias.tiled"], ACT_NONE, nullptr, nullptr, nullptr, p.d_s));
-    pixel_shuffle_kernel<<<ew_grid((long long)M * 4 * 24), 256, 0, c.st>>>(p.d_s, vc, hh, ww, 2, 192, p.d_u);
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               pixel_shuffle_kernel<<<ew_grid((long long)M * 4 * 24), 256, 0, c.st>>>(p.d_s, vc, hh, ww, 2, 192, p.d_u));
     MAB_TRY(c.conv3(p.d_u, vc, 2 * hh, 2 * ww, 192, sc + "layer2_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[1], p.lvl_relu[1]));
     // layer 2: 1x1 (768->384) -> 3x3 (384->256)
     MAB_TRY(c.linear(f2, M, A, A, ip + "2.0.0.weight", 384, h->F(ip + "2.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
     MAB_TRY(c.conv3(p.d_a, vc, hh, ww, 384, sc + "layer3_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[2], p.lvl_relu[2]));
     // layer 3: 1x1 (768->768) -> 3x3/s2 (im2col + GEMM) -> 3x3 (768->256)
     MAB_TRY(c.linear(f3, M, A, A, ip + "3.0.0.weight", 768, h->F(ip + "3.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
-    im2col3x3_s2_kernel<<<ew_grid((long long)vc * h3 * w3 * 9 * 96), 256, 0, c.st>>>(p.d_a, vc, hh, ww, 768, h3, w3, p.d_s);
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               im2col3x3_s2_kernel<<<ew_grid((long long)vc * h3 * w3 * 9 * 96), 256, 0, c.st>>>(p.d_a, vc, hh, ww, 768, h3, w3, p.d_s));
     MAB_TRY(c.linear(p.d_s, vc * h3 * w3, 9 * 768, 9 * 768, ip + "3.0.1.weight", 768, h->F(ip + "3.0.1.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_u));
     MAB_TRY(c.conv3(p.d_u, vc, h3, w3, 768, sc + "layer4_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[3], p.lvl_relu[3]));
     MAB_CUDA(cudaGetLastError());
@@ -765,12 +867,13 @@ extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs*
 extern "C" int mab_forward(mab_handle* h, const mab_inputs* in, mab_outputs* out, void* workspace,
                            size_t workspace_bytes, void* stream) {
   MAB_ARG(h && in && out, "null argument");
-  MAB_TRY(mab_stage_encode(h, in, workspace, workspace_bytes, 3, stream));
+  MAB_TRY(mab_stage_encode(h, in, in->views, workspace, workspace_bytes, 3, stream));
   for (int l = 0; l < h->cfg.aat_depth; ++l) {
-    MAB_TRY(mab_stage_aat_qkv(h, l, workspace, nullptr, nullptr, stream));
-    MAB_TRY(mab_stage_aat_block(h, l, workspace, nullptr, 0, stream));
+    MAB_TRY(mab_stage_aat_qkv(h, l, nullptr, nullptr, stream));
+    MAB_TRY(mab_stage_aat_attend(h, l, nullptr, 0, MAB_RING_FIRST | MAB_RING_LAST, stream));
+    MAB_TRY(mab_stage_aat_finish(h, l, stream));
   }
-  return mab_stage_heads(h, in, out, workspace, nullptr, stream);
+  return mab_stage_heads(h, in, out, nullptr, stream);
 }
 
 // workspace: views*H*W*17 bytes + 256
@@ -784,11 +887,13 @@ extern "C" int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs*
   MAB_ARG(workspace_bytes >= (size_t)npix * 17 + 256, "post-process workspace too small");
   if (opt->apply_confidence_mask)
     return fail(-6, "apply_confidence_mask is not wired into this build yet");
-  denorm_image_kernel<<<ew_grid(npix), 256, 0, st>>>(in->images, V, H, W, 0.485f, 0.456f, 0.406f,
-                                                     0.229f, 0.224f, 0.225f, post->img_no_norm);
-  intrinsics_pose_kernel<<<V, 256, 0, st>>>(raw->ray_directions, H, W, raw->pose, raw->metric_scale,
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
+             denorm_image_kernel<<<ew_grid(npix), 256, 0, st>>>(in->images, V, H, W, 0.485f, 0.456f, 0.406f,
+                                                     0.229f, 0.224f, 0.225f, post->img_no_norm));
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
+             intrinsics_pose_kernel<<<V, 256, 0, st>>>(raw->ray_directions, H, W, raw->pose, raw->metric_scale,
                                             post->intrinsics, post->camera_poses, post->cam_trans,
-                                            post->cam_quats);
+                                            post->cam_quats));
   if (opt->apply_mask) {
     if (opt->mask_edges) {
       MAB_TRY(mab_edge_mask(raw->pts3d, raw->pts3d_cam, raw->non_ambiguous_mask, V, H, W,
@@ -798,8 +903,9 @@ extern "C" int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs*
       MAB_CUDA(cudaMemcpyAsync(post->mask, raw->non_ambiguous_mask, npix, cudaMemcpyDeviceToDevice, st));
     }
   }
-  apply_mask_kernel<<<ew_grid(npix), 256, 0, st>>>(post->mask, npix, opt->apply_mask, raw->pts3d,
-                                                   raw->pts3d_cam, raw->depth_along_ray, post->depth_z);
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
+             apply_mask_kernel<<<ew_grid(npix), 256, 0, st>>>(post->mask, npix, opt->apply_mask, raw->pts3d,
+                                                   raw->pts3d_cam, raw->depth_along_ray, post->depth_z));
   MAB_CUDA(cudaGetLastError());
   return 0;
 }

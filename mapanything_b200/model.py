@@ -98,6 +98,8 @@ class MapAnything(torch.nn.Module):
                    "mab_create")
         self._finalized = False
         self._workspace = None
+        self._post_ws = None
+        self._ring_bufs = None
         if pretrained_checkpoint_path is not None:
             ckpt = torch.load(pretrained_checkpoint_path, map_location="cpu", weights_only=False)
             self.load_state_dict(ckpt["model"] if "model" in ckpt else ckpt)
@@ -211,20 +213,109 @@ class MapAnything(torch.nn.Module):
     def _out_struct(o):
         return _lib.MabOutputs(**{k: (o[k].data_ptr() if k in o else None) for k, _ in _lib.MabOutputs._fields_})
 
-    def _run_forward(self, imgs, H, W, want_logits=False):
-        """One whole forward on this GPU: returns the raw output tensors (all views stacked)."""
+    def _run_forward(self, imgs, H, W, want_logits=False, view_lo=0, total_views=None):
+        """One whole forward of this rank's views: returns the raw output tensors (views stacked).
+
+        Single GPU (total_views == views): one `mab_forward` call.  View-sharded
+        (total_views > views, torch.distributed initialised, rank r holds views [view_lo, ...)): the
+        staged C ABI with ring global attention (parallel.ring_pass) and a broadcast of the metric
+        scale from the rank that owns the scale token."""
         V = imgs.shape[0]
+        total = int(total_views or V)
         with torch.cuda.device(self._device):
-            nbytes = self._lib.mab_workspace_bytes(self._handle, V, V, H, W)
+            nbytes = self._lib.mab_workspace_bytes(self._handle, V, total, H, W)
             if nbytes == 0:
                 raise RuntimeError("mab_workspace_bytes rejected the problem shape")
             ws = self._get_workspace(nbytes)
             outs = self._alloc_outputs(V, H, W, want_logits)
             inp = _lib.MabInputs(views=V, H=H, W=W, images=imgs.data_ptr())
             ost = self._out_struct(outs)
-            _lib.check(self._lib.mab_forward(self._handle, C.byref(inp), C.byref(ost), ws.data_ptr(),
-                                             ws.numel(), self._stream_ptr()), "mab_forward")
+            if total == V:
+                _lib.check(self._lib.mab_forward(self._handle, C.byref(inp), C.byref(ost), ws.data_ptr(),
+                                                 ws.numel(), self._stream_ptr()), "mab_forward")
+            else:
+                self._forward_sharded(inp, ost, outs, ws, V, H, W, view_lo, total)
         return outs
+
+    def _forward_sharded(self, inp, ost, outs, ws, V, H, W, view_lo, total):
+        import torch.distributed as dist
+
+        from . import parallel
+
+        lib, hd = self._lib, self._handle
+        world, rank = dist.get_world_size(), dist.get_rank()
+        assert parallel.shard_views(total, world, rank) == (view_lo, view_lo + V), "views do not match the shard table"
+        T = (H // 14) * (W // 14)
+        width = 3 * self._cfg.aat_dim
+        rows = parallel.rows_per_rank(total, world, T)
+        if self._ring_bufs is None or self._ring_bufs[0].shape[0] < max(rows):
+            self._ring_bufs = [torch.empty((max(rows), width), dtype=torch.bfloat16, device=self._device)
+                               for _ in range(2)]
+        own_first = 3 if view_lo == 0 else 0
+        _lib.check(lib.mab_stage_encode(hd, C.byref(inp), total, ws.data_ptr(), ws.numel(), own_first,
+                                        self._stream_ptr()), "mab_stage_encode")
+        qkv_ptr, n_rows = C.c_void_p(), C.c_int()
+        both = _lib.RING_FIRST | _lib.RING_LAST
+        for layer in range(self._cfg.aat_depth):
+            _lib.check(lib.mab_stage_aat_qkv(hd, layer, C.byref(qkv_ptr), C.byref(n_rows), self._stream_ptr()),
+                       "mab_stage_aat_qkv")
+            if layer % 2 == 0:
+                assert n_rows.value == rows[rank]
+                off = qkv_ptr.value - ws.data_ptr()
+                local = ws[off: off + n_rows.value * width * 2].view(torch.bfloat16).view(n_rows.value, width)
+
+                def attend(block, n, step, src, layer=layer):
+                    flags = (_lib.RING_FIRST if step == 0 else 0) | (_lib.RING_LAST if step == world - 1 else 0)
+                    _lib.check(lib.mab_stage_aat_attend(hd, layer, block.data_ptr(), n, flags, self._stream_ptr()),
+                               "mab_stage_aat_attend")
+
+                parallel.ring_pass(local, rows, self._ring_bufs, attend)
+            else:
+                _lib.check(lib.mab_stage_aat_attend(hd, layer, None, 0, both, self._stream_ptr()),
+                           "mab_stage_aat_attend")
+            _lib.check(lib.mab_stage_aat_finish(hd, layer, self._stream_ptr()), "mab_stage_aat_finish")
+        if view_lo == 0:
+            _lib.check(lib.mab_stage_scale_head(hd, outs["metric_scale"].data_ptr(), self._stream_ptr()),
+                       "mab_stage_scale_head")
+        dist.broadcast(outs["metric_scale"], src=0)
+        _lib.check(lib.mab_stage_heads(hd, C.byref(inp), C.byref(ost), outs["metric_scale"].data_ptr(),
+                                       self._stream_ptr()), "mab_stage_heads")
+
+    def _run_postprocess(self, imgs, outs, H, W, apply_mask=True, mask_edges=True, edge_normal_threshold=5.0,
+                         edge_depth_threshold=0.03, apply_confidence_mask=False, confidence_percentile=10):
+        """inference.py:314-506 on the device, all views of this rank at once."""
+        V, dev = imgs.shape[0], self._device
+        post = dict(
+            img_no_norm=torch.empty((V, H, W, 3), dtype=torch.float32, device=dev),
+            depth_z=torch.empty((V, H, W, 1), dtype=torch.float32, device=dev),
+            intrinsics=torch.empty((V, 3, 3), dtype=torch.float32, device=dev),
+            camera_poses=torch.empty((V, 4, 4), dtype=torch.float32, device=dev),
+            cam_trans=torch.empty((V, 3), dtype=torch.float32, device=dev),
+            cam_quats=torch.empty((V, 4), dtype=torch.float32, device=dev),
+            mask=torch.empty((V, H, W, 1), dtype=torch.bool, device=dev),
+        )
+        with torch.cuda.device(dev):
+            need = V * H * W * 17 + 256
+            if self._post_ws is None or self._post_ws.numel() < need:
+                self._post_ws = torch.empty(need, dtype=torch.uint8, device=dev)
+            inp = _lib.MabInputs(views=V, H=H, W=W, images=imgs.data_ptr())
+            ost = self._out_struct(outs)
+            pst = _lib.MabPostOutputs(**{k: post[k].data_ptr() for k, _ in _lib.MabPostOutputs._fields_})
+            opt = _lib.MabPostOptions(int(apply_mask), int(mask_edges), float(edge_normal_threshold),
+                                      float(edge_depth_threshold), int(apply_confidence_mask),
+                                      float(confidence_percentile))
+            _lib.check(self._lib.mab_postprocess(self._handle, C.byref(inp), C.byref(ost), C.byref(pst),
+                                                 C.byref(opt), self._post_ws.data_ptr(), self._post_ws.numel(),
+                                                 self._stream_ptr()), "mab_postprocess")
+        return post
+
+    @torch.inference_mode()
+    def run_resident(self, imgs, H, W, view_range=None, total_views=None, **post_kw):
+        """Forward + post-processing on an image stack that is already resident on the device
+        ((views,3,H,W) fp32).  Returns the stacked raw and post-processed tensors (no dicts)."""
+        lo = view_range[0] if view_range else 0
+        outs = self._run_forward(imgs, H, W, view_lo=lo, total_views=total_views)
+        return outs, self._run_postprocess(imgs, outs, H, W, **post_kw)
 
     def _raw_dicts(self, outs, V):
         scale = outs["metric_scale"]
@@ -268,10 +359,14 @@ class MapAnything(torch.nn.Module):
               confidence_percentile: float = 10, ignore_calibration_inputs: bool = False,
               ignore_depth_inputs: bool = False, ignore_pose_inputs: bool = False,
               ignore_depth_scale_inputs: bool = False, ignore_pose_scale_inputs: bool = False,
-              ) -> List[Dict[str, torch.Tensor]]:
+              view_range=None, total_views: Optional[int] = None) -> List[Dict[str, torch.Tensor]]:
         """model.py:2206-2355.  The kernels always compute in bf16 with fp32 accumulation / fp32
         residual streams (the reference's bf16-autocast semantics); `use_amp`/`amp_dtype` are
-        accepted for signature compatibility."""
+        accepted for signature compatibility.
+
+        Extension for view-sharded scenes (one process per GPU, torch.distributed initialised):
+        `views` are THIS rank's views [view_range[0], view_range[1]) of a scene of `total_views`
+        views (parallel.shard_views gives the table); the returned list covers the same views."""
         if not self._finalized:
             raise RuntimeError("load_state_dict() / from_pretrained() must be called before inference")
         views = validate_input_views_for_inference(views)
@@ -289,29 +384,9 @@ class MapAnything(torch.nn.Module):
                     v[name] = v[name].to(self._device, non_blocking=True)
         V = len(views)
         imgs, H, W = self._pack_images(views)
-        outs = self._run_forward(imgs, H, W)
-        dev = self._device
-        post = dict(
-            img_no_norm=torch.empty((V, H, W, 3), dtype=torch.float32, device=dev),
-            depth_z=torch.empty((V, H, W, 1), dtype=torch.float32, device=dev),
-            intrinsics=torch.empty((V, 3, 3), dtype=torch.float32, device=dev),
-            camera_poses=torch.empty((V, 4, 4), dtype=torch.float32, device=dev),
-            cam_trans=torch.empty((V, 3), dtype=torch.float32, device=dev),
-            cam_quats=torch.empty((V, 4), dtype=torch.float32, device=dev),
-            mask=torch.empty((V, H, W, 1), dtype=torch.bool, device=dev),
-        )
-        with torch.cuda.device(dev):
-            need = V * H * W * 17 + 256
-            ws = self._get_workspace(need)
-            inp = _lib.MabInputs(views=V, H=H, W=W, images=imgs.data_ptr())
-            ost = self._out_struct(outs)
-            pst = _lib.MabPostOutputs(**{k: post[k].data_ptr() for k, _ in _lib.MabPostOutputs._fields_})
-            opt = _lib.MabPostOptions(int(apply_mask), int(mask_edges), float(edge_normal_threshold),
-                                      float(edge_depth_threshold), int(apply_confidence_mask),
-                                      float(confidence_percentile))
-            _lib.check(self._lib.mab_postprocess(self._handle, C.byref(inp), C.byref(ost), C.byref(pst),
-                                                 C.byref(opt), ws.data_ptr(), ws.numel(),
-                                                 self._stream_ptr()), "mab_postprocess")
+        outs = self._run_forward(imgs, H, W, view_lo=view_range[0] if view_range else 0, total_views=total_views)
+        post = self._run_postprocess(imgs, outs, H, W, apply_mask, mask_edges, edge_normal_threshold,
+                                     edge_depth_threshold, apply_confidence_mask, confidence_percentile)
         preds = []
         scale = outs["metric_scale"]
         for i in range(V):

@@ -426,8 +426,36 @@ DEFAULT_FLAGS = dict(use_calibration=True, use_depth=True, use_pose=True, use_de
                      use_pose_scale=True)
 
 
-def forward(sd, views, flags=None, taps=None):
-    """Raw (un-post-processed) per-view prediction dicts; views already pre-processed; B=1/view."""
+import contextlib
+
+
+def _trunk_ctx(amp, device_type):
+    """amp=True reproduces the precision regions of the reference's default GPU path: encoder and
+    info-sharing under torch.autocast(bf16) (model.py:2335-2338), everything else with autocast
+    disabled (model.py:1377, 1774)."""
+    if amp:
+        return torch.autocast(device_type, dtype=torch.bfloat16)
+    return contextlib.nullcontext()
+
+
+def forward(sd, views, flags=None, taps=None, amp=False):
+    """See _forward_impl.  amp=True on CUDA also allows TF32 in the fp32 regions, as the reference
+    does at import time (model.py:89-93; cuDNN conv TF32 is PyTorch's default)."""
+    if not (amp and views[0]["img"].device.type == "cuda"):
+        return _forward_impl(sd, views, flags, taps, amp)
+    prev = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    torch.backends.cuda.matmul.allow_tf32 = True
+    torch.backends.cudnn.allow_tf32 = True
+    try:
+        return _forward_impl(sd, views, flags, taps, amp)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = prev
+
+
+def _forward_impl(sd, views, flags=None, taps=None, amp=False):
+    """Raw (un-post-processed) per-view prediction dicts; views already pre-processed; B=1/view.
+    amp=False: fp32 everywhere (infer(use_amp=False)); amp=True: the reference's bf16-autocast
+    regions (used on the GPU box as the yardstick for "the reference's own bf16 path")."""
     flags = dict(DEFAULT_FLAGS, **(flags or {}))
     V = len(views)
     assert all(v["img"].shape == views[0]["img"].shape for v in views)
@@ -435,13 +463,17 @@ def forward(sd, views, flags=None, taps=None):
     assert B == 1, "the oracle restates the B=1-per-view case used by every config"
     h, w = H // PATCH, W // PATCH
     imgs = torch.cat([v["img"] for v in views], dim=0).float()
-    enc = dinov2_encoder(imgs, sd, taps=taps)  # (V,T,1024)
+    dev_type = imgs.device.type
+    with _trunk_ctx(amp, dev_type):
+        enc = dinov2_encoder(imgs, sd, taps=taps).float()  # (V,T,1024)
     if taps is not None:
         taps["enc_out"] = enc
     fused = fuse_geometric_inputs(enc, views, sd, flags)
     if taps is not None:
         taps["fused"] = fused
-    final, inter, scale_tok = alternating_attention_transformer(fused, sd, taps=taps)
+    with _trunk_ctx(amp, dev_type):
+        final, inter, scale_tok = alternating_attention_transformer(fused, sd, taps=taps)
+    final, inter, scale_tok = final.float(), [t.float() for t in inter], scale_tok.float()
     if taps is not None:
         taps["aat_tap11"], taps["aat_tap17"], taps["aat_final"] = inter[0], inter[1], final
         taps["scale_token_final"] = scale_tok
@@ -650,13 +682,17 @@ def validate_views(views):
 def infer(sd, views, apply_mask=True, mask_edges=True, edge_normal_threshold=5.0,
           edge_depth_threshold=0.03, apply_confidence_mask=False, confidence_percentile=10,
           ignore_calibration_inputs=False, ignore_depth_inputs=False, ignore_pose_inputs=False,
-          ignore_depth_scale_inputs=False, ignore_pose_scale_inputs=False, taps=None):
-    """model.py:2206-2355 in fp32 (use_amp=False)."""
+          ignore_depth_scale_inputs=False, ignore_pose_scale_inputs=False, taps=None, amp=False):
+    """model.py:2206-2355; fp32 (use_amp=False) unless amp=True (see forward).  Tensors may live on
+    any device; post-processing runs on the CPU like the reference's numpy code."""
     with torch.inference_mode():
         pv = preprocess_views(validate_views(views))
         flags = dict(use_calibration=not ignore_calibration_inputs, use_depth=not ignore_depth_inputs,
                      use_pose=not ignore_pose_inputs, use_depth_scale=not ignore_depth_scale_inputs,
                      use_pose_scale=not ignore_pose_scale_inputs)
-        raw = forward(sd, pv, flags, taps=taps)
+        raw = forward(sd, pv, flags, taps=taps, amp=amp)
+        if raw[0]["pts3d"].device.type != "cpu":
+            raw = [{k: v.cpu() for k, v in r.items()} for r in raw]
+            pv = [{k: (v.cpu() if torch.is_tensor(v) else v) for k, v in view.items()} for view in pv]
         return postprocess(raw, pv, apply_mask, mask_edges, edge_normal_threshold,
                            edge_depth_threshold, apply_confidence_mask, confidence_percentile)

@@ -68,18 +68,41 @@ def compare_with_golden(preds, g, stride, tol_dense, tol_pose_deg, tol_small=Non
             assert p[k].shape == g[f"v{i}.{k}"].shape, k
             report[f"v{i}.{k}"] = rel_l2(p[k], g[f"v{i}.{k}"])
         report[f"v{i}.cam_quats_deg"] = quat_angle_deg(p["cam_quats"], g[f"v{i}.cam_quats"])
-    bad = []
-    for k, v in report.items():
-        if k.endswith("_agree"):
-            if v < min_mask_agree:
-                bad.append((k, v))
-        elif k.endswith("_deg"):
-            if v > tol_pose_deg:
-                bad.append((k, v))
-        elif k.split(".")[1] in ("cam_trans", "camera_poses", "intrinsics", "metric_scaling_factor"):
-            if v > (tol_small if tol_small is not None else tol_dense):
-                bad.append((k, v))
-        elif v > tol_dense:
-            bad.append((k, v))
+    if tol_dense is None:
+        return report
+    bad = out_of_tolerance(report, tol_dense, tol_pose_deg, tol_small, min_mask_agree)
     assert not bad, f"out of tolerance: {bad}\nfull report: {report}"
     return report
+
+
+SMALL_REPORT_KEYS = ("cam_trans", "camera_poses", "intrinsics", "metric_scaling_factor")
+# quantities that contain the predicted camera pose (world-frame points, pose matrices): their error
+# is dominated by the pose head's amplification of bf16 trunk noise, see DESIGN.md "Parity"
+POSE_DEPENDENT_KEYS = ("pts3d", "cam_trans", "camera_poses", "cam_quats_deg")
+
+
+def out_of_tolerance(report, tol_dense, tol_pose_deg, tol_small=None, min_mask_agree=0.0, yardstick=None,
+                     slack=1.5):
+    """Keys of `report` that exceed their tolerance.  With `yardstick` (the report of the oracle run
+    with the reference's own bf16-autocast precision regions against the same fp32 golden), a key
+    passes when it is within max(tolerance, slack * yardstick error): the CUDA path has to be as
+    close to the fp32 reference as the reference's own bf16 path is."""
+    bad = []
+    for k, v in report.items():
+        name = k.split(".", 1)[1]
+        y = slack * yardstick[k] if yardstick is not None and k in yardstick else 0.0
+        if k.endswith("_agree"):
+            floor = min_mask_agree
+            if yardstick is not None and k in yardstick:
+                floor = min(floor, 1.0 - slack * (1.0 - yardstick[k]))
+            if v < floor:
+                bad.append((k, v))
+        elif k.endswith("_deg"):
+            if v > max(tol_pose_deg, y):
+                bad.append((k, v))
+        elif name in SMALL_REPORT_KEYS:
+            if v > max(tol_small if tol_small is not None else tol_dense, y):
+                bad.append((k, v))
+        elif v > max(tol_dense, y):
+            bad.append((k, v))
+    return bad

@@ -59,3 +59,29 @@ def test_attention_separate_kv():
     out = g.attention(q, heads, 1, 1037, 3109, 0, 0, kv=kv)
     ref, _ = _ref(q, heads, 1, 1037, 3109, 0, 0, kv=kv)
     assert g.rel(out.float(), ref) < 8e-3
+
+
+def test_attention_ring_carry():
+    """ring global attention on one GPU: the K/V of the scene arrive as uneven blocks (as they do
+    from the other ranks of a view-sharded run) and the online-softmax state is carried between the
+    per-block launches; the result must equal attention over the concatenated K/V."""
+    import ctypes as C
+    from tests import gpu_helpers as g
+
+    torch.manual_seed(9)
+    heads, D = 12, 768
+    q = (torch.randn(2 * 1036 + 1, 3 * D, device="cuda") * 2).bfloat16()
+    blocks = [q, (torch.randn(2072, 3 * D, device="cuda") * 2).bfloat16(),
+              (torch.randn(1036, 3 * D, device="cuda") * 2).bfloat16()]
+    rows = q.shape[0]
+    out = torch.zeros((rows, D), dtype=torch.bfloat16, device="cuda")
+    co = torch.empty((rows, D), dtype=torch.float32, device="cuda")
+    cml = torch.empty((rows, heads, 2), dtype=torch.float32, device="cuda")
+    for i, b in enumerate(blocks):
+        g.check(g.lib().mab_attention_carry(g.ptr(q), rows, g.ptr(b), b.shape[0], heads, 1, rows, b.shape[0], 0, 0,
+                                            0.125, g.ptr(out), g.ptr(co), g.ptr(cml), int(i > 0),
+                                            int(i < len(blocks) - 1), g.stream()), "mab_attention_carry")
+    torch.cuda.synchronize()
+    kv = torch.cat(blocks, 0)
+    ref, _ = _ref(q, heads, 1, rows, kv.shape[0], 0, 0, kv=kv)
+    assert g.rel(out.float(), ref) < 8e-3

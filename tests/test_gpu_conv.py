@@ -89,7 +89,7 @@ def test_edge_mask_matches_numpy():
     yy, xx = torch.meshgrid(torch.linspace(-1, 1, H), torch.linspace(-1, 1, W), indexing="ij")
     total_diff = 0
     for v in range(V):
-        z = 2 + 0.5 * torch.sin(3 * xx + v) * torch.cos(2 * yy) + 0.05 * torch.randn(H, W)
+        z = 2 + 0.5 * torch.sin(3 * xx + v) * torch.cos(2 * yy) + 0.004 * torch.randn(H, W)
         z[20:30, 30:50] += 1.5  # a depth discontinuity
         pts_cam = torch.stack([xx * z, yy * z, z], -1)
         Rm = torch.linalg.qr(torch.randn(3, 3))[0]
