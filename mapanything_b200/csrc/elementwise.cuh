@@ -25,7 +25,8 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows_out, int 
                                  const float* __restrict__ b, const float* __restrict__ w2,
                                  const float* __restrict__ b2, float eps,
                                  __nv_bfloat16* __restrict__ out_bf16, float* __restrict__ out_f32,
-                                 float* __restrict__ out_mid_f32) {
+                                 float* __restrict__ out_mid_f32,
+                                 __nv_bfloat16* __restrict__ out_split) {
   constexpr int C = 128 * VPL;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= rows_out) return;
@@ -72,6 +73,15 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows_out, int 
     if (out_bf16)
       reinterpret_cast<uint2*>(out_bf16 + (long long)warp * C)[lane + 32 * i] =
           make_uint2(pack_bf16(v[i].x, v[i].y), pack_bf16(v[i].z, v[i].w));
+    if (out_split) {  // bf16x3 A operand: row = [hi | lo | hi], pitch 3*C (see GemmEpilogue::split_n)
+      const uint2 hi = make_uint2(pack_bf16(v[i].x, v[i].y), pack_bf16(v[i].z, v[i].w));
+      const uint2 lo = make_uint2(pack_bf16(v[i].x - bf16_lo(hi.x), v[i].y - bf16_hi(hi.x)),
+                                  pack_bf16(v[i].z - bf16_lo(hi.y), v[i].w - bf16_hi(hi.y)));
+      uint2* row = reinterpret_cast<uint2*>(out_split + (long long)warp * 3 * C);
+      row[lane + 32 * i] = hi;
+      row[C / 4 + lane + 32 * i] = lo;
+      row[2 * (C / 4) + lane + 32 * i] = hi;
+    }
   }
 }
 
@@ -261,15 +271,19 @@ __global__ void im2col3x3_s2_kernel(const __nv_bfloat16* __restrict__ in, int vi
 }
 
 // mean over the T tokens of each view: bf16 [views*T, C] -> fp32 [views, C]  (pose_head.py:150)
-__global__ void token_mean_kernel(const __nv_bfloat16* __restrict__ x, int T, int C,
+// ld = row pitch in elements; lo_off > 0: x is a bf16x2 split value, the low part lo_off elements
+// behind the high part
+__global__ void token_mean_kernel(const __nv_bfloat16* __restrict__ x, int T, int C, int ld, int lo_off,
                                   float* __restrict__ out) {
   const int v = blockIdx.y;
   const int c = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim.x channels, blockDim.y row lanes
   __shared__ float part[8][128];
   float s = 0.f;
   if (c < C)
-    for (int t = threadIdx.y; t < T; t += blockDim.y)
-      s += __bfloat162float(x[((long long)v * T + t) * C + c]);
+    for (int t = threadIdx.y; t < T; t += blockDim.y) {
+      const __nv_bfloat16* r = x + ((long long)v * T + t) * ld + c;
+      s += __bfloat162float(r[0]) + (lo_off ? __bfloat162float(r[lo_off]) : 0.f);
+    }
   part[threadIdx.y][threadIdx.x] = s;
   __syncthreads();
   if (threadIdx.y == 0 && c < C) {

@@ -39,6 +39,9 @@ struct GemmEpilogue {
   __nv_bfloat16* out_relu;       // relu(value) (input of the next ResidualConvUnit)
   int ldo;                       // output row pitch in elements
   int act;                       // ACT_*
+  int split_n;                   // > 0: out_bf16 row = [hi | lo | hi] with hi at col, lo at col +
+                                 // split_n, hi again at col + 2*split_n (bf16x3 operand of the next
+                                 // GEMM: x ~ hi + lo, |x - hi - lo| <= 2^-17 |x|)
 };
 
 // Fused tail of the dense head: ReLU -> 1x1 conv 128->6 -> adaptor -> pointmap (EPI_REGRESS)
@@ -342,9 +345,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             a.x += bf16_lo(r2.x); a.y += bf16_hi(r2.x); a.z += bf16_lo(r2.y); a.w += bf16_hi(r2.y);
           }
           if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + off) = a;
-          if (ep.out_bf16)
-            *reinterpret_cast<uint2*>(ep.out_bf16 + off) =
-                make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
+          if (ep.out_bf16) {
+            const uint2 hi = make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
+            *reinterpret_cast<uint2*>(ep.out_bf16 + off) = hi;
+            if (ep.split_n) {
+              const uint2 lo = make_uint2(pack_bf16(a.x - bf16_lo(hi.x), a.y - bf16_hi(hi.x)),
+                                          pack_bf16(a.z - bf16_lo(hi.y), a.w - bf16_hi(hi.y)));
+              *reinterpret_cast<uint2*>(ep.out_bf16 + off + ep.split_n) = lo;
+              *reinterpret_cast<uint2*>(ep.out_bf16 + off + 2 * ep.split_n) = hi;
+            }
+          }
           if (ep.out_relu)
             *reinterpret_cast<uint2*>(ep.out_relu + off) =
                 make_uint2(pack_bf16(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f)),

@@ -276,24 +276,25 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
 inline int launch_layernorm(const float* x, int rows_out, int C, int group_out, int group_in,
                             int skip, const float* w, const float* b, const float* w2,
                             const float* b2, float eps, void* out_bf16, float* out_f32,
-                            float* out_mid, cudaStream_t st) {
+                            float* out_mid, cudaStream_t st, void* out_split = nullptr) {
   if (rows_out <= 0) return 0;
+  auto os = reinterpret_cast<__nv_bfloat16*>(out_split);
   const int block = 256, rows_per_block = block / 32;
   const int grid = (rows_out + rows_per_block - 1) / rows_per_block;
   auto ob = reinterpret_cast<__nv_bfloat16*>(out_bf16);
   // algorithmic bytes: fp32 row in, bf16 and/or fp32 row(s) out
   const double bytes = (double)rows_out * C * (4.0 + (out_bf16 ? 2.0 : 0.0) + (out_f32 ? 4.0 : 0.0) +
-                                               (out_mid ? 4.0 : 0.0));
+                                               (out_mid ? 4.0 : 0.0) + (out_split ? 6.0 : 0.0));
   ProfScope ps(CAT_LAYERNORM, 0.0, bytes, st);
   if (C == 768)
     layernorm_kernel<6><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
-                                                 b2, eps, ob, out_f32, out_mid);
+                                                 b2, eps, ob, out_f32, out_mid, os);
   else if (C == 1024)
     layernorm_kernel<8><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
-                                                 b2, eps, ob, out_f32, out_mid);
+                                                 b2, eps, ob, out_f32, out_mid, os);
   else if (C == 128)
     layernorm_kernel<1><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
-                                                 b2, eps, ob, out_f32, out_mid);
+                                                 b2, eps, ob, out_f32, out_mid, os);
   else
     return fail(-1, "layernorm: unsupported width %d (supported 128, 768, 1024)", C);
   MAB_CUDA(cudaGetLastError());

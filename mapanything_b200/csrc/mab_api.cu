@@ -27,6 +27,23 @@ __global__ void pack_matrix_kernel(const float* __restrict__ w, int rows, int co
   }
 }
 
+// fp32 [rows, cols] -> bf16 [rows, 3*cols] = [hi | hi | lo]: B operand of a bf16x3 GEMM whose A rows
+// are [hi | lo | hi], so that A.B^T = a_hi.w_hi + a_lo.w_hi + a_hi.w_lo ~ fp32 a.w (error ~2^-16)
+__global__ void pack_matrix_split_kernel(const float* __restrict__ w, int rows, int cols,
+                                         bf16* __restrict__ out) {
+  const long long total = (long long)rows * cols;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = i % cols;
+    const long long r = i / cols;
+    const float x = w[i];
+    const bf16 hi = __float2bfloat16(x);
+    const bf16 lo = __float2bfloat16(x - __bfloat162float(hi));
+    bf16* o = out + r * 3 * cols;
+    o[c] = hi; o[cols + c] = hi; o[2 * cols + c] = lo;
+  }
+}
+
 // conv weight [Cout, Cin, 3, 3] fp32 -> [Cout, 9, Cpad] bf16 (tap = ky*3+kx), zero padded channels
 __global__ void pack_conv3_kernel(const float* __restrict__ w, int Cout, int Cin, int Cpad,
                                   bf16* __restrict__ out) {
@@ -242,7 +259,7 @@ struct Plan {  // every workspace pointer of one forward
   // info sharing
   float* ys; bf16* tap[2]; bf16* fin; float* scale_tok; float* carry_o; float* carry_ml;
   // heads (small)
-  float* scale_tmp; float* pose_pool; float* pose_tmp; float* pose_raw; bf16* ph_a; bf16* ph_b; bf16* ph_c;
+  float* scale_tmp; float* pose_pool; float* pose_tmp; float* pose_raw; bf16* ph_in; bf16* ph_a; bf16* ph_b; bf16* ph_c; bf16* ph_d;
   // dense head chunk buffers
   int vc = 0;
   bf16* d_a; bf16* d_s; bf16* d_u; bf16* lvl[4]; bf16* lvl_relu[4]; bf16* t0; bf16* t1; bf16* t2; bf16* t3;
@@ -306,12 +323,14 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
   p.pose_pool = b.take<float>((long long)V * 784);
   p.pose_tmp = b.take<float>((long long)V * 784 * 2);
   p.pose_raw = b.take<float>((long long)V * 8);
-  p.ph_a = b.take<bf16>(VT * 784);
-  p.ph_b = b.take<bf16>(VT * 784);
-  p.ph_c = b.take<bf16>(VT * 784);
-  // dense head, per chunk of vc views
+  // pose + dense head, per chunk of vc views
   p.vc = c.head_chunk < 1 ? 1 : (c.head_chunk > V ? V : c.head_chunk);
   const long long vc = p.vc, T = p.T;
+  p.ph_in = b.take<bf16>(vc * T * 3 * A);
+  p.ph_a = b.take<bf16>(vc * T * 3 * 784);
+  p.ph_b = b.take<bf16>(vc * T * 3 * 784);
+  p.ph_c = b.take<bf16>(vc * T * 3 * 784);
+  p.ph_d = b.take<bf16>(vc * T * 3 * 784);
   const int h = p.h, w = p.w;
   p.d_a = b.take<bf16>(vc * T * 768);
   p.d_s = b.take<bf16>(vc * T * 6912 / 1);  // >= T*1536 (convT) and >= Ho*Wo*9*768 (im2col s2)
@@ -391,6 +410,21 @@ int pack_linear(mab_handle* h, const std::string& key, int ld_pad, cudaStream_t 
   return 0;
 }
 
+int pack_linear_split(mab_handle* h, const std::string& key, cudaStream_t st) {
+  auto it = h->raw.find(key);
+  if (it == h->raw.end()) return fail(-4, "missing weight %s", key.c_str());
+  const RawTensor& t = it->second;
+  const int rows = (int)t.shape[0];
+  const int cols = (int)(t.numel / rows);
+  bf16* out;
+  MAB_CUDA(cudaMalloc(&out, (size_t)rows * 3 * cols * sizeof(bf16)));
+  h->owned.push_back(out);
+  pack_matrix_split_kernel<<<ew_grid((long long)rows * cols), 256, 0, st>>>(t.p, rows, cols, out);
+  MAB_CUDA(cudaGetLastError());
+  h->packed[key] = out;
+  return 0;
+}
+
 int pack_conv3(mab_handle* h, const std::string& key, cudaStream_t st) {
   auto it = h->raw.find(key);
   if (it == h->raw.end()) return fail(-4, "missing weight %s", key.c_str());
@@ -463,10 +497,12 @@ extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
   }
   MAB_TRY(pack_conv3(h, "dpt_regressor_head.conv1.weight", st));
   MAB_TRY(pack_conv3(h, "dpt_regressor_head.conv2.0.weight", st));
-  MAB_TRY(pack_linear(h, "pose_head.proj.weight", 0, st));
+  // pose head: bf16x3 operands (the reference runs it in fp32/TF32, model.py:1774; its output is
+  // normalised to a unit quaternion, which plain bf16 operands do not resolve to 0.1 deg)
+  MAB_TRY(pack_linear_split(h, "pose_head.proj.weight", st));
   for (int b = 0; b < 2; ++b)
     for (int k = 1; k <= 3; ++k)
-      MAB_TRY(pack_linear(h, "pose_head.res_conv." + std::to_string(b) + ".res_conv" + std::to_string(k) + ".weight", 0, st));
+      MAB_TRY(pack_linear_split(h, "pose_head.res_conv." + std::to_string(b) + ".res_conv" + std::to_string(k) + ".weight", st));
   // required fp32 tensors that are used as-is
   for (const char* k : {"encoder.model.cls_token", "encoder.model.pos_embed", "encoder.model.norm.weight",
                         "fusion_norm_layer.weight", "scale_token", "info_sharing.view_pos_table",
@@ -539,6 +575,17 @@ struct Ctx {
     ep.bias = bias; ep.gamma = gamma; ep.res_f32 = res_f32; ep.out_f32 = out_f32;
     ep.out_bf16 = out_bf16; ep.res1 = res1; ep.ldo = N; ep.act = act;
     return launch_gemm(A, lda, W, ldw > 0 ? ldw : K, M, N, K, ep, st);
+  }
+  // bf16x3 linear: A rows are [hi | lo | hi] (pitch 3K), W rows [hi | hi | lo]; the output is
+  // written in the same split form (pitch 3N) so that layers chain; the residual is a split value
+  int linear_x3(const bf16* A, int M, int K, const std::string& wkey, int N, const float* bias, int act,
+                const bf16* res_split, bf16* out_split) {
+    const bf16* W = h->P(wkey);
+    if (!W) return fail(-4, "weight %s was not packed", wkey.c_str());
+    GemmEpilogue ep{};
+    ep.bias = bias; ep.act = act; ep.out_bf16 = out_split; ep.ldo = 3 * N; ep.split_n = N;
+    ep.res1 = res_split; ep.res2 = res_split ? res_split + N : nullptr;
+    return launch_gemm(A, 3LL * K, W, 3LL * K, M, N, 3 * K, ep, st);
   }
   int conv3(const bf16* x, int batch, int H, int W, int C, const std::string& wkey, int Cout,
             const float* bias, int act, const bf16* res1, const bf16* res2, bf16* out, bf16* out_relu) {
@@ -765,34 +812,6 @@ extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs*
     MAB_TRY(mab_stage_scale_head(h, out->metric_scale, stream));
   }
 
-  // ---- pose head (pose_head.py:115-159, adaptors.py:714-732) -----------------------------------
-  {
-    const std::string ph = "pose_head.";
-    MAB_TRY(c.linear(p.fin, (int)VT, A, A, ph + "proj.weight", 784, h->F(ph + "proj.bias"), ACT_NONE,
-                     nullptr, nullptr, nullptr, p.ph_a));
-    bf16* feat = p.ph_a; bf16* other = p.att;  // p.att is free after the transformer
-    for (int b = 0; b < 2; ++b) {
-      const std::string r = ph + "res_conv." + std::to_string(b) + ".res_conv";
-      MAB_TRY(c.linear(feat, (int)VT, 784, 784, r + "1.weight", 784, h->F(r + "1.bias"), ACT_RELU, nullptr, nullptr, nullptr, p.ph_b));
-      MAB_TRY(c.linear(p.ph_b, (int)VT, 784, 784, r + "2.weight", 784, h->F(r + "2.bias"), ACT_RELU, nullptr, nullptr, nullptr, p.ph_c));
-      MAB_TRY(c.linear(p.ph_c, (int)VT, 784, 784, r + "3.weight", 784, h->F(r + "3.bias"), ACT_RELU, nullptr, nullptr, nullptr, other, feat));
-      bf16* t = feat; feat = other; other = t;
-    }
-    dim3 blk(128, 8), grd((784 + 127) / 128, V);
-    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
-               token_mean_kernel<<<grd, blk, 0, c.st>>>(feat, T, 784, p.pose_pool));
-    MAB_CUDA(cudaGetLastError());
-    float* m0 = p.pose_tmp; float* m1 = p.pose_tmp + (long long)V * 784;
-    MAB_TRY(small_linear(c.st, p.pose_pool, h->F(ph + "more_mlps.0.weight"), h->F(ph + "more_mlps.0.bias"), V, 784, 784, 2, m0));
-    MAB_TRY(small_linear(c.st, m0, h->F(ph + "more_mlps.2.weight"), h->F(ph + "more_mlps.2.bias"), V, 784, 784, 2, m1));
-    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
-               small_linear_kernel<<<(int)(((long long)7 * ((V + 7) / 8) * 32 + 255) / 256), 256, 0, c.st>>>(
-        m1, h->extra["pose_head.fc7.weight"], h->extra["pose_head.fc7.bias"], V, 784, 7, 0, p.pose_raw, 784, 7));
-    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
-               pose_finalize_kernel<<<(V + 127) / 128, 128, 0, c.st>>>(p.pose_raw, V, out->pose));
-    MAB_CUDA(cudaGetLastError());
-  }
-
   // ---- dense head: DPT feature pyramid + regressor + fused adaptor/pointmap epilogue -----------
   const std::string ip = "dpt_feature_head.input_process.";
   const std::string sc = "dpt_feature_head.scratch.";
@@ -804,6 +823,39 @@ extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs*
     const bf16* f1 = p.tap[0] + (long long)v0 * T * A;
     const bf16* f2 = p.tap[1] + (long long)v0 * T * A;
     const bf16* f3 = p.fin + (long long)v0 * T * A;
+    // ---- pose head (pose_head.py:115-159, adaptors.py:714-732) in bf16x3 (~fp32) arithmetic:
+    // final norm of this chunk's tokens as a split value, 7 token-wise GEMMs, mean over tokens
+    {
+      const std::string ph = "pose_head.";
+      MAB_TRY(launch_layernorm(p.ys + (long long)v0 * T * A, M, A, M, M, 0, h->F("info_sharing.norm.weight"),
+                               h->F("info_sharing.norm.bias"), nullptr, nullptr, 1e-6f, nullptr, nullptr,
+                               nullptr, c.st, p.ph_in));
+      MAB_TRY(c.linear_x3(p.ph_in, M, A, ph + "proj.weight", 784, h->F(ph + "proj.bias"), ACT_NONE, nullptr, p.ph_a));
+      bf16* feat = p.ph_a; bf16* other = p.ph_d;
+      for (int b = 0; b < 2; ++b) {
+        const std::string r = ph + "res_conv." + std::to_string(b) + ".res_conv";
+        MAB_TRY(c.linear_x3(feat, M, 784, r + "1.weight", 784, h->F(r + "1.bias"), ACT_RELU, nullptr, p.ph_b));
+        MAB_TRY(c.linear_x3(p.ph_b, M, 784, r + "2.weight", 784, h->F(r + "2.bias"), ACT_RELU, nullptr, p.ph_c));
+        MAB_TRY(c.linear_x3(p.ph_c, M, 784, r + "3.weight", 784, h->F(r + "3.bias"), ACT_RELU, feat, other));
+        bf16* t = feat; feat = other; other = t;
+      }
+      dim3 blk(128, 8), grd((784 + 127) / 128, vc);
+      MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+                 token_mean_kernel<<<grd, blk, 0, c.st>>>(feat, T, 784, 3 * 784, 784, p.pose_pool + (long long)v0 * 784));
+      MAB_CUDA(cudaGetLastError());
+      float* pool = p.pose_pool + (long long)v0 * 784;
+      float* m0 = p.pose_tmp; float* m1 = p.pose_tmp + (long long)V * 784;
+      MAB_TRY(small_linear(c.st, pool, h->F(ph + "more_mlps.0.weight"), h->F(ph + "more_mlps.0.bias"), vc, 784, 784, 2, m0));
+      MAB_TRY(small_linear(c.st, m0, h->F(ph + "more_mlps.2.weight"), h->F(ph + "more_mlps.2.bias"), vc, 784, 784, 2, m1));
+      MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+                 small_linear_kernel<<<(int)(((long long)7 * ((vc + 7) / 8) * 32 + 255) / 256), 256, 0, c.st>>>(
+                     m1, h->extra["pose_head.fc7.weight"], h->extra["pose_head.fc7.bias"], vc, 784, 7, 0,
+                     p.pose_raw + (long long)v0 * 7, 784, 7));
+      MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+                 pose_finalize_kernel<<<(vc + 127) / 128, 128, 0, c.st>>>(p.pose_raw + (long long)v0 * 7, vc,
+                                                                          out->pose + (long long)v0 * 8));
+      MAB_CUDA(cudaGetLastError());
+    }
     // layer 0: 1x1 (1024->96) -> convT 4x4/s4 -> 3x3 (96->256, no bias)           dpt.py:107-128
     MAB_TRY(c.linear(f0, M, cf.enc_dim, cf.enc_dim, ip + "0.0.0.weight", 96, h->F(ip + "0.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
     MAB_TRY(c.linear(p.d_a, M, 96, 96, ip + "0.0.1.weight", 16 * 96, h->extra[ip + "0.0.1.bias.tiled"], ACT_NONE, nullptr, nullptr, nullptr, p.d_s));

@@ -88,13 +88,19 @@ def out_of_tolerance(report, tol_dense, tol_pose_deg, tol_small=None, min_mask_a
     passes when it is within max(tolerance, slack * yardstick error): the CUDA path has to be as
     close to the fp32 reference as the reference's own bf16 path is."""
     bad = []
+    # the two paths carry independent bf16 noise realisations, so the yardstick of a key is its
+    # worst view in the scene, not the same view
+    worst = {}
+    for k, v in (yardstick or {}).items():
+        name = k.split(".", 1)[1]
+        worst[name] = min(worst.get(name, 1.0), v) if k.endswith("_agree") else max(worst.get(name, 0.0), v)
     for k, v in report.items():
         name = k.split(".", 1)[1]
-        y = slack * yardstick[k] if yardstick is not None and k in yardstick else 0.0
+        y = slack * worst[name] if name in worst else 0.0
         if k.endswith("_agree"):
             floor = min_mask_agree
-            if yardstick is not None and k in yardstick:
-                floor = min(floor, 1.0 - slack * (1.0 - yardstick[k]))
+            if name in worst:
+                floor = min(floor, 1.0 - slack * (1.0 - worst[name]))
             if v < floor:
                 bad.append((k, v))
         elif k.endswith("_deg"):
