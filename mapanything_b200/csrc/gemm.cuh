@@ -11,7 +11,7 @@
 //               coordinates are zero-filled by the TMA unit, so no im2col buffer ever exists.
 //
 // Persistent, warp-specialised: warp0 = TMA producer, warp1 = MMA issuer (+TMEM owner),
-// warps 2..5 = epilogue.  smem ring of STAGES {A 128x64, B BNx64}; TMEM holds two BN-column fp32
+// warps 2..9 = epilogue.  smem ring of STAGES {A 128x64, B BNx64}; TMEM holds two BN-column fp32
 // accumulators so the epilogue of tile i overlaps the main loop of tile i+1.
 #pragma once
 #include "common.cuh"
@@ -20,7 +20,8 @@ namespace mab {
 
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_EPI_WARPS = 8;   // two per TMEM lane quarter, each owns half of the tile's columns
+constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
 constexpr int CONV_TH = 8;   // conv tile: 8 rows x 16 cols of output pixels = 128 GEMM rows
 constexpr int CONV_TW = 16;
 
@@ -69,17 +70,27 @@ struct GemmShape {
 };
 
 __device__ __forceinline__ float gelu_erf(float x) {
-  // exact-erf GELU (nn.GELU default, transformer_blocks.py:68).  erf via Abramowitz-Stegun
-  // 7.1.26 (|err| < 1.5e-7, far below the bf16 rounding of the stored activation).
+  // exact-erf GELU (nn.GELU default, transformer_blocks.py:68) as x * sigmoid(2u) with
+  // erf(x/sqrt2) ~ tanh(u), u = x (a0 + a1 x^2 + a2 x^4) on |x| <= 5 (minimax fit: |gelu error|
+  // <= 2.6e-5 absolute, below the bf16 rounding of the stored activation); the sigmoid form has no
+  // cancellation in the negative tail.  2 MUFU + 7 FP32 ops per element.
+#ifdef MAB_GELU_AS
   const float z = fabsf(x) * 0.70710678118654752f;
   const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
   float p = fmaf(1.061405429f, t, -1.453152027f);
   p = fmaf(p, t, 1.421413741f);
   p = fmaf(p, t, -0.284496736f);
   p = fmaf(p, t, 0.254829592f);
-  const float e = 1.0f - p * t * __expf(-z * z);
-  const float erfv = copysignf(e, x);
-  return 0.5f * x * (1.0f + erfv);
+  const float e_ = 1.0f - p * t * __expf(-z * z);
+  return 0.5f * x * (1.0f + copysignf(e_, x));
+#endif
+  const float xc = fminf(fmaxf(x, -5.0f), 5.0f);
+  const float x2 = xc * xc;
+  // -2 * log2(e) * (a0 + a1 x^2 + a2 x^4)
+  float pnl = fmaf(x2, 1.01537568e-03f, -1.06782574e-01f);
+  pnl = fmaf(pnl, x2, -2.30111381e+00f);
+  const float e = fast_exp2(xc * pnl);
+  return x * __frcp_rn(1.0f + e);
 }
 
 template <int BN, int STAGES>
@@ -87,8 +98,9 @@ struct GemmSmem {
   static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
   static constexpr int B_BYTES = BN * GEMM_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int EPI_PITCH = 36;  // floats; conflict-free 32x32 transpose (see below)
-  static constexpr int EPI_BYTES = 4 * 32 * EPI_PITCH * 4;
+  // per epilogue warp: 32 rows x 32 floats, float4 columns XOR-swizzled by (row & 7): both the
+  // row-per-lane writes and the 4-rows-per-instruction reads are bank-conflict free
+  static constexpr int EPI_BYTES = GEMM_EPI_WARPS * 32 * 32 * 4;
   static constexpr int BAR_BYTES = 256;
   static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +align slack
 };
@@ -136,7 +148,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 4);  // one arrive per epilogue warp
+      mbar_init(&tempty_bar[s], GEMM_EPI_WARPS);  // one arrive per epilogue warp
     }
     fence_barrier_init();
   }
@@ -208,9 +220,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else {
-    // ================================ epilogue (warps 2..5) ==================================
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
-    float* stg = reinterpret_cast<float*>(epi_smem) + q * 32 * SM::EPI_PITCH;
+    // ================================ epilogue (warps 2..9) ==================================
+    const int q = warp & 3;             // TMEM lane quarter this warp may access (warp id % 4)
+    const int chalf = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
+    float* stg = reinterpret_cast<float*>(epi_smem) + (warp - 2) * 32 * 32;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
@@ -239,7 +252,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       };
 
       if (EPI == EPI_REGRESS) {
-        // thread = one output pixel holding all BN(=128) channels of conv2.0
+        // thread = one output pixel holding all BN(=128) channels of conv2.0 (column-half 1 warps idle)
+        if (chalf == 1) {
+          if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+          continue;
+        }
         float lg[6];
 #pragma unroll
         for (int k = 0; k < 6; ++k) lg[k] = __ldg(rg.b3 + k);
@@ -295,12 +312,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         continue;
       }
 
-      // ---- generic epilogue: TMEM -> regs -> smem transpose -> coalesced global ------------
+      // ---- generic epilogue: TMEM -> regs -> swizzled smem transpose -> coalesced global ------
       // pass 1 thread = row `lane` of this warp's 32-row slab, 32 columns per chunk
       // pass 2 thread = (row 4*i + lane/8, columns 4*(lane%8)..+3): 8 lanes cover 128 contiguous B
-      const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;
+      const int sub_r = lane >> 3, sub_c4 = lane & 7;
+      long long ro[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ro[i] = row_offset(q * 32 + 4 * i + sub_r);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
         const int ncol0 = n_blk * BN + c0;
         if (ncol0 >= shp.N) break;
         uint32_t v[32];
@@ -309,56 +329,62 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         __syncwarp();  // previous chunk's readers are done with stg
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4*>(stg + lane * SM::EPI_PITCH + 4 * j) =
+          *reinterpret_cast<float4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) =
               make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
                           __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
         __syncwarp();
-        const int col = ncol0 + sub_c;
+        const int col = ncol0 + sub_c4 * 4;
         const bool col_ok = col < shp.N;  // N is a multiple of 4 for every layer of the path
         float4 b4 = make_float4(0, 0, 0, 0), g4 = make_float4(1, 1, 1, 1);
         if (col_ok && ep.bias) b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
         if (col_ok && ep.gamma) g4 = __ldg(reinterpret_cast<const float4*>(ep.gamma + col));
+        // all loads of the chunk are issued before any arithmetic (one warp per scheduler has to
+        // cover its own latencies)
+        float4 a[8], rf[8];
+        uint2 r1[8], r2[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int r = 4 * i + sub_r;
-          const long long ro = row_offset(q * 32 + r);
-          if (ro < 0 || !col_ok) continue;
-          float4 a = *reinterpret_cast<const float4*>(stg + r * SM::EPI_PITCH + sub_c);
-          a.x += b4.x; a.y += b4.y; a.z += b4.z; a.w += b4.w;
+          a[i] = *reinterpret_cast<const float4*>(stg + r * 32 + ((sub_c4 ^ (r & 7)) << 2));
+          const bool ok = col_ok && ro[i] >= 0;
+          const long long off = ok ? ro[i] * ep.ldo + col : 0;
+          rf[i] = make_float4(0, 0, 0, 0);
+          r1[i] = make_uint2(0, 0);
+          r2[i] = make_uint2(0, 0);
+          if (ok && ep.res_f32) rf[i] = *reinterpret_cast<const float4*>(ep.res_f32 + off);
+          if (ok && ep.res1) r1[i] = *reinterpret_cast<const uint2*>(ep.res1 + off);
+          if (ok && ep.res2) r2[i] = *reinterpret_cast<const uint2*>(ep.res2 + off);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (!(col_ok && ro[i] >= 0)) continue;
+          float4 x = a[i];
+          x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
           if (ep.act == ACT_GELU) {
-            a.x = gelu_erf(a.x); a.y = gelu_erf(a.y); a.z = gelu_erf(a.z); a.w = gelu_erf(a.w);
+            x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
           } else if (ep.act == ACT_RELU) {
-            a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); a.z = fmaxf(a.z, 0.f); a.w = fmaxf(a.w, 0.f);
+            x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
           }
-          a.x *= g4.x; a.y *= g4.y; a.z *= g4.z; a.w *= g4.w;
-          const long long off = ro * ep.ldo + col;
-          if (ep.res_f32) {
-            const float4 r4 = *reinterpret_cast<const float4*>(ep.res_f32 + off);
-            a.x += r4.x; a.y += r4.y; a.z += r4.z; a.w += r4.w;
-          }
-          if (ep.res1) {
-            const uint2 r2 = *reinterpret_cast<const uint2*>(ep.res1 + off);
-            a.x += bf16_lo(r2.x); a.y += bf16_hi(r2.x); a.z += bf16_lo(r2.y); a.w += bf16_hi(r2.y);
-          }
-          if (ep.res2) {
-            const uint2 r2 = *reinterpret_cast<const uint2*>(ep.res2 + off);
-            a.x += bf16_lo(r2.x); a.y += bf16_hi(r2.x); a.z += bf16_lo(r2.y); a.w += bf16_hi(r2.y);
-          }
-          if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + off) = a;
+          x.x = fmaf(x.x, g4.x, rf[i].x + bf16_lo(r1[i].x) + bf16_lo(r2[i].x));
+          x.y = fmaf(x.y, g4.y, rf[i].y + bf16_hi(r1[i].x) + bf16_hi(r2[i].x));
+          x.z = fmaf(x.z, g4.z, rf[i].z + bf16_lo(r1[i].y) + bf16_lo(r2[i].y));
+          x.w = fmaf(x.w, g4.w, rf[i].w + bf16_hi(r1[i].y) + bf16_hi(r2[i].y));
+          const long long off = ro[i] * ep.ldo + col;
+          if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + off) = x;
           if (ep.out_bf16) {
-            const uint2 hi = make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
+            const uint2 hi = make_uint2(pack_bf16(x.x, x.y), pack_bf16(x.z, x.w));
             *reinterpret_cast<uint2*>(ep.out_bf16 + off) = hi;
             if (ep.split_n) {
-              const uint2 lo = make_uint2(pack_bf16(a.x - bf16_lo(hi.x), a.y - bf16_hi(hi.x)),
-                                          pack_bf16(a.z - bf16_lo(hi.y), a.w - bf16_hi(hi.y)));
+              const uint2 lo = make_uint2(pack_bf16(x.x - bf16_lo(hi.x), x.y - bf16_hi(hi.x)),
+                                          pack_bf16(x.z - bf16_lo(hi.y), x.w - bf16_hi(hi.y)));
               *reinterpret_cast<uint2*>(ep.out_bf16 + off + ep.split_n) = lo;
               *reinterpret_cast<uint2*>(ep.out_bf16 + off + 2 * ep.split_n) = hi;
             }
           }
           if (ep.out_relu)
             *reinterpret_cast<uint2*>(ep.out_relu + off) =
-                make_uint2(pack_bf16(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f)),
-                           pack_bf16(fmaxf(a.z, 0.f), fmaxf(a.w, 0.f)));
+                make_uint2(pack_bf16(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)),
+                           pack_bf16(fmaxf(x.z, 0.f), fmaxf(x.w, 0.f)));
         }
       }
       tc_fence_before();

@@ -78,7 +78,9 @@ def compare_with_golden(preds, g, stride, tol_dense, tol_pose_deg, tol_small=Non
 SMALL_REPORT_KEYS = ("cam_trans", "camera_poses", "intrinsics", "metric_scaling_factor")
 # quantities that contain the predicted camera pose (world-frame points, pose matrices): their error
 # is dominated by the pose head's amplification of bf16 trunk noise, see DESIGN.md "Parity"
-POSE_DEPENDENT_KEYS = ("pts3d", "cam_trans", "camera_poses", "cam_quats_deg")
+# "intrinsics" is a least-squares fit through ~50x50 ray samples (fewer on small images): it amplifies
+# ray noise the same way, in both paths
+POSE_DEPENDENT_KEYS = ("pts3d", "cam_trans", "camera_poses", "cam_quats_deg", "intrinsics")
 
 
 def out_of_tolerance(report, tol_dense, tol_pose_deg, tol_small=None, min_mask_agree=0.0, yardstick=None,

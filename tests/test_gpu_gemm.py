@@ -49,7 +49,8 @@ def test_gemm(M, N, K, act, use_res):
     ref = _ref(A, B, bias, gamma, res, act)
     e32 = g.rel(of, ref)
     e16 = g.rel(ob.float(), ref)
-    assert e32 < 2e-5, f"fp32 output rel-L2 {e32}"
+    # GELU is evaluated as x*sigmoid(2u), erf ~ tanh(u) (|error| <= 2.6e-5 absolute, gemm.cuh)
+    assert e32 < (1e-4 if act == 1 else 2e-5), f"fp32 output rel-L2 {e32}"
     assert e16 < 4e-3, f"bf16 output rel-L2 {e16}"
     # in-place residual update (res aliases out) as used for the residual stream
     if use_res:
