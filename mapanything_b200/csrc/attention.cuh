@@ -6,24 +6,30 @@
 // [tokens, 3*D] (q | k | v, each heads x 64: the layout `reshape(B,N,3,H,hd)` implies), O is
 // written as [tokens, D] (= `x.transpose(1,2).reshape(B,N,C)`).
 //
-// One CTA = one (sequence, head, 128-query tile).  warp0: TMA loader (Q once, K/V rings),
-// warp1: MMA issuer, warps 2..5: softmax (thread = query row).
-//   S_j = Q K_j^T           SS MMA  128x128x64 -> TMEM S[j&1]
-//   P_j = exp2(...)         softmax warps, bf16, written back over S[j&1] (TMEM)
-//   O_j = P_j V_j           TS MMA  128x64x128 (A from TMEM, V MN-major from smem) -> TMEM O[j&1]
-//   O   = O*alpha_j + O_j   accumulated in registers by the softmax warps (no TMEM read-modify-write)
+// One CTA = one (sequence, head, 256-query tile) = two 128-query tiles A and B that ping-pong on
+// the tensor core while sharing every K/V tile in shared memory:
+//   warp0      TMA loader (Q_A, Q_B once; 4-stage K and V rings)
+//   warp1      MMA issuer (one elected thread)
+//   warps 2-5  softmax of tile A, warps 6-9 softmax of tile B (thread = one query row)
+//   S_t(j) = Q_t K_j^T      SS MMA 128x128x64 -> TMEM S_t                       (t = A, B)
+//   P_t(j) = exp2(...)      softmax warps, bf16, written over the first 64 columns of S_t
+//   O_t(j) = P_t(j) V_j     TS MMA 128x64x128 (A operand from TMEM, V MN-major from smem) -> O_t[j&1]
+//   O_t    = O_t*alpha + O_t(j)   accumulated in registers by the softmax warps
+// While the softmax warps of A work on S_A(j), the tensor core runs P_B V and the next Q_B K^T, and
+// vice versa, so neither the exp-bound softmax nor the MMAs sit on the other's critical path.
 #pragma once
 #include "common.cuh"
 
 namespace mab {
 
-constexpr int ATT_BQ = 128;
+constexpr int ATT_BQ = 128;    // rows of one Q tile (one UMMA M)
+constexpr int ATT_QT = 2;      // Q tiles per CTA
 constexpr int ATT_BKV = 128;
 constexpr int ATT_D = 64;
 constexpr int ATT_KV_STAGES = 4;
-constexpr int ATT_THREADS = 192;
+constexpr int ATT_THREADS = 64 + ATT_QT * 128;
 constexpr int ATT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: Q, K and V tiles alike
-constexpr int ATT_SMEM_BYTES = (1 + 2 * ATT_KV_STAGES) * ATT_TILE_BYTES + 512 + 1024;
+constexpr int ATT_SMEM_BYTES = (ATT_QT + 2 * ATT_KV_STAGES) * ATT_TILE_BYTES + 512 + 1024;
 
 struct AttnParams {
   int num_seqs, heads;
@@ -43,32 +49,64 @@ struct AttnParams {
   int carry_out;                    // 1: store the state, skip the normalised bf16 output
 };
 
+// packed fp32x2 helpers (FFMA2 / FADD2 on sm_100a) and the 3-input max (FMNMX3)
+__device__ __forceinline__ uint64_t pack_f2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack_f2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t add_f2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+__device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
-  uint8_t* sQ = smem;
-  uint8_t* sK = smem + ATT_TILE_BYTES;
-  uint8_t* sV = sK + ATT_KV_STAGES * ATT_TILE_BYTES;
+  uint8_t* sQ = smem;                                   // [QT] tiles
+  uint8_t* sK = smem + ATT_QT * ATT_TILE_BYTES;         // [KS] tiles
+  uint8_t* sV = sK + ATT_KV_STAGES * ATT_TILE_BYTES;    // [KS] tiles
   uint64_t* bars = reinterpret_cast<uint64_t*>(sV + ATT_KV_STAGES * ATT_TILE_BYTES);
   uint64_t* q_full = bars;                         // [1]
   uint64_t* k_full = bars + 1;                     // [KS]
   uint64_t* k_empty = k_full + ATT_KV_STAGES;      // [KS]
   uint64_t* v_full = k_empty + ATT_KV_STAGES;      // [KS]
   uint64_t* v_empty = v_full + ATT_KV_STAGES;      // [KS]
-  uint64_t* s_full = v_empty + ATT_KV_STAGES;      // [2]
-  uint64_t* p_full = s_full + 2;                   // [2]
-  uint64_t* o_full = p_full + 2;                   // [2]
-  uint64_t* o_empty = o_full + 2;                  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2);
+  uint64_t* s_full = v_empty + ATT_KV_STAGES;      // [QT]      S_t(j) is in TMEM
+  uint64_t* p_full = s_full + ATT_QT;              // [QT]      P_t(j) is in TMEM
+  uint64_t* o_full = p_full + ATT_QT;              // [QT][2]   O_t(j) is in TMEM buffer j&1
+  uint64_t* o_empty = o_full + 2 * ATT_QT;         // [QT][2]   ... and has been folded into registers
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2 * ATT_QT);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q_tile = blockIdx.x, head = blockIdx.y, seq = blockIdx.z;
-  const int q_row0 = seq * p.q_seq_stride + q_tile * ATT_BQ;
+  const int q_row0 = seq * p.q_seq_stride + q_tile * (ATT_QT * ATT_BQ);
   const int kv_row0 = seq * p.kv_seq_stride;
   const int nkv = (p.kv_len + ATT_BKV - 1) / ATT_BKV;
+  // the second Q tile of the last CTA of a sequence may hold no query at all: skip it entirely
+  const int ntile = (q_tile * (ATT_QT * ATT_BQ) + ATT_BQ < p.q_len) ? 2 : 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQ);
@@ -81,11 +119,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       mbar_init(&v_full[s], 1);
       mbar_init(&v_empty[s], 1);
     }
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(&s_full[s], 1);
-      mbar_init(&p_full[s], 4);
-      mbar_init(&o_full[s], 1);
-      mbar_init(&o_empty[s], 4);
+    for (int t = 0; t < ATT_QT; ++t) {
+      mbar_init(&s_full[t], 1);
+      mbar_init(&p_full[t], 4);  // one arrive per softmax warp of the tile
+      for (int b = 0; b < 2; ++b) {
+        mbar_init(&o_full[t * 2 + b], 1);
+        mbar_init(&o_empty[t * 2 + b], 4);
+      }
     }
     fence_barrier_init();
   }
@@ -94,14 +134,17 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t TM_S = tmem_base;         // S0 @ +0, S1 @ +128 ; P_j overlays the first 64 cols
-  const uint32_t TM_O = tmem_base + 256;   // O0 @ +256, O1 @ +320
+  // TMEM columns: S_A @0, S_B @128 (P_t overlays the first 64 columns of S_t),
+  //               O_A[0] @256, O_A[1] @320, O_B[0] @384, O_B[1] @448
+  auto TM_S = [&](int t) { return tmem_base + t * 128; };
+  auto TM_O = [&](int t, int b) { return tmem_base + 256 + t * 128 + b * 64; };
 
   if (warp == 0) {
     // ===================================== loader =========================================
     if (lane == 0) {
-      mbar_arrive_expect_tx(q_full, ATT_TILE_BYTES);
-      tma_load_2d(sQ, &tmQ, q_full, p.q_col0 + head * ATT_D, q_row0);
+      mbar_arrive_expect_tx(q_full, ntile * ATT_TILE_BYTES);
+      for (int t = 0; t < ntile; ++t)
+        tma_load_2d(sQ + t * ATT_TILE_BYTES, &tmQ, q_full, p.q_col0 + head * ATT_D, q_row0 + t * ATT_BQ);
       for (int j = 0; j < nkv; ++j) {
         const int st = j % ATT_KV_STAGES;
         const uint32_t ph = (j / ATT_KV_STAGES) & 1;
@@ -119,155 +162,194 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     // ===================================== MMA issuer =====================================
     constexpr uint32_t IDESC_QK = make_idesc_bf16(ATT_BQ, ATT_BKV, 0, 0);
     constexpr uint32_t IDESC_PV = make_idesc_bf16(ATT_BQ, ATT_D, 0, 1);  // B (=V) is MN-major
-    auto issue_qk = [&](int j) {
-      const int st = j % ATT_KV_STAGES;
-      mbar_wait(&k_full[st], (j / ATT_KV_STAGES) & 1);
-      tc_fence_after();
+    auto issue_qk = [&](int t, int j) {  // S_t(j) = Q_t K_j^T ; overwrites P_t(j-1): issue after PV_t(j-1)
       if (lane == 0) {
-        const uint32_t a = smem_u32(sQ), b = smem_u32(sK + st * ATT_TILE_BYTES);
+        const int st = j % ATT_KV_STAGES;
+        const uint32_t a = smem_u32(sQ + t * ATT_TILE_BYTES), b = smem_u32(sK + st * ATT_TILE_BYTES);
 #pragma unroll
         for (int k = 0; k < ATT_D / 16; ++k)
-          umma_ss(TM_S + (j & 1) * 128, make_sw128_desc(a + k * 32), make_sw128_desc(b + k * 32),
-                  IDESC_QK, k != 0);
-        umma_commit(&k_empty[st]);
-        umma_commit(&s_full[j & 1]);
+          umma_ss(TM_S(t), make_sw128_desc(a + k * 32), make_sw128_desc(b + k * 32), IDESC_QK, k != 0);
+        umma_commit(&s_full[t]);
+        if (t == ntile - 1) umma_commit(&k_empty[st]);
       }
       __syncwarp();
     };
     mbar_wait(q_full, 0);
-    issue_qk(0);
-    if (nkv > 1) issue_qk(1);
+    mbar_wait(&k_full[0], 0);
+    tc_fence_after();
+    for (int t = 0; t < ntile; ++t) issue_qk(t, 0);
     for (int j = 0; j < nkv; ++j) {
       const int st = j % ATT_KV_STAGES;
       const int b = j & 1;
       const uint32_t use = (j >> 1) & 1;
-      mbar_wait(&p_full[b], use);          // P_j is in TMEM
       mbar_wait(&v_full[st], (j / ATT_KV_STAGES) & 1);
-      mbar_wait(&o_empty[b], use ^ 1);     // O_{j-2} has been consumed
-      tc_fence_after();
-      if (lane == 0) {
-        const uint32_t vb = smem_u32(sV + st * ATT_TILE_BYTES);
+      for (int t = 0; t < ntile; ++t) {
+        mbar_wait(&p_full[t], j & 1);                 // P_t(j) is in TMEM
+        mbar_wait(&o_empty[t * 2 + b], use ^ 1);      // O_t(j-2) has been consumed
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t vb = smem_u32(sV + st * ATT_TILE_BYTES);
 #pragma unroll
-        for (int k = 0; k < ATT_BKV / 16; ++k)
-          umma_ts(TM_O + b * 64, TM_S + b * 128 + k * 8, make_sw128_desc(vb + k * 2048, 1024, 1024),
-                  IDESC_PV, k != 0);
-        umma_commit(&v_empty[st]);
-        umma_commit(&o_full[b]);
+          for (int k = 0; k < ATT_BKV / 16; ++k)
+            umma_ts(TM_O(t, b), TM_S(t) + k * 8, make_sw128_desc(vb + k * 2048, 1024, 1024), IDESC_PV,
+                    k != 0);
+          umma_commit(&o_full[t * 2 + b]);
+          if (t == ntile - 1) umma_commit(&v_empty[st]);
+        }
+        __syncwarp();
+        if (j + 1 < nkv) {
+          if (t == 0) {
+            mbar_wait(&k_full[(j + 1) % ATT_KV_STAGES], ((j + 1) / ATT_KV_STAGES) & 1);
+            tc_fence_after();
+          }
+          issue_qk(t, j + 1);
+        }
       }
-      __syncwarp();
-      if (j + 2 < nkv) issue_qk(j + 2);    // overwrites S[b] (and P_j) after PV(j) in issue order
     }
   } else {
     // ===================================== softmax ========================================
-    const int q = warp & 3;
+    const int t = (warp - 2) >> 2;                      // Q tile of this warp
+    const int q = warp & 3;                             // TMEM lane quarter (warp id % 4)
     const int row = q * 32 + lane;                      // query row within the tile
     const uint32_t lane_addr = uint32_t(q * 32) << 16;
-    float m_run = -INFINITY, l_run = 0.f, alpha_pending = 1.f;
-    float o_acc[ATT_D];
+    const bool row_ok = q_tile * (ATT_QT * ATT_BQ) + t * ATT_BQ + row < p.q_len;
+    const long long grow = (long long)q_row0 + t * ATT_BQ + row;
+    if (t < ntile) {
+      float m_run = -INFINITY, l_run = 0.f, alpha_pending = 1.f;
+      float o_acc[ATT_D];
 #pragma unroll
-    for (int d = 0; d < ATT_D; ++d) o_acc[d] = 0.f;
-    const bool row_ok = q_tile * ATT_BQ + row < p.q_len;
-    if (p.carry_in && row_ok) {
-      const long long grow = (long long)q_row0 + row;
-      const float2 ml = *reinterpret_cast<const float2*>(p.carry_ml + (grow * p.heads + head) * 2);
-      m_run = ml.x; l_run = ml.y;
-      const float4* src = reinterpret_cast<const float4*>(p.carry_o + grow * p.ldo + head * ATT_D);
+      for (int d = 0; d < ATT_D; ++d) o_acc[d] = 0.f;
+      if (p.carry_in && row_ok) {
+        const float2 ml = *reinterpret_cast<const float2*>(p.carry_ml + (grow * p.heads + head) * 2);
+        m_run = ml.x; l_run = ml.y;
+        const float4* src = reinterpret_cast<const float4*>(p.carry_o + grow * p.ldo + head * ATT_D);
 #pragma unroll
-      for (int d = 0; d < ATT_D / 4; ++d) {
-        const float4 v = src[d];
-        o_acc[4 * d] = v.x; o_acc[4 * d + 1] = v.y; o_acc[4 * d + 2] = v.z; o_acc[4 * d + 3] = v.w;
-      }
-    }
-
-    auto consume_o = [&](int j, float alpha) {
-      const int b = j & 1;
-      mbar_wait(&o_full[b], (j >> 1) & 1);
-      tc_fence_after();
-      uint32_t v0[32], v1[32];
-      MAB_TMEM_LD_32(TM_O + lane_addr + b * 64, v0);
-      MAB_TMEM_LD_32(TM_O + lane_addr + b * 64 + 32, v1);
-      tmem_wait_ld();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&o_empty[b]);
-#pragma unroll
-      for (int d = 0; d < 32; ++d) {
-        o_acc[d] = fmaf(o_acc[d], alpha, __uint_as_float(v0[d]));
-        o_acc[d + 32] = fmaf(o_acc[d + 32], alpha, __uint_as_float(v1[d]));
-      }
-    };
-
-    for (int j = 0; j < nkv; ++j) {
-      const int b = j & 1;
-      const uint32_t ts = TM_S + lane_addr + b * 128;
-      const int valid = p.kv_len - j * ATT_BKV;  // columns >= valid are padding / next sequence
-      mbar_wait(&s_full[b], (j >> 1) & 1);
-      tc_fence_after();
-      // pass 1: row max
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        MAB_TMEM_LD_32(ts + c * 32, v);
-        tmem_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(v[i]));
-      }
-      const float m_new = fmaxf(m_run, mx);  // finite: every tile has >= 1 valid column
-      const float alpha = fast_exp2((m_run - m_new) * p.scale_log2e);  // 0 on the first tile
-      const float mb = m_new * p.scale_log2e;
-      float sum = 0.f;
-      // pass 2: P = exp2(S*c - m*c) -> bf16 -> TMEM (overlaying already-consumed S columns)
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32], pk[16];
-        MAB_TMEM_LD_32(ts + c * 32, v);
-        tmem_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float e0 = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -mb));
-          float e1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2e, -mb));
-          if (c * 32 + i >= valid) e0 = 0.f;
-          if (c * 32 + i + 1 >= valid) e1 = 0.f;
-          const uint32_t pr = pack_bf16(e0, e1);
-          // the row sum uses the bf16-rounded probabilities that the PV MMA actually sees
-          sum += bf16_lo(pr) + bf16_hi(pr);
-          pk[i >> 1] = pr;
+        for (int d = 0; d < ATT_D / 4; ++d) {
+          const float4 v = src[d];
+          o_acc[4 * d] = v.x; o_acc[4 * d + 1] = v.y; o_acc[4 * d + 2] = v.z; o_acc[4 * d + 3] = v.w;
         }
-        MAB_TMEM_ST_16(ts + c * 16, pk);
       }
-      tmem_wait_st();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[b]);
-      l_run = l_run * alpha + sum;
-      m_run = m_new;
-      // fold the previous tile's PV product while the tensor core works on this one
-      if (j > 0) consume_o(j - 1, alpha_pending);
-      alpha_pending = alpha;
-    }
-    consume_o(nkv - 1, alpha_pending);
 
-    if (row_ok && p.carry_out) {
-      const long long grow = (long long)q_row0 + row;
-      *reinterpret_cast<float2*>(p.carry_ml + (grow * p.heads + head) * 2) = make_float2(m_run, l_run);
-      float4* dst = reinterpret_cast<float4*>(p.carry_o + grow * p.ldo + head * ATT_D);
+      auto consume_o = [&](int j, float alpha) {  // o_acc = o_acc * alpha + O_t(j)
+        const int b = j & 1;
+        mbar_wait(&o_full[t * 2 + b], (j >> 1) & 1);
+        tc_fence_after();
+        uint32_t v0[32], v1[32];
+        MAB_TMEM_LD_32(TM_O(t, b) + lane_addr, v0);
+        MAB_TMEM_LD_32(TM_O(t, b) + lane_addr + 32, v1);
+        tmem_wait_ld();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&o_empty[t * 2 + b]);
+        const uint64_t a2 = pack_f2(alpha, alpha);
 #pragma unroll
-      for (int d = 0; d < ATT_D / 4; ++d)
-        dst[d] = make_float4(o_acc[4 * d], o_acc[4 * d + 1], o_acc[4 * d + 2], o_acc[4 * d + 3]);
-    } else if (row_ok) {
-      const float inv = 1.0f / l_run;
-      const long long grow = (long long)q_row0 + row;
-      uint4* dst = reinterpret_cast<uint4*>(p.out + grow * p.ldo + head * ATT_D);
+        for (int d = 0; d < 32; d += 2) {
+          unpack_f2(fma_f2(pack_f2(o_acc[d], o_acc[d + 1]), a2,
+                           pack_f2(__uint_as_float(v0[d]), __uint_as_float(v0[d + 1]))),
+                    o_acc[d], o_acc[d + 1]);
+          unpack_f2(fma_f2(pack_f2(o_acc[d + 32], o_acc[d + 33]), a2,
+                           pack_f2(__uint_as_float(v1[d]), __uint_as_float(v1[d + 1]))),
+                    o_acc[d + 32], o_acc[d + 33]);
+        }
+      };
+
+      const uint32_t ts = TM_S(t) + lane_addr;
+      const float sc = p.scale_log2e;
+      const uint64_t sc2 = pack_f2(sc, sc);
+      for (int j = 0; j < nkv; ++j) {
+        const int valid = p.kv_len - j * ATT_BKV;  // columns >= valid are padding / next sequence
+        const bool full = valid >= ATT_BKV;
+        mbar_wait(&s_full[t], j & 1);
+        tc_fence_after();
+        // ---- pass 1: row max (loads of chunk c+1 in flight while chunk c is reduced) ----
+        float mx = -INFINITY;
+        {
+          uint32_t va[32], vb[32];
+          MAB_TMEM_LD_32(ts, va);
+          tmem_wait_ld();
 #pragma unroll
-      for (int d = 0; d < ATT_D; d += 8)
-        dst[d >> 3] = make_uint4(pack_bf16(o_acc[d] * inv, o_acc[d + 1] * inv),
-                                 pack_bf16(o_acc[d + 2] * inv, o_acc[d + 3] * inv),
-                                 pack_bf16(o_acc[d + 4] * inv, o_acc[d + 5] * inv),
-                                 pack_bf16(o_acc[d + 6] * inv, o_acc[d + 7] * inv));
-      if (p.lse)
-        p.lse[grow * p.heads + head] = m_run * p.scale_log2e * 0.6931471805599453f + logf(l_run);
+          for (int c = 0; c < 4; ++c) {
+            uint32_t* cur = (c & 1) ? vb : va;
+            uint32_t* nxt = (c & 1) ? va : vb;
+            if (c < 3) MAB_TMEM_LD_32(ts + (c + 1) * 32, nxt);
+            if (full) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 2)
+                mx = max3(mx, __uint_as_float(cur[i]), __uint_as_float(cur[i + 1]));
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(cur[i]));
+            }
+            if (c < 3) tmem_wait_ld();
+          }
+        }
+        const float m_new = fmaxf(m_run, mx);  // finite: every tile has >= 1 valid column
+        const float alpha = fast_exp2((m_run - m_new) * sc);  // 0 on the first tile without carry
+        const float nmb = -m_new * sc;
+        const uint64_t nmb2 = pack_f2(nmb, nmb);
+        uint64_t sum2 = pack_f2(0.f, 0.f);
+        // ---- pass 2: P = exp2(S*c - m*c) -> bf16 -> TMEM (over already-consumed S columns) ----
+        {
+          uint32_t va[32], vb[32];
+          MAB_TMEM_LD_32(ts, va);
+          tmem_wait_ld();
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t* cur = (c & 1) ? vb : va;
+            uint32_t* nxt = (c & 1) ? va : vb;
+            if (c < 3) MAB_TMEM_LD_32(ts + (c + 1) * 32, nxt);
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              float x0, x1;
+              unpack_f2(fma_f2(pack_f2(__uint_as_float(cur[i]), __uint_as_float(cur[i + 1])), sc2, nmb2),
+                        x0, x1);
+              float e0 = fast_exp2(x0), e1 = fast_exp2(x1);
+              if (!full) {
+                if (c * 32 + i >= valid) e0 = 0.f;
+                if (c * 32 + i + 1 >= valid) e1 = 0.f;
+              }
+              sum2 = add_f2(sum2, pack_f2(e0, e1));
+              pk[i >> 1] = cvt_bf16x2(e0, e1);
+            }
+            // chunk c of P (16 columns) lands on S columns [16c, 16c+16): all read by now
+            if (c < 3) tmem_wait_ld();
+            MAB_TMEM_ST_16(ts + c * 16, pk);
+          }
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[t]);
+        float s0, s1;
+        unpack_f2(sum2, s0, s1);
+        l_run = fmaf(l_run, alpha, s0 + s1);
+        m_run = m_new;
+        // fold the previous tile's PV product while the tensor core works on this one
+        if (j > 0) consume_o(j - 1, alpha_pending);
+        alpha_pending = alpha;
+      }
+      consume_o(nkv - 1, alpha_pending);
+
+      if (row_ok && p.carry_out) {
+        *reinterpret_cast<float2*>(p.carry_ml + (grow * p.heads + head) * 2) = make_float2(m_run, l_run);
+        float4* dst = reinterpret_cast<float4*>(p.carry_o + grow * p.ldo + head * ATT_D);
+#pragma unroll
+        for (int d = 0; d < ATT_D / 4; ++d)
+          dst[d] = make_float4(o_acc[4 * d], o_acc[4 * d + 1], o_acc[4 * d + 2], o_acc[4 * d + 3]);
+      } else if (row_ok) {
+        const float inv = 1.0f / l_run;
+        uint4* dst = reinterpret_cast<uint4*>(p.out + grow * p.ldo + head * ATT_D);
+#pragma unroll
+        for (int d = 0; d < ATT_D; d += 8)
+          dst[d >> 3] = make_uint4(pack_bf16(o_acc[d] * inv, o_acc[d + 1] * inv),
+                                   pack_bf16(o_acc[d + 2] * inv, o_acc[d + 3] * inv),
+                                   pack_bf16(o_acc[d + 4] * inv, o_acc[d + 5] * inv),
+                                   pack_bf16(o_acc[d + 6] * inv, o_acc[d + 7] * inv));
+        if (p.lse)
+          p.lse[grow * p.heads + head] = m_run * p.scale_log2e * 0.6931471805599453f + logf(l_run);
+      }
     }
   }
 

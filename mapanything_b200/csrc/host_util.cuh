@@ -266,7 +266,7 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
                                   ATT_SMEM_BYTES));
     attr_done = true;
   }
-  dim3 grid((q_len + ATT_BQ - 1) / ATT_BQ, heads, num_seqs);
+  dim3 grid((q_len + ATT_QT * ATT_BQ - 1) / (ATT_QT * ATT_BQ), heads, num_seqs);
   ProfScope ps(CAT_ATTENTION, 4.0 * q_len * (double)kv_len * 64.0 * heads * num_seqs, 0.0, st);
   attention_kernel<<<grid, ATT_THREADS, ATT_SMEM_BYTES, st>>>(tQ, tKV, tKV, p);
   MAB_CUDA(cudaGetLastError());
