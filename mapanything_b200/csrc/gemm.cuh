@@ -105,7 +105,11 @@ struct GemmSmem {
   static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +align slack
 };
 
-template <int BN, int STAGES, int MODE, int EPI>
+// CL = thread-block cluster size: CL CTAs work on CL adjacent M tiles of the SAME N tile and share
+// the B (weight) tile: each CTA loads 1/CL of it and TMA-multicasts that slice to all, which cuts
+// the L2 -> SM traffic per CTA and k-block from 48 KB to 16 + 32/CL KB (the SM's L2 port, not the
+// tensor core, bounds a 128x256 tile otherwise).
+template <int BN, int STAGES, int MODE, int EPI, int CL>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             GemmShape shp, GemmEpilogue ep, RegressEpilogue rg) {
@@ -134,7 +138,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     num_m = (shp.M + GEMM_BM - 1) / GEMM_BM;
   }
   const int num_n = (shp.N + BN - 1) / BN;
-  const int num_tiles = num_m * num_n;
+  const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
+  const int num_mg = (num_m + CL - 1) / CL;   // groups of CL adjacent M tiles
+  const int num_tiles = num_mg * num_n;       // per cluster
+  const int cluster_id = blockIdx.x / CL, num_clusters = gridDim.x / CL;
+  // tile index -> (m_blk, n_blk); m_blk may be >= num_m for the last group (loads zero-fill,
+  // stores are predicated off) so that every CTA of a cluster runs the same number of tiles
+  auto tile_m = [&](int tile) { return (tile % num_mg) * CL + crank; };
+  auto tile_n = [&](int tile) { return tile / num_mg; };
   const int num_kb = (MODE == MODE_CONV3) ? 9 * shp.cblocks : (shp.K + GEMM_BK - 1) / GEMM_BK;
   constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128
                                  : (2 * BN <= 256) ? 256 : 512;
@@ -144,7 +155,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tma_prefetch_desc(&tmB);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
+      mbar_init(&empty_bar[s], CL);  // the MMA issuer of every CTA of the cluster releases the slot
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
@@ -154,7 +165,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
-  __syncthreads();
+  if (CL > 1) cluster_sync_all(); else __syncthreads();  // peers' barriers are initialised too
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -163,8 +174,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_blk = tile % num_m, n_blk = tile / num_m;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const int m_blk = tile_m(tile), n_blk = tile_n(tile);
         int cn = 0, cy = 0, cx = 0;
         if (MODE == MODE_CONV3) {
           cx = (m_blk % tiles_x) * CONV_TW;
@@ -183,7 +194,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           } else {
             tma_load_2d(sa, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * GEMM_BM);
           }
-          tma_load_2d(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN);
+          if (CL == 1)
+            tma_load_2d(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN);
+          else  // this CTA's 1/CL of the B tile, to every CTA of the cluster
+            tma_load_2d_mc(sb + crank * (SM::B_BYTES / CL), &tmB, &full_bar[stage], kb * GEMM_BK,
+                           n_blk * BN + crank * (BN / CL), uint16_t((1u << CL) - 1));
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -194,7 +209,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(&tempty_bar[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
@@ -212,7 +227,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             umma_ss(d_tmem, make_sw128_desc(sa + k * 32), make_sw128_desc(sb + k * 32), IDESC,
                     (kb | k) != 0);
           }
-          umma_commit(&empty_bar[stage]);                      // frees the smem slot
+          if (CL == 1) umma_commit(&empty_bar[stage]);         // frees the smem slot
+          else umma_commit_mc(&empty_bar[stage], uint16_t((1u << CL) - 1));  // ... in every CTA
           if (kb == num_kb - 1) umma_commit(&tfull_bar[acc]);  // accumulator complete
         }
         __syncwarp();
@@ -225,10 +241,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int chalf = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
     float* stg = reinterpret_cast<float*>(epi_smem) + (warp - 2) * 32 * 32;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
-      const int m_blk = tile % num_m, n_blk = tile / num_m;
+      const int m_blk = tile_m(tile), n_blk = tile_n(tile);
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (uint32_t(q * 32) << 16) + acc * BN;
@@ -243,7 +259,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       auto row_offset = [&](int r) -> long long {
         if (MODE == MODE_CONV3) {
           const int y = cy + r / CONV_TW, x = cx + r % CONV_TW;
-          if (y >= shp.H || x >= shp.W) return -1;
+          if (y >= shp.H || x >= shp.W || cn >= shp.batch) return -1;
           return ((long long)(cn * shp.H + y) * shp.W + x);
         } else {
           const int m = m_blk * GEMM_BM + r;
@@ -394,7 +410,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 
   tc_fence_before();
-  __syncthreads();
+  // no CTA may exit while a peer can still multicast into its smem or arrive on its barriers
+  if (CL > 1) cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);

@@ -165,11 +165,13 @@ inline int ew_grid(long long total, int block = 256) {
 }
 
 // ---- GEMM / conv launchers ---------------------------------------------------------------------
-template <int BN, int STAGES, int MODE, int EPI>
+constexpr int GEMM_CL = 2;  // CTAs per cluster sharing one multicast B tile (gemm.cuh)
+
+template <int BN, int STAGES, int MODE, int EPI, int CL>
 inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const GemmShape& shp,
                          const GemmEpilogue& ep, const RegressEpilogue& rg, cudaStream_t st) {
   using SM = GemmSmem<BN, STAGES>;
-  auto kern = gemm_kernel<BN, STAGES, MODE, EPI>;
+  auto kern = gemm_kernel<BN, STAGES, MODE, EPI, CL>;
   static bool attr_done = false;
   if (!attr_done) {
     MAB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::TOTAL));
@@ -180,9 +182,10 @@ inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const Gem
     num_m = shp.batch * ((shp.W + CONV_TW - 1) / CONV_TW) * ((shp.H + CONV_TH - 1) / CONV_TH);
   else
     num_m = (shp.M + GEMM_BM - 1) / GEMM_BM;
-  const int tiles = num_m * ((shp.N + BN - 1) / BN);
-  if (tiles <= 0) return 0;
-  const int grid = tiles < sm_count() ? tiles : sm_count();
+  const int groups = ((num_m + CL - 1) / CL) * ((shp.N + BN - 1) / BN);  // tiles per cluster slot
+  if (groups <= 0) return 0;
+  const int max_clusters = sm_count() / CL;
+  const int grid = (groups < max_clusters ? groups : max_clusters) * CL;
   double flops;
   if (MODE == MODE_CONV3)
     flops = 2.0 * shp.batch * shp.H * shp.W * (double)shp.N * 9.0 * shp.creal;
@@ -190,8 +193,19 @@ inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const Gem
     flops = 2.0 * shp.M * (double)shp.N * shp.K;
   const int cat = MODE == MODE_CONV3 ? (EPI == EPI_REGRESS ? CAT_CONV3_REGRESS : CAT_CONV3) : CAT_GEMM;
   ProfScope ps(cat, flops, 0.0, st);
-  kern<<<grid, GEMM_THREADS, SM::TOTAL, st>>>(tA, tB, shp, ep, rg);
-  MAB_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = SM::TOTAL;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  MAB_CUDA(cudaLaunchKernelEx(&cfg, kern, tA, tB, shp, ep, rg));
   return 0;
 }
 
@@ -205,11 +219,11 @@ inline int launch_gemm(const void* A, long long lda, const void* B, long long ld
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM));
   if (N > 128) {
-    MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 256));
-    return launch_gemm_t<256, 4, MODE_GEMM, EPI_GENERIC>(tA, tB, shp, ep, rg, st);
+    MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 256 / GEMM_CL));
+    return launch_gemm_t<256, 4, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
   }
-  MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 128));
-  return launch_gemm_t<128, 6, MODE_GEMM, EPI_GENERIC>(tA, tB, shp, ep, rg, st);
+  MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 128 / GEMM_CL));
+  return launch_gemm_t<128, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
 }
 
 // 3x3/s1/p1 conv, x NHWC bf16 [batch,H,W,C], w packed [Cout, 9*Cpad] (Cpad = ceil64(C))
@@ -221,11 +235,11 @@ inline int launch_conv3(const void* x, int batch, int H, int W, int C, const voi
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, C));
   if (Cout > 128) {
-    MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 256));
-    return launch_gemm_t<256, 4, MODE_CONV3, EPI_GENERIC>(tA, tB, shp, ep, rg, st);
+    MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 256 / GEMM_CL));
+    return launch_gemm_t<256, 4, MODE_CONV3, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
   }
-  MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 128));
-  return launch_gemm_t<128, 6, MODE_CONV3, EPI_GENERIC>(tA, tB, shp, ep, rg, st);
+  MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 128 / GEMM_CL));
+  return launch_gemm_t<128, 6, MODE_CONV3, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
 }
 
 // last conv of the dense head with the fused 1x1 + adaptor + pointmap epilogue (C = Cout = 128)
@@ -235,8 +249,8 @@ inline int launch_conv3_regress(const void* x, int batch, int H, int W, const vo
   GemmShape shp{0, 128, 9 * 2 * 64, batch, H, W, 2, 128};
   GemmEpilogue ep{};
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, 128));
-  MAB_TRY(make_tmap_2d(&tB, w, 128, 9LL * 128, 9LL * 128, 128));
-  return launch_gemm_t<128, 6, MODE_CONV3, EPI_REGRESS>(tA, tB, shp, ep, rg, st);
+  MAB_TRY(make_tmap_2d(&tB, w, 128, 9LL * 128, 9LL * 128, 128 / GEMM_CL));
+  return launch_gemm_t<128, 6, MODE_CONV3, EPI_REGRESS, GEMM_CL>(tA, tB, shp, ep, rg, st);
 }
 
 // ---- attention launcher ------------------------------------------------------------------------
