@@ -96,7 +96,7 @@ __device__ __forceinline__ float gelu_erf(float x) {
 template <int BN, int STAGES>
 struct GemmSmem {
   static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
-  static constexpr int B_BYTES = BN * GEMM_BK * 2;
+  static constexpr int B_BYTES = (BN / 2) * GEMM_BK * 2;  // this CTA's half of the pair's B tile
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   // per epilogue warp: 32 rows x 32 floats, float4 columns XOR-swizzled by (row & 7): both the
   // row-per-lane writes and the 4-rows-per-instruction reads are bank-conflict free
@@ -105,10 +105,110 @@ struct GemmSmem {
   static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +align slack
 };
 
-// CL = thread-block cluster size: CL CTAs work on CL adjacent M tiles of the SAME N tile and share
-// the B (weight) tile: each CTA loads 1/CL of it and TMA-multicasts that slice to all, which cuts
-// the L2 -> SM traffic per CTA and k-block from 48 KB to 16 + 32/CL KB (the SM's L2 port, not the
-// tensor core, bounds a 128x256 tile otherwise).
+// ---- store half of the generic epilogue, specialised on the operands that exist -----------------
+enum {
+  EF_OUTBF16 = 1, EF_OUTF32 = 2, EF_OUTRELU = 4, EF_RESF32 = 8, EF_RES1 = 16, EF_RES2 = 32,
+  EF_GAMMA = 64, EF_GELU = 128, EF_RELU = 256, EF_GENERIC = 1 << 20  // generic: test pointers at run time
+};
+__device__ __forceinline__ int epilogue_flags(const GemmEpilogue& ep) {
+  if (ep.split_n) return EF_GENERIC;
+  return (ep.out_bf16 ? EF_OUTBF16 : 0) | (ep.out_f32 ? EF_OUTF32 : 0) | (ep.out_relu ? EF_OUTRELU : 0) |
+         (ep.res_f32 ? EF_RESF32 : 0) | (ep.res1 ? EF_RES1 : 0) | (ep.res2 ? EF_RES2 : 0) |
+         (ep.gamma ? EF_GAMMA : 0) | (ep.act == ACT_GELU ? EF_GELU : 0) | (ep.act == ACT_RELU ? EF_RELU : 0);
+}
+
+template <int F>
+__device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, uint32_t t_row, float* stg,
+                                                int lane, int sub_r, int sub_c4, const long long (&ro)[8],
+                                                uint32_t row_mask, int c_begin, int c_end, int n0) {
+  constexpr bool G = (F & EF_GENERIC) != 0;
+  const bool has_of = G ? ep.out_f32 != nullptr : (F & EF_OUTF32) != 0;
+  const bool has_ob = G ? ep.out_bf16 != nullptr : (F & EF_OUTBF16) != 0;
+  const bool has_or = G ? ep.out_relu != nullptr : (F & EF_OUTRELU) != 0;
+  const bool has_rf = G ? ep.res_f32 != nullptr : (F & EF_RESF32) != 0;
+  const bool has_r1 = G ? ep.res1 != nullptr : (F & EF_RES1) != 0;
+  const bool has_r2 = G ? ep.res2 != nullptr : (F & EF_RES2) != 0;
+  const bool has_g = G ? ep.gamma != nullptr : (F & EF_GAMMA) != 0;
+  const bool gelu = G ? ep.act == ACT_GELU : (F & EF_GELU) != 0;
+  const bool relu = G ? ep.act == ACT_RELU : (F & EF_RELU) != 0;
+#pragma unroll 1
+  for (int c0 = c_begin; c0 < c_end; c0 += 32) {
+    const int ncol0 = n0 + c0;
+    if (ncol0 >= N) break;
+    uint32_t v[32];
+    MAB_TMEM_LD_32(t_row + c0, v);
+    tmem_wait_ld();
+    __syncwarp();  // previous chunk's readers are done with stg
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<float4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) =
+          make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                      __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+    __syncwarp();
+    const int col = ncol0 + sub_c4 * 4;
+    const uint32_t mask = col < N ? row_mask : 0u;  // N is a multiple of 4 for every layer of the path
+    float4 b4 = make_float4(0, 0, 0, 0), g4 = make_float4(1, 1, 1, 1);
+    if (mask && ep.bias) b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
+    if (mask && has_g) g4 = __ldg(reinterpret_cast<const float4*>(ep.gamma + col));
+    // every load of the chunk is issued before any arithmetic (one or two warps per scheduler have
+    // to cover their own latencies)
+    float4 a[8], rf[8];
+    uint2 r1[8], r2[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = 4 * i + sub_r;
+      a[i] = *reinterpret_cast<const float4*>(stg + r * 32 + ((sub_c4 ^ (r & 7)) << 2));
+      const bool ok = (mask >> i) & 1;
+      const long long off = ro[i] + col;
+      if (has_rf) rf[i] = ok ? *reinterpret_cast<const float4*>(ep.res_f32 + off) : make_float4(0, 0, 0, 0);
+      if (has_r1) r1[i] = ok ? *reinterpret_cast<const uint2*>(ep.res1 + off) : make_uint2(0, 0);
+      if (has_r2) r2[i] = ok ? *reinterpret_cast<const uint2*>(ep.res2 + off) : make_uint2(0, 0);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (!((mask >> i) & 1)) continue;
+      float4 x = a[i];
+      x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
+      if (gelu) {
+        x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
+      } else if (relu) {
+        x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+      }
+      if (has_g) { x.x *= g4.x; x.y *= g4.y; x.z *= g4.z; x.w *= g4.w; }
+      if (has_rf) { x.x += rf[i].x; x.y += rf[i].y; x.z += rf[i].z; x.w += rf[i].w; }
+      if (has_r1) {
+        x.x += bf16_lo(r1[i].x); x.y += bf16_hi(r1[i].x); x.z += bf16_lo(r1[i].y); x.w += bf16_hi(r1[i].y);
+      }
+      if (has_r2) {
+        x.x += bf16_lo(r2[i].x); x.y += bf16_hi(r2[i].x); x.z += bf16_lo(r2[i].y); x.w += bf16_hi(r2[i].y);
+      }
+      const long long off = ro[i] + col;
+      if (has_of) *reinterpret_cast<float4*>(ep.out_f32 + off) = x;
+      if (has_ob) {
+        const uint2 hi = make_uint2(pack_bf16(x.x, x.y), pack_bf16(x.z, x.w));
+        *reinterpret_cast<uint2*>(ep.out_bf16 + off) = hi;
+        if (G && ep.split_n) {
+          const uint2 lo = make_uint2(pack_bf16(x.x - bf16_lo(hi.x), x.y - bf16_hi(hi.x)),
+                                      pack_bf16(x.z - bf16_lo(hi.y), x.w - bf16_hi(hi.y)));
+          *reinterpret_cast<uint2*>(ep.out_bf16 + off + ep.split_n) = lo;
+          *reinterpret_cast<uint2*>(ep.out_bf16 + off + 2 * ep.split_n) = hi;
+        }
+      }
+      if (has_or)
+        *reinterpret_cast<uint2*>(ep.out_relu + off) =
+            make_uint2(pack_bf16(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)),
+                       pack_bf16(fmaxf(x.z, 0.f), fmaxf(x.w, 0.f)));
+    }
+  }
+}
+
+// CTA pairs (cta_group::2): the two CTAs of a cluster (two SMs of one TPC) compute ONE 256 x BN
+// tile.  Each CTA stages its own 128 A rows and its own BN/2 B rows; the leader CTA issues
+// tcgen05.mma.cta_group::2 (UMMA M = 256) which reads both CTAs' shared memory and writes both
+// CTAs' TMEM (128 lanes each).  Per CTA and k-block that is 16 + BN/4 KB of TMA traffic and of
+// operand reads instead of 16 + BN/2 KB: a single-CTA 128x256 tile is bound by shared-memory
+// bandwidth (TMA writes + UMMA operand reads ~192 B/clk against 128 B/clk), not by the tensor core
+// (measured: 44 % of peak in the main loop, independent of L2 traffic).
 template <int BN, int STAGES, int MODE, int EPI, int CL>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -154,18 +254,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], CL);  // the MMA issuer of every CTA of the cluster releases the slot
+      mbar_init(&full_bar[s], 1);   // leader only: its producer arms it with BOTH CTAs' bytes
+      mbar_init(&empty_bar[s], 1);  // the leader's MMA commit arrives in both CTAs
     }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], GEMM_EPI_WARPS);  // one arrive per epilogue warp
+      mbar_init(&tfull_bar[s], 1);                     // the leader's MMA commit arrives in both CTAs
+      mbar_init(&tempty_bar[s], 2 * GEMM_EPI_WARPS);   // leader only: epilogue warps of both CTAs
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  static_assert(CL == 2, "the kernel is written for CTA pairs");
+  if (warp == 1) tmem_alloc2(tmem_slot, TMEM_COLS);
   tc_fence_before();
-  if (CL > 1) cluster_sync_all(); else __syncthreads();  // peers' barriers are initialised too
+  cluster_sync_all();  // peers' barriers are initialised and TMEM is allocated in both CTAs
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -183,29 +284,30 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           cn = m_blk / (tiles_x * tiles_y);
         }
         for (int kb = 0; kb < num_kb; ++kb) {
+#ifdef MAB_GEMM_NOLOAD
+          continue;  // experiment: MMA rate without any operand traffic
+#endif
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * SM::STAGE_BYTES;
           uint8_t* sb = sa + SM::A_BYTES;
-          mbar_arrive_expect_tx(&full_bar[stage], SM::STAGE_BYTES);
+          // both CTAs' loads complete on the LEADER's full barrier, armed once with all the bytes
+          if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * SM::STAGE_BYTES);
+          const uint32_t fb = mapa_u32(smem_u32(&full_bar[stage]), 0);
           if (MODE == MODE_CONV3) {
             const int tap = kb / shp.cblocks, cb = kb - tap * shp.cblocks;
             const int dy = tap / 3 - 1, dx = tap % 3 - 1;
-            tma_load_4d(sa, &tmA, &full_bar[stage], cb * GEMM_BK, cx + dx, cy + dy, cn);
+            tma_load_4d_cg2(sa, &tmA, fb, cb * GEMM_BK, cx + dx, cy + dy, cn);
           } else {
-            tma_load_2d(sa, &tmA, &full_bar[stage], kb * GEMM_BK, m_blk * GEMM_BM);
+            tma_load_2d_cg2(sa, &tmA, fb, kb * GEMM_BK, m_blk * GEMM_BM);
           }
-          if (CL == 1)
-            tma_load_2d(sb, &tmB, &full_bar[stage], kb * GEMM_BK, n_blk * BN);
-          else  // this CTA's 1/CL of the B tile, to every CTA of the cluster
-            tma_load_2d_mc(sb + crank * (SM::B_BYTES / CL), &tmB, &full_bar[stage], kb * GEMM_BK,
-                           n_blk * BN + crank * (BN / CL), uint16_t((1u << CL) - 1));
+          tma_load_2d_cg2(sb, &tmB, fb, kb * GEMM_BK, n_blk * BN + crank * (BN / 2));
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
-  } else if (warp == 1) {
-    // ================================ MMA issuer =============================================
-    constexpr uint32_t IDESC = make_idesc_bf16(GEMM_BM, BN);
+  } else if (warp == 1 && crank == 0) {
+    // ================================ MMA issuer (leader CTA) ================================
+    constexpr uint32_t IDESC = make_idesc_bf16(2 * GEMM_BM, BN);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
@@ -216,7 +318,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * BN;
       for (int kb = 0; kb < num_kb; ++kb) {
+#if !defined(MAB_GEMM_NOLOAD) && !defined(MAB_GEMM_NOWAIT)
         mbar_wait(&full_bar[stage], phase);
+#endif
         tc_fence_after();
         if (lane == 0) {
           const uint32_t sa = smem_u32(smem + stage * SM::STAGE_BYTES);
@@ -224,22 +328,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
           for (int k = 0; k < GEMM_BK / 16; ++k) {
             // +32 bytes per UMMA_K=16 step inside the 128B swizzle atom
-            umma_ss(d_tmem, make_sw128_desc(sa + k * 32), make_sw128_desc(sb + k * 32), IDESC,
-                    (kb | k) != 0);
+            umma_ss2(d_tmem, make_sw128_desc(sa + k * 32), make_sw128_desc(sb + k * 32), IDESC,
+                     (kb | k) != 0);
           }
-          if (CL == 1) umma_commit(&empty_bar[stage]);         // frees the smem slot
-          else umma_commit_mc(&empty_bar[stage], uint16_t((1u << CL) - 1));  // ... in every CTA
-          if (kb == num_kb - 1) umma_commit(&tfull_bar[acc]);  // accumulator complete
+          umma_commit2(&empty_bar[stage]);                      // frees the smem slot in both CTAs
+          if (kb == num_kb - 1) umma_commit2(&tfull_bar[acc]);  // accumulator complete, both CTAs
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
-  } else {
+  } else if (warp >= 2) {
     // ================================ epilogue (warps 2..9) ==================================
     const int q = warp & 3;             // TMEM lane quarter this warp may access (warp id % 4)
     const int chalf = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
     float* stg = reinterpret_cast<float*>(epi_smem) + (warp - 2) * 32 * 32;
+    const int epi_flags = epilogue_flags(ep);
     int it = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
       const int acc = it & 1;
@@ -270,7 +374,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (EPI == EPI_REGRESS) {
         // thread = one output pixel holding all BN(=128) channels of conv2.0 (column-half 1 warps idle)
         if (chalf == 1) {
-          if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+          if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[acc]), 0));
           continue;
         }
         float lg[6];
@@ -290,7 +394,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[acc]), 0));
         const long long pix = row_offset(q * 32 + lane);
         if (pix >= 0) {
           // adaptors.py:432-466 (unit-sphere rays), :256-280 (exp depth), :1044-1073 (1+exp conf),
@@ -331,90 +435,48 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       // ---- generic epilogue: TMEM -> regs -> swizzled smem transpose -> coalesced global ------
       // pass 1 thread = row `lane` of this warp's 32-row slab, 32 columns per chunk
       // pass 2 thread = (row 4*i + lane/8, columns 4*(lane%8)..+3): 8 lanes cover 128 contiguous B
+      // The store half is specialised at compile time on which optional operands exist (EF_*): a
+      // warp's chunk is ~100 instructions instead of ~450 of null-pointer predication.
       const int sub_r = lane >> 3, sub_c4 = lane & 7;
       long long ro[8];
+      uint32_t row_mask = 0;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) ro[i] = row_offset(q * 32 + 4 * i + sub_r);
-#pragma unroll 1
-      for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
-        const int ncol0 = n_blk * BN + c0;
-        if (ncol0 >= shp.N) break;
-        uint32_t v[32];
-        MAB_TMEM_LD_32(t_row + c0, v);
-        tmem_wait_ld();
-        __syncwarp();  // previous chunk's readers are done with stg
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) =
-              make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
-                          __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-        __syncwarp();
-        const int col = ncol0 + sub_c4 * 4;
-        const bool col_ok = col < shp.N;  // N is a multiple of 4 for every layer of the path
-        float4 b4 = make_float4(0, 0, 0, 0), g4 = make_float4(1, 1, 1, 1);
-        if (col_ok && ep.bias) b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
-        if (col_ok && ep.gamma) g4 = __ldg(reinterpret_cast<const float4*>(ep.gamma + col));
-        // all loads of the chunk are issued before any arithmetic (one warp per scheduler has to
-        // cover its own latencies)
-        float4 a[8], rf[8];
-        uint2 r1[8], r2[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = 4 * i + sub_r;
-          a[i] = *reinterpret_cast<const float4*>(stg + r * 32 + ((sub_c4 ^ (r & 7)) << 2));
-          const bool ok = col_ok && ro[i] >= 0;
-          const long long off = ok ? ro[i] * ep.ldo + col : 0;
-          rf[i] = make_float4(0, 0, 0, 0);
-          r1[i] = make_uint2(0, 0);
-          r2[i] = make_uint2(0, 0);
-          if (ok && ep.res_f32) rf[i] = *reinterpret_cast<const float4*>(ep.res_f32 + off);
-          if (ok && ep.res1) r1[i] = *reinterpret_cast<const uint2*>(ep.res1 + off);
-          if (ok && ep.res2) r2[i] = *reinterpret_cast<const uint2*>(ep.res2 + off);
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (!(col_ok && ro[i] >= 0)) continue;
-          float4 x = a[i];
-          x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
-          if (ep.act == ACT_GELU) {
-            x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
-          } else if (ep.act == ACT_RELU) {
-            x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
-          }
-          x.x = fmaf(x.x, g4.x, rf[i].x + bf16_lo(r1[i].x) + bf16_lo(r2[i].x));
-          x.y = fmaf(x.y, g4.y, rf[i].y + bf16_hi(r1[i].x) + bf16_hi(r2[i].x));
-          x.z = fmaf(x.z, g4.z, rf[i].z + bf16_lo(r1[i].y) + bf16_lo(r2[i].y));
-          x.w = fmaf(x.w, g4.w, rf[i].w + bf16_hi(r1[i].y) + bf16_hi(r2[i].y));
-          const long long off = ro[i] * ep.ldo + col;
-          if (ep.out_f32) *reinterpret_cast<float4*>(ep.out_f32 + off) = x;
-          if (ep.out_bf16) {
-            const uint2 hi = make_uint2(pack_bf16(x.x, x.y), pack_bf16(x.z, x.w));
-            *reinterpret_cast<uint2*>(ep.out_bf16 + off) = hi;
-            if (ep.split_n) {
-              const uint2 lo = make_uint2(pack_bf16(x.x - bf16_lo(hi.x), x.y - bf16_hi(hi.x)),
-                                          pack_bf16(x.z - bf16_lo(hi.y), x.w - bf16_hi(hi.y)));
-              *reinterpret_cast<uint2*>(ep.out_bf16 + off + ep.split_n) = lo;
-              *reinterpret_cast<uint2*>(ep.out_bf16 + off + 2 * ep.split_n) = hi;
-            }
-          }
-          if (ep.out_relu)
-            *reinterpret_cast<uint2*>(ep.out_relu + off) =
-                make_uint2(pack_bf16(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)),
-                           pack_bf16(fmaxf(x.z, 0.f), fmaxf(x.w, 0.f)));
-        }
+      for (int i = 0; i < 8; ++i) {
+        ro[i] = row_offset(q * 32 + 4 * i + sub_r);
+        if (ro[i] >= 0) row_mask |= 1u << i;
+        ro[i] = (ro[i] < 0 ? 0 : ro[i]) * ep.ldo;
+      }
+      const int c_begin = chalf * (BN / 2), c_end = (chalf + 1) * (BN / 2);
+      const int n0 = n_blk * BN;
+      switch (epi_flags) {
+#define MAB_EPI_CASE(F) \
+  case F: epilogue_chunks<F>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro, row_mask, c_begin, c_end, n0); break;
+        MAB_EPI_CASE(EF_OUTBF16)
+        MAB_EPI_CASE(EF_OUTBF16 | EF_GELU)
+        MAB_EPI_CASE(EF_OUTBF16 | EF_RELU)
+        MAB_EPI_CASE(EF_OUTF32)
+        MAB_EPI_CASE(EF_OUTF32 | EF_RESF32)
+        MAB_EPI_CASE(EF_OUTF32 | EF_RESF32 | EF_GAMMA)
+        MAB_EPI_CASE(EF_OUTBF16 | EF_OUTRELU)
+        MAB_EPI_CASE(EF_OUTBF16 | EF_RES1)
+        MAB_EPI_CASE(EF_OUTBF16 | EF_RES1 | EF_OUTRELU)
+        MAB_EPI_CASE(EF_OUTBF16 | EF_RES1 | EF_RES2 | EF_OUTRELU)
+        default:
+          epilogue_chunks<EF_GENERIC>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro, row_mask, c_begin, c_end, n0);
+#undef MAB_EPI_CASE
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[acc]), 0));
     }
   }
 
   tc_fence_before();
   // no CTA may exit while a peer can still multicast into its smem or arrive on its barriers
-  if (CL > 1) cluster_sync_all(); else __syncthreads();
+  cluster_sync_all();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    tmem_dealloc2(tmem_base, TMEM_COLS);
   }
 }
 

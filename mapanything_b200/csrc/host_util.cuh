@@ -165,7 +165,7 @@ inline int ew_grid(long long total, int block = 256) {
 }
 
 // ---- GEMM / conv launchers ---------------------------------------------------------------------
-constexpr int GEMM_CL = 2;  // CTAs per cluster sharing one multicast B tile (gemm.cuh)
+constexpr int GEMM_CL = 2;  // CTA pair (cta_group::2): one 256 x BN tile per cluster (gemm.cuh)
 
 template <int BN, int STAGES, int MODE, int EPI, int CL>
 inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const GemmShape& shp,
@@ -220,10 +220,10 @@ inline int launch_gemm(const void* A, long long lda, const void* B, long long ld
   MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM));
   if (N > 128) {
     MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 256 / GEMM_CL));
-    return launch_gemm_t<256, 4, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
+    return launch_gemm_t<256, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
   }
   MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 128 / GEMM_CL));
-  return launch_gemm_t<128, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
+  return launch_gemm_t<128, 8, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
 }
 
 // 3x3/s1/p1 conv, x NHWC bf16 [batch,H,W,C], w packed [Cout, 9*Cpad] (Cpad = ceil64(C))
@@ -236,10 +236,10 @@ inline int launch_conv3(const void* x, int batch, int H, int W, int C, const voi
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, C));
   if (Cout > 128) {
     MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 256 / GEMM_CL));
-    return launch_gemm_t<256, 4, MODE_CONV3, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
+    return launch_gemm_t<256, 6, MODE_CONV3, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
   }
   MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 128 / GEMM_CL));
-  return launch_gemm_t<128, 6, MODE_CONV3, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
+  return launch_gemm_t<128, 8, MODE_CONV3, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
 }
 
 // last conv of the dense head with the fused 1x1 + adaptor + pointmap epilogue (C = Cout = 128)
@@ -250,7 +250,7 @@ inline int launch_conv3_regress(const void* x, int batch, int H, int W, const vo
   GemmEpilogue ep{};
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, 128));
   MAB_TRY(make_tmap_2d(&tB, w, 128, 9LL * 128, 9LL * 128, 128 / GEMM_CL));
-  return launch_gemm_t<128, 6, MODE_CONV3, EPI_REGRESS, GEMM_CL>(tA, tB, shp, ep, rg, st);
+  return launch_gemm_t<128, 8, MODE_CONV3, EPI_REGRESS, GEMM_CL>(tA, tB, shp, ep, rg, st);
 }
 
 // ---- attention launcher ------------------------------------------------------------------------

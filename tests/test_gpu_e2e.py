@@ -61,10 +61,10 @@ def test_infer_matches_reference_golden(name, model, sd_cuda):
                  and k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
     bad = helpers.out_of_tolerance(cam_frame, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97)
     assert not bad, f"camera-frame keys out of absolute tolerance: {bad}"
-    # (2) every key: no further from fp32 than 2x the reference's own bf16 path
+    # (2) every key: no further from fp32 than 3x the reference's own bf16 path
     rest = {k: v for k, v in rep.items() if k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
     bad = helpers.out_of_tolerance(rest, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97,
-                                   yardstick=yard, slack=2.0)
+                                   yardstick=yard, slack=3.0)
     bad += [(k, v) for k, v in rep.items() if k.endswith("non_ambiguous_mask_logits") and v > TOL_MASK_LOGITS]
     assert not bad, f"further from the fp32 reference than the reference's bf16 path: {bad}\nyardstick {yard}"
     p = preds[0]
@@ -96,11 +96,11 @@ def test_forward_raw_matches_oracle(model, synthetic_sd, sd_cuda):
             assert p[k].shape == r[k].shape, k
             e = helpers.rel_l2(p[k].float().cpu().numpy(), r[k].numpy())
             y = max(helpers.rel_l2(a2[k].numpy(), r2[k].numpy()) for a2, r2 in zip(amp, ref))
-            tol = TOL_MASK_LOGITS if k == "non_ambiguous_mask_logits" else max(TOL_DENSE, 2.0 * y)
+            tol = TOL_MASK_LOGITS if k == "non_ambiguous_mask_logits" else max(TOL_DENSE, 3.0 * y)
             assert e < tol, (k, e, y)
         e = helpers.quat_angle_deg(p["cam_quats"].cpu().numpy(), r["cam_quats"].numpy())
         y = max(helpers.quat_angle_deg(a2["cam_quats"].numpy(), r2["cam_quats"].numpy()) for a2, r2 in zip(amp, ref))
-        assert e < max(TOL_POSE_DEG, 2.0 * y), (e, y)
+        assert e < max(TOL_POSE_DEG, 3.0 * y), (e, y)
         agree = float((p["non_ambiguous_mask"].cpu() == r["non_ambiguous_mask"]).float().mean())
         assert agree > 0.98
 
