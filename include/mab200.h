@@ -107,9 +107,18 @@ size_t mab_workspace_bytes(mab_handle* h, int views_local, int views_total, int 
 /* Whole forward on one GPU (views_total == views). */
 int mab_forward(mab_handle* h, const mab_inputs* in, mab_outputs* out, void* workspace,
                 size_t workspace_bytes, void* stream);
+/* inference.py:314-506 for all views of this rank.  workspace: views*H*W*18 + views*8 + 512 bytes. */
 int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs* raw, mab_post_outputs* post,
                     const mab_post_options* opt, void* workspace, size_t workspace_bytes,
                     void* stream);
+
+/* ---- pre-processing of the optional geometric inputs (mapanything/utils/inference.py:222-311) ----
+ * Device pointers, fp32.  K [views,3,3] -> unit rays [views,H,W,3] (geometry.py:186-241);
+ * rays / (|rays| + 1e-8) (inference.py:251-256); z-depth -> depth along the ray (inference.py:263-274). */
+int mab_rays_from_intrinsics(const void* K, int views, int H, int W, void* rays, void* stream);
+int mab_normalize_rays(const void* rays_in, long long pixels, void* rays_out, void* stream);
+int mab_depth_z_to_along_ray(const void* depth_z, const void* rays, long long pixels, void* out,
+                             void* stream);
 
 /* ---- staged forward (view-sharded multi-GPU: the caller exchanges K/V between the stages) ----
  * Rank r holds a contiguous block of the scene's views; the rank that holds view 0 also owns the

@@ -86,11 +86,15 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows_out, int 
 }
 
 // ----------------------------------------------------------------------------------------------
-// Patch im2col for the 14x14/s14 patch-embed conv (patch_embed.py:65-80): fp32 NCHW image ->
-// bf16 [views*h*w, KP] with k = c*196 + ky*14 + kx (the flattening of the conv weight), zero pad
-// to KP.
+// Patch im2col = PixelUnshuffle(14) in token-major form: [views, nch, H, W] (or NHWC) fp32 ->
+// bf16 [views*h*w, KP] with k = c*196 + ky*14 + kx, zero padded to KP.  This is both the
+// flattening of the 14x14/s14 patch-embed conv weight (patch_embed.py:65-80) and the channel
+// order of nn.PixelUnshuffle(14) in DenseRepresentationEncoder (dense_rep_encoder.py:112-114).
+// Optional depth transform (model.py:1021-1137): x / norm[view], then sign(x) * log1p(|x|)
+// (normalize_depth_using_non_zero_pixels + apply_log_to_norm, geometry.py:1594-1626,1737-1750).
 // ----------------------------------------------------------------------------------------------
-__global__ void patch_im2col_kernel(const float* __restrict__ img, int views, int H, int W, int KP,
+__global__ void patch_im2col_kernel(const float* __restrict__ img, int views, int H, int W, int nch,
+                                    int nhwc, int KP, const float* __restrict__ view_norm, int log_mode,
                                     __nv_bfloat16* __restrict__ out) {
   const int h = H / 14, w = W / 14;
   const long long total = (long long)views * h * w * KP;
@@ -99,12 +103,160 @@ __global__ void patch_im2col_kernel(const float* __restrict__ img, int views, in
     const int k = i % KP;
     const long long row = i / KP;
     float val = 0.f;
-    if (k < 588) {
+    if (k < nch * 196) {
       const int c = k / 196, ky = (k % 196) / 14, kx = k % 14;
       const int px = row % w, py = (row / w) % h, v = row / (w * h);
-      val = img[(((long long)v * 3 + c) * H + py * 14 + ky) * W + px * 14 + kx];
+      const int y = py * 14 + ky, x = px * 14 + kx;
+      val = nhwc ? img[(((long long)v * H + y) * W + x) * nch + c]
+                 : img[(((long long)v * nch + c) * H + y) * W + x];
+      if (view_norm) val = val / view_norm[v];
+      if (log_mode) val = copysignf(log1pf(fabsf(val)), val);
     }
     out[i] = __float2bfloat16(val);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// a1 pre-processing (inference.py:222-311), one thread per pixel
+// ----------------------------------------------------------------------------------------------
+// unit rays of a pinhole camera (get_rays_in_camera_frame, geometry.py:186-241): K [views,3,3]
+__global__ void rays_from_intrinsics_kernel(const float* __restrict__ K, int views, int H, int W,
+                                            float* __restrict__ rays) {
+  const long long total = (long long)views * H * W;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int x = i % W, y = (i / W) % H, v = i / ((long long)W * H);
+    const float* k = K + v * 9;
+    const float xx = ((float)x - k[2]) / k[0], yy = ((float)y - k[5]) / k[4];
+    const float n = sqrtf(xx * xx + yy * yy + 1.0f);
+    rays[i * 3 + 0] = xx / n; rays[i * 3 + 1] = yy / n; rays[i * 3 + 2] = 1.0f / n;
+  }
+}
+
+// r / (|r| + 1e-8)   (inference.py:251-256)
+__global__ void normalize_rays_kernel(const float* __restrict__ in, long long npix, float* __restrict__ out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < npix;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float a = in[i * 3], b = in[i * 3 + 1], c = in[i * 3 + 2];
+    const float n = sqrtf(a * a + b * b + c * c) + 1e-8f;
+    out[i * 3] = a / n; out[i * 3 + 1] = b / n; out[i * 3 + 2] = c / n;
+  }
+}
+
+// depth_along_ray = | depth_z * (r / r_z) |   (convert_z_depth_to_depth_along_ray, inference.py:263-274)
+__global__ void depth_z_to_along_ray_kernel(const float* __restrict__ depth_z, const float* __restrict__ rays,
+                                            long long npix, float* __restrict__ out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < npix;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float z = depth_z[i], rz = rays[i * 3 + 2];
+    const float a = z * (rays[i * 3] / rz), b = z * (rays[i * 3 + 1] / rz), c = z * (rz / rz);
+    out[i] = sqrtf(a * a + b * b + c * c);
+  }
+}
+
+// mean of the non-zero (valid > 0) pixels of each view's depth map, clipped to >= 1e-8
+// (normalize_depth_using_non_zero_pixels, geometry.py:1594-1626).  One block per view.
+__global__ void depth_norm_kernel(const float* __restrict__ depth, long long npix, float* __restrict__ norm) {
+  const int v = blockIdx.x;
+  const float* d = depth + (long long)v * npix;
+  float s = 0.f, n = 0.f;
+  for (long long i = threadIdx.x; i < npix; i += blockDim.x) {
+    const float x = d[i];
+    if (x > 0.f) { s += x; n += 1.f; }
+  }
+  __shared__ float ss[256], sn[256];
+  ss[threadIdx.x] = s; sn[threadIdx.x] = n;
+  __syncthreads();
+  for (int k = blockDim.x / 2; k > 0; k >>= 1) {
+    if (threadIdx.x < k) { ss[threadIdx.x] += ss[threadIdx.x + k]; sn[threadIdx.x] += sn[threadIdx.x + k]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) norm[v] = fmaxf(ss[0] / (sn[0] + 1e-8f), 1e-8f);
+}
+
+// dst[row, :] (+)= scale[view(row)] * src[row, :]   (token-major [views*T, C] fp32; model.py:968,1137)
+__global__ void accum_masked_rows_kernel(float* __restrict__ dst, const float* __restrict__ src,
+                                         const float* __restrict__ scale, int T, int C, long long total4,
+                                         int first) {
+  const int c4n = C / 4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / c4n;
+    const float m = scale[row / T];
+    float4 s4 = reinterpret_cast<const float4*>(src)[i];
+    float4 d4 = first ? make_float4(0, 0, 0, 0) : reinterpret_cast<float4*>(dst)[i];
+    d4.x += m * s4.x; d4.y += m * s4.y; d4.z += m * s4.z; d4.w += m * s4.w;
+    reinterpret_cast<float4*>(dst)[i] = d4;
+  }
+}
+
+// small per-view preparation of the geometric-input MLP encoders' inputs and masks
+// (model.py:1141-1167,1170-1289): one thread per view.
+//   in_scale[v]  = log(depth_norm[v] + 1e-8)          m_scale[v] = depth_mask & depth_metric_mask
+//   in_trans[v]  = trans[v] / pose_norm               m_cam[v]   = cam_mask
+//   in_tscale[v] = log(pose_norm + 1e-8)              m_tscale[v]= cam_mask & pose_metric_mask
+__global__ void geo_prepare_kernel(int views, const float* __restrict__ depth_norm,
+                                   const float* __restrict__ trans, float pose_norm,
+                                   const unsigned char* __restrict__ ray_mask,
+                                   const unsigned char* __restrict__ depth_mask,
+                                   const unsigned char* __restrict__ cam_mask,
+                                   const unsigned char* __restrict__ depth_metric,
+                                   const unsigned char* __restrict__ pose_metric,
+                                   float* __restrict__ in_scale, float* __restrict__ in_trans,
+                                   float* __restrict__ in_tscale, float* __restrict__ m_ray,
+                                   float* __restrict__ m_depth, float* __restrict__ m_scale,
+                                   float* __restrict__ m_cam, float* __restrict__ m_tscale) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= views) return;
+  const bool dm = depth_mask && depth_mask[v], cm = cam_mask && cam_mask[v];
+  m_ray[v] = (ray_mask && ray_mask[v]) ? 1.f : 0.f;
+  m_depth[v] = dm ? 1.f : 0.f;
+  m_scale[v] = (dm && depth_metric && depth_metric[v]) ? 1.f : 0.f;
+  m_cam[v] = cm ? 1.f : 0.f;
+  m_tscale[v] = (cm && pose_metric && pose_metric[v]) ? 1.f : 0.f;
+  in_scale[v] = depth_norm ? logf(depth_norm[v] + 1e-8f) : 0.f;
+  const float pn = fmaxf(pose_norm, 1e-8f);
+  for (int k = 0; k < 3; ++k) in_trans[v * 3 + k] = trans ? trans[v * 3 + k] / pn : 0.f;
+  in_tscale[v] = logf(pn + 1e-8f);
+}
+
+// fused = LayerNorm(enc[row] + dense[row] + vec[view(row)])  -> bf16   (model.py:1423-1431)
+// one warp per row, C = 128 * VPL
+template <int VPL>
+__global__ void fuse_norm_kernel(const float* __restrict__ enc, const float* __restrict__ dense,
+                                 const float* __restrict__ vec, int rows, int T,
+                                 const float* __restrict__ w, const float* __restrict__ b, float eps,
+                                 __nv_bfloat16* __restrict__ out) {
+  constexpr int C = 128 * VPL;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const float4* er = reinterpret_cast<const float4*>(enc + (long long)warp * C);
+  const float4* dr = dense ? reinterpret_cast<const float4*>(dense + (long long)warp * C) : nullptr;
+  const float4* vr = vec ? reinterpret_cast<const float4*>(vec + (long long)(warp / T) * C) : nullptr;
+  float4 v[VPL];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    v[i] = er[lane + 32 * i];
+    if (dr) { const float4 d = dr[lane + 32 * i]; v[i].x += d.x; v[i].y += d.y; v[i].z += d.z; v[i].w += d.w; }
+    if (vr) { const float4 d = vr[lane + 32 * i]; v[i].x += d.x; v[i].y += d.y; v[i].z += d.z; v[i].w += d.w; }
+    s += v[i].x + v[i].y + v[i].z + v[i].w;
+  }
+  const float mean = warp_sum(s) * (1.0f / C);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const float a = v[i].x - mean, b_ = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+    q += a * a + b_ * b_ + c * c + d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(q) * (1.0f / C) + eps);
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const float4 g = __ldg(reinterpret_cast<const float4*>(w) + lane + 32 * i);
+    const float4 h = __ldg(reinterpret_cast<const float4*>(b) + lane + 32 * i);
+    reinterpret_cast<uint2*>(out + (long long)warp * C)[lane + 32 * i] =
+        make_uint2(pack_bf16((v[i].x - mean) * rstd * g.x + h.x, (v[i].y - mean) * rstd * g.y + h.y),
+                   pack_bf16((v[i].z - mean) * rstd * g.z + h.z, (v[i].w - mean) * rstd * g.w + h.w));
   }
 }
 

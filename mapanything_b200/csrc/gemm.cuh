@@ -43,6 +43,8 @@ struct GemmEpilogue {
   int split_n;                   // > 0: out_bf16 row = [hi | lo | hi] with hi at col, lo at col +
                                  // split_n, hi again at col + 2*split_n (bf16x3 operand of the next
                                  // GEMM: x ~ hi + lo, |x - hi - lo| <= 2^-17 |x|)
+  int act_post;                  // 1: the activation is applied AFTER the residual adds
+                                 // (ResidualBlock: act(conv2(.) + shortcut), dense_rep_encoder.py:31-52)
 };
 
 // Fused tail of the dense head: ReLU -> 1x1 conv 128->6 -> adaptor -> pointmap (EPI_REGRESS)
@@ -111,7 +113,7 @@ enum {
   EF_GAMMA = 64, EF_GELU = 128, EF_RELU = 256, EF_GENERIC = 1 << 20  // generic: test pointers at run time
 };
 __device__ __forceinline__ int epilogue_flags(const GemmEpilogue& ep) {
-  if (ep.split_n) return EF_GENERIC;
+  if (ep.split_n || ep.act_post) return EF_GENERIC;
   return (ep.out_bf16 ? EF_OUTBF16 : 0) | (ep.out_f32 ? EF_OUTF32 : 0) | (ep.out_relu ? EF_OUTRELU : 0) |
          (ep.res_f32 ? EF_RESF32 : 0) | (ep.res1 ? EF_RES1 : 0) | (ep.res2 ? EF_RES2 : 0) |
          (ep.gamma ? EF_GAMMA : 0) | (ep.act == ACT_GELU ? EF_GELU : 0) | (ep.act == ACT_RELU ? EF_RELU : 0);
@@ -169,9 +171,10 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
       if (!((mask >> i) & 1)) continue;
       float4 x = a[i];
       x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
-      if (gelu) {
+      const bool post = G && ep.act_post;
+      if (gelu && !post) {
         x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
-      } else if (relu) {
+      } else if (relu && !post) {
         x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
       }
       if (has_g) { x.x *= g4.x; x.y *= g4.y; x.z *= g4.z; x.w *= g4.w; }
@@ -181,6 +184,11 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
       }
       if (has_r2) {
         x.x += bf16_lo(r2[i].x); x.y += bf16_hi(r2[i].x); x.z += bf16_lo(r2[i].y); x.w += bf16_hi(r2[i].y);
+      }
+      if (post && gelu) {
+        x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
+      } else if (post && relu) {
+        x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
       }
       const long long off = ro[i] + col;
       if (has_of) *reinterpret_cast<float4*>(ep.out_f32 + off) = x;

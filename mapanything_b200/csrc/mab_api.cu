@@ -106,6 +106,37 @@ extern "C" int mab_prof_query(int cat, long long* launches, double* ms, double* 
   return 0;
 }
 
+// ---- a1 pre-processing entry points (inference.py:222-311) ---------------------------------------
+extern "C" int mab_rays_from_intrinsics(const void* K, int views, int H, int W, void* rays, void* stream) {
+  MAB_ARG(K && rays && views > 0 && H > 0 && W > 0, "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, st,
+             rays_from_intrinsics_kernel<<<ew_grid((long long)views * H * W), 256, 0, st>>>(
+                 (const float*)K, views, H, W, (float*)rays));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int mab_normalize_rays(const void* rays_in, long long pixels, void* rays_out, void* stream) {
+  MAB_ARG(rays_in && rays_out && pixels > 0, "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, st,
+             normalize_rays_kernel<<<ew_grid(pixels), 256, 0, st>>>((const float*)rays_in, pixels,
+                                                                    (float*)rays_out));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int mab_depth_z_to_along_ray(const void* depth_z, const void* rays, long long pixels, void* out,
+                                        void* stream) {
+  MAB_ARG(depth_z && rays && out && pixels > 0, "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, st,
+             depth_z_to_along_ray_kernel<<<ew_grid(pixels), 256, 0, st>>>((const float*)depth_z,
+                                                                          (const float*)rays, pixels,
+                                                                          (float*)out));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int mab_layernorm(const float* x, int rows, int C, const float* w, const float* b,
                              float eps, void* out_bf16, float* out_f32, void* stream) {
   return launch_layernorm(x, rows, C, rows > 0 ? rows : 1, rows > 0 ? rows : 1, 0, w, b, nullptr,
@@ -255,7 +286,7 @@ struct Plan {  // every workspace pointer of one forward
   long long Lenc = 0, L = 0;  // encoder rows V*(T+1); info-sharing rows V*T (+1)
   // encoder
   bf16* im2col; float* patch; float* pos; float* xs; bf16* ln; bf16* qkv; bf16* att; bf16* hid;
-  float* enc_out; bf16* fused;
+  float* enc_out; bf16* fused; float* geo_sum; float* geo_vec; float* geo_small;
   // info sharing
   float* ys; bf16* tap[2]; bf16* fin; float* scale_tok; float* carry_o; float* carry_ml;
   // heads (small)
@@ -312,6 +343,9 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
   p.hid = b.take<bf16>(p.Lenc * 4 * D);
   p.enc_out = b.take<float>(VT * D);
   p.fused = b.take<bf16>((VT + 1) * D);
+  p.geo_sum = b.take<float>(VT * D);          // sum of the masked dense geometric features
+  p.geo_vec = b.take<float>((long long)V * D); // sum of the masked per-view (global) features
+  p.geo_small = b.take<float>((long long)V * 4096 + 64);  // MLP scratch + masks + scalar inputs
   p.ys = b.take<float>((VT + 1) * A);
   p.tap[0] = b.take<bf16>(VT * A);
   p.tap[1] = b.take<bf16>(VT * A);
@@ -503,6 +537,19 @@ extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
   for (int b = 0; b < 2; ++b)
     for (int k = 1; k <= 3; ++k)
       MAB_TRY(pack_linear_split(h, "pose_head.res_conv." + std::to_string(b) + ".res_conv" + std::to_string(k) + ".weight", st));
+  // geometric-input encoders (model.py:176-210): dense conv stacks as bf16 implicit GEMMs
+  for (const char* enc : {"ray_dirs_encoder", "depth_encoder"}) {
+    const std::string e = enc;
+    if (!h->F(e + ".conv_in.weight")) continue;
+    MAB_TRY(pack_conv3(h, e + ".conv_in.weight", st));
+    for (int i = 0; i < 2; ++i) {
+      const std::string r = e + ".encoder." + std::to_string(i);
+      MAB_TRY(pack_conv3(h, r + ".conv1.weight", st));
+      MAB_TRY(pack_conv3(h, r + ".conv2.weight", st));
+      MAB_TRY(pack_linear(h, r + ".shortcut.weight", i == 0 ? 640 : 0, st));
+    }
+    MAB_TRY(pack_linear(h, e + ".encoder.2.weight", 0, st));
+  }
   // required fp32 tensors that are used as-is
   for (const char* k : {"encoder.model.cls_token", "encoder.model.pos_embed", "encoder.model.norm.weight",
                         "fusion_norm_layer.weight", "scale_token", "info_sharing.view_pos_table",
@@ -622,6 +669,149 @@ int block_tail(Ctx& c, const std::string& p, float* x, long long rows, int D, bf
 
 }  // namespace
 
+namespace {
+
+// DenseRepresentationEncoder (dense_rep_encoder.py:234-287) on the token-major PixelUnshuffle of
+// the input: conv3x3 -> 2 x ResidualBlock(conv3x3, GELU, conv3x3, + 1x1 shortcut, GELU) -> conv1x1
+// -> LayerNorm; the result is accumulated into p.geo_sum scaled by the per-view mask.
+int dense_rep_encode(Ctx& c, const std::string& e, const bf16* unshuffled, int cin_pad, const float* mask,
+                     bool first, Bump& scratch) {
+  mab_handle* h = c.h;
+  Plan& p = h->plan;
+  const int V = p.V, hh = p.h, ww = p.w;
+  const long long VT = (long long)V * p.T;
+  bf16* a0 = scratch.take<bf16>(VT * 640);   // conv_in output, 588 channels padded to 640
+  bf16* sc0 = scratch.take<bf16>(VT * 768);
+  bf16* b0 = scratch.take<bf16>(VT * 768);
+  bf16* x1 = scratch.take<bf16>(VT * 768);
+  bf16* sc1 = scratch.take<bf16>(VT * 1024);
+  bf16* b1 = scratch.take<bf16>(VT * 1024);
+  bf16* x2 = scratch.take<bf16>(VT * 1024);
+  float* y = scratch.take<float>(VT * 1024);
+  MAB_CUDA(cudaMemsetAsync(a0, 0, (size_t)VT * 640 * sizeof(bf16), c.st));  // zero the 52 pad channels
+  GemmEpilogue ep{};
+  ep.bias = h->F(e + ".conv_in.bias"); ep.out_bf16 = a0; ep.ldo = 640; ep.act = ACT_NONE;
+  MAB_TRY(launch_conv3(unshuffled, V, hh, ww, cin_pad, h->P(e + ".conv_in.weight"), 588, ep, c.st));
+  const bf16* x = a0;
+  int cin = 640;
+  bf16* scb[2] = {sc0, sc1}; bf16* bb[2] = {b0, b1}; bf16* xo[2] = {x1, x2};
+  const int cout[2] = {768, 1024};
+  for (int i = 0; i < 2; ++i) {
+    const std::string r = e + ".encoder." + std::to_string(i);
+    MAB_TRY(c.linear(x, (int)VT, cin, cin, r + ".shortcut.weight", cout[i], h->F(r + ".shortcut.bias"),
+                     ACT_NONE, nullptr, nullptr, nullptr, scb[i], nullptr, cin));
+    MAB_TRY(c.conv3(x, V, hh, ww, cin, r + ".conv1.weight", cout[i], h->F(r + ".conv1.bias"), ACT_GELU,
+                    nullptr, nullptr, bb[i], nullptr));
+    GemmEpilogue e2{};
+    e2.bias = h->F(r + ".conv2.bias"); e2.res1 = scb[i]; e2.out_bf16 = xo[i]; e2.ldo = cout[i];
+    e2.act = ACT_GELU; e2.act_post = 1;
+    MAB_TRY(launch_conv3(bb[i], V, hh, ww, cout[i], h->P(r + ".conv2.weight"), cout[i], e2, c.st));
+    x = xo[i]; cin = cout[i];
+  }
+  MAB_TRY(c.linear(x, (int)VT, 1024, 1024, e + ".encoder.2.weight", 1024, h->F(e + ".encoder.2.bias"),
+                   ACT_NONE, nullptr, nullptr, y, nullptr));
+  MAB_TRY(launch_layernorm(y, (int)VT, 1024, (int)VT, (int)VT, 0, h->F(e + ".norm_layer.weight"),
+                           h->F(e + ".norm_layer.bias"), nullptr, nullptr, 1e-6f, nullptr, y, nullptr, c.st));
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+             accum_masked_rows_kernel<<<ew_grid(VT * 256), 256, 0, c.st>>>(p.geo_sum, y, mask, p.T, 1024,
+                                                                          VT * 256, first ? 1 : 0));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// GlobalRepresentationEncoder (global_rep_encoder.py:54-67,83-105): Linear-GELU x3, Linear,
+// LayerNorm; accumulated into p.geo_vec scaled by the per-view mask.  x [V, cin] fp32.
+int global_rep_encode(Ctx& c, const std::string& e, const float* x, int cin, const float* mask, bool first,
+                      float* t0, float* t1) {
+  mab_handle* h = c.h;
+  Plan& p = h->plan;
+  const int V = p.V;
+  auto lin = [&](const char* name, const float* in, int K, int N, int act, float* out) {
+    const std::string k = e + "." + name;
+    const long long warps = (long long)N * ((V + 7) / 8);
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               small_linear_kernel<<<(int)((warps * 32 + 255) / 256), 256, 0, c.st>>>(
+                   in, h->F(k + ".weight"), h->F(k + ".bias"), V, K, N, act, out, K, N));
+  };
+  if (!h->F(e + ".encoder.1.weight")) return fail(-4, "missing weights of %s", e.c_str());
+  lin("encoder.0.0.0.0", x, cin, 128, 1, t0);
+  lin("encoder.0.0.1", t0, 128, 256, 1, t1);
+  lin("encoder.0.1", t1, 256, 512, 1, t0);
+  lin("encoder.1", t0, 512, 1024, 0, t1);
+  MAB_TRY(launch_layernorm(t1, V, 1024, V, V, 0, h->F(e + ".norm_layer.weight"), h->F(e + ".norm_layer.bias"),
+                           nullptr, nullptr, 1e-6f, nullptr, t1, nullptr, c.st));
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+             accum_masked_rows_kernel<<<ew_grid((long long)V * 256), 256, 0, c.st>>>(
+                 p.geo_vec, t1, mask, 1, 1024, (long long)V * 256, first ? 1 : 0));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// a6: model.py:1377-1436.  p.enc_out holds the encoder-normed patch tokens (fp32); writes p.fused.
+int encode_geometric_inputs(Ctx& c, const mab_inputs* in) {
+  mab_handle* h = c.h;
+  Plan& p = h->plan;
+  const int V = p.V, T = p.T, D = h->cfg.enc_dim;
+  const long long VT = (long long)V * T;
+  // small per-view scratch: [0,V) depth norm | masks 5 x V | in_scale V | in_trans 3V | in_tscale V | MLP 2 x V*1024
+  float* s = p.geo_small;
+  float* depth_norm = s; float* m_ray = s + V; float* m_depth = s + 2 * V; float* m_scale = s + 3 * V;
+  float* m_cam = s + 4 * V; float* m_tscale = s + 5 * V; float* in_scale = s + 6 * V;
+  float* in_trans = s + 7 * V; float* in_tscale = s + 10 * V;
+  float* t0 = s + 16 * V; float* t1 = t0 + (long long)V * 1024;
+  const bool has_rays = in->ray_dirs && in->ray_mask, has_depth = in->depth_along_ray && in->depth_mask;
+  const bool has_cam = in->cam_quats && in->cam_trans && in->cam_mask;
+  if (has_depth)
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               depth_norm_kernel<<<V, 256, 0, c.st>>>(in->depth_along_ray, (long long)p.H * p.W, depth_norm));
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+             geo_prepare_kernel<<<(V + 127) / 128, 128, 0, c.st>>>(
+                 V, has_depth ? depth_norm : nullptr, has_cam ? in->cam_trans : nullptr, in->pose_trans_norm,
+                 has_rays ? in->ray_mask : nullptr, has_depth ? in->depth_mask : nullptr,
+                 has_cam ? in->cam_mask : nullptr, in->depth_metric_mask, in->pose_metric_mask, in_scale,
+                 in_trans, in_tscale, m_ray, m_depth, m_scale, m_cam, m_tscale));
+  MAB_CUDA(cudaGetLastError());
+  // the encoder's activation buffers (ln | qkv | att | hid, contiguous in the plan) are free here
+  bool first_dense = true, first_vec = true;
+  for (int which = 0; which < 2; ++which) {
+    if ((which == 0 && !has_rays) || (which == 1 && !has_depth)) continue;
+    Bump scratch; scratch.base = reinterpret_cast<uint8_t*>(p.ln);
+    const int cpad = which == 0 ? 640 : 256;
+    bf16* unsh = scratch.take<bf16>(VT * cpad);
+    if (which == 0)
+      MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+                 patch_im2col_kernel<<<ew_grid(VT * cpad), 256, 0, c.st>>>(in->ray_dirs, V, p.H, p.W, 3, 1, cpad,
+                                                                          nullptr, 0, unsh));
+    else
+      MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+                 patch_im2col_kernel<<<ew_grid(VT * cpad), 256, 0, c.st>>>(in->depth_along_ray, V, p.H, p.W, 1, 0,
+                                                                          cpad, depth_norm, 1, unsh));
+    MAB_TRY(dense_rep_encode(c, which == 0 ? "ray_dirs_encoder" : "depth_encoder", unsh, cpad,
+                             which == 0 ? m_ray : m_depth, first_dense, scratch));
+    if (scratch.off > (size_t)((uint8_t*)(p.hid + p.Lenc * 4 * D) - (uint8_t*)p.ln))
+      return fail(-5, "geometric encoder scratch overflows the encoder activation buffers");
+    first_dense = false;
+  }
+  if (has_depth) {
+    MAB_TRY(global_rep_encode(c, "depth_scale_encoder", in_scale, 1, m_scale, first_vec, t0, t1));
+    first_vec = false;
+  }
+  if (has_cam) {
+    MAB_TRY(global_rep_encode(c, "cam_rot_encoder", in->cam_quats, 4, m_cam, first_vec, t0, t1));
+    MAB_TRY(global_rep_encode(c, "cam_trans_encoder", in_trans, 3, m_cam, false, t0, t1));
+    MAB_TRY(global_rep_encode(c, "cam_trans_scale_encoder", in_tscale, 1, m_tscale, false, t0, t1));
+    first_vec = false;
+  }
+  MAB_LAUNCH(CAT_LAYERNORM, 0.0, (double)VT * D * 6.0, c.st,
+             fuse_norm_kernel<8><<<(int)((VT + 7) / 8), 256, 0, c.st>>>(
+                 p.enc_out, first_dense ? nullptr : p.geo_sum, first_vec ? nullptr : p.geo_vec, (int)VT, T,
+                 h->F("fusion_norm_layer.weight"), h->F("fusion_norm_layer.bias"), 1e-6f, p.fused));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
 // a2-a7: patch embed, 24 DINOv2 blocks, encoder norm (+ fusion norm), proj_embed, ref-view PE
 extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_total, void* workspace,
                                 size_t workspace_bytes, int has_scale_token, void* stream) {
@@ -639,10 +829,12 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
   const int V = p.V, T = p.T, D = cf.enc_dim;
   const long long VT = (long long)V * T;
   const bool multimodal = in->ray_dirs || in->depth_along_ray || in->cam_quats;
-  if (multimodal) return fail(-6, "geometric inputs are not wired into this build yet");
+  if (multimodal && !h->P("ray_dirs_encoder.conv_in.weight"))
+    return fail(-4, "geometric inputs given but the checkpoint has no geometric encoders");
 
   MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
-             patch_im2col_kernel<<<ew_grid(VT * 640), 256, 0, c.st>>>(in->images, V, p.H, p.W, 640, p.im2col));
+             patch_im2col_kernel<<<ew_grid(VT * 640), 256, 0, c.st>>>(in->images, V, p.H, p.W, 3, 0, 640,
+                                                                      nullptr, 0, p.im2col));
   MAB_TRY(c.linear(p.im2col, (int)VT, 640, 640, "encoder.model.patch_embed.proj.weight", D,
                    h->F("encoder.model.patch_embed.proj.bias"), ACT_NONE, nullptr, nullptr, p.patch,
                    nullptr, nullptr, 640));
@@ -659,11 +851,18 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
     MAB_TRY(block_tail(c, b, p.xs, p.Lenc, D, p.att, p.ln, p.hid, h->F(b + ".ls1.gamma"),
                        h->F(b + ".ls2.gamma")));
   }
-  // encoder norm on the patch tokens only (drop cls), immediately followed by the fusion norm
-  // (image-only: the geometric features are exactly zero, model.py:931-968 / SURVEY 8a a6)
-  MAB_TRY(launch_layernorm(p.xs, (int)VT, D, T, T + 1, 1, h->F("encoder.model.norm.weight"),
-                           h->F("encoder.model.norm.bias"), h->F("fusion_norm_layer.weight"),
-                           h->F("fusion_norm_layer.bias"), 1e-6f, p.fused, nullptr, nullptr, c.st));
+  if (!multimodal) {
+    // encoder norm on the patch tokens only (drop cls), immediately followed by the fusion norm
+    // (image-only: the geometric features are exactly zero, model.py:931-968 / SURVEY 8a a6)
+    MAB_TRY(launch_layernorm(p.xs, (int)VT, D, T, T + 1, 1, h->F("encoder.model.norm.weight"),
+                             h->F("encoder.model.norm.bias"), h->F("fusion_norm_layer.weight"),
+                             h->F("fusion_norm_layer.bias"), 1e-6f, p.fused, nullptr, nullptr, c.st));
+  } else {
+    MAB_TRY(launch_layernorm(p.xs, (int)VT, D, T, T + 1, 1, h->F("encoder.model.norm.weight"),
+                             h->F("encoder.model.norm.bias"), nullptr, nullptr, 1e-6f, nullptr, p.enc_out,
+                             nullptr, c.st));
+    MAB_TRY(encode_geometric_inputs(c, in));
+  }
   if (p.has_scale) {
     MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
                f32_to_bf16_kernel<<<4, 256, 0, c.st>>>(h->F("scale_token"), p.fused + VT * D, D));
@@ -928,7 +1127,7 @@ extern "C" int mab_forward(mab_handle* h, const mab_inputs* in, mab_outputs* out
   return mab_stage_heads(h, in, out, nullptr, stream);
 }
 
-// workspace: views*H*W*17 bytes + 256
+// workspace: views*H*W*18 + views*8 + 512 bytes
 extern "C" int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs* raw,
                                mab_post_outputs* post, const mab_post_options* opt, void* workspace,
                                size_t workspace_bytes, void* stream) {
@@ -936,9 +1135,24 @@ extern "C" int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs*
   cudaStream_t st = (cudaStream_t)stream;
   const int V = in->views, H = in->H, W = in->W;
   const long long npix = (long long)V * H * W;
-  MAB_ARG(workspace_bytes >= (size_t)npix * 17 + 256, "post-process workspace too small");
-  if (opt->apply_confidence_mask)
-    return fail(-6, "apply_confidence_mask is not wired into this build yet");
+  MAB_ARG(workspace_bytes >= (size_t)npix * 18 + (size_t)V * 8 + 512, "post-process workspace too small");
+  const unsigned char* fmask = raw->non_ambiguous_mask;
+  if (opt->apply_mask && opt->apply_confidence_mask) {
+    // inference.py:440-452: torch.quantile(conf[b], p/100) per view, linear interpolation
+    unsigned char* fm = reinterpret_cast<unsigned char*>(workspace) + ((size_t)npix * 17 + 255) / 256 * 256;
+    float* stat = reinterpret_cast<float*>(fm + ((size_t)npix + 255) / 256 * 256);
+    const long long n = (long long)H * W;
+    const float q = (float)((double)opt->confidence_percentile / 100.0);
+    MAB_ARG(q >= 0.f && q <= 1.f, "confidence_percentile must be in [0, 100]");
+    const float rank = q * (float)(n - 1);
+    const long long k_lo = (long long)floorf(rank), k_hi = (long long)ceilf(rank);
+    MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
+               conf_order_stat_kernel<<<dim3(2, V), 1024, 0, st>>>(raw->conf, n, k_lo, k_hi, stat));
+    MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
+               conf_mask_kernel<<<ew_grid(npix), 256, 0, st>>>(raw->conf, raw->non_ambiguous_mask, stat,
+                                                              rank - (float)k_lo, n, npix, fm));
+    fmask = fm;
+  }
   MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
              denorm_image_kernel<<<ew_grid(npix), 256, 0, st>>>(in->images, V, H, W, 0.485f, 0.456f, 0.406f,
                                                      0.229f, 0.224f, 0.225f, post->img_no_norm));
@@ -948,11 +1162,10 @@ extern "C" int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs*
                                             post->cam_quats));
   if (opt->apply_mask) {
     if (opt->mask_edges) {
-      MAB_TRY(mab_edge_mask(raw->pts3d, raw->pts3d_cam, raw->non_ambiguous_mask, V, H, W,
-                            opt->edge_normal_threshold_deg, opt->edge_depth_threshold, workspace,
-                            post->mask, st));
+      MAB_TRY(mab_edge_mask(raw->pts3d, raw->pts3d_cam, fmask, V, H, W, opt->edge_normal_threshold_deg,
+                            opt->edge_depth_threshold, workspace, post->mask, st));
     } else {
-      MAB_CUDA(cudaMemcpyAsync(post->mask, raw->non_ambiguous_mask, npix, cudaMemcpyDeviceToDevice, st));
+      MAB_CUDA(cudaMemcpyAsync(post->mask, fmask, npix, cudaMemcpyDeviceToDevice, st));
     }
   }
   MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,

@@ -205,6 +205,61 @@ __global__ void edge_mask_apply_kernel(const float* __restrict__ ang, const unsi
   }
 }
 
+// ---- confidence mask (inference.py:440-452): per-view torch.quantile(conf, q) with linear
+// interpolation = exact order statistics k_lo, k_hi of the view's H*W confidences, found by an
+// 8-bit-digit radix select over the order-preserving integer image of the floats.
+// grid (2, views): blockIdx.x selects k_lo / k_hi.  stat[view*2 + which] receives the value.
+__global__ void conf_order_stat_kernel(const float* __restrict__ conf, long long npix_view, long long k_lo,
+                                       long long k_hi, float* __restrict__ stat) {
+  __shared__ unsigned int hist[256];
+  __shared__ unsigned int s_prefix;
+  __shared__ long long s_k;
+  const float* c = conf + (long long)blockIdx.y * npix_view;
+  if (threadIdx.x == 0) { s_prefix = 0u; s_k = blockIdx.x == 0 ? k_lo : k_hi; }
+  unsigned int mask = 0u;
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    for (int b = threadIdx.x; b < 256; b += blockDim.x) hist[b] = 0u;
+    __syncthreads();
+    const unsigned int prefix = s_prefix;
+    for (long long i = threadIdx.x; i < npix_view; i += blockDim.x) {
+      unsigned int u = __float_as_uint(c[i]);
+      u ^= (u >> 31) ? 0xffffffffu : 0x80000000u;
+      if ((u & mask) == prefix) atomicAdd(&hist[(u >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      long long k = s_k;
+      int b = 0;
+      for (; b < 255; ++b) {
+        if (k < (long long)hist[b]) break;
+        k -= hist[b];
+      }
+      s_k = k;
+      s_prefix = prefix | ((unsigned int)b << shift);
+    }
+    mask |= 0xffu << shift;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    unsigned int u = s_prefix;
+    u ^= (u >> 31) ? 0x80000000u : 0xffffffffu;
+    stat[blockIdx.y * 2 + blockIdx.x] = __uint_as_float(u);
+  }
+}
+
+// fm = non_ambiguous & (conf > lerp(stat_lo, stat_hi, w))   (at::lerp's two-sided formula)
+__global__ void conf_mask_kernel(const float* __restrict__ conf, const unsigned char* __restrict__ fmask,
+                                 const float* __restrict__ stat, float w, long long npix_view, long long total,
+                                 unsigned char* __restrict__ out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long v = i / npix_view;
+    const float a = stat[v * 2], b = stat[v * 2 + 1];
+    const float thr = w < 0.5f ? __fmaf_rn(w, __fsub_rn(b, a), a) : __fsub_rn(b, __fmul_rn(__fsub_rn(b, a), __fsub_rn(1.0f, w)));
+    out[i] = (fmask[i] && conf[i] > thr) ? 1 : 0;
+  }
+}
+
 // depth_z = pts3d_cam[..., 2] and masking happen in a second pass so that stage 3 reads unmasked z
 __global__ void apply_mask_kernel(const unsigned char* __restrict__ mask, long long npix, int apply,
                                   float* __restrict__ pts3d, float* __restrict__ pts3d_cam,

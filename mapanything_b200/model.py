@@ -15,12 +15,14 @@ from typing import Any, Dict, List, Optional
 
 import torch
 
-from . import _lib
+from . import _lib, pose_math
 
 # keys a view may carry (inference.py:28-46)
 REQUIRED_KEYS = {"data_norm_type"}
 CONFLICTING_KEYS = [("intrinsics", "ray_directions")]
 _PASS_THROUGH = {"instance", "idx", "true_shape", "data_norm_type"}
+_ALL_INPUTS = dict(use_calibration=True, use_depth=True, use_pose=True, use_depth_scale=True,
+                   use_pose_scale=True)
 
 
 def validate_input_views_for_inference(views):
@@ -192,6 +194,108 @@ class MapAnything(torch.nn.Module):
             imgs[i].copy_(v["img"][0], non_blocking=True)
         return imgs, H, W
 
+    def _pack_geometry(self, views, flags, H, W, view_lo=0, total_views=None):
+        """a1 + the host part of a6: pre-process the optional geometric inputs of this rank's views
+        (inference.py:222-311) into the stacked device buffers `mab_inputs` takes, with the per-view
+        availability masks of model.py:1336-1369 made deterministic by `flags`
+        (model.py:2154-2197).  Returns None when nothing geometric is used (image-only path).
+
+        Per-pixel work (rays from intrinsics, ray normalisation, z-depth -> depth along ray) runs
+        in libmab200 kernels; the pose algebra (views x 7 floats) is host code (pose_math.py)."""
+        V, dev, lib, st = len(views), self._device, self._lib, self._stream_ptr()
+        if not (flags["use_calibration"] or flags["use_depth"] or flags["use_pose"]):
+            return None
+        rays = torch.zeros((V, H, W, 3), dtype=torch.float32, device=dev)
+        depth = torch.zeros((V, H, W), dtype=torch.float32, device=dev)
+        has_ray, has_depth, has_cam, metric = [0] * V, [0] * V, [0] * V, [1] * V
+        quats, trans = [None] * V, [None] * V
+        npix = H * W
+        with torch.cuda.device(dev):
+            for i, v in enumerate(views):
+                if "intrinsics" in v:
+                    K = v["intrinsics"].to(dev, torch.float32).reshape(-1, 3, 3)[:1].contiguous()
+                    _lib.check(lib.mab_rays_from_intrinsics(K.data_ptr(), 1, H, W, rays[i].data_ptr(), st))
+                    has_ray[i] = 1
+                elif "ray_directions" in v or "ray_directions_cam" in v:
+                    key = "ray_directions" if "ray_directions" in v else "ray_directions_cam"
+                    r = v[key].to(dev, torch.float32).reshape(-1, H, W, 3)[:1].contiguous()
+                    if key == "ray_directions":
+                        _lib.check(lib.mab_normalize_rays(r.data_ptr(), npix, rays[i].data_ptr(), st))
+                    else:  # already pre-processed (forward() on the output of preprocess_input_views)
+                        rays[i].copy_(r[0])
+                    has_ray[i] = 1
+                if "depth_z" in v:
+                    z = v["depth_z"].to(dev, torch.float32).reshape(-1, H, W)[:1].contiguous()
+                    _lib.check(lib.mab_depth_z_to_along_ray(z.data_ptr(), rays[i].data_ptr(), npix,
+                                                            depth[i].data_ptr(), st))
+                    has_depth[i] = 1
+                elif "depth_along_ray" in v:
+                    depth[i].copy_(v["depth_along_ray"].to(dev, torch.float32).reshape(-1, H, W)[0])
+                    has_depth[i] = 1
+                if "camera_poses" in v:
+                    q, t = pose_math.split_camera_poses(v["camera_poses"], view_lo + i)
+                    quats[i], trans[i], has_cam[i] = q, t, 1
+                elif "camera_pose_quats" in v and "camera_pose_trans" in v:
+                    quats[i], trans[i], has_cam[i] = v["camera_pose_quats"], v["camera_pose_trans"], 1
+                if "is_metric_scale" in v:  # default True, inference.py:298-306
+                    metric[i] = int(bool(torch.as_tensor(v["is_metric_scale"]).reshape(-1)[0]))
+        ray_mask = [int(flags["use_calibration"] and has_ray[i]) for i in range(V)]
+        depth_mask = [int(flags["use_depth"] and has_depth[i]) for i in range(V)]
+        cam_mask = [int(flags["use_pose"] and has_cam[i]) for i in range(V)]
+
+        # poses relative to the scene's view 0 and the scene-wide translation norm (model.py:792-896,
+        # geometry.py:1629-1666).  A view-sharded scene exchanges the handful of pose floats first.
+        local = [(cam_mask[i], None if not cam_mask[i] else
+                  (torch.as_tensor(quats[i]).detach().float().cpu().reshape(-1, 4)[:1],
+                   torch.as_tensor(trans[i]).detach().float().cpu().reshape(-1, 3)[:1])) for i in range(V)]
+        total = int(total_views or V)
+        scene = local
+        if total > V:
+            import torch.distributed as dist
+            gathered = [None] * dist.get_world_size()
+            dist.all_gather_object(gathered, local)
+            scene = [e for part in gathered for e in part]
+        q_rel = torch.tensor([0.0, 0.0, 0.0, 1.0]).repeat(len(scene), 1)
+        t_rel = torch.zeros(len(scene), 3)
+        pose_norm = 1.0
+        posed = [i for i, (m, _) in enumerate(scene) if m]
+        if posed:
+            if not scene[0][0]:
+                raise ValueError("camera poses are given but the reference view (view 0) has none")
+            q_all = torch.cat([scene[i][1][0] for i in posed], 0)
+            t_all = torch.cat([scene[i][1][1] for i in posed], 0)
+            q, t = pose_math.relative_to_first(scene[0][1][0], scene[0][1][1], q_all, t_all)
+            q_rel[posed], t_rel[posed] = q, t
+            pose_norm = pose_math.translation_norm(t_rel)
+        sl = slice(view_lo, view_lo + V) if total > V else slice(0, V)
+
+        def u8(x):
+            return torch.tensor(x, dtype=torch.uint8).to(dev, non_blocking=True)
+
+        geo = dict(
+            ray_dirs=rays if any(ray_mask) else None,
+            depth_along_ray=depth if any(depth_mask) else None,
+            cam_quats=q_rel[sl].contiguous().to(dev) if any(cam_mask) else None,
+            cam_trans=t_rel[sl].contiguous().to(dev) if any(cam_mask) else None,
+            ray_mask=u8(ray_mask), depth_mask=u8(depth_mask), cam_mask=u8(cam_mask),
+            depth_metric_mask=u8([int(metric[i] and flags["use_depth_scale"]) for i in range(V)]),
+            pose_metric_mask=u8([int(metric[i] and flags["use_pose_scale"]) for i in range(V)]),
+            pose_trans_norm=float(pose_norm),
+        )
+        if not (any(ray_mask) or any(depth_mask) or any(cam_mask)):
+            return None
+        return geo
+
+    def _input_struct(self, imgs, H, W, geo=None):
+        inp = _lib.MabInputs(views=imgs.shape[0], H=H, W=W, images=imgs.data_ptr())
+        if geo:
+            for k in ("ray_dirs", "depth_along_ray", "cam_quats", "cam_trans", "ray_mask", "depth_mask",
+                      "cam_mask", "depth_metric_mask", "pose_metric_mask"):
+                if geo[k] is not None:
+                    setattr(inp, k, geo[k].data_ptr())
+            inp.pose_trans_norm = geo["pose_trans_norm"]
+        return inp
+
     def _alloc_outputs(self, V, H, W, want_logits=False):
         dev = self._device
         o = dict(
@@ -213,7 +317,7 @@ class MapAnything(torch.nn.Module):
     def _out_struct(o):
         return _lib.MabOutputs(**{k: (o[k].data_ptr() if k in o else None) for k, _ in _lib.MabOutputs._fields_})
 
-    def _run_forward(self, imgs, H, W, want_logits=False, view_lo=0, total_views=None):
+    def _run_forward(self, imgs, H, W, want_logits=False, view_lo=0, total_views=None, geo=None):
         """One whole forward of this rank's views: returns the raw output tensors (views stacked).
 
         Single GPU (total_views == views): one `mab_forward` call.  View-sharded
@@ -228,7 +332,7 @@ class MapAnything(torch.nn.Module):
                 raise RuntimeError("mab_workspace_bytes rejected the problem shape")
             ws = self._get_workspace(nbytes)
             outs = self._alloc_outputs(V, H, W, want_logits)
-            inp = _lib.MabInputs(views=V, H=H, W=W, images=imgs.data_ptr())
+            inp = self._input_struct(imgs, H, W, geo)
             ost = self._out_struct(outs)
             if total == V:
                 _lib.check(self._lib.mab_forward(self._handle, C.byref(inp), C.byref(ost), ws.data_ptr(),
@@ -295,7 +399,7 @@ class MapAnything(torch.nn.Module):
             mask=torch.empty((V, H, W, 1), dtype=torch.bool, device=dev),
         )
         with torch.cuda.device(dev):
-            need = V * H * W * 17 + 256
+            need = V * H * W * 18 + V * 8 + 1024
             if self._post_ws is None or self._post_ws.numel() < need:
                 self._post_ws = torch.empty(need, dtype=torch.uint8, device=dev)
             inp = _lib.MabInputs(views=V, H=H, W=W, images=imgs.data_ptr())
@@ -345,10 +449,9 @@ class MapAnything(torch.nn.Module):
         no-op here (the dense head always streams `head_chunk` views through a fixed workspace)."""
         if not self._finalized:
             raise RuntimeError("load_state_dict() / from_pretrained() must be called before inference")
-        if any(k in v for v in views for k in ("ray_directions_cam", "depth_along_ray", "camera_pose_quats")):
-            raise NotImplementedError("geometric inputs are not wired into this build yet")
         imgs, H, W = self._pack_images(views)
-        outs = self._run_forward(imgs, H, W)
+        geo = self._pack_geometry(views, dict(_ALL_INPUTS), H, W)
+        outs = self._run_forward(imgs, H, W, geo=geo)
         return self._raw_dicts(outs, len(views))
 
     @torch.inference_mode()
@@ -373,10 +476,9 @@ class MapAnything(torch.nn.Module):
         for v in views:
             if v["data_norm_type"][0] != self.data_norm_type:  # encoders/base.py:83-96
                 raise AssertionError(f"data_norm_type {v['data_norm_type']} != encoder's {self.data_norm_type}")
-        geo = [k for v in views for k in ("intrinsics", "ray_directions", "depth_z", "camera_poses") if k in v]
-        use_geo = geo and not (ignore_calibration_inputs and ignore_depth_inputs and ignore_pose_inputs)
-        if use_geo:
-            raise NotImplementedError("geometric inputs are not wired into this build yet")
+        flags = dict(use_calibration=not ignore_calibration_inputs, use_depth=not ignore_depth_inputs,
+                     use_pose=not ignore_pose_inputs, use_depth_scale=not ignore_depth_scale_inputs,
+                     use_pose_scale=not ignore_pose_scale_inputs)  # model.py:2154-2197
         # move the caller's tensors to the model device in place, like model.py:2316-2320
         for v in views:
             for name in list(v.keys()):
@@ -384,7 +486,9 @@ class MapAnything(torch.nn.Module):
                     v[name] = v[name].to(self._device, non_blocking=True)
         V = len(views)
         imgs, H, W = self._pack_images(views)
-        outs = self._run_forward(imgs, H, W, view_lo=view_range[0] if view_range else 0, total_views=total_views)
+        lo = view_range[0] if view_range else 0
+        geo = self._pack_geometry(views, flags, H, W, view_lo=lo, total_views=total_views)
+        outs = self._run_forward(imgs, H, W, view_lo=lo, total_views=total_views, geo=geo)
         post = self._run_postprocess(imgs, outs, H, W, apply_mask, mask_edges, edge_normal_threshold,
                                      edge_depth_threshold, apply_confidence_mask, confidence_percentile)
         preds = []

@@ -36,7 +36,8 @@ def _to_cuda(views):
     return [{k: (v.cuda() if torch.is_tensor(v) else v) for k, v in view.items()} for view in views]
 
 
-@pytest.mark.parametrize("name", ["small_n3_70x98", "c1_loose_n2_392x518", "c1_n2_392x518"])
+@pytest.mark.parametrize("name", ["small_n3_70x98", "small_mm_n3_70x98", "small_conf_n2_56x84",
+                                  "c1_loose_n2_392x518", "c1_n2_392x518"])
 def test_infer_matches_reference_golden(name, model, sd_cuda):
     """CUDA path vs golden vectors of the LIVE reference (fp32).  Camera-frame geometry must meet
     BASELINE.json's absolute bf16 tolerances.  Pose-dependent keys are additionally allowed to be as
@@ -153,3 +154,60 @@ def test_validation_errors_match_reference(model):
         model.infer([v, dict(v, camera_poses=torch.eye(4)[None])])
     with pytest.raises(AssertionError):
         model.infer([dict(v, img=torch.zeros(1, 3, 30, 28))])
+
+
+def test_geometric_input_preprocessing_matches_oracle(model):
+    """a1: rays from intrinsics, ray normalisation, z-depth -> depth along ray, poses relative to
+    view 0 and the translation norm, against the oracle's restatement of inference.py:222-311 and
+    model.py:792-896 on the same inputs (fp32 elementwise arithmetic: tight tolerance)."""
+    from oracle import mapanything_oracle as orc, weights
+    from mapanything_b200 import pose_math
+
+    H, W = 70, 98
+    views = weights.add_multimodal_inputs(weights.synthetic_views(3, H, W, seed=5), seed=6, sparse=False)
+    views[1]["ray_directions"] = 3.0 * orc.get_rays_in_camera_frame(views[1].pop("intrinsics"), H, W)
+    pv = orc.preprocess_views([dict(v) for v in views])
+    flags = dict(use_calibration=True, use_depth=True, use_pose=True, use_depth_scale=True, use_pose_scale=True)
+    geo = model._pack_geometry(_to_cuda(views), flags, H, W)
+    torch.cuda.synchronize()
+    for i in range(3):
+        torch.testing.assert_close(geo["ray_dirs"][i].cpu(), pv[i]["ray_directions_cam"][0], rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(geo["depth_along_ray"][i].cpu(), pv[i]["depth_along_ray"][0, ..., 0],
+                                   rtol=1e-5, atol=1e-6)
+    q1, t1 = pv[0]["camera_pose_quats"], pv[0]["camera_pose_trans"]
+    q2 = torch.cat([v["camera_pose_quats"] for v in pv]); t2 = torch.cat([v["camera_pose_trans"] for v in pv])
+    q, t = orc.transform_pose_2_to_1(q1.repeat(3, 1), t1.repeat(3, 1), q2, t2)
+    torch.testing.assert_close(geo["cam_quats"].cpu(), q, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(geo["cam_trans"].cpu(), t, rtol=1e-5, atol=1e-6)
+    dis = t.norm(dim=-1)
+    assert abs(geo["pose_trans_norm"] - float(dis.sum() / ((dis > 0).sum() + 1e-8))) < 1e-6
+    assert geo["ray_mask"].tolist() == [1, 1, 1] and geo["depth_mask"].tolist() == [1, 1, 1]
+    # ignore_* flags (model.py:2154-2197)
+    off = dict(flags, use_calibration=False, use_pose=False)
+    g2 = model._pack_geometry(_to_cuda(views), off, H, W)
+    assert g2["ray_dirs"] is None and g2["cam_quats"] is None and g2["depth_along_ray"] is not None
+    assert model._pack_geometry(_to_cuda(views), {k: False for k in flags}, H, W) is None
+    assert pose_math.rotmat_to_quat(torch.eye(3)[None]).tolist() == [[0.0, 0.0, 0.0, 1.0]]
+
+
+@pytest.mark.parametrize("ignore", [dict(ignore_depth_inputs=True), dict(ignore_pose_inputs=True, ignore_depth_scale_inputs=True),
+                                    dict(ignore_calibration_inputs=True, ignore_pose_scale_inputs=True)])
+def test_multimodal_ignore_flags_match_oracle(ignore, model, sd_cuda):
+    """a6 with subsets of the geometric inputs switched off: CUDA path vs the fp32 oracle, with the
+    oracle's bf16-autocast run as the yardstick."""
+    from oracle import mapanything_oracle as orc, weights
+    from tests import helpers
+
+    views = weights.add_multimodal_inputs(weights.synthetic_views(2, 56, 84, seed=3), seed=4)
+    preds = model.infer(_to_cuda(views), **ignore)
+    torch.cuda.synchronize()
+    ref = orc.infer(sd_cuda, _to_cuda(views), **ignore)
+    amp = orc.infer(sd_cuda, _to_cuda(views), amp=True, **ignore)
+    for p, r, a in zip(preds, ref, amp):
+        for k in ("pts3d_cam", "ray_directions", "depth_along_ray", "conf"):
+            m = (p["mask"].cpu() & r["mask"]).float() if k in helpers.MASKED_KEYS else 1.0
+            if k == "ray_directions" or k == "conf":
+                m = 1.0
+            e = helpers.rel_l2((p[k].float().cpu() * m).numpy(), (r[k] * m).numpy())
+            y = helpers.rel_l2((a[k] * m).numpy(), (r[k] * m).numpy())
+            assert e < max(TOL_DENSE, 3.0 * y), (k, e, y)
