@@ -133,6 +133,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();     // prologue above overlapped the previous kernel's tail (PDL)
+  pdl_trigger();
   const uint32_t tmem_base = *tmem_slot;
   // TMEM columns: S_A @0, S_B @128 (P_t overlays the first 64 columns of S_t),
   //               O_A[0] @256, O_A[1] @320, O_B[0] @384, O_B[1] @448

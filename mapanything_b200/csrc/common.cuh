@@ -32,6 +32,18 @@ __device__ __forceinline__ float fast_exp2(float x) {  // MUFU.EX2, 2 ulp; exp2(
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization
+// attribute may become resident while its predecessor in the stream is still running; it must not
+// touch global memory before pdl_wait() (which returns once the predecessor has completed and its
+// writes are visible).  pdl_trigger() lets the successor's CTAs start filling free SM slots.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+__device__ __forceinline__ float fast_rcp(float x) {  // MUFU.RCP, 1 ulp, branch-free (rcp.rn is a call)
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 

@@ -29,6 +29,8 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows_out, int 
                                  __nv_bfloat16* __restrict__ out_split) {
   constexpr int C = 128 * VPL;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  pdl_wait();
+  pdl_trigger();
   if (warp >= rows_out) return;
   const long long in_row = (long long)(warp / group_out) * group_in + skip + warp % group_out;
   const float4* xr = reinterpret_cast<const float4*>(x + in_row * C);

@@ -75,7 +75,8 @@ __device__ __forceinline__ float gelu_erf(float x) {
   // exact-erf GELU (nn.GELU default, transformer_blocks.py:68) as x * sigmoid(2u) with
   // erf(x/sqrt2) ~ tanh(u), u = x (a0 + a1 x^2 + a2 x^4) on |x| <= 5 (minimax fit: |gelu error|
   // <= 2.6e-5 absolute, below the bf16 rounding of the stored activation); the sigmoid form has no
-  // cancellation in the negative tail.  2 MUFU + 7 FP32 ops per element.
+  // cancellation in the negative tail.  2 MUFU + 7 FP32 ops per element, branch-free (rcp.approx:
+  // the IEEE rcp.rn compiles to a guarded slow-path call that serialises the whole chunk).
 #ifdef MAB_GELU_AS
   const float z = fabsf(x) * 0.70710678118654752f;
   const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
@@ -92,7 +93,7 @@ __device__ __forceinline__ float gelu_erf(float x) {
   float pnl = fmaf(x2, 1.01537568e-03f, -1.06782574e-01f);
   pnl = fmaf(pnl, x2, -2.30111381e+00f);
   const float e = fast_exp2(xc * pnl);
-  return x * __frcp_rn(1.0f + e);
+  return x * fast_rcp(1.0f + e);
 }
 
 template <int BN, int STAGES>
@@ -277,6 +278,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   cluster_sync_all();  // peers' barriers are initialised and TMEM is allocated in both CTAs
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above overlapped the tail of the previous kernel in the stream (PDL)
+  pdl_wait();
+  pdl_trigger();
 
   if (warp == 0) {
     // ================================ TMA producer ==========================================

@@ -95,6 +95,44 @@ struct ProfScope {
     __VA_ARGS__;                                     \
   } while (0)
 
+// Launch with the programmatic-stream-serialization attribute (PDL): only for kernels that call
+// pdl_wait() before their first global-memory access.  MAB_NO_PDL=1 in the environment turns the
+// attribute off (plain stream order) for debugging.
+inline bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("MAB_NO_PDL");
+    on = (e && e[0] == '1') ? 0 : 1;
+  }
+  return on == 1;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              int cluster, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (cluster > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 // ---- cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda link dependency)
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -193,19 +231,7 @@ inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const Gem
     flops = 2.0 * shp.M * (double)shp.N * shp.K;
   const int cat = MODE == MODE_CONV3 ? (EPI == EPI_REGRESS ? CAT_CONV3_REGRESS : CAT_CONV3) : CAT_GEMM;
   ProfScope ps(cat, flops, 0.0, st);
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(GEMM_THREADS);
-  cfg.dynamicSmemBytes = SM::TOTAL;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = CL;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  MAB_CUDA(cudaLaunchKernelEx(&cfg, kern, tA, tB, shp, ep, rg));
+  MAB_CUDA(launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), SM::TOTAL, st, CL, tA, tB, shp, ep, rg));
   return 0;
 }
 
@@ -219,6 +245,19 @@ inline int launch_gemm(const void* A, long long lda, const void* B, long long ld
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM));
   if (N > 128) {
+    // tile width by wave quantisation: the persistent grid has sm_count/2 clusters, each 256 x BN
+    // tile costs ~BN (x1.04 at BN = 192: the B half-tile amortises less of the A traffic); e.g. the
+    // info-sharing width 768 gives 99 tiles of 256 (2 waves on 74 clusters, 67 % full) but 132
+    // tiles of 192 (2 waves, 89 % full)
+    const int num_mg = ((M + GEMM_BM - 1) / GEMM_BM + GEMM_CL - 1) / GEMM_CL, clusters = sm_count() / GEMM_CL;
+    auto cost = [&](int bn, double unit) {
+      const int tiles = num_mg * ((N + bn - 1) / bn);
+      return ((tiles + clusters - 1) / clusters) * bn * unit;
+    };
+    if (cost(192, 1.04) < cost(256, 1.0)) {
+      MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 192 / GEMM_CL));
+      return launch_gemm_t<192, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
+    }
     MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 256 / GEMM_CL));
     return launch_gemm_t<256, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
   }
@@ -282,7 +321,7 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
   }
   dim3 grid((q_len + ATT_QT * ATT_BQ - 1) / (ATT_QT * ATT_BQ), heads, num_seqs);
   ProfScope ps(CAT_ATTENTION, 4.0 * q_len * (double)kv_len * 64.0 * heads * num_seqs, 0.0, st);
-  attention_kernel<<<grid, ATT_THREADS, ATT_SMEM_BYTES, st>>>(tQ, tKV, tKV, p);
+  MAB_CUDA(launch_pdl(attention_kernel, grid, dim3(ATT_THREADS), ATT_SMEM_BYTES, st, 1, tQ, tKV, tKV, p));
   MAB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -301,14 +340,14 @@ inline int launch_layernorm(const float* x, int rows_out, int C, int group_out, 
                                                (out_mid ? 4.0 : 0.0) + (out_split ? 6.0 : 0.0));
   ProfScope ps(CAT_LAYERNORM, 0.0, bytes, st);
   if (C == 768)
-    layernorm_kernel<6><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
-                                                 b2, eps, ob, out_f32, out_mid, os);
+    MAB_CUDA(launch_pdl(layernorm_kernel<6>, dim3(grid), dim3(block), 0, st, 1, x, rows_out, group_out,
+                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os));
   else if (C == 1024)
-    layernorm_kernel<8><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
-                                                 b2, eps, ob, out_f32, out_mid, os);
+    MAB_CUDA(launch_pdl(layernorm_kernel<8>, dim3(grid), dim3(block), 0, st, 1, x, rows_out, group_out,
+                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os));
   else if (C == 128)
-    layernorm_kernel<1><<<grid, block, 0, st>>>(x, rows_out, group_out, group_in, skip, w, b, w2,
-                                                 b2, eps, ob, out_f32, out_mid, os);
+    MAB_CUDA(launch_pdl(layernorm_kernel<1>, dim3(grid), dim3(block), 0, st, 1, x, rows_out, group_out,
+                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os));
   else
     return fail(-1, "layernorm: unsupported width %d (supported 128, 768, 1024)", C);
   MAB_CUDA(cudaGetLastError());

@@ -29,6 +29,8 @@ def _ref(A, B, bias, gamma, res, act):
     (777, 3072, 768, 1, False),    # fc1 + exact GELU
     (500, 768, 3072, 0, True),     # fc2
     (1036, 1024, 640, 0, False),   # patch embed (K padded 588 -> 640)
+    (8289, 768, 768, 0, True),     # info-sharing proj at 8 views: 192-wide tiles, two waves
+    (8289, 2304, 768, 0, False),   # info-sharing qkv at 8 views: 192-wide tiles
     (1036, 96, 1024, 0, False),    # DPT 1x1 to 96 channels (N < tile)
     (1036, 1536, 96, 0, False),    # convT as GEMM, K tail (96 = 1.5 k-blocks)
     (1036, 784, 768, 2, False),    # pose head proj + ReLU, N tail (784 = 3*256 + 16)
