@@ -182,6 +182,16 @@ int mab_conv3x3(const void* x, int batch, int H, int W, int C, const void* w_pac
                 const float* bias, const void* res1, const void* res2, int act, void* out_bf16,
                 void* out_relu, void* stream);
 int mab_pack_conv3_weight(const float* w_oihw, int Cout, int Cin, void* out_packed, void* stream);
+/* TF32 variants for the reference's fp32 regions (model.py:1377): fp32 row-major / NHWC operands,
+ * fp32 output, out = act(A B^T + bias) + res (act_post = 1: act(A B^T + bias + res)).
+ * Conv weight packed [Cout, 9, Cpad] fp32 with Cpad = the activation's (padded) channel count. */
+int mab_gemm_tf32(const float* A, const float* B, int M, int N, int K, const float* bias,
+                  const float* res_f32, int act, int act_post, float* out_f32, void* stream);
+int mab_pack_conv3_weight_f32(const float* w_oihw, int Cout, int Cin, int Cpad, float* out_packed,
+                              void* stream);
+int mab_conv3x3_tf32(const float* x, int batch, int H, int W, int C, const float* w_packed, int Cout,
+                     const float* bias, const float* res_f32, int act, int act_post, float* out_f32,
+                     void* stream);
 int mab_resize_bilinear(const void* x, int batch, int Hi, int Wi, int C, int Hv, int Wv, int Ho,
                         int Wo, void* out, void* out_relu, void* stream);
 int mab_posembed_resize(const float* pos, int grid, int C, int h, int w, float* out, void* stream);

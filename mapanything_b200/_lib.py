@@ -72,6 +72,9 @@ SYMBOLS = {
     "mab_attention_carry": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _i, _i, _vp]),
     "mab_conv3x3": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
     "mab_pack_conv3_weight": (_i, [_vp, _i, _i, _vp, _vp]),
+    "mab_gemm_tf32": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp]),
+    "mab_pack_conv3_weight_f32": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "mab_conv3x3_tf32": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "mab_resize_bilinear": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "mab_posembed_resize": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "mab_edge_mask": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp, _vp]),

@@ -97,7 +97,7 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows_out, int 
 // ----------------------------------------------------------------------------------------------
 __global__ void patch_im2col_kernel(const float* __restrict__ img, int views, int H, int W, int nch,
                                     int nhwc, int KP, const float* __restrict__ view_norm, int log_mode,
-                                    __nv_bfloat16* __restrict__ out) {
+                                    __nv_bfloat16* __restrict__ out, float* __restrict__ out_f32) {
   const int h = H / 14, w = W / 14;
   const long long total = (long long)views * h * w * KP;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -114,7 +114,8 @@ __global__ void patch_im2col_kernel(const float* __restrict__ img, int views, in
       if (view_norm) val = val / view_norm[v];
       if (log_mode) val = copysignf(log1pf(fabsf(val)), val);
     }
-    out[i] = __float2bfloat16(val);
+    if (out) out[i] = __float2bfloat16(val);
+    if (out_f32) out_f32[i] = val;  // fp32 operand of the TF32 geometric-input encoders
   }
 }
 

@@ -218,7 +218,10 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
 // operand reads instead of 16 + BN/2 KB: a single-CTA 128x256 tile is bound by shared-memory
 // bandwidth (TMA writes + UMMA operand reads ~192 B/clk against 128 B/clk), not by the tensor core
 // (measured: 44 % of peak in the main loop, independent of L2 traffic).
-template <int BN, int STAGES, int MODE, int EPI, int CL>
+// TF = 1: fp32 operands consumed as TF32 (kind::tf32) for the reference's fp32/TF32 regions
+// (geometric-input encoders, model.py:1377): a k-block is 32 fp32 = the same 128-byte swizzled rows,
+// so the pipeline, descriptors and byte counts are those of the bf16 kernel.
+template <int BN, int STAGES, int MODE, int EPI, int CL, int TF = 0>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             GemmShape shp, GemmEpilogue ep, RegressEpilogue rg) {
@@ -255,7 +258,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   // stores are predicated off) so that every CTA of a cluster runs the same number of tiles
   auto tile_m = [&](int tile) { return (tile % num_mg) * CL + crank; };
   auto tile_n = [&](int tile) { return tile / num_mg; };
-  const int num_kb = (MODE == MODE_CONV3) ? 9 * shp.cblocks : (shp.K + GEMM_BK - 1) / GEMM_BK;
+  constexpr int BKE = TF ? GEMM_BK / 2 : GEMM_BK;  // elements per 128-byte k-block row
+  const int num_kb = (MODE == MODE_CONV3) ? 9 * shp.cblocks : (shp.K + BKE - 1) / BKE;
   constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128
                                  : (2 * BN <= 256) ? 256 : 512;
 
@@ -308,18 +312,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (MODE == MODE_CONV3) {
             const int tap = kb / shp.cblocks, cb = kb - tap * shp.cblocks;
             const int dy = tap / 3 - 1, dx = tap % 3 - 1;
-            tma_load_4d_cg2(sa, &tmA, fb, cb * GEMM_BK, cx + dx, cy + dy, cn);
+            tma_load_4d_cg2(sa, &tmA, fb, cb * BKE, cx + dx, cy + dy, cn);
           } else {
-            tma_load_2d_cg2(sa, &tmA, fb, kb * GEMM_BK, m_blk * GEMM_BM);
+            tma_load_2d_cg2(sa, &tmA, fb, kb * BKE, m_blk * GEMM_BM);
           }
-          tma_load_2d_cg2(sb, &tmB, fb, kb * GEMM_BK, n_blk * BN + crank * (BN / 2));
+          tma_load_2d_cg2(sb, &tmB, fb, kb * BKE, n_blk * BN + crank * (BN / 2));
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1 && crank == 0) {
     // ================================ MMA issuer (leader CTA) ================================
-    constexpr uint32_t IDESC = make_idesc_bf16(2 * GEMM_BM, BN);
+    constexpr uint32_t IDESC = TF ? make_idesc_tf32(2 * GEMM_BM, BN) : make_idesc_bf16(2 * GEMM_BM, BN);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
@@ -339,9 +343,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const uint32_t sb = sa + SM::A_BYTES;
 #pragma unroll
           for (int k = 0; k < GEMM_BK / 16; ++k) {
-            // +32 bytes per UMMA_K=16 step inside the 128B swizzle atom
-            umma_ss2(d_tmem, make_sw128_desc(sa + k * 32), make_sw128_desc(sb + k * 32), IDESC,
-                     (kb | k) != 0);
+            // +32 bytes per UMMA_K step (16 bf16 or 8 tf32) inside the 128B swizzle atom
+            if (TF)
+              umma_ss2_tf32(d_tmem, make_sw128_desc(sa + k * 32), make_sw128_desc(sb + k * 32), IDESC,
+                            (kb | k) != 0);
+            else
+              umma_ss2(d_tmem, make_sw128_desc(sa + k * 32), make_sw128_desc(sb + k * 32), IDESC,
+                       (kb | k) != 0);
           }
           umma_commit2(&empty_bar[stage]);                      // frees the smem slot in both CTAs
           if (kb == num_kb - 1) umma_commit2(&tfull_bar[acc]);  // accumulator complete, both CTAs

@@ -153,16 +153,18 @@ inline EncodeTiledFn get_encode_fn() {
 
 // bf16 row-major [rows, cols] (row pitch ld elements), box = [box_rows, 64 cols], 128B swizzle
 inline int make_tmap_2d(CUtensorMap* m, const void* ptr, long long rows, long long cols,
-                        long long ld, int box_rows) {
+                        long long ld, int box_rows, bool f32 = false) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return fail(-2, "cuTensorMapEncodeTiled entry point not available");
-  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * 2) & 15))
+  const int es = f32 ? 4 : 2;  // fp32 operands (TF32 GEMM): 32 elements per 128-byte box row
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * es) & 15))
     return fail(-1, "TMA operand must be 16B aligned with a 16B-multiple row pitch (ld=%lld)", ld);
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * es};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / es), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box,
+  CUresult r = fn(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(ptr), dims, strides, box,
                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(-3, "cuTensorMapEncodeTiled(2d) failed: %d", (int)r);
@@ -170,16 +172,19 @@ inline int make_tmap_2d(CUtensorMap* m, const void* ptr, long long rows, long lo
 }
 
 // bf16 NHWC [batch,H,W,C], box = [1, CONV_TH, CONV_TW, 64], 128B swizzle
-inline int make_tmap_nhwc(CUtensorMap* m, const void* ptr, int batch, int H, int W, int C) {
+inline int make_tmap_nhwc(CUtensorMap* m, const void* ptr, int batch, int H, int W, int C,
+                          bool f32 = false) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return fail(-2, "cuTensorMapEncodeTiled entry point not available");
-  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((C * 2) & 15))
-    return fail(-1, "NHWC TMA operand must be 16B aligned with C a multiple of 8 (C=%d)", C);
+  const cuuint64_t es = f32 ? 4 : 2;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((C * es) & 15))
+    return fail(-1, "NHWC TMA operand must be 16B aligned with a 16B-multiple pixel pitch (C=%d)", C);
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)batch};
-  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-  cuuint32_t box[4] = {64, CONV_TW, CONV_TH, 1};
+  cuuint64_t strides[3] = {(cuuint64_t)C * es, (cuuint64_t)W * C * es, (cuuint64_t)H * W * C * es};
+  cuuint32_t box[4] = {(cuuint32_t)(128 / es), CONV_TW, CONV_TH, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box,
+  CUresult r = fn(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                  const_cast<void*>(ptr), dims, strides, box,
                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(-3, "cuTensorMapEncodeTiled(4d) failed: %d", (int)r);
@@ -205,11 +210,11 @@ inline int ew_grid(long long total, int block = 256) {
 // ---- GEMM / conv launchers ---------------------------------------------------------------------
 constexpr int GEMM_CL = 2;  // CTA pair (cta_group::2): one 256 x BN tile per cluster (gemm.cuh)
 
-template <int BN, int STAGES, int MODE, int EPI, int CL>
+template <int BN, int STAGES, int MODE, int EPI, int CL, int TF = 0>
 inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const GemmShape& shp,
                          const GemmEpilogue& ep, const RegressEpilogue& rg, cudaStream_t st) {
   using SM = GemmSmem<BN, STAGES>;
-  auto kern = gemm_kernel<BN, STAGES, MODE, EPI, CL>;
+  auto kern = gemm_kernel<BN, STAGES, MODE, EPI, CL, TF>;
   static bool attr_done = false;
   if (!attr_done) {
     MAB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::TOTAL));
@@ -279,6 +284,30 @@ inline int launch_conv3(const void* x, int batch, int H, int W, int C, const voi
   }
   MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 128 / GEMM_CL));
   return launch_gemm_t<128, 8, MODE_CONV3, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
+}
+
+// ---- TF32 variants for the reference's fp32 regions: fp32 operands, same tiles --------------------
+// C[M,N] = epilogue(A[M,K] B[N,K]^T), A/B fp32 row-major, K a multiple of 4
+inline int launch_gemm_tf32(const float* A, long long lda, const float* B, long long ldb, int M, int N,
+                            int K, const GemmEpilogue& ep, cudaStream_t st) {
+  MAB_ARG(M > 0 && N > 0 && K > 0 && N % 4 == 0, "bad TF32 GEMM shape");
+  CUtensorMap tA, tB;
+  GemmShape shp{M, N, K, 0, 0, 0, 0, 0};
+  RegressEpilogue rg{};
+  MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM, true));
+  MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 256 / GEMM_CL, true));
+  return launch_gemm_t<256, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL, 1>(tA, tB, shp, ep, rg, st);
+}
+// 3x3/s1/p1 conv, x NHWC fp32 [batch,H,W,C], w packed fp32 [Cout, 9*Cpad] (Cpad = ceil32(C))
+inline int launch_conv3_tf32(const float* x, int batch, int H, int W, int C, int Creal, const float* w,
+                             int Cout, const GemmEpilogue& ep, cudaStream_t st) {
+  const int cblocks = (C + 31) / 32;
+  CUtensorMap tA, tB;
+  GemmShape shp{0, Cout, 9 * cblocks * 32, batch, H, W, cblocks, Creal};
+  RegressEpilogue rg{};
+  MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, C, true));
+  MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 32, 9LL * cblocks * 32, 256 / GEMM_CL, true));
+  return launch_gemm_t<256, 6, MODE_CONV3, EPI_GENERIC, GEMM_CL, 1>(tA, tB, shp, ep, rg, st);
 }
 
 // last conv of the dense head with the fused 1x1 + adaptor + pointmap epilogue (C = Cout = 128)

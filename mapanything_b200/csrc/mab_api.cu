@@ -16,14 +16,18 @@ typedef __nv_bfloat16 bf16;
 namespace {
 
 // fp32 [rows, cols] -> bf16 [rows, ldo] zero padded
+__device__ __forceinline__ void store_as(bf16* p, float v) { *p = __float2bfloat16(v); }
+__device__ __forceinline__ void store_as(float* p, float v) { *p = v; }
+
+template <typename T>
 __global__ void pack_matrix_kernel(const float* __restrict__ w, int rows, int cols, int ldo,
-                                   bf16* __restrict__ out) {
+                                   T* __restrict__ out) {
   const long long total = (long long)rows * ldo;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = i % ldo;
     const long long r = i / ldo;
-    out[i] = __float2bfloat16(c < cols ? w[r * cols + c] : 0.f);
+    store_as(out + i, c < cols ? w[r * cols + c] : 0.f);
   }
 }
 
@@ -45,15 +49,16 @@ __global__ void pack_matrix_split_kernel(const float* __restrict__ w, int rows, 
 }
 
 // conv weight [Cout, Cin, 3, 3] fp32 -> [Cout, 9, Cpad] bf16 (tap = ky*3+kx), zero padded channels
+template <typename T>
 __global__ void pack_conv3_kernel(const float* __restrict__ w, int Cout, int Cin, int Cpad,
-                                  bf16* __restrict__ out) {
+                                  T* __restrict__ out) {
   const long long total = (long long)Cout * 9 * Cpad;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = i % Cpad;
     const int tap = (i / Cpad) % 9;
     const int co = i / ((long long)Cpad * 9);
-    out[i] = __float2bfloat16(c < Cin ? w[((long long)co * Cin + c) * 9 + tap] : 0.f);
+    store_as(out + i, c < Cin ? w[((long long)co * Cin + c) * 9 + tap] : 0.f);
   }
 }
 
@@ -188,6 +193,28 @@ extern "C" int mab_conv3x3(const void* x, int batch, int H, int W, int C, const 
   return launch_conv3(x, batch, H, W, C, w_packed, Cout, ep, (cudaStream_t)stream);
 }
 
+// ---- TF32 variants (fp32 operands) used by the geometric-input encoders ---------------------------
+extern "C" int mab_gemm_tf32(const float* A, const float* B, int M, int N, int K, const float* bias,
+                             const float* res_f32, int act, int act_post, float* out_f32, void* stream) {
+  GemmEpilogue ep{};
+  ep.bias = bias; ep.res_f32 = res_f32; ep.out_f32 = out_f32; ep.ldo = N; ep.act = act; ep.act_post = act_post;
+  return launch_gemm_tf32(A, K, B, K, M, N, K, ep, (cudaStream_t)stream);
+}
+extern "C" int mab_pack_conv3_weight_f32(const float* w, int Cout, int Cin, int Cpad, float* out, void* stream) {
+  MAB_ARG(Cpad >= Cin && Cpad % 32 == 0, "Cpad must be a multiple of 32 and >= Cin");
+  pack_conv3_kernel<<<ew_grid((long long)Cout * 9 * Cpad), 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, Cpad, out);
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int mab_conv3x3_tf32(const float* x, int batch, int H, int W, int C, const float* w_packed,
+                                int Cout, const float* bias, const float* res_f32, int act, int act_post,
+                                float* out_f32, void* stream) {
+  MAB_ARG(C % 32 == 0, "C must be a multiple of 32 (pad the channels)");
+  GemmEpilogue ep{};
+  ep.bias = bias; ep.res_f32 = res_f32; ep.out_f32 = out_f32; ep.ldo = Cout; ep.act = act; ep.act_post = act_post;
+  return launch_conv3_tf32(x, batch, H, W, C, C, w_packed, Cout, ep, (cudaStream_t)stream);
+}
+
 extern "C" int mab_resize_bilinear(const void* x, int batch, int Hi, int Wi, int C, int Hv, int Wv,
                                    int Ho, int Wo, void* out, void* out_relu, void* stream) {
   MAB_ARG(C % 8 == 0, "C must be a multiple of 8");
@@ -306,6 +333,7 @@ struct mab_handle {
   bool finalized = false;
   std::map<std::string, RawTensor> raw;       // fp32 device copies, canonical keys
   std::map<std::string, bf16*> packed;        // bf16 GEMM / conv operands
+  std::map<std::string, float*> packed32;     // fp32 (TF32) GEMM / conv operands, padded layouts
   std::map<std::string, float*> extra;        // derived fp32 tensors (tiled biases)
   std::vector<void*> owned;
   Plan plan;
@@ -317,6 +345,10 @@ struct mab_handle {
   const bf16* P(const std::string& k) const {
     auto it = packed.find(k);
     return it == packed.end() ? nullptr : it->second;
+  }
+  const float* P32(const std::string& k) const {
+    auto it = packed32.find(k);
+    return it == packed32.end() ? nullptr : it->second;
   }
 };
 
@@ -438,7 +470,7 @@ int pack_linear(mab_handle* h, const std::string& key, int ld_pad, cudaStream_t 
   bf16* out;
   MAB_CUDA(cudaMalloc(&out, (size_t)rows * ld * sizeof(bf16)));
   h->owned.push_back(out);
-  pack_matrix_kernel<<<ew_grid((long long)rows * ld), 256, 0, st>>>(t.p, rows, cols, ld, out);
+  pack_matrix_kernel<bf16><<<ew_grid((long long)rows * ld), 256, 0, st>>>(t.p, rows, cols, ld, out);
   MAB_CUDA(cudaGetLastError());
   h->packed[key] = out;
   return 0;
@@ -468,9 +500,39 @@ int pack_conv3(mab_handle* h, const std::string& key, cudaStream_t st) {
   bf16* out;
   MAB_CUDA(cudaMalloc(&out, (size_t)Cout * 9 * Cpad * sizeof(bf16)));
   h->owned.push_back(out);
-  pack_conv3_kernel<<<ew_grid((long long)Cout * 9 * Cpad), 256, 0, st>>>(t.p, Cout, Cin, Cpad, out);
+  pack_conv3_kernel<bf16><<<ew_grid((long long)Cout * 9 * Cpad), 256, 0, st>>>(t.p, Cout, Cin, Cpad, out);
   MAB_CUDA(cudaGetLastError());
   h->packed[key] = out;
+  return 0;
+}
+
+// fp32 operands of the TF32 kernels: [rows, ld] zero padded / [Cout, 9, ceil32(Cin) or cpad]
+int pack_linear_f32(mab_handle* h, const std::string& key, int ld_pad, cudaStream_t st) {
+  auto it = h->raw.find(key);
+  if (it == h->raw.end()) return fail(-4, "missing weight %s", key.c_str());
+  const RawTensor& t = it->second;
+  const int rows = (int)t.shape[0];
+  const int cols = (int)(t.numel / rows);
+  const int ld = ld_pad > 0 ? ld_pad : cols;
+  float* out;
+  MAB_CUDA(cudaMalloc(&out, (size_t)rows * ld * sizeof(float)));
+  h->owned.push_back(out);
+  pack_matrix_kernel<float><<<ew_grid((long long)rows * ld), 256, 0, st>>>(t.p, rows, cols, ld, out);
+  MAB_CUDA(cudaGetLastError());
+  h->packed32[key] = out;
+  return 0;
+}
+int pack_conv3_f32(mab_handle* h, const std::string& key, int cpad, cudaStream_t st) {
+  auto it = h->raw.find(key);
+  if (it == h->raw.end()) return fail(-4, "missing weight %s", key.c_str());
+  const RawTensor& t = it->second;
+  const int Cout = (int)t.shape[0], Cin = (int)t.shape[1];
+  float* out;
+  MAB_CUDA(cudaMalloc(&out, (size_t)Cout * 9 * cpad * sizeof(float)));
+  h->owned.push_back(out);
+  pack_conv3_kernel<float><<<ew_grid((long long)Cout * 9 * cpad), 256, 0, st>>>(t.p, Cout, Cin, cpad, out);
+  MAB_CUDA(cudaGetLastError());
+  h->packed32[key] = out;
   return 0;
 }
 
@@ -541,14 +603,15 @@ extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
   for (const char* enc : {"ray_dirs_encoder", "depth_encoder"}) {
     const std::string e = enc;
     if (!h->F(e + ".conv_in.weight")) continue;
-    MAB_TRY(pack_conv3(h, e + ".conv_in.weight", st));
+    // fp32 in the reference (autocast off, TF32 on GPU; model.py:1377): kept as fp32/TF32 operands
+    MAB_TRY(pack_conv3_f32(h, e + ".conv_in.weight", e == "depth_encoder" ? 256 : 640, st));
     for (int i = 0; i < 2; ++i) {
       const std::string r = e + ".encoder." + std::to_string(i);
-      MAB_TRY(pack_conv3(h, r + ".conv1.weight", st));
-      MAB_TRY(pack_conv3(h, r + ".conv2.weight", st));
-      MAB_TRY(pack_linear(h, r + ".shortcut.weight", i == 0 ? 640 : 0, st));
+      MAB_TRY(pack_conv3_f32(h, r + ".conv1.weight", i == 0 ? 640 : 768, st));
+      MAB_TRY(pack_conv3_f32(h, r + ".conv2.weight", i == 0 ? 768 : 1024, st));
+      MAB_TRY(pack_linear_f32(h, r + ".shortcut.weight", i == 0 ? 640 : 0, st));
     }
-    MAB_TRY(pack_linear(h, e + ".encoder.2.weight", 0, st));
+    MAB_TRY(pack_linear_f32(h, e + ".encoder.2.weight", 0, st));
   }
   // required fp32 tensors that are used as-is
   for (const char* k : {"encoder.model.cls_token", "encoder.model.pos_embed", "encoder.model.norm.weight",
@@ -674,42 +737,56 @@ namespace {
 // DenseRepresentationEncoder (dense_rep_encoder.py:234-287) on the token-major PixelUnshuffle of
 // the input: conv3x3 -> 2 x ResidualBlock(conv3x3, GELU, conv3x3, + 1x1 shortcut, GELU) -> conv1x1
 // -> LayerNorm; the result is accumulated into p.geo_sum scaled by the per-view mask.
-int dense_rep_encode(Ctx& c, const std::string& e, const bf16* unshuffled, int cin_pad, const float* mask,
-                     bool first, Bump& scratch) {
+// fp32 activations, TF32 tensor-core contractions (the reference's precision for this region).
+// `scratch` holds 3840 floats per token: R0 640 | R1 640 | R2 768 | R3 768 | R5 1024, where the
+// second block's shortcut/output reuses R0+R1 (dead by then).
+int dense_rep_encode(Ctx& c, const std::string& e, float* scratch, int cin_pad, int cin_real, const float* mask,
+                     bool first) {
   mab_handle* h = c.h;
   Plan& p = h->plan;
   const int V = p.V, hh = p.h, ww = p.w;
   const long long VT = (long long)V * p.T;
-  bf16* a0 = scratch.take<bf16>(VT * 640);   // conv_in output, 588 channels padded to 640
-  bf16* sc0 = scratch.take<bf16>(VT * 768);
-  bf16* b0 = scratch.take<bf16>(VT * 768);
-  bf16* x1 = scratch.take<bf16>(VT * 768);
-  bf16* sc1 = scratch.take<bf16>(VT * 1024);
-  bf16* b1 = scratch.take<bf16>(VT * 1024);
-  bf16* x2 = scratch.take<bf16>(VT * 1024);
-  float* y = scratch.take<float>(VT * 1024);
-  MAB_CUDA(cudaMemsetAsync(a0, 0, (size_t)VT * 640 * sizeof(bf16), c.st));  // zero the 52 pad channels
-  GemmEpilogue ep{};
-  ep.bias = h->F(e + ".conv_in.bias"); ep.out_bf16 = a0; ep.ldo = 640; ep.act = ACT_NONE;
-  MAB_TRY(launch_conv3(unshuffled, V, hh, ww, cin_pad, h->P(e + ".conv_in.weight"), 588, ep, c.st));
-  const bf16* x = a0;
-  int cin = 640;
-  bf16* scb[2] = {sc0, sc1}; bf16* bb[2] = {b0, b1}; bf16* xo[2] = {x1, x2};
+  float* unsh = scratch;                       // R0 [VT, cin_pad] (written by the caller)
+  float* a0 = scratch + VT * 640;              // R1 conv_in output, 588 channels padded to 640
+  float* x1 = a0 + VT * 640;                   // R2 shortcut of block 0, then its output (in place)
+  float* b0 = x1 + VT * 768;                   // R3 conv1 output of block 0
+  float* b1 = b0 + VT * 768;                   // R5 conv1 output of block 1, later the 1x1 output
+  float* x2 = scratch;                         // R0+R1: shortcut of block 1, then its output
+  float* y = b1;
+  MAB_CUDA(cudaMemsetAsync(a0, 0, (size_t)VT * 640 * sizeof(float), c.st));  // zero the 52 pad channels
+  auto conv = [&](const float* x, int C, int Creal, const std::string& key, int Cout, const float* bias,
+                  int act, const float* res, int act_post, float* out, int ldo) {
+    const float* W = h->P32(key);
+    if (!W) return fail(-4, "weight %s was not packed", key.c_str());
+    GemmEpilogue ep{};
+    ep.bias = bias; ep.out_f32 = out; ep.ldo = ldo; ep.act = act; ep.res_f32 = res; ep.act_post = act_post;
+    return launch_conv3_tf32(x, V, hh, ww, C, Creal, W, Cout, ep, c.st);
+  };
+  auto lin = [&](const float* x, int K, int lda, const std::string& key, int N, const float* bias, float* out) {
+    const float* W = h->P32(key);
+    if (!W) return fail(-4, "weight %s was not packed", key.c_str());
+    GemmEpilogue ep{};
+    ep.bias = bias; ep.out_f32 = out; ep.ldo = N;
+    return launch_gemm_tf32(x, lda, W, K, (int)VT, N, K, ep, c.st);
+  };
+  MAB_TRY(conv(unsh, cin_pad, cin_real, e + ".conv_in.weight", 588, h->F(e + ".conv_in.bias"), ACT_NONE,
+               nullptr, 0, a0, 640));
+  const float* x = a0;
+  int cin = 640, creal = 588;
+  float* xo[2] = {x1, x2};
+  float* bb[2] = {b0, b1};
   const int cout[2] = {768, 1024};
   for (int i = 0; i < 2; ++i) {
     const std::string r = e + ".encoder." + std::to_string(i);
-    MAB_TRY(c.linear(x, (int)VT, cin, cin, r + ".shortcut.weight", cout[i], h->F(r + ".shortcut.bias"),
-                     ACT_NONE, nullptr, nullptr, nullptr, scb[i], nullptr, cin));
-    MAB_TRY(c.conv3(x, V, hh, ww, cin, r + ".conv1.weight", cout[i], h->F(r + ".conv1.bias"), ACT_GELU,
-                    nullptr, nullptr, bb[i], nullptr));
-    GemmEpilogue e2{};
-    e2.bias = h->F(r + ".conv2.bias"); e2.res1 = scb[i]; e2.out_bf16 = xo[i]; e2.ldo = cout[i];
-    e2.act = ACT_GELU; e2.act_post = 1;
-    MAB_TRY(launch_conv3(bb[i], V, hh, ww, cout[i], h->P(r + ".conv2.weight"), cout[i], e2, c.st));
-    x = xo[i]; cin = cout[i];
+    MAB_TRY(conv(x, cin, creal, r + ".conv1.weight", cout[i], h->F(r + ".conv1.bias"), ACT_GELU, nullptr, 0,
+                 bb[i], cout[i]));
+    // block 1 writes its shortcut over R0+R1 = block 0's input, so conv1 above must read x first
+    MAB_TRY(lin(x, cin, cin, r + ".shortcut.weight", cout[i], h->F(r + ".shortcut.bias"), xo[i]));
+    MAB_TRY(conv(bb[i], cout[i], cout[i], r + ".conv2.weight", cout[i], h->F(r + ".conv2.bias"), ACT_GELU,
+                 xo[i], 1, xo[i], cout[i]));
+    x = xo[i]; cin = creal = cout[i];
   }
-  MAB_TRY(c.linear(x, (int)VT, 1024, 1024, e + ".encoder.2.weight", 1024, h->F(e + ".encoder.2.bias"),
-                   ACT_NONE, nullptr, nullptr, y, nullptr));
+  MAB_TRY(lin(x, 1024, 1024, e + ".encoder.2.weight", 1024, h->F(e + ".encoder.2.bias"), y));
   MAB_TRY(launch_layernorm(y, (int)VT, 1024, (int)VT, (int)VT, 0, h->F(e + ".norm_layer.weight"),
                            h->F(e + ".norm_layer.bias"), nullptr, nullptr, 1e-6f, nullptr, y, nullptr, c.st));
   MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
@@ -773,23 +850,22 @@ int encode_geometric_inputs(Ctx& c, const mab_inputs* in) {
   MAB_CUDA(cudaGetLastError());
   // the encoder's activation buffers (ln | qkv | att | hid, contiguous in the plan) are free here
   bool first_dense = true, first_vec = true;
+  float* scratch = reinterpret_cast<float*>(p.ln);
+  if ((size_t)VT * 3840 * sizeof(float) > (size_t)((uint8_t*)(p.hid + p.Lenc * 4 * D) - (uint8_t*)p.ln))
+    return fail(-5, "geometric encoder scratch overflows the encoder activation buffers");
   for (int which = 0; which < 2; ++which) {
     if ((which == 0 && !has_rays) || (which == 1 && !has_depth)) continue;
-    Bump scratch; scratch.base = reinterpret_cast<uint8_t*>(p.ln);
     const int cpad = which == 0 ? 640 : 256;
-    bf16* unsh = scratch.take<bf16>(VT * cpad);
     if (which == 0)
       MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
                  patch_im2col_kernel<<<ew_grid(VT * cpad), 256, 0, c.st>>>(in->ray_dirs, V, p.H, p.W, 3, 1, cpad,
-                                                                          nullptr, 0, unsh));
+                                                                          nullptr, 0, nullptr, scratch));
     else
       MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
                  patch_im2col_kernel<<<ew_grid(VT * cpad), 256, 0, c.st>>>(in->depth_along_ray, V, p.H, p.W, 1, 0,
-                                                                          cpad, depth_norm, 1, unsh));
-    MAB_TRY(dense_rep_encode(c, which == 0 ? "ray_dirs_encoder" : "depth_encoder", unsh, cpad,
-                             which == 0 ? m_ray : m_depth, first_dense, scratch));
-    if (scratch.off > (size_t)((uint8_t*)(p.hid + p.Lenc * 4 * D) - (uint8_t*)p.ln))
-      return fail(-5, "geometric encoder scratch overflows the encoder activation buffers");
+                                                                          cpad, depth_norm, 1, nullptr, scratch));
+    MAB_TRY(dense_rep_encode(c, which == 0 ? "ray_dirs_encoder" : "depth_encoder", scratch, cpad,
+                             which == 0 ? 588 : 196, which == 0 ? m_ray : m_depth, first_dense));
     first_dense = false;
   }
   if (has_depth) {
@@ -829,12 +905,12 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
   const int V = p.V, T = p.T, D = cf.enc_dim;
   const long long VT = (long long)V * T;
   const bool multimodal = in->ray_dirs || in->depth_along_ray || in->cam_quats;
-  if (multimodal && !h->P("ray_dirs_encoder.conv_in.weight"))
+  if (multimodal && !h->P32("ray_dirs_encoder.conv_in.weight"))
     return fail(-4, "geometric inputs given but the checkpoint has no geometric encoders");
 
   MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
              patch_im2col_kernel<<<ew_grid(VT * 640), 256, 0, c.st>>>(in->images, V, p.H, p.W, 3, 0, 640,
-                                                                      nullptr, 0, p.im2col));
+                                                                      nullptr, 0, p.im2col, nullptr));
   MAB_TRY(c.linear(p.im2col, (int)VT, 640, 640, "encoder.model.patch_embed.proj.weight", D,
                    h->F("encoder.model.patch_embed.proj.bias"), ACT_NONE, nullptr, nullptr, p.patch,
                    nullptr, nullptr, 640));

@@ -114,3 +114,18 @@ def out_of_tolerance(report, tol_dense, tol_pose_deg, tol_small=None, min_mask_a
         elif v > max(tol_dense, y):
             bad.append((k, v))
     return bad
+
+
+class strict_fp32:
+    """Context manager: no TF32 in cuBLAS / cuDNN, so that an oracle run on the GPU is true fp32
+    (PyTorch allows TF32 cuDNN convolutions by default, which is ~1e-3 noise of its own)."""
+
+    def __enter__(self):
+        self.prev = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+        torch.backends.cuda.matmul.allow_tf32 = False
+        torch.backends.cudnn.allow_tf32 = False
+        return self
+
+    def __exit__(self, *exc):
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = self.prev
+        return False

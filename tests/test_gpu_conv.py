@@ -109,3 +109,53 @@ def test_edge_mask_matches_numpy():
         total_diff += diff
         assert 0.05 < ref.mean() < 0.95, "test scene should exercise both mask values"
     assert total_diff <= 2, f"{total_diff} mask pixels differ from numpy"
+
+
+@pytest.mark.parametrize("M,N,K,act,post", [(300, 768, 640, 0, 0), (2072, 1024, 1024, 0, 0),
+                                             (1037, 1024, 768, 1, 1), (128, 256, 32, 1, 0)])
+def test_gemm_tf32(M, N, K, act, post):
+    """fp32-operand GEMM on the TF32 tensor-core path (geometric-input encoders' 1x1 convs) vs torch
+    fp32: TF32 keeps 10 mantissa bits, so the error budget is ~1e-3 of bf16's."""
+    from tests import gpu_helpers as g
+
+    torch.manual_seed(M + N)
+    A = torch.randn(M, K, device="cuda")
+    B = torch.randn(N, K, device="cuda") / K ** 0.5
+    bias = torch.randn(N, device="cuda") * 0.1
+    res = torch.randn(M, N, device="cuda")
+    out = torch.empty(M, N, device="cuda")
+    g.check(g.lib().mab_gemm_tf32(g.ptr(A), g.ptr(B), M, N, K, g.ptr(bias), g.ptr(res), act, post, g.ptr(out),
+                                  g.stream()))
+    torch.cuda.synchronize()
+    y = A.double() @ B.double().t() + bias.double()
+    if post:
+        ref = F.gelu(y + res.double()) if act else y + res.double()
+    else:
+        ref = (F.gelu(y) if act else y) + res.double()
+    e = g.rel(out.double(), ref)
+    assert e < 1.5e-3, f"tf32 gemm rel-L2 {e}"
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cpad,Cout", [(1, 8, 16, 32, 32, 256), (2, 5, 7, 196, 256, 588),
+                                                  (1, 28, 37, 588, 640, 768)])
+def test_conv3x3_tf32(B, H, W, Cin, Cpad, Cout):
+    """fp32 NHWC implicit-GEMM conv on the TF32 path with padded channels, GELU after the residual
+    (ResidualBlock, dense_rep_encoder.py:31-52), in place on the residual buffer."""
+    from tests import gpu_helpers as g
+
+    torch.manual_seed(H * W + Cin)
+    x = torch.zeros(B, H, W, Cpad, device="cuda")
+    x[..., :Cin] = torch.randn(B, H, W, Cin, device="cuda")
+    w = torch.randn(Cout, Cin, 3, 3, device="cuda") / (9 * Cin) ** 0.5
+    b = torch.randn(Cout, device="cuda") * 0.1
+    res = torch.randn(B, H, W, Cout, device="cuda")
+    wp = torch.empty(Cout, 9, Cpad, device="cuda")
+    g.check(g.lib().mab_pack_conv3_weight_f32(g.ptr(w), Cout, Cin, Cpad, g.ptr(wp), g.stream()))
+    out = res.clone()
+    g.check(g.lib().mab_conv3x3_tf32(g.ptr(x), B, H, W, Cpad, g.ptr(wp), Cout, g.ptr(b), g.ptr(out), 1, 1,
+                                     g.ptr(out), g.stream()))
+    torch.cuda.synchronize()
+    ref = F.conv2d(x[..., :Cin].double().permute(0, 3, 1, 2), w.double(), b.double(), padding=1).permute(0, 2, 3, 1)
+    ref = F.gelu(ref + res.double())
+    e = g.rel(out.double(), ref)
+    assert e < 1.5e-3, f"tf32 conv rel-L2 {e}"
