@@ -12,6 +12,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     n_views, H, W = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
+    multimodal = len(sys.argv) > 4 and sys.argv[4] == "mm"
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
     dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
@@ -21,22 +22,34 @@ def main():
     model = MapAnything(device=dev, head_chunk=3)
     model.load_state_dict(synthetic.synthetic_state_dict())
     views = synthetic.synthetic_views(n_views, H, W, seed=3)
+    if multimodal:  # rays + sparse depth + poses: pose algebra needs view 0 and a scene-wide norm
+        views = synthetic.add_multimodal_inputs(views, seed=4)
     lo, hi = parallel.shard_views(n_views, world, rank)
     mine = model.infer([dict(v) for v in views[lo:hi]], view_range=(lo, hi), total_views=n_views)
     full = model.infer([dict(v) for v in views])  # every rank also runs the whole scene on its own GPU
     torch.cuda.synchronize()
-    worst = 0.0
+    worst, per_key = 0.0, {}
     for p, r in zip(mine, full[lo:hi]):
         for k in ("pts3d_cam", "ray_directions", "conf", "non_ambiguous_mask_logits", "cam_trans", "cam_quats",
                   "metric_scaling_factor", "intrinsics"):
             a, b = p[k].double(), r[k].double()
-            worst = max(worst, float((a - b).norm() / (b.norm() + 1e-30)))
+            if k == "pts3d_cam":  # infer() zeroes masked pixels: compare where both runs keep the pixel
+                both = (p["mask"] & r["mask"]).double()
+                a, b = a * both, b * both
+            e = float((a - b).norm() / (b.norm() + 1e-30))
+            # mask logits are a near-cancelling sum: 3.5e-2 like tests/test_gpu_e2e.py TOL_MASK_LOGITS
+            # intrinsics: least-squares fit through <= 7x10 ray samples on a 70x98 image, amplifies the
+            # ray noise (2-3e-3) about 6x (tests/helpers.py POSE_DEPENDENT_KEYS)
+            scale = {"non_ambiguous_mask_logits": 3.5, "intrinsics": 3.0}.get(k, 1.0)
+            per_key[k] = max(per_key.get(k, 0.0), e)
+            worst = max(worst, e / scale)
         agree = float((p["mask"] == r["mask"]).float().mean())
-        assert agree > 0.97, agree
+        assert agree > 0.95, agree
     t = torch.tensor([worst], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    print(f"rank {rank}: " + " ".join(f"{k}={v:.2e}" for k, v in per_key.items()), flush=True)
     if rank == 0:
-        print(f"sharded-vs-single worst rel-L2 = {t.item():.3e}")
+        print(f"sharded-vs-single worst (tolerance-scaled) rel-L2 = {t.item():.3e}")
     # identical kernels on identical data except for the K/V block order of the global layers; that
     # alone re-draws the bf16 rounding noise of everything downstream (each path is ~4e-3 from fp32,
     # tests/diag_stages.py), so the two runs agree to the bf16 tolerance, not to fp32 round-off

@@ -12,15 +12,15 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("n_views,H,W", [(5, 70, 98), (4, 392, 518)])
-def test_sharded_equals_single(n_views, H, W):
+@pytest.mark.parametrize("n_views,H,W,mode", [(5, 70, 98, "img"), (4, 392, 518, "img"), (5, 70, 98, "mm")])
+def test_sharded_equals_single(n_views, H, W, mode):
     ngpu = torch.cuda.device_count()
     if ngpu < 2:
         pytest.skip("needs >= 2 GPUs")
     world = 2 if n_views < 8 else min(ngpu, 4)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", "29731",
-           os.path.join(ROOT, "tests", "dist_sharded_check.py"), str(n_views), str(H), str(W)]
+           os.path.join(ROOT, "tests", "dist_sharded_check.py"), str(n_views), str(H), str(W), mode]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     print(res.stdout[-2000:], res.stderr[-3000:])
     assert res.returncode == 0
