@@ -137,6 +137,12 @@ int mab_stage_aat_qkv(mab_handle* h, int layer, void** qkv_out, int* rows_out, v
 enum { MAB_RING_FIRST = 1, MAB_RING_LAST = 2 };
 int mab_stage_aat_attend(mab_handle* h, int layer, const void* kv, int kv_rows, int flags,
                          void* stream);
+/* Gather variant of the exchange step: export this rank's K|V rows ([rows, 2*aat_dim] bf16,
+ * contiguous) for the other ranks, and attend against a gathered K|V block of any rank(s).  Same
+ * flags / carried state as mab_stage_aat_attend; blocks may be presented in any order. */
+int mab_stage_aat_export_kv(mab_handle* h, void* dst, void* stream);
+int mab_stage_aat_attend_kv(mab_handle* h, int layer, const void* kv, int kv_rows, int flags,
+                            void* stream);
 /* proj + MLP of block `layer` (+ intermediate taps / final norm) */
 int mab_stage_aat_finish(mab_handle* h, int layer, void* stream);
 /* metric scale from the final scale token (rank owning it); broadcast the float to the others */

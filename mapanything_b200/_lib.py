@@ -55,6 +55,8 @@ SYMBOLS = {
     "mab_stage_encode": (_i, [_vp, C.POINTER(MabInputs), _i, _vp, C.c_size_t, _i, _vp]),
     "mab_stage_aat_qkv": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_i), _vp]),
     "mab_stage_aat_attend": (_i, [_vp, _i, _vp, _i, _i, _vp]),
+    "mab_stage_aat_export_kv": (_i, [_vp, _vp, _vp]),
+    "mab_stage_aat_attend_kv": (_i, [_vp, _i, _vp, _i, _i, _vp]),
     "mab_stage_aat_finish": (_i, [_vp, _i, _vp]),
     "mab_stage_scale_head": (_i, [_vp, _vp, _vp]),
     "mab_stage_heads": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), _vp, _vp]),

@@ -327,17 +327,19 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
                             long long kv_rows_total, int heads, int num_seqs, int q_len, int kv_len,
                             int q_seq_stride, int kv_seq_stride, float scale, void* out, float* lse,
                             cudaStream_t st, float* carry_o = nullptr, float* carry_ml = nullptr,
-                            int carry_in = 0, int carry_out = 0) {
+                            int carry_in = 0, int carry_out = 0, int kv_packed = 0) {
   MAB_ARG(!(carry_in || carry_out) || (carry_o && carry_ml), "carry buffers missing");
   MAB_ARG(heads > 0 && num_seqs > 0 && q_len > 0 && kv_len > 0, "empty attention");
   const int D = heads * 64;
   CUtensorMap tQ, tKV;
   MAB_TRY(make_tmap_2d(&tQ, q_src, q_rows_total, 3LL * D, 3LL * D, ATT_BQ));
-  MAB_TRY(make_tmap_2d(&tKV, kv_src, kv_rows_total, 3LL * D, 3LL * D, ATT_BKV));
+  // kv_packed: kv_src is a [rows, 2*heads*64] K|V buffer (gathered from the other ranks)
+  const long long kv_ld = kv_packed ? 2LL * D : 3LL * D;
+  MAB_TRY(make_tmap_2d(&tKV, kv_src, kv_rows_total, kv_ld, kv_ld, ATT_BKV));
   AttnParams p;
   p.num_seqs = num_seqs; p.heads = heads; p.q_len = q_len; p.kv_len = kv_len;
   p.q_seq_stride = q_seq_stride; p.kv_seq_stride = kv_seq_stride;
-  p.q_col0 = 0; p.k_col0 = D; p.v_col0 = 2 * D;
+  p.q_col0 = 0; p.k_col0 = kv_packed ? 0 : D; p.v_col0 = kv_packed ? D : 2 * D;
   p.out = reinterpret_cast<__nv_bfloat16*>(out); p.ldo = D;
   p.scale_log2e = scale * 1.4426950408889634f;
   p.lse = lse;

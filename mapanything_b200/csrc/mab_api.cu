@@ -995,6 +995,31 @@ extern "C" int mab_stage_aat_attend(mab_handle* h, int layer, const void* kv, in
                           nullptr, c.st);
 }
 
+// K|V columns of this rank's current qkv rows -> dst [rows, 2*aat_dim] bf16 (contiguous), the block
+// the other ranks gather for the global attention of an even layer.
+extern "C" int mab_stage_aat_export_kv(mab_handle* h, void* dst, void* stream) {
+  MAB_ARG(h && h->plan.V > 0 && dst, "mab_stage_aat_qkv must run first");
+  Plan& p = h->plan;
+  const size_t A = h->cfg.aat_dim;
+  MAB_CUDA(cudaMemcpy2DAsync(dst, 2 * A * sizeof(bf16), p.qkv + A, 3 * A * sizeof(bf16), 2 * A * sizeof(bf16),
+                             (size_t)p.L, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+
+// Global attention of even block `layer` against a gathered K|V block [kv_rows, 2*aat_dim]; the
+// online-softmax state is carried between calls exactly as in mab_stage_aat_attend.
+extern "C" int mab_stage_aat_attend_kv(mab_handle* h, int layer, const void* kv, int kv_rows, int flags,
+                                       void* stream) {
+  MAB_ARG(h && h->plan.V > 0 && kv && kv_rows > 0, "mab_stage_encode must run first");
+  MAB_ARG(layer % 2 == 0, "only the global (even) layers attend across ranks");
+  const mab_config& cf = h->cfg;
+  Plan& p = h->plan;
+  const int first = flags & MAB_RING_FIRST, last = flags & MAB_RING_LAST;
+  MAB_ARG((first && last) || p.carry_o, "carried attention needs views_total > views at mab_stage_encode");
+  return launch_attention(p.qkv, p.L, kv, kv_rows, cf.aat_heads, 1, (int)p.L, kv_rows, 0, 0, 0.125f, p.att,
+                          nullptr, (cudaStream_t)stream, p.carry_o, p.carry_ml, first ? 0 : 1, last ? 0 : 1, 1);
+}
+
 // proj + residual, LN2, MLP + residual of block `layer`, intermediate taps and the final norm
 extern "C" int mab_stage_aat_finish(mab_handle* h, int layer, void* stream) {
   MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");

@@ -102,6 +102,7 @@ class MapAnything(torch.nn.Module):
         self._workspace = None
         self._post_ws = None
         self._ring_bufs = None
+        self._kv_all = None
         if pretrained_checkpoint_path is not None:
             ckpt = torch.load(pretrained_checkpoint_path, map_location="cpu", weights_only=False)
             self.load_state_dict(ckpt["model"] if "model" in ckpt else ckpt)
@@ -352,7 +353,16 @@ class MapAnything(torch.nn.Module):
         T = (H // 14) * (W // 14)
         width = 3 * self._cfg.aat_dim
         rows = parallel.rows_per_rank(total, world, T)
-        if self._ring_bufs is None or self._ring_bufs[0].shape[0] < max(rows):
+        # exchange step of the global layers: all-to-all gather of K|V (default) or the ring; the
+        # gather needs the whole scene's K|V resident on every rank (1.6 GB at 512 views)
+        kv_bytes = sum(rows) * 2 * self._cfg.aat_dim * 2
+        mode = os.environ.get("MAB_EXCHANGE", "gather")
+        if mode == "gather" and kv_bytes > int(os.environ.get("MAB_GATHER_MAX_BYTES", 24 << 30)):
+            mode = "ring"
+        if mode == "gather" and (self._kv_all is None or self._kv_all.shape[0] != sum(rows)):
+            self._kv_all = torch.empty((sum(rows), 2 * self._cfg.aat_dim), dtype=torch.bfloat16,
+                                       device=self._device)
+        if mode == "ring" and (self._ring_bufs is None or self._ring_bufs[0].shape[0] < max(rows)):
             self._ring_bufs = [torch.empty((max(rows), width), dtype=torch.bfloat16, device=self._device)
                                for _ in range(2)]
         own_first = 3 if view_lo == 0 else 0
@@ -373,7 +383,25 @@ class MapAnything(torch.nn.Module):
                     _lib.check(lib.mab_stage_aat_attend(hd, layer, block.data_ptr(), n, flags, self._stream_ptr()),
                                "mab_stage_aat_attend")
 
-                parallel.ring_pass(local, rows, self._ring_bufs, attend)
+                def flags_of(first, last):
+                    return (_lib.RING_FIRST if first else 0) | (_lib.RING_LAST if last else 0)
+
+                def export_local(dst):
+                    _lib.check(lib.mab_stage_aat_export_kv(hd, dst.data_ptr(), self._stream_ptr()),
+                               "mab_stage_aat_export_kv")
+
+                def attend_local(first, last, layer=layer):
+                    _lib.check(lib.mab_stage_aat_attend(hd, layer, None, 0, flags_of(first, last),
+                                                        self._stream_ptr()), "mab_stage_aat_attend")
+
+                def attend_kv(block, n, first, last, layer=layer):
+                    _lib.check(lib.mab_stage_aat_attend_kv(hd, layer, block.data_ptr(), n, flags_of(first, last),
+                                                           self._stream_ptr()), "mab_stage_aat_attend_kv")
+
+                if mode == "gather":
+                    parallel.gather_pass(rows, self._kv_all, export_local, attend_local, attend_kv)
+                else:
+                    parallel.ring_pass(local, rows, self._ring_bufs, attend)
             else:
                 _lib.check(lib.mab_stage_aat_attend(hd, layer, None, 0, both, self._stream_ptr()),
                            "mab_stage_aat_attend")

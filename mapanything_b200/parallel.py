@@ -72,3 +72,43 @@ def ring_pass(local_block: torch.Tensor, rows: Sequence[int], recv_bufs: Sequenc
             r.wait()
         if step < world - 1:
             cur = incoming
+
+
+def gather_pass(rows: Sequence[int], kv_all: torch.Tensor, export_local: Callable[[torch.Tensor], None],
+                attend_local: Callable[[bool, bool], None],
+                attend_kv: Callable[[torch.Tensor, int, bool, bool], None], group=None) -> None:
+    """One global-attention layer with an all-to-all gather of the K|V blocks.
+
+    rows         : rows held by every rank
+    kv_all       : [sum(rows), C] buffer, the same layout on every rank: rank r's K|V block occupies
+                   rows offs[r]:offs[r+1]
+    export_local(dst)                  : write this rank's K|V block into dst (its slice of kv_all)
+    attend_local(first, last)          : attention of the local queries against the local block
+    attend_kv(block, n, first, last)   : ... against n gathered rows
+
+    Every rank posts its sends to and receives from all peers in one group (NVSwitch gives each pair
+    full bandwidth) and runs the local-block attention while the blocks travel; the remote blocks
+    are then attended in at most two contiguous spans (before / after the own block), the
+    online-softmax state being carried between the calls.  Traffic per rank and layer: the other
+    ranks' K|V rows once -- the same bytes as the ring, in one step instead of world-1."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    offs = [0]
+    for r in rows:
+        offs.append(offs[-1] + r)
+    own = kv_all[offs[rank]: offs[rank + 1]]
+    export_local(own)
+    ops = []
+    for d in range(1, world):
+        dst, src = (rank + d) % world, (rank - d) % world
+        gdst = dist.get_global_rank(group, dst) if group is not None else dst
+        gsrc = dist.get_global_rank(group, src) if group is not None else src
+        ops.append(dist.P2POp(dist.isend, own, gdst, group))
+        ops.append(dist.P2POp(dist.irecv, kv_all[offs[src]: offs[src + 1]], gsrc, group))
+    reqs = dist.batch_isend_irecv(ops) if ops else []
+    spans = [(a, b) for a, b in ((0, offs[rank]), (offs[rank + 1], offs[world])) if b > a]
+    attend_local(True, not spans)
+    for r in reqs:
+        r.wait()
+    for i, (a, b) in enumerate(spans):
+        attend_kv(kv_all[a:b], b - a, False, i == len(spans) - 1)

@@ -37,7 +37,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, n_views, T, result):
+def _worker(rank, world, port, n_views, T, result, schedule="ring"):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -70,9 +70,36 @@ def _worker(rank, world, port, n_views, T, result):
             state["m"] = m_new
             state["seen"].append(src)
 
-        bufs = [torch.empty(max(rows), 3 * D) for _ in range(2)]
-        parallel.ring_pass(local, rows, bufs, attend)
-        assert sorted(state["seen"]) == list(range(world))
+        if schedule == "ring":
+            bufs = [torch.empty(max(rows), 3 * D) for _ in range(2)]
+            parallel.ring_pass(local, rows, bufs, attend)
+            assert sorted(state["seen"]) == list(range(world))
+        else:  # all-to-all gather of the K|V columns, local block first, then <= 2 remote spans
+            kv_all = torch.full((sum(rows), 2 * D), float("nan"))
+            calls = []
+
+            def attend_span(kv, n, first, last):
+                calls.append((n, first, last))
+                blk = torch.cat([torch.zeros(n, D), kv[:n]], dim=1)  # attend() reads columns D:3D
+                state["seen"].append(-1)
+                k = blk[:n, D:2 * D].view(n, heads, hd).transpose(0, 1)
+                v = blk[:n, 2 * D:].view(n, heads, hd).transpose(0, 1)
+                sc = q @ k.transpose(1, 2) * hd ** -0.5
+                m_new = torch.maximum(state["m"], sc.max(-1).values)
+                alpha = torch.exp(state["m"] - m_new)
+                pr = torch.exp(sc - m_new[..., None])
+                state["l"] = state["l"] * alpha + pr.sum(-1)
+                state["o"] = state["o"] * alpha[..., None] + pr @ v
+                state["m"] = m_new
+
+            parallel.gather_pass(rows, kv_all, lambda dst: dst.copy_(local[:, D:]),
+                                 lambda first, last: attend_span(local[:, D:], rows[rank], first, last),
+                                 attend_span)
+            assert not torch.isnan(kv_all).any()  # every block arrived
+            assert torch.equal(kv_all, qkv_all[:, D:])
+            assert sum(n for n, _, _ in calls) == sum(rows) and len(calls) <= 3
+            assert calls[0][1] and calls[-1][2] and not any(c[1] for c in calls[1:])
+            assert not any(c[2] for c in calls[:-1])
         out = (state["o"] / state["l"][..., None]).transpose(0, 1).reshape(rows[rank], D)
         K = qkv_all[:, D:2 * D].view(-1, heads, hd).transpose(0, 1)
         Vv = qkv_all[:, 2 * D:].view(-1, heads, hd).transpose(0, 1)
@@ -89,6 +116,23 @@ def test_ring_pass_gloo(world, n_views):
         result = man.dict()
         port = _free_port()
         procs = [ctx.Process(target=_worker, args=(r, world, port, n_views, 11, result)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(120)
+            assert p.exitcode == 0, f"rank exited with {p.exitcode}"
+        assert len(result) == world
+        assert max(result.values()) < 1e-5, dict(result)
+
+
+@pytest.mark.parametrize("world,n_views", [(2, 3), (3, 7)])
+def test_gather_pass_gloo(world, n_views):
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as man:
+        result = man.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_worker, args=(r, world, port, n_views, 11, result, "gather"))
+                 for r in range(world)]
         for p in procs:
             p.start()
         for p in procs:
