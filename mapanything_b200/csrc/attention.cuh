@@ -12,11 +12,16 @@
 //   warp1      MMA issuer (one elected thread)
 //   warps 2-5  softmax of tile A, warps 6-9 softmax of tile B (thread = one query row)
 //   S_t(j) = Q_t K_j^T      SS MMA 128x128x64 -> TMEM S_t                       (t = A, B)
-//   P_t(j) = exp2(...)      softmax warps, bf16, written over the first 64 columns of S_t
-//   O_t(j) = P_t(j) V_j     TS MMA 128x64x128 (A operand from TMEM, V MN-major from smem) -> O_t[j&1]
-//   O_t    = O_t*alpha + O_t(j)   accumulated in registers by the softmax warps
-// While the softmax warps of A work on S_A(j), the tensor core runs P_B V and the next Q_B K^T, and
-// vice versa, so neither the exp-bound softmax nor the MMAs sit on the other's critical path.
+//   P_t(j) = exp2(...)      softmax warps: S row read ONCE into registers, bf16 P -> TMEM P_t
+//   O_t   += P_t(j) V_j     TS MMA 128x64x128 (A operand from TMEM, V MN-major from smem),
+//                           accumulated in TMEM over the whole K/V loop
+// TMEM reads are the scarce resource of the softmax (64-128 B/clk/SM): S is therefore loaded once
+// (128 registers per row) and O never leaves TMEM inside the loop.  The running max is only
+// advanced when a row's new maximum exceeds the reference by more than 2^8 (exp2 domain), so the
+// O rescale (TMEM load-scale-store by the row's own thread) is rare; P <= 256 stays exact enough
+// in bf16 and the final O / l is mathematically unchanged.  S_t is released to the tensor core as
+// soon as it is in registers (P_t has its own TMEM columns), so Q K^T of the next K/V tile runs
+// under the exp pass of the current one.
 #pragma once
 #include "common.cuh"
 
@@ -94,11 +99,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint64_t* k_empty = k_full + ATT_KV_STAGES;      // [KS]
   uint64_t* v_full = k_empty + ATT_KV_STAGES;      // [KS]
   uint64_t* v_empty = v_full + ATT_KV_STAGES;      // [KS]
-  uint64_t* s_full = v_empty + ATT_KV_STAGES;      // [QT]      S_t(j) is in TMEM
-  uint64_t* p_full = s_full + ATT_QT;              // [QT]      P_t(j) is in TMEM
-  uint64_t* o_full = p_full + ATT_QT;              // [QT][2]   O_t(j) is in TMEM buffer j&1
-  uint64_t* o_empty = o_full + 2 * ATT_QT;         // [QT][2]   ... and has been folded into registers
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2 * ATT_QT);
+  uint64_t* s_full = v_empty + ATT_KV_STAGES;      // [QT]  S_t(j) is in TMEM
+  uint64_t* s_free = s_full + ATT_QT;              // [QT]  S_t(j) is in registers: S_t may be overwritten
+  uint64_t* p_full = s_free + ATT_QT;              // [QT]  P_t(j) is in TMEM (and O_t rescaled)
+  uint64_t* pv_done = p_full + ATT_QT;             // [QT]  O_t += P_t(j) V_j has completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + ATT_QT);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q_tile = blockIdx.x, head = blockIdx.y, seq = blockIdx.z;
@@ -121,11 +126,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     }
     for (int t = 0; t < ATT_QT; ++t) {
       mbar_init(&s_full[t], 1);
-      mbar_init(&p_full[t], 4);  // one arrive per softmax warp of the tile
-      for (int b = 0; b < 2; ++b) {
-        mbar_init(&o_full[t * 2 + b], 1);
-        mbar_init(&o_empty[t * 2 + b], 4);
-      }
+      mbar_init(&s_free[t], 4);  // one arrive per softmax warp of the tile
+      mbar_init(&p_full[t], 4);
+      mbar_init(&pv_done[t], 1);
     }
     fence_barrier_init();
   }
@@ -135,11 +138,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   tc_fence_after();
   pdl_wait();     // prologue above overlapped the previous kernel's tail (PDL)
   pdl_trigger();
-  const uint32_t tmem_base = *tmem_slot;
-  // TMEM columns: S_A @0, S_B @128 (P_t overlays the first 64 columns of S_t),
-  //               O_A[0] @256, O_A[1] @320, O_B[0] @384, O_B[1] @448
+  // broadcast through a shuffle so that the compiler knows the TMEM base is warp-uniform: otherwise every
+  // tcgen05.mma is wrapped in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~100 cycles per instruction)
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  // TMEM columns: S_A @0, S_B @128, O_A @256, O_B @320, P_A @384, P_B @448 (bf16 pairs: 64 columns)
   auto TM_S = [&](int t) { return tmem_base + t * 128; };
-  auto TM_O = [&](int t, int b) { return tmem_base + 256 + t * 128 + b * 64; };
+  auto TM_O = [&](int t) { return tmem_base + 256 + t * 64; };
+  auto TM_P = [&](int t) { return tmem_base + 384 + t * 64; };
 
   if (warp == 0) {
     // ===================================== loader =========================================
@@ -164,8 +169,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     // ===================================== MMA issuer =====================================
     constexpr uint32_t IDESC_QK = make_idesc_bf16(ATT_BQ, ATT_BKV, 0, 0);
     constexpr uint32_t IDESC_PV = make_idesc_bf16(ATT_BQ, ATT_D, 0, 1);  // B (=V) is MN-major
-    auto issue_qk = [&](int t, int j) {  // S_t(j) = Q_t K_j^T ; overwrites P_t(j-1): issue after PV_t(j-1)
-      if (lane == 0) {
+    auto issue_qk = [&](int t, int j) {  // S_t(j) = Q_t K_j^T
+      if (elect_one()) {
         const int st = j % ATT_KV_STAGES;
         const uint32_t a = smem_u32(sQ + t * ATT_TILE_BYTES), b = smem_u32(sK + st * ATT_TILE_BYTES);
 #pragma unroll
@@ -182,30 +187,26 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     for (int t = 0; t < ntile; ++t) issue_qk(t, 0);
     for (int j = 0; j < nkv; ++j) {
       const int st = j % ATT_KV_STAGES;
-      const int b = j & 1;
-      const uint32_t use = (j >> 1) & 1;
+      if (j + 1 < nkv) mbar_wait(&k_full[(j + 1) % ATT_KV_STAGES], ((j + 1) / ATT_KV_STAGES) & 1);
       mbar_wait(&v_full[st], (j / ATT_KV_STAGES) & 1);
       for (int t = 0; t < ntile; ++t) {
-        mbar_wait(&p_full[t], j & 1);                 // P_t(j) is in TMEM
-        mbar_wait(&o_empty[t * 2 + b], use ^ 1);      // O_t(j-2) has been consumed
+        if (j + 1 < nkv) {
+          mbar_wait(&s_free[t], j & 1);  // S_t(j) has been read: the next Q K^T may overwrite it
+          tc_fence_after();
+          issue_qk(t, j + 1);
+        }
+        mbar_wait(&p_full[t], j & 1);    // P_t(j) is in TMEM, O_t carries the right scale
         tc_fence_after();
-        if (lane == 0) {
+        if (elect_one()) {
           const uint32_t vb = smem_u32(sV + st * ATT_TILE_BYTES);
 #pragma unroll
           for (int k = 0; k < ATT_BKV / 16; ++k)
-            umma_ts(TM_O(t, b), TM_S(t) + k * 8, make_sw128_desc(vb + k * 2048, 1024, 1024), IDESC_PV,
-                    k != 0);
-          umma_commit(&o_full[t * 2 + b]);
+            umma_ts(TM_O(t), TM_P(t) + k * 8, make_sw128_desc(vb + k * 2048, 1024, 1024), IDESC_PV,
+                    (j > 0 || p.carry_in || k != 0) ? 1u : 0u);
+          umma_commit(&pv_done[t]);
           if (t == ntile - 1) umma_commit(&v_empty[st]);
         }
         __syncwarp();
-        if (j + 1 < nkv) {
-          if (t == 0) {
-            mbar_wait(&k_full[(j + 1) % ATT_KV_STAGES], ((j + 1) / ATT_KV_STAGES) & 1);
-            tc_fence_after();
-          }
-          issue_qk(t, j + 1);
-        }
       }
     }
   } else {
@@ -217,140 +218,166 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     const bool row_ok = q_tile * (ATT_QT * ATT_BQ) + t * ATT_BQ + row < p.q_len;
     const long long grow = (long long)q_row0 + t * ATT_BQ + row;
     if (t < ntile) {
-      float m_run = -INFINITY, l_run = 0.f, alpha_pending = 1.f;
-      float o_acc[ATT_D];
-#pragma unroll
-      for (int d = 0; d < ATT_D; ++d) o_acc[d] = 0.f;
-      if (p.carry_in && row_ok) {
-        const float2 ml = *reinterpret_cast<const float2*>(p.carry_ml + (grow * p.heads + head) * 2);
-        m_run = ml.x; l_run = ml.y;
-        const float4* src = reinterpret_cast<const float4*>(p.carry_o + grow * p.ldo + head * ATT_D);
-#pragma unroll
-        for (int d = 0; d < ATT_D / 4; ++d) {
-          const float4 v = src[d];
-          o_acc[4 * d] = v.x; o_acc[4 * d + 1] = v.y; o_acc[4 * d + 2] = v.z; o_acc[4 * d + 3] = v.w;
-        }
-      }
-
-      auto consume_o = [&](int j, float alpha) {  // o_acc = o_acc * alpha + O_t(j)
-        const int b = j & 1;
-        mbar_wait(&o_full[t * 2 + b], (j >> 1) & 1);
-        tc_fence_after();
-        uint32_t v0[32], v1[32];
-        MAB_TMEM_LD_32(TM_O(t, b) + lane_addr, v0);
-        MAB_TMEM_LD_32(TM_O(t, b) + lane_addr + 32, v1);
-        tmem_wait_ld();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&o_empty[t * 2 + b]);
-        const uint64_t a2 = pack_f2(alpha, alpha);
-#pragma unroll
-        for (int d = 0; d < 32; d += 2) {
-          unpack_f2(fma_f2(pack_f2(o_acc[d], o_acc[d + 1]), a2,
-                           pack_f2(__uint_as_float(v0[d]), __uint_as_float(v0[d + 1]))),
-                    o_acc[d], o_acc[d + 1]);
-          unpack_f2(fma_f2(pack_f2(o_acc[d + 32], o_acc[d + 33]), a2,
-                           pack_f2(__uint_as_float(v1[d]), __uint_as_float(v1[d + 1]))),
-                    o_acc[d + 32], o_acc[d + 33]);
-        }
-      };
-
-      const uint32_t ts = TM_S(t) + lane_addr;
+      const uint32_t ts = TM_S(t) + lane_addr, to = TM_O(t) + lane_addr, tp = TM_P(t) + lane_addr;
       const float sc = p.scale_log2e;
       const uint64_t sc2 = pack_f2(sc, sc);
+      float m_ref = -INFINITY, l_run = 0.f;  // reference max of the exponentials, running sum
+      if (p.carry_in) {  // resume from the carried state: O_t <- carry_o
+        uint32_t o[32];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          if (row_ok) {
+            const float4* src = reinterpret_cast<const float4*>(p.carry_o + grow * p.ldo + head * ATT_D + h * 32);
+#pragma unroll
+            for (int d = 0; d < 8; ++d) {
+              const float4 v = src[d];
+              o[4 * d] = __float_as_uint(v.x); o[4 * d + 1] = __float_as_uint(v.y);
+              o[4 * d + 2] = __float_as_uint(v.z); o[4 * d + 3] = __float_as_uint(v.w);
+            }
+          } else {
+#pragma unroll
+            for (int d = 0; d < 32; ++d) o[d] = 0u;
+          }
+          MAB_TMEM_ST_16(to + h * 32, o);
+          MAB_TMEM_ST_16(to + h * 32 + 16, (o + 16));
+        }
+        if (row_ok) {
+          const float2 ml = *reinterpret_cast<const float2*>(p.carry_ml + (grow * p.heads + head) * 2);
+          m_ref = ml.x; l_run = ml.y;
+        }
+        tmem_wait_st();
+      }
+
       for (int j = 0; j < nkv; ++j) {
         const int valid = p.kv_len - j * ATT_BKV;  // columns >= valid are padding / next sequence
         const bool full = valid >= ATT_BKV;
         mbar_wait(&s_full[t], j & 1);
         tc_fence_after();
-        // ---- pass 1: row max (loads of chunk c+1 in flight while chunk c is reduced) ----
-        float mx = -INFINITY;
-        {
-          uint32_t va[32], vb[32];
-          MAB_TMEM_LD_32(ts, va);
-          tmem_wait_ld();
+        // ---- the whole S row into registers, then hand S_t back to the tensor core ----
+        uint32_t v[128];
+        MAB_TMEM_LD_32(ts, v);
+        MAB_TMEM_LD_32(ts + 32, (v + 32));
+        MAB_TMEM_LD_32(ts + 64, (v + 64));
+        MAB_TMEM_LD_32(ts + 96, (v + 96));
+        tmem_wait_ld();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_free[t]);
+        // ---- row max (four independent chains) ----
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+        if (full) {
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            uint32_t* cur = (c & 1) ? vb : va;
-            uint32_t* nxt = (c & 1) ? va : vb;
-            if (c < 3) MAB_TMEM_LD_32(ts + (c + 1) * 32, nxt);
-            if (full) {
-#pragma unroll
-              for (int i = 0; i < 32; i += 2)
-                mx = max3(mx, __uint_as_float(cur[i]), __uint_as_float(cur[i + 1]));
-            } else {
-#pragma unroll
-              for (int i = 0; i < 32; ++i)
-                if (c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(cur[i]));
-            }
-            if (c < 3) tmem_wait_ld();
+          for (int i = 0; i < 128; i += 8) {
+            mx0 = max3(mx0, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
+            mx1 = max3(mx1, __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+            mx2 = max3(mx2, __uint_as_float(v[i + 4]), __uint_as_float(v[i + 5]));
+            mx3 = max3(mx3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
           }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 128; ++i)
+            if (i < valid) mx0 = fmaxf(mx0, __uint_as_float(v[i]));
         }
-        const float m_new = fmaxf(m_run, mx);  // finite: every tile has >= 1 valid column
-        const float alpha = fast_exp2((m_run - m_new) * sc);  // 0 on the first tile without carry
+        const float mx = fmaxf(max3(mx0, mx1, mx2), mx3);  // finite: every tile has >= 1 valid column
+        // advance the reference max only when it is exceeded by more than 2^8 in the exp2 domain
+        const bool grow_ref = (mx - m_ref) * sc > 8.0f;  // true on the first tile (m_ref = -inf)
+        const float m_new = grow_ref ? mx : m_ref;
+        const float alpha = grow_ref ? fast_exp2((m_ref - m_new) * sc) : 1.0f;  // exp2(-inf) = 0
+        const bool rescale = __any_sync(0xffffffffu, grow_ref) && (j > 0 || p.carry_in);
         const float nmb = -m_new * sc;
         const uint64_t nmb2 = pack_f2(nmb, nmb);
-        uint64_t sum2 = pack_f2(0.f, 0.f);
-        // ---- pass 2: P = exp2(S*c - m*c) -> bf16 -> TMEM (over already-consumed S columns) ----
-        {
-          uint32_t va[32], vb[32];
-          MAB_TMEM_LD_32(ts, va);
-          tmem_wait_ld();
+        // ---- P = exp2(S*c - m*c) -> bf16 (registers), row sum ----
+        uint32_t pk[64];
+        uint64_t sum_a = pack_f2(0.f, 0.f), sum_b = sum_a;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            uint32_t* cur = (c & 1) ? vb : va;
-            uint32_t* nxt = (c & 1) ? va : vb;
-            if (c < 3) MAB_TMEM_LD_32(ts + (c + 1) * 32, nxt);
-            uint32_t pk[16];
+        for (int i = 0; i < 128; i += 4) {
+          float x0, x1, x2, x3;
+          unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])), sc2, nmb2), x0, x1);
+          unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i + 2]), __uint_as_float(v[i + 3])), sc2, nmb2), x2, x3);
+          float e0 = fast_exp2(x0), e1 = fast_exp2(x1), e2 = fast_exp2(x2), e3 = fast_exp2(x3);
+          if (!full) {
+            if (i >= valid) e0 = 0.f;
+            if (i + 1 >= valid) e1 = 0.f;
+            if (i + 2 >= valid) e2 = 0.f;
+            if (i + 3 >= valid) e3 = 0.f;
+          }
+          sum_a = add_f2(sum_a, pack_f2(e0, e1));
+          sum_b = add_f2(sum_b, pack_f2(e2, e3));
+          pk[i >> 1] = cvt_bf16x2(e0, e1);
+          pk[(i >> 1) + 1] = cvt_bf16x2(e2, e3);
+        }
+        // ---- P_t and O_t are free once P_t(j-1) V has completed ----
+        if (j > 0) {
+          mbar_wait(&pv_done[t], (j - 1) & 1);
+          tc_fence_after();
+        }
+        if (rescale) {  // warp-uniform; rows that keep their reference multiply by 1
+          const uint64_t a2 = pack_f2(alpha, alpha);
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-              float x0, x1;
-              unpack_f2(fma_f2(pack_f2(__uint_as_float(cur[i]), __uint_as_float(cur[i + 1])), sc2, nmb2),
-                        x0, x1);
-              float e0 = fast_exp2(x0), e1 = fast_exp2(x1);
-              if (!full) {
-                if (c * 32 + i >= valid) e0 = 0.f;
-                if (c * 32 + i + 1 >= valid) e1 = 0.f;
-              }
-              sum2 = add_f2(sum2, pack_f2(e0, e1));
-              pk[i >> 1] = cvt_bf16x2(e0, e1);
+          for (int h = 0; h < 2; ++h) {
+            uint32_t o[32];
+            MAB_TMEM_LD_32(to + h * 32, o);
+            tmem_wait_ld();
+#pragma unroll
+            for (int d = 0; d < 32; d += 2) {
+              float y0, y1;
+              unpack_f2(fma_f2(pack_f2(__uint_as_float(o[d]), __uint_as_float(o[d + 1])), a2, pack_f2(0.f, 0.f)),
+                        y0, y1);
+              o[d] = __float_as_uint(y0); o[d + 1] = __float_as_uint(y1);
             }
-            // chunk c of P (16 columns) lands on S columns [16c, 16c+16): all read by now
-            if (c < 3) tmem_wait_ld();
-            MAB_TMEM_ST_16(ts + c * 16, pk);
+            MAB_TMEM_ST_16(to + h * 32, o);
+            MAB_TMEM_ST_16(to + h * 32 + 16, (o + 16));
           }
         }
+        MAB_TMEM_ST_16(tp, pk);
+        MAB_TMEM_ST_16(tp + 16, (pk + 16));
+        MAB_TMEM_ST_16(tp + 32, (pk + 32));
+        MAB_TMEM_ST_16(tp + 48, (pk + 48));
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[t]);
         float s0, s1;
-        unpack_f2(sum2, s0, s1);
+        unpack_f2(add_f2(sum_a, sum_b), s0, s1);
         l_run = fmaf(l_run, alpha, s0 + s1);
-        m_run = m_new;
-        // fold the previous tile's PV product while the tensor core works on this one
-        if (j > 0) consume_o(j - 1, alpha_pending);
-        alpha_pending = alpha;
+        m_ref = m_new;
       }
-      consume_o(nkv - 1, alpha_pending);
 
+      // ---- epilogue: O_t out of TMEM once the last P V has completed ----
+      mbar_wait(&pv_done[t], (nkv - 1) & 1);
+      tc_fence_after();
+      uint32_t o0[32], o1[32];
+      MAB_TMEM_LD_32(to, o0);
+      MAB_TMEM_LD_32(to + 32, o1);
+      tmem_wait_ld();
       if (row_ok && p.carry_out) {
-        *reinterpret_cast<float2*>(p.carry_ml + (grow * p.heads + head) * 2) = make_float2(m_run, l_run);
+        *reinterpret_cast<float2*>(p.carry_ml + (grow * p.heads + head) * 2) = make_float2(m_ref, l_run);
         float4* dst = reinterpret_cast<float4*>(p.carry_o + grow * p.ldo + head * ATT_D);
 #pragma unroll
-        for (int d = 0; d < ATT_D / 4; ++d)
-          dst[d] = make_float4(o_acc[4 * d], o_acc[4 * d + 1], o_acc[4 * d + 2], o_acc[4 * d + 3]);
+        for (int d = 0; d < 8; ++d) {
+          dst[d] = make_float4(__uint_as_float(o0[4 * d]), __uint_as_float(o0[4 * d + 1]),
+                               __uint_as_float(o0[4 * d + 2]), __uint_as_float(o0[4 * d + 3]));
+          dst[d + 8] = make_float4(__uint_as_float(o1[4 * d]), __uint_as_float(o1[4 * d + 1]),
+                                   __uint_as_float(o1[4 * d + 2]), __uint_as_float(o1[4 * d + 3]));
+        }
       } else if (row_ok) {
         const float inv = 1.0f / l_run;
         uint4* dst = reinterpret_cast<uint4*>(p.out + grow * p.ldo + head * ATT_D);
 #pragma unroll
-        for (int d = 0; d < ATT_D; d += 8)
-          dst[d >> 3] = make_uint4(pack_bf16(o_acc[d] * inv, o_acc[d + 1] * inv),
-                                   pack_bf16(o_acc[d + 2] * inv, o_acc[d + 3] * inv),
-                                   pack_bf16(o_acc[d + 4] * inv, o_acc[d + 5] * inv),
-                                   pack_bf16(o_acc[d + 6] * inv, o_acc[d + 7] * inv));
+        for (int d = 0; d < 32; d += 8) {
+          dst[d >> 3] = make_uint4(
+              pack_bf16(__uint_as_float(o0[d]) * inv, __uint_as_float(o0[d + 1]) * inv),
+              pack_bf16(__uint_as_float(o0[d + 2]) * inv, __uint_as_float(o0[d + 3]) * inv),
+              pack_bf16(__uint_as_float(o0[d + 4]) * inv, __uint_as_float(o0[d + 5]) * inv),
+              pack_bf16(__uint_as_float(o0[d + 6]) * inv, __uint_as_float(o0[d + 7]) * inv));
+          dst[(d >> 3) + 4] = make_uint4(
+              pack_bf16(__uint_as_float(o1[d]) * inv, __uint_as_float(o1[d + 1]) * inv),
+              pack_bf16(__uint_as_float(o1[d + 2]) * inv, __uint_as_float(o1[d + 3]) * inv),
+              pack_bf16(__uint_as_float(o1[d + 4]) * inv, __uint_as_float(o1[d + 5]) * inv),
+              pack_bf16(__uint_as_float(o1[d + 6]) * inv, __uint_as_float(o1[d + 7]) * inv));
+        }
         if (p.lse)
-          p.lse[grow * p.heads + head] = m_run * p.scale_log2e * 0.6931471805599453f + logf(l_run);
+          p.lse[grow * p.heads + head] = m_ref * p.scale_log2e * 0.6931471805599453f + logf(l_run);
       }
     }
   }

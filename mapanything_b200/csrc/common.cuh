@@ -39,6 +39,14 @@ __device__ __forceinline__ float fast_exp2(float x) {  // MUFU.EX2, 2 ulp; exp2(
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// named barriers (ids 1..15; 0 is __syncthreads): producer/consumer hand-off between warp groups
+__device__ __forceinline__ void bar_sync_named(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void bar_arrive_named(int id, int threads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
 __device__ __forceinline__ float fast_rcp(float x) {  // MUFU.RCP, 1 ulp, branch-free (rcp.rn is a call)
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

@@ -281,7 +281,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   tc_fence_before();
   cluster_sync_all();  // peers' barriers are initialised and TMEM is allocated in both CTAs
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  // broadcast through a shuffle so that the compiler knows the TMEM base is warp-uniform: otherwise every
+  // tcgen05.mma is wrapped in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~100 cycles per instruction)
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   // everything above overlapped the tail of the previous kernel in the stream (PDL)
   pdl_wait();
   pdl_trigger();
@@ -338,7 +340,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         mbar_wait(&full_bar[stage], phase);
 #endif
         tc_fence_after();
-        if (lane == 0) {
+        if (elect_one()) {
           const uint32_t sa = smem_u32(smem + stage * SM::STAGE_BYTES);
           const uint32_t sb = sa + SM::A_BYTES;
 #pragma unroll

@@ -1,14 +1,8 @@
-import ctypes as C, os, sys, torch
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from mapanything_b200 import _lib
-lib = _lib.load()
-heads, length = 12, int(sys.argv[1]) if len(sys.argv) > 1 else 16577
-D = heads * 64
-qkv = torch.randn(length, 3 * D, device="cuda").bfloat16()
-out = torch.empty(length, D, device="cuda", dtype=torch.bfloat16)
-st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-for _ in range(3):
-    _lib.check(lib.mab_attention(C.c_void_p(qkv.data_ptr()), length, C.c_void_p(qkv.data_ptr()), length, heads, 1, length, length,
-                                 length, length, 0.125, C.c_void_p(out.data_ptr()), None, st))
-torch.cuda.synchronize()
-print("done")
+"""Attention microbench only (through the C ABI): python profiles/attn_only.py"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from attn_microbench import attn
+attn(16, 8, 1037)      # encoder, 8 views
+attn(12, 8, 1036)      # frame, 8 views
+attn(12, 1, 8289)      # global, 8 views
+attn(12, 1, 66305)     # global, 64 views
