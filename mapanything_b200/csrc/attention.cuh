@@ -9,8 +9,10 @@
 // One CTA = one (sequence, head, 256-query tile) = two 128-query tiles A and B that ping-pong on
 // the tensor core while sharing every K/V tile in shared memory:
 //   warp0      TMA loader (Q_A, Q_B once; 4-stage K and V rings)
-//   warp1      MMA issuer (one elected thread)
-//   warps 2-5  softmax of tile A, warps 6-9 softmax of tile B (thread = one query row)
+//   warp1/2    MMA issuer of tile A / tile B (one elected thread each; a tcgen05.mma that waits for
+//              room in the tensor-core queue stalls the scheduler partition it is issued from, so
+//              the two tiles' issue streams sit on different partitions), warp3 idle
+//   warps 4-7  softmax of tile A, warps 8-11 softmax of tile B (thread = one query row)
 //   S_t(j) = Q_t K_j^T      SS MMA 128x128x64 -> TMEM S_t                       (t = A, B)
 //   P_t(j) = exp2(...)      softmax warps: S row read ONCE into registers, bf16 P -> TMEM P_t
 //   O_t   += P_t(j) V_j     TS MMA 128x64x128 (A operand from TMEM, V MN-major from smem),
@@ -32,7 +34,7 @@ constexpr int ATT_QT = 2;      // Q tiles per CTA
 constexpr int ATT_BKV = 128;
 constexpr int ATT_D = 64;
 constexpr int ATT_KV_STAGES = 4;
-constexpr int ATT_THREADS = 64 + ATT_QT * 128;
+constexpr int ATT_THREADS = 128 + ATT_QT * 128;  // 4 control warps (one per scheduler) + 8 softmax warps
 constexpr int ATT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: Q, K and V tiles alike
 constexpr int ATT_SMEM_BYTES = (ATT_QT + 2 * ATT_KV_STAGES) * ATT_TILE_BYTES + 512 + 1024;
 
@@ -120,9 +122,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     mbar_init(q_full, 1);
     for (int s = 0; s < ATT_KV_STAGES; ++s) {
       mbar_init(&k_full[s], 1);
-      mbar_init(&k_empty[s], 1);
+      mbar_init(&k_empty[s], ntile);  // one commit per tile's MMA issuer
       mbar_init(&v_full[s], 1);
-      mbar_init(&v_empty[s], 1);
+      mbar_init(&v_empty[s], ntile);
     }
     for (int t = 0; t < ATT_QT; ++t) {
       mbar_init(&s_full[t], 1);
@@ -165,11 +167,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
                     kv_row0 + j * ATT_BKV);
       }
     }
-  } else if (warp == 1) {
-    // ===================================== MMA issuer =====================================
+  } else if (warp == 1 || warp == 2) {
+    // ============================== MMA issuer of tile (warp - 1) ==============================
+    const int t = warp - 1;
     constexpr uint32_t IDESC_QK = make_idesc_bf16(ATT_BQ, ATT_BKV, 0, 0);
     constexpr uint32_t IDESC_PV = make_idesc_bf16(ATT_BQ, ATT_D, 0, 1);  // B (=V) is MN-major
-    auto issue_qk = [&](int t, int j) {  // S_t(j) = Q_t K_j^T
+    auto issue_qk = [&](int j) {  // S_t(j) = Q_t K_j^T
       if (elect_one()) {
         const int st = j % ATT_KV_STAGES;
         const uint32_t a = smem_u32(sQ + t * ATT_TILE_BYTES), b = smem_u32(sK + st * ATT_TILE_BYTES);
@@ -177,24 +180,24 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         for (int k = 0; k < ATT_D / 16; ++k)
           umma_ss(TM_S(t), make_sw128_desc(a + k * 32), make_sw128_desc(b + k * 32), IDESC_QK, k != 0);
         umma_commit(&s_full[t]);
-        if (t == ntile - 1) umma_commit(&k_empty[st]);
+        umma_commit(&k_empty[st]);
       }
       __syncwarp();
     };
-    mbar_wait(q_full, 0);
-    mbar_wait(&k_full[0], 0);
-    tc_fence_after();
-    for (int t = 0; t < ntile; ++t) issue_qk(t, 0);
-    for (int j = 0; j < nkv; ++j) {
-      const int st = j % ATT_KV_STAGES;
-      if (j + 1 < nkv) mbar_wait(&k_full[(j + 1) % ATT_KV_STAGES], ((j + 1) / ATT_KV_STAGES) & 1);
-      mbar_wait(&v_full[st], (j / ATT_KV_STAGES) & 1);
-      for (int t = 0; t < ntile; ++t) {
+    if (t < ntile) {
+      mbar_wait(q_full, 0);
+      mbar_wait(&k_full[0], 0);
+      tc_fence_after();
+      issue_qk(0);
+      for (int j = 0; j < nkv; ++j) {
+        const int st = j % ATT_KV_STAGES;
         if (j + 1 < nkv) {
+          mbar_wait(&k_full[(j + 1) % ATT_KV_STAGES], ((j + 1) / ATT_KV_STAGES) & 1);
           mbar_wait(&s_free[t], j & 1);  // S_t(j) has been read: the next Q K^T may overwrite it
           tc_fence_after();
-          issue_qk(t, j + 1);
+          issue_qk(j + 1);
         }
+        mbar_wait(&v_full[st], (j / ATT_KV_STAGES) & 1);
         mbar_wait(&p_full[t], j & 1);    // P_t(j) is in TMEM, O_t carries the right scale
         tc_fence_after();
         if (elect_one()) {
@@ -204,14 +207,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             umma_ts(TM_O(t), TM_P(t) + k * 8, make_sw128_desc(vb + k * 2048, 1024, 1024), IDESC_PV,
                     (j > 0 || p.carry_in || k != 0) ? 1u : 0u);
           umma_commit(&pv_done[t]);
-          if (t == ntile - 1) umma_commit(&v_empty[st]);
+          umma_commit(&v_empty[st]);
         }
         __syncwarp();
       }
     }
-  } else {
+  } else if (warp >= 4) {
     // ===================================== softmax ========================================
-    const int t = (warp - 2) >> 2;                      // Q tile of this warp
+    const int t = (warp - 4) >> 2;                      // Q tile of this warp
     const int q = warp & 3;                             // TMEM lane quarter (warp id % 4)
     const int row = q * 32 + lane;                      // query row within the tile
     const uint32_t lane_addr = uint32_t(q * 32) << 16;
@@ -248,6 +251,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tmem_wait_st();
       }
 
+      // The exp pass is bound by the SM's 16 MUFU lanes: the two tiles take turns on it (named
+      // barriers 1 = "A's turn", 2 = "B's turn") so that one tile's TMEM traffic, barrier waits and
+      // MMA latency always sit under the other tile's exp pass.
+      const bool take_turns = ntile == 2;
+      if (take_turns && t == 1) bar_arrive_named(1, 2 * ATT_BQ);  // tile A goes first
       for (int j = 0; j < nkv; ++j) {
         const int valid = p.kv_len - j * ATT_BKV;  // columns >= valid are padding / next sequence
         const bool full = valid >= ATT_BKV;
@@ -263,6 +271,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&s_free[t]);
+        if (take_turns) bar_sync_named(1 + t, 2 * ATT_BQ);
         // ---- row max (four independent chains) ----
         float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
         if (full) {
@@ -306,6 +315,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           pk[i >> 1] = cvt_bf16x2(e0, e1);
           pk[(i >> 1) + 1] = cvt_bf16x2(e2, e3);
         }
+        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named(1 + (t ^ 1), 2 * ATT_BQ);
         // ---- P_t and O_t are free once P_t(j-1) V has completed ----
         if (j > 0) {
           mbar_wait(&pv_done[t], (j - 1) & 1);
