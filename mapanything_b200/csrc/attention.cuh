@@ -271,7 +271,6 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&s_free[t]);
-        if (take_turns) bar_sync_named(1 + t, 2 * ATT_BQ);
         // ---- row max (four independent chains) ----
         float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
         if (full) {
@@ -293,7 +292,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         const float m_new = grow_ref ? mx : m_ref;
         const float alpha = grow_ref ? fast_exp2((m_ref - m_new) * sc) : 1.0f;  // exp2(-inf) = 0
         const bool rescale = __any_sync(0xffffffffu, grow_ref) && (j > 0 || p.carry_in);
-        const float nmb = -m_new * sc;
+        float nmb = -m_new * sc;
+        if (take_turns) bar_sync_named_dep(1 + t, 2 * ATT_BQ, nmb);  // every exp below depends on nmb
         const uint64_t nmb2 = pack_f2(nmb, nmb);
         // ---- P = exp2(S*c - m*c) -> bf16 (registers), row sum ----
         uint32_t pk[64];
@@ -315,7 +315,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           pk[i >> 1] = cvt_bf16x2(e0, e1);
           pk[(i >> 1) + 1] = cvt_bf16x2(e2, e3);
         }
-        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named(1 + (t ^ 1), 2 * ATT_BQ);
+        float s0, s1;
+        unpack_f2(add_f2(sum_a, sum_b), s0, s1);
+        const float row_sum = s0 + s1;  // depends on every exp of the row
+        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named_dep(1 + (t ^ 1), 2 * ATT_BQ, row_sum);
         // ---- P_t and O_t are free once P_t(j-1) V has completed ----
         if (j > 0) {
           mbar_wait(&pv_done[t], (j - 1) & 1);
@@ -347,9 +350,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[t]);
-        float s0, s1;
-        unpack_f2(add_f2(sum_a, sum_b), s0, s1);
-        l_run = fmaf(l_run, alpha, s0 + s1);
+        l_run = fmaf(l_run, alpha, row_sum);
         m_ref = m_new;
       }
 

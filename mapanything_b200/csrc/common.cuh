@@ -47,6 +47,16 @@ __device__ __forceinline__ void bar_arrive_named(int id, int threads) {
   asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
+// Same, tied into the data flow: register arithmetic is free to move across an asm volatile, so the
+// value that everything after the barrier depends on is passed through it (sync), and the value
+// that everything before it produces is consumed by it (arrive).
+__device__ __forceinline__ void bar_sync_named_dep(int id, int threads, float& x) {
+  asm volatile("bar.sync %1, %2;" : "+f"(x) : "r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void bar_arrive_named_dep(int id, int threads, float x) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads), "f"(x) : "memory");
+}
+
 __device__ __forceinline__ float fast_rcp(float x) {  // MUFU.RCP, 1 ulp, branch-free (rcp.rn is a call)
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

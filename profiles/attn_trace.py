@@ -1,4 +1,5 @@
-"""Debug: per-iteration timeline of the softmax warps (library built with -DMAB_ATT_TRACE)."""
+"""Debug: per-iteration timeline of one softmax warp per tile (library built with -DMAB_ATT_TRACE and
+trace points inserted by the developer; not part of the product build)."""
 import ctypes as C, os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from mapanything_b200 import _lib
@@ -14,20 +15,12 @@ for _ in range(2):
     trace.zero_()
     _lib.check(lib.mab_attention(p(qkv), length, p(qkv), length, heads, 1, length, length, length, length, 0.125, p(out), p(trace), st))
 torch.cuda.synchronize()
-all64 = trace.view(torch.int64)
-tr = all64[:2 * 16 * 8].view(2, 16, 8).cpu()
-mt = all64[256:256 + 2 * 16 * 8].view(2, 16, 8).cpu()
+tr = trace.view(torch.int64)[:2 * 16 * 8].view(2, 16, 8).cpu()
 base = int(tr[0, 0, 0])
-names = ["loop_top", "s_full", "S_in_regs", "exp_done", "pv_done_seen", "p_arrive"]
+names = ["top", "s_full", "S_regs", "turn", "exp_done", "pv_done", "p_arrive"]
 for t in range(2):
-    print(f"tile {t}: columns = {names} (cycles since tile0 iter8 loop_top); deltas in ()")
-    for j in range(16):
-        row = [int(tr[t, j, k]) - base for k in range(6)]
-        d = [row[0]] + [row[k] - row[k - 1] for k in range(1, 6)]
-        print(f"  j={j+8:2d} " + " ".join(f"{row[k]:7d}({d[k]:5d})" for k in range(6)))
-
-print("MMA warp: [top, s_free seen, QK issued, p_full seen, PV issued]")
-for j in range(2, 8):
-    for t in range(2):
-        row = [int(mt[t, j, k]) - base for k in range(5)]
-        print(f"  j={j+8:2d} t={t} " + " ".join(f"{x:7d}" for x in row))
+    print(f"tile {t}: {names}; absolute(delta)")
+    for j in range(2, 6):
+        row = [int(tr[t, j, k]) - base for k in range(7)]
+        d = [0] + [row[k] - row[k - 1] for k in range(1, 7)]
+        print(f"  j={j+8:2d} " + " ".join(f"{row[k]:6d}({d[k]:4d})" for k in range(7)))
