@@ -25,6 +25,8 @@
 // soon as it is in registers (P_t has its own TMEM columns), so Q K^T of the next K/V tile runs
 // under the exp pass of the current one.
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace mab {
@@ -34,6 +36,9 @@ constexpr int ATT_QT = 2;      // Q tiles per CTA
 constexpr int ATT_BKV = 128;
 constexpr int ATT_D = 64;
 constexpr int ATT_KV_STAGES = 4;
+#ifndef ATT_POLY_OF_8
+#define ATT_POLY_OF_8 0   // share (x/8) of the exponentials evaluated by polynomial on the FMA pipe
+#endif
 constexpr int ATT_THREADS = 128 + ATT_QT * 128;  // 4 control warps (one per scheduler) + 8 softmax warps
 constexpr int ATT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: Q, K and V tiles alike
 constexpr int ATT_SMEM_BYTES = (ATT_QT + 2 * ATT_KV_STAGES) * ATT_TILE_BYTES + 512 + 1024;
@@ -271,20 +276,20 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&s_free[t]);
-        // ---- row max (four independent chains) ----
-        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-        if (full) {
-#pragma unroll
-          for (int i = 0; i < 128; i += 8) {
-            mx0 = max3(mx0, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
-            mx1 = max3(mx1, __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
-            mx2 = max3(mx2, __uint_as_float(v[i + 4]), __uint_as_float(v[i + 5]));
-            mx3 = max3(mx3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
-          }
-        } else {
+        if (take_turns) bar_sync_named(1 + t, 2 * ATT_BQ);
+        if (!full) {  // partial last tile: columns >= valid become -inf (exp2 -> 0), common path unmasked
 #pragma unroll
           for (int i = 0; i < 128; ++i)
-            if (i < valid) mx0 = fmaxf(mx0, __uint_as_float(v[i]));
+            if (i >= valid) v[i] = 0xff800000u;
+        }
+        // ---- row max (four independent chains) ----
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 128; i += 8) {
+          mx0 = max3(mx0, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
+          mx1 = max3(mx1, __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+          mx2 = max3(mx2, __uint_as_float(v[i + 4]), __uint_as_float(v[i + 5]));
+          mx3 = max3(mx3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
         }
         const float mx = fmaxf(max3(mx0, mx1, mx2), mx3);  // finite: every tile has >= 1 valid column
         // advance the reference max only when it is exceeded by more than 2^8 in the exp2 domain
@@ -292,33 +297,50 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         const float m_new = grow_ref ? mx : m_ref;
         const float alpha = grow_ref ? fast_exp2((m_ref - m_new) * sc) : 1.0f;  // exp2(-inf) = 0
         const bool rescale = __any_sync(0xffffffffu, grow_ref) && (j > 0 || p.carry_in);
-        float nmb = -m_new * sc;
-        if (take_turns) bar_sync_named_dep(1 + t, 2 * ATT_BQ, nmb);  // every exp below depends on nmb
+        const float nmb = -m_new * sc;
         const uint64_t nmb2 = pack_f2(nmb, nmb);
         // ---- P = exp2(S*c - m*c) -> bf16 (registers), row sum ----
+        // ATT_POLY_OF_8 of every 8 groups of four exponentials are evaluated on the FMA/ALU pipes
+        // (round-to-nearest split x = n + f, |f| <= 0.5, degree-3 minimax 2^f, exponent add: relative
+        // error 7.5e-5, far below the bf16 rounding of P) instead of the 16-lane MUFU, which is the
+        // unit that bounds this loop.
         uint32_t pk[64];
         uint64_t sum_a = pack_f2(0.f, 0.f), sum_b = sum_a;
+        const uint64_t magic2 = pack_f2(12582912.f, 12582912.f), nmagic2 = pack_f2(-12582912.f, -12582912.f);
+        const uint64_t neg1_2 = pack_f2(-1.f, -1.f);
+        const uint64_t pc3 = pack_f2(0.0551716685f, 0.0551716685f), pc2 = pack_f2(0.2426111251f, 0.2426111251f);
+        const uint64_t pc1 = pack_f2(0.6932609677f, 0.6932609677f), pc0 = pack_f2(0.9999280572f, 0.9999280572f);
+        auto exp2_poly2 = [&](float xa, float xb, float& ea, float& eb) {
+          const uint64_t x2 = pack_f2(fmaxf(xa, -125.f), fmaxf(xb, -125.f));
+          const uint64_t r2 = add_f2(x2, magic2);          // low mantissa bits = round(x)
+          const uint64_t f2 = fma_f2(add_f2(r2, nmagic2), neg1_2, x2);
+          uint64_t p2 = fma_f2(pc3, f2, pc2);
+          p2 = fma_f2(p2, f2, pc1);
+          p2 = fma_f2(p2, f2, pc0);
+          float ra, rb, pa, pb;
+          unpack_f2(r2, ra, rb);
+          unpack_f2(p2, pa, pb);
+          ea = __int_as_float(__float_as_int(pa) + (__float_as_int(ra) << 23));
+          eb = __int_as_float(__float_as_int(pb) + (__float_as_int(rb) << 23));
+        };
 #pragma unroll
         for (int i = 0; i < 128; i += 4) {
           float x0, x1, x2, x3;
           unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])), sc2, nmb2), x0, x1);
           unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i + 2]), __uint_as_float(v[i + 3])), sc2, nmb2), x2, x3);
-          float e0 = fast_exp2(x0), e1 = fast_exp2(x1), e2 = fast_exp2(x2), e3 = fast_exp2(x3);
-          if (!full) {
-            if (i >= valid) e0 = 0.f;
-            if (i + 1 >= valid) e1 = 0.f;
-            if (i + 2 >= valid) e2 = 0.f;
-            if (i + 3 >= valid) e3 = 0.f;
+          float e0, e1, e2, e3;
+          if (((i >> 2) & 7) < ATT_POLY_OF_8) {
+            exp2_poly2(x0, x1, e0, e1);
+            exp2_poly2(x2, x3, e2, e3);
+          } else {
+            e0 = fast_exp2(x0); e1 = fast_exp2(x1); e2 = fast_exp2(x2); e3 = fast_exp2(x3);
           }
           sum_a = add_f2(sum_a, pack_f2(e0, e1));
           sum_b = add_f2(sum_b, pack_f2(e2, e3));
           pk[i >> 1] = cvt_bf16x2(e0, e1);
           pk[(i >> 1) + 1] = cvt_bf16x2(e2, e3);
         }
-        float s0, s1;
-        unpack_f2(add_f2(sum_a, sum_b), s0, s1);
-        const float row_sum = s0 + s1;  // depends on every exp of the row
-        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named_dep(1 + (t ^ 1), 2 * ATT_BQ, row_sum);
+        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named(1 + (t ^ 1), 2 * ATT_BQ);
         // ---- P_t and O_t are free once P_t(j-1) V has completed ----
         if (j > 0) {
           mbar_wait(&pv_done[t], (j - 1) & 1);
@@ -350,7 +372,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[t]);
-        l_run = fmaf(l_run, alpha, row_sum);
+        float s0, s1;
+        unpack_f2(add_f2(sum_a, sum_b), s0, s1);
+        l_run = fmaf(l_run, alpha, s0 + s1);
         m_ref = m_new;
       }
 
