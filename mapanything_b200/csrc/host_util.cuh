@@ -251,7 +251,7 @@ inline int launch_gemm(const void* A, long long lda, const void* B, long long ld
   MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM));
   if (N > 128) {
     // tile width by wave quantisation: the persistent grid has sm_count/2 clusters, each 256 x BN
-    // tile costs ~BN (x1.04 at BN = 192: the B half-tile amortises less of the A traffic); e.g. the
+    // tile costs ~BN (x1.12 at BN = 192, measured: the B half-tile amortises less of the A traffic); e.g. the
     // info-sharing width 768 gives 99 tiles of 256 (2 waves on 74 clusters, 67 % full) but 132
     // tiles of 192 (2 waves, 89 % full)
     const int num_mg = ((M + GEMM_BM - 1) / GEMM_BM + GEMM_CL - 1) / GEMM_CL, clusters = sm_count() / GEMM_CL;
@@ -259,7 +259,7 @@ inline int launch_gemm(const void* A, long long lda, const void* B, long long ld
       const int tiles = num_mg * ((N + bn - 1) / bn);
       return ((tiles + clusters - 1) / clusters) * bn * unit;
     };
-    if (cost(192, 1.04) < cost(256, 1.0)) {
+    if (cost(192, 1.12) < cost(256, 1.0)) {
       MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 192 / GEMM_CL));
       return launch_gemm_t<192, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
     }
