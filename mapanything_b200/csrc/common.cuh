@@ -39,6 +39,27 @@ __device__ __forceinline__ float fast_exp2(float x) {  // MUFU.EX2, 2 ulp; exp2(
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// L2 residency hints: the fp32 residual stream (34 MB at 8 views) is re-read by every LayerNorm and
+// residual epilogue while > 150 MB of single-use activations (qkv, attention output, MLP hidden)
+// stream through the 126 MB L2 per layer; evict_last keeps the stream resident.
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ float4 ld_f4_l2hint(const float* p, uint64_t pol) {
+  float4 v;
+  asm volatile("ld.global.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ void st_f4_l2hint(float* p, float4 v, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w), "l"(pol)
+               : "memory");
+}
+
 // named barriers (ids 1..15; 0 is __syncthreads): producer/consumer hand-off between warp groups
 __device__ __forceinline__ void bar_sync_named(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");

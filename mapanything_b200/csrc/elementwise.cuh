@@ -33,12 +33,13 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows_out, int 
   pdl_trigger();
   if (warp >= rows_out) return;
   const long long in_row = (long long)(warp / group_out) * group_in + skip + warp % group_out;
-  const float4* xr = reinterpret_cast<const float4*>(x + in_row * C);
+  const float* xr = x + in_row * C;
+  const uint64_t keep = l2_policy_evict_last();  // the residual stream is read again by the next epilogue
   float4 v[VPL];
   float s = 0.f;
 #pragma unroll
   for (int i = 0; i < VPL; ++i) {
-    v[i] = xr[lane + 32 * i];
+    v[i] = ld_f4_l2hint(xr + 4 * (lane + 32 * i), keep);
     s += v[i].x + v[i].y + v[i].z + v[i].w;
   }
   auto normalise = [&](const float* ww, const float* bb) {

@@ -134,6 +134,7 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
   const bool has_g = G ? ep.gamma != nullptr : (F & EF_GAMMA) != 0;
   const bool gelu = G ? ep.act == ACT_GELU : (F & EF_GELU) != 0;
   const bool relu = G ? ep.act == ACT_RELU : (F & EF_RELU) != 0;
+  const uint64_t keep = l2_policy_evict_last();
 #pragma unroll 1
   for (int c0 = c_begin; c0 < c_end; c0 += 32) {
     const int ncol0 = n0 + c0;
@@ -163,7 +164,7 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
       a[i] = *reinterpret_cast<const float4*>(stg + r * 32 + ((sub_c4 ^ (r & 7)) << 2));
       const bool ok = (mask >> i) & 1;
       const long long off = ro[i] + col;
-      if (has_rf) rf[i] = ok ? *reinterpret_cast<const float4*>(ep.res_f32 + off) : make_float4(0, 0, 0, 0);
+      if (has_rf) rf[i] = ok ? ld_f4_l2hint(ep.res_f32 + off, keep) : make_float4(0, 0, 0, 0);
       if (has_r1) r1[i] = ok ? *reinterpret_cast<const uint2*>(ep.res1 + off) : make_uint2(0, 0);
       if (has_r2) r2[i] = ok ? *reinterpret_cast<const uint2*>(ep.res2 + off) : make_uint2(0, 0);
     }
@@ -192,7 +193,10 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
         x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
       }
       const long long off = ro[i] + col;
-      if (has_of) *reinterpret_cast<float4*>(ep.out_f32 + off) = x;
+      if (has_of) {
+        if (has_rf) st_f4_l2hint(ep.out_f32 + off, x, keep);  // the residual stream stays in L2
+        else *reinterpret_cast<float4*>(ep.out_f32 + off) = x;
+      }
       if (has_ob) {
         const uint2 hi = make_uint2(pack_bf16(x.x, x.y), pack_bf16(x.z, x.w));
         *reinterpret_cast<uint2*>(ep.out_bf16 + off) = hi;
