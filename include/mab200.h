@@ -151,6 +151,11 @@ int mab_stage_scale_head(mab_handle* h, float* metric_scale_out, void* stream);
  * the scale-token rank, or NULL to compute it here (single GPU). */
 int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out,
                     const float* metric_scale_in, void* stream);
+/* The same for the views [view_lo, view_hi) of this rank only; out->metric_scale must already hold
+ * the scene's metric scale.  Lets the caller post-process and copy out finished views while the
+ * heads of later views compute (MapAnything.infer(host_outputs=True)). */
+int mab_stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, int view_lo,
+                          int view_hi, void* stream);
 
 /* Launch accounting for bench.py: kernels launched by this library since load, and an optional
  * per-launch CUDA-event profiler (events recorded on the launch stream around every kernel). */

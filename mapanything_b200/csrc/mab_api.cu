@@ -1093,9 +1093,30 @@ extern "C" int mab_stage_scale_head(mab_handle* h, float* metric_scale_out, void
   return 0;
 }
 
+namespace {
+int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, const float* metric_scale_in,
+                      int view_lo, int view_hi, bool with_scale, void* stream);
+}
+
 extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out,
                                const float* metric_scale_in, void* stream) {
   MAB_ARG(h && in && out && h->plan.V > 0, "mab_stage_encode must run first");
+  return stage_heads_range(h, in, out, metric_scale_in, 0, h->plan.V, true, stream);
+}
+
+// Heads of the views [view_lo, view_hi) of this rank only (pointers in `out` address the rank's whole
+// arrays).  out->metric_scale must already hold the scene's metric scale (mab_stage_scale_head or
+// a broadcast).  Lets the caller post-process and copy out finished views while later ones compute.
+extern "C" int mab_stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, int view_lo,
+                                     int view_hi, void* stream) {
+  MAB_ARG(h && in && out && h->plan.V > 0, "mab_stage_encode must run first");
+  MAB_ARG(view_lo >= 0 && view_lo < view_hi && view_hi <= h->plan.V, "bad view range");
+  return stage_heads_range(h, in, out, out->metric_scale, view_lo, view_hi, false, stream);
+}
+
+namespace {
+int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, const float* metric_scale_in,
+                      int view_lo, int view_hi, bool with_scale, void* stream) {
   const mab_config& cf = h->cfg;
   Ctx c{h, (cudaStream_t)stream};
   Plan& p = h->plan;
@@ -1104,7 +1125,9 @@ extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs*
 
   // ---- scale head: computed here by the rank that owns the scale token, unless the caller
   // already ran mab_stage_scale_head and broadcast its result (view-sharded run) ------------------
-  if (metric_scale_in) {
+  if (!with_scale) {
+    // the caller has placed the metric scale in out->metric_scale
+  } else if (metric_scale_in) {
     if (metric_scale_in != out->metric_scale)
       MAB_CUDA(cudaMemcpyAsync(out->metric_scale, metric_scale_in, sizeof(float), cudaMemcpyDeviceToDevice, c.st));
   } else {
@@ -1116,8 +1139,8 @@ extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs*
   const std::string ip = "dpt_feature_head.input_process.";
   const std::string sc = "dpt_feature_head.scratch.";
   const int h3 = (hh + 1) / 2, w3 = (ww + 1) / 2;
-  for (int v0 = 0; v0 < V; v0 += p.vc) {
-    const int vc = (V - v0 < p.vc) ? V - v0 : p.vc;
+  for (int v0 = view_lo; v0 < view_hi; v0 += p.vc) {
+    const int vc = (view_hi - v0 < p.vc) ? view_hi - v0 : p.vc;
     const int M = vc * T;
     const bf16* f0 = p.fused + (long long)v0 * T * cf.enc_dim;
     const bf16* f1 = p.tap[0] + (long long)v0 * T * A;
@@ -1215,6 +1238,7 @@ extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs*
   }
   return 0;
 }
+}  // namespace
 
 extern "C" int mab_forward(mab_handle* h, const mab_inputs* in, mab_outputs* out, void* workspace,
                            size_t workspace_bytes, void* stream) {

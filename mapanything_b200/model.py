@@ -101,6 +101,8 @@ class MapAnything(torch.nn.Module):
         self._finalized = False
         self._workspace = None
         self._post_ws = None
+        self._host_pool = None
+        self._copy_stream = None
         self._ring_bufs = None
         self._kv_all = None
         if pretrained_checkpoint_path is not None:
@@ -318,7 +320,8 @@ class MapAnything(torch.nn.Module):
     def _out_struct(o):
         return _lib.MabOutputs(**{k: (o[k].data_ptr() if k in o else None) for k, _ in _lib.MabOutputs._fields_})
 
-    def _run_forward(self, imgs, H, W, want_logits=False, view_lo=0, total_views=None, geo=None):
+    def _run_forward(self, imgs, H, W, want_logits=False, view_lo=0, total_views=None, geo=None,
+                     on_views=None, stream_chunk=0):
         """One whole forward of this rank's views: returns the raw output tensors (views stacked).
 
         Single GPU (total_views == views): one `mab_forward` call.  View-sharded
@@ -335,14 +338,41 @@ class MapAnything(torch.nn.Module):
             outs = self._alloc_outputs(V, H, W, want_logits)
             inp = self._input_struct(imgs, H, W, geo)
             ost = self._out_struct(outs)
-            if total == V:
+            if on_views is not None:
+                # streamed heads: trunk for all views, then the heads `stream_chunk` views at a time,
+                # handing every finished range to the caller (post-processing + copy-out overlap the
+                # heads of the later views)
+                if total == V:
+                    self._trunk_single(inp, outs, ws)
+                else:
+                    self._forward_sharded(inp, ost, outs, ws, V, H, W, view_lo, total, heads=False)
+                step = max(1, int(stream_chunk) or self._cfg.head_chunk)
+                for v0 in range(0, V, step):
+                    v1 = min(V, v0 + step)
+                    _lib.check(self._lib.mab_stage_heads_range(self._handle, C.byref(inp), C.byref(ost), v0, v1,
+                                                               self._stream_ptr()), "mab_stage_heads_range")
+                    on_views(outs, v0, v1)
+            elif total == V:
                 _lib.check(self._lib.mab_forward(self._handle, C.byref(inp), C.byref(ost), ws.data_ptr(),
                                                  ws.numel(), self._stream_ptr()), "mab_forward")
             else:
                 self._forward_sharded(inp, ost, outs, ws, V, H, W, view_lo, total)
         return outs
 
-    def _forward_sharded(self, inp, ost, outs, ws, V, H, W, view_lo, total):
+    def _trunk_single(self, inp, outs, ws):
+        """Encoder + info sharing + scale head of a whole scene on this GPU through the staged ABI
+        (what mab_forward does internally), leaving the per-view heads to the caller."""
+        lib, hd, st = self._lib, self._handle, self._stream_ptr()
+        _lib.check(lib.mab_stage_encode(hd, C.byref(inp), inp.views, ws.data_ptr(), ws.numel(), 3, st),
+                   "mab_stage_encode")
+        both = _lib.RING_FIRST | _lib.RING_LAST
+        for layer in range(self._cfg.aat_depth):
+            _lib.check(lib.mab_stage_aat_qkv(hd, layer, None, None, st), "mab_stage_aat_qkv")
+            _lib.check(lib.mab_stage_aat_attend(hd, layer, None, 0, both, st), "mab_stage_aat_attend")
+            _lib.check(lib.mab_stage_aat_finish(hd, layer, st), "mab_stage_aat_finish")
+        _lib.check(lib.mab_stage_scale_head(hd, outs["metric_scale"].data_ptr(), st), "mab_stage_scale_head")
+
+    def _forward_sharded(self, inp, ost, outs, ws, V, H, W, view_lo, total, heads=True):
         import torch.distributed as dist
 
         from . import parallel
@@ -410,14 +440,13 @@ class MapAnything(torch.nn.Module):
             _lib.check(lib.mab_stage_scale_head(hd, outs["metric_scale"].data_ptr(), self._stream_ptr()),
                        "mab_stage_scale_head")
         dist.broadcast(outs["metric_scale"], src=0)
-        _lib.check(lib.mab_stage_heads(hd, C.byref(inp), C.byref(ost), outs["metric_scale"].data_ptr(),
-                                       self._stream_ptr()), "mab_stage_heads")
+        if heads:
+            _lib.check(lib.mab_stage_heads(hd, C.byref(inp), C.byref(ost), outs["metric_scale"].data_ptr(),
+                                           self._stream_ptr()), "mab_stage_heads")
 
-    def _run_postprocess(self, imgs, outs, H, W, apply_mask=True, mask_edges=True, edge_normal_threshold=5.0,
-                         edge_depth_threshold=0.03, apply_confidence_mask=False, confidence_percentile=10):
-        """inference.py:314-506 on the device, all views of this rank at once."""
-        V, dev = imgs.shape[0], self._device
-        post = dict(
+    def _alloc_post(self, V, H, W):
+        dev = self._device
+        return dict(
             img_no_norm=torch.empty((V, H, W, 3), dtype=torch.float32, device=dev),
             depth_z=torch.empty((V, H, W, 1), dtype=torch.float32, device=dev),
             intrinsics=torch.empty((V, 3, 3), dtype=torch.float32, device=dev),
@@ -426,13 +455,26 @@ class MapAnything(torch.nn.Module):
             cam_quats=torch.empty((V, 4), dtype=torch.float32, device=dev),
             mask=torch.empty((V, H, W, 1), dtype=torch.bool, device=dev),
         )
+
+    def _run_postprocess(self, imgs, outs, H, W, apply_mask=True, mask_edges=True, edge_normal_threshold=5.0,
+                         edge_depth_threshold=0.03, apply_confidence_mask=False, confidence_percentile=10,
+                         post=None, view_lo=0, view_hi=None):
+        """inference.py:314-506 on the device: all views of this rank at once, or the range
+        [view_lo, view_hi) of them (every step is per-view independent)."""
+        dev = self._device
+        view_hi = imgs.shape[0] if view_hi is None else view_hi
+        if post is None:
+            post = self._alloc_post(imgs.shape[0], H, W)
+        V = view_hi - view_lo
+        sl = slice(view_lo, view_hi)
         with torch.cuda.device(dev):
             need = V * H * W * 18 + V * 8 + 1024
             if self._post_ws is None or self._post_ws.numel() < need:
                 self._post_ws = torch.empty(need, dtype=torch.uint8, device=dev)
-            inp = _lib.MabInputs(views=V, H=H, W=W, images=imgs.data_ptr())
-            ost = self._out_struct(outs)
-            pst = _lib.MabPostOutputs(**{k: post[k].data_ptr() for k, _ in _lib.MabPostOutputs._fields_})
+            inp = _lib.MabInputs(views=V, H=H, W=W, images=imgs[sl].data_ptr())
+            ost = _lib.MabOutputs(**{k: ((outs[k] if k == "metric_scale" else outs[k][sl]).data_ptr() if k in outs else None)
+                                     for k, _ in _lib.MabOutputs._fields_})
+            pst = _lib.MabPostOutputs(**{k: post[k][sl].data_ptr() for k, _ in _lib.MabPostOutputs._fields_})
             opt = _lib.MabPostOptions(int(apply_mask), int(mask_edges), float(edge_normal_threshold),
                                       float(edge_depth_threshold), int(apply_confidence_mask),
                                       float(confidence_percentile))
@@ -469,6 +511,64 @@ class MapAnything(torch.nn.Module):
             })
         return res
 
+    # prediction key -> (source dict, key there)
+    _PRED_KEYS = (("pts3d", "raw", "pts3d"), ("pts3d_cam", "raw", "pts3d_cam"),
+                  ("ray_directions", "raw", "ray_directions"), ("depth_along_ray", "raw", "depth_along_ray"),
+                  ("cam_trans", "post", "cam_trans"), ("cam_quats", "post", "cam_quats"),
+                  ("conf", "raw", "conf"), ("non_ambiguous_mask", "raw", "non_ambiguous_mask"),
+                  ("non_ambiguous_mask_logits", "raw", "mask_logits"), ("img_no_norm", "post", "img_no_norm"),
+                  ("depth_z", "post", "depth_z"), ("intrinsics", "post", "intrinsics"),
+                  ("camera_poses", "post", "camera_poses"), ("mask", "post", "mask"))
+
+    def _infer_to_host(self, imgs, H, W, view_lo, total_views, geo, post_args, stream_chunk):
+        """infer(host_outputs=True): heads in ranges of `stream_chunk` views; post-processing of a
+        finished range on the compute stream, its device-to-host copies on a second stream."""
+        V, dev = imgs.shape[0], self._device
+        apply_mask = post_args[0]
+        post = self._alloc_post(V, H, W)
+        key = (V, H, W)
+        if self._host_pool is None or self._host_pool[0] != key:
+            raw_shapes = self._alloc_outputs(1, H, W)  # one view: shapes / dtypes only
+            bufs = {}
+            for name, src, k in self._PRED_KEYS:
+                t = raw_shapes[k] if src == "raw" else self._alloc_post(1, H, W)[k]
+                bufs[name] = torch.empty((V,) + tuple(t.shape[1:]), dtype=t.dtype, pin_memory=True)
+            bufs["metric_scaling_factor"] = torch.empty((1, 1), dtype=torch.float32, pin_memory=True)
+            self._host_pool = (key, bufs)
+        host = self._host_pool[1]
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        side = self._copy_stream
+        main = torch.cuda.current_stream(dev)
+
+        def on_views(outs, v0, v1):
+            self._run_postprocess(imgs, outs, H, W, *post_args, post=post, view_lo=v0, view_hi=v1)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            with torch.cuda.stream(side):
+                side.wait_event(ev)
+                for name, src, k in self._PRED_KEYS:
+                    if name == "mask" and not apply_mask:
+                        continue
+                    host[name][v0:v1].copy_((outs if src == "raw" else post)[k][v0:v1], non_blocking=True)
+                if v0 == 0:
+                    host["metric_scaling_factor"].copy_(outs["metric_scale"], non_blocking=True)
+
+        with torch.cuda.device(dev):
+            side.wait_stream(main)  # the pool may still be read by copies of the previous call
+            outs = self._run_forward(imgs, H, W, view_lo=view_lo, total_views=total_views, geo=geo,
+                                     on_views=on_views, stream_chunk=stream_chunk)
+            side.synchronize()
+        # the device tensors were only consumed on `side`: tell the caching allocator
+        for t in list(outs.values()) + list(post.values()):
+            t.record_stream(side)
+        preds = []
+        for i in range(V):
+            d = {name: host[name][i:i + 1] for name, _, _ in self._PRED_KEYS if name != "mask" or apply_mask}
+            d["metric_scaling_factor"] = host["metric_scaling_factor"]
+            preds.append(d)
+        return preds
+
     # ------------------------------------------------------------------ public API
     @torch.inference_mode()
     def forward(self, views, memory_efficient_inference: bool = False):
@@ -490,14 +590,22 @@ class MapAnything(torch.nn.Module):
               confidence_percentile: float = 10, ignore_calibration_inputs: bool = False,
               ignore_depth_inputs: bool = False, ignore_pose_inputs: bool = False,
               ignore_depth_scale_inputs: bool = False, ignore_pose_scale_inputs: bool = False,
-              view_range=None, total_views: Optional[int] = None) -> List[Dict[str, torch.Tensor]]:
+              view_range=None, total_views: Optional[int] = None, host_outputs: bool = False,
+              stream_chunk: int = 4) -> List[Dict[str, torch.Tensor]]:
         """model.py:2206-2355.  The kernels always compute in bf16 with fp32 accumulation / fp32
         residual streams (the reference's bf16-autocast semantics); `use_amp`/`amp_dtype` are
         accepted for signature compatibility.
 
         Extension for view-sharded scenes (one process per GPU, torch.distributed initialised):
         `views` are THIS rank's views [view_range[0], view_range[1]) of a scene of `total_views`
-        views (parallel.shard_views gives the table); the returned list covers the same views."""
+        views (parallel.shard_views gives the table); the returned list covers the same views.
+
+        Extension `host_outputs=True`: the prediction tensors are returned in PINNED HOST memory.
+        The heads then run `stream_chunk` views at a time and every finished range is post-processed
+        and copied out on a second stream while the heads of the later views compute, so the
+        107 MB of predictions per 8 views leave the device under the dense head instead of after
+        it.  The returned tensors are views into a buffer the model reuses: valid until the next
+        `infer(host_outputs=True)` call on this model."""
         if not self._finalized:
             raise RuntimeError("load_state_dict() / from_pretrained() must be called before inference")
         views = validate_input_views_for_inference(views)
@@ -507,18 +615,24 @@ class MapAnything(torch.nn.Module):
         flags = dict(use_calibration=not ignore_calibration_inputs, use_depth=not ignore_depth_inputs,
                      use_pose=not ignore_pose_inputs, use_depth_scale=not ignore_depth_scale_inputs,
                      use_pose_scale=not ignore_pose_scale_inputs)  # model.py:2154-2197
-        # move the caller's tensors to the model device in place, like model.py:2316-2320
-        for v in views:
-            for name in list(v.keys()):
-                if name not in _PASS_THROUGH and torch.is_tensor(v[name]):
-                    v[name] = v[name].to(self._device, non_blocking=True)
+        # move the caller's tensors to the model device in place, like model.py:2316-2320; the images
+        # go host -> device stack in ONE copy and the caller's dict receives a view of that stack
         V = len(views)
         imgs, H, W = self._pack_images(views)
+        for i, v in enumerate(views):
+            for name in list(v.keys()):
+                if name == "img":
+                    v[name] = imgs[i:i + 1]
+                elif name not in _PASS_THROUGH and torch.is_tensor(v[name]):
+                    v[name] = v[name].to(self._device, non_blocking=True)
         lo = view_range[0] if view_range else 0
         geo = self._pack_geometry(views, flags, H, W, view_lo=lo, total_views=total_views)
+        post_args = (apply_mask, mask_edges, edge_normal_threshold, edge_depth_threshold, apply_confidence_mask,
+                     confidence_percentile)
+        if host_outputs:
+            return self._infer_to_host(imgs, H, W, lo, total_views, geo, post_args, stream_chunk)
         outs = self._run_forward(imgs, H, W, view_lo=lo, total_views=total_views, geo=geo)
-        post = self._run_postprocess(imgs, outs, H, W, apply_mask, mask_edges, edge_normal_threshold,
-                                     edge_depth_threshold, apply_confidence_mask, confidence_percentile)
+        post = self._run_postprocess(imgs, outs, H, W, *post_args)
         preds = []
         scale = outs["metric_scale"]
         for i in range(V):

@@ -214,3 +214,23 @@ def test_multimodal_ignore_flags_match_oracle(ignore, model, sd_cuda):
             e = helpers.rel_l2((p[k].float().cpu() * m).numpy(), (r[k] * m).numpy())
             y = helpers.rel_l2((a[k] * m).numpy(), (r[k] * m).numpy())
             assert e < max(TOL_DENSE, 3.0 * y), (k, e, y)
+
+
+def test_infer_host_outputs_equals_device_outputs(model):
+    """infer(host_outputs=True) streams the heads in ranges and copies finished views out on a second
+    stream: same kernels on the same data, so the host tensors must equal the device path bit for bit."""
+    from oracle import weights
+
+    views = weights.add_multimodal_inputs(weights.synthetic_views(5, 56, 84, seed=21), seed=22)
+    kw = dict(apply_confidence_mask=True, confidence_percentile=30)
+    dev = model.infer([dict(v) for v in views], **kw)
+    torch.cuda.synchronize()
+    for chunk in (1, 2, 8):
+        host = model.infer([dict(v) for v in views], host_outputs=True, stream_chunk=chunk, **kw)
+        assert len(host) == len(dev)
+        for h, d in zip(host, dev):
+            assert set(h.keys()) == set(d.keys())
+            for k in d:
+                assert h[k].device.type == "cpu" and h[k].is_pinned(), k
+                assert h[k].shape == d[k].shape and h[k].dtype == d[k].dtype, k
+                assert torch.equal(h[k], d[k].cpu()), (k, chunk)
