@@ -32,16 +32,26 @@
 namespace mab {
 
 constexpr int ATT_BQ = 128;    // rows of one Q tile (one UMMA M)
-constexpr int ATT_QT = 2;      // Q tiles per CTA
+constexpr int ATT_QT = 2;      // Q tiles per CTA (long sequences); short sequences use 1, two CTAs per SM
 constexpr int ATT_BKV = 128;
 constexpr int ATT_D = 64;
 constexpr int ATT_KV_STAGES = 4;
 #ifndef ATT_POLY_OF_8
 #define ATT_POLY_OF_8 0   // share (x/8) of the exponentials evaluated by polynomial on the FMA pipe
 #endif
-constexpr int ATT_THREADS = 128 + ATT_QT * 128;  // 4 control warps (one per scheduler) + 8 softmax warps
+// QT = 2: 4 control warps (one per scheduler partition) + 8 softmax warps, 4-stage K/V rings, 512 TMEM columns.
+// QT = 1: 2 control warps + 4 softmax warps, 2-stage rings, 256 TMEM columns -> two CTAs per SM whose
+//         prologues / epilogues / MMA latencies overlap each other (short sequences: 9 K/V tiles per CTA).
+template <int QT> struct AttCfg {
+  static constexpr int CTRL_WARPS = QT == 2 ? 4 : 2;
+  static constexpr int THREADS = 32 * CTRL_WARPS + QT * 128;
+  static constexpr int STAGES = QT == 2 ? 4 : 2;
+  static constexpr int TMEM_COLS = QT == 2 ? 512 : 256;
+  static constexpr int SMEM_BYTES = (QT + 2 * STAGES) * 128 * 64 * 2 + 512 + 1024;
+};
+constexpr int ATT_THREADS = AttCfg<2>::THREADS;
 constexpr int ATT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: Q, K and V tiles alike
-constexpr int ATT_SMEM_BYTES = (ATT_QT + 2 * ATT_KV_STAGES) * ATT_TILE_BYTES + 512 + 1024;
+constexpr int ATT_SMEM_BYTES = AttCfg<2>::SMEM_BYTES;
 
 struct AttnParams {
   int num_seqs, heads;
@@ -91,47 +101,50 @@ __device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
   return r;
 }
 
-__global__ void __launch_bounds__(ATT_THREADS, 1)
+template <int QT>
+__global__ void __launch_bounds__(AttCfg<QT>::THREADS, QT == 2 ? 1 : 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, AttnParams p) {
+  constexpr int KS = AttCfg<QT>::STAGES;
+  constexpr int CTRL = AttCfg<QT>::CTRL_WARPS;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   uint8_t* sQ = smem;                                   // [QT] tiles
-  uint8_t* sK = smem + ATT_QT * ATT_TILE_BYTES;         // [KS] tiles
-  uint8_t* sV = sK + ATT_KV_STAGES * ATT_TILE_BYTES;    // [KS] tiles
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + ATT_KV_STAGES * ATT_TILE_BYTES);
+  uint8_t* sK = smem + QT * ATT_TILE_BYTES;         // [KS] tiles
+  uint8_t* sV = sK + KS * ATT_TILE_BYTES;    // [KS] tiles
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KS * ATT_TILE_BYTES);
   uint64_t* q_full = bars;                         // [1]
   uint64_t* k_full = bars + 1;                     // [KS]
-  uint64_t* k_empty = k_full + ATT_KV_STAGES;      // [KS]
-  uint64_t* v_full = k_empty + ATT_KV_STAGES;      // [KS]
-  uint64_t* v_empty = v_full + ATT_KV_STAGES;      // [KS]
-  uint64_t* s_full = v_empty + ATT_KV_STAGES;      // [QT]  S_t(j) is in TMEM
-  uint64_t* s_free = s_full + ATT_QT;              // [QT]  S_t(j) is in registers: S_t may be overwritten
-  uint64_t* p_full = s_free + ATT_QT;              // [QT]  P_t(j) is in TMEM (and O_t rescaled)
-  uint64_t* pv_done = p_full + ATT_QT;             // [QT]  O_t += P_t(j) V_j has completed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + ATT_QT);
+  uint64_t* k_empty = k_full + KS;      // [KS]
+  uint64_t* v_full = k_empty + KS;      // [KS]
+  uint64_t* v_empty = v_full + KS;      // [KS]
+  uint64_t* s_full = v_empty + KS;      // [QT]  S_t(j) is in TMEM
+  uint64_t* s_free = s_full + QT;              // [QT]  S_t(j) is in registers: S_t may be overwritten
+  uint64_t* p_full = s_free + QT;              // [QT]  P_t(j) is in TMEM (and O_t rescaled)
+  uint64_t* pv_done = p_full + QT;             // [QT]  O_t += P_t(j) V_j has completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + QT);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q_tile = blockIdx.x, head = blockIdx.y, seq = blockIdx.z;
-  const int q_row0 = seq * p.q_seq_stride + q_tile * (ATT_QT * ATT_BQ);
+  const int q_row0 = seq * p.q_seq_stride + q_tile * (QT * ATT_BQ);
   const int kv_row0 = seq * p.kv_seq_stride;
   const int nkv = (p.kv_len + ATT_BKV - 1) / ATT_BKV;
   // the second Q tile of the last CTA of a sequence may hold no query at all: skip it entirely
-  const int ntile = (q_tile * (ATT_QT * ATT_BQ) + ATT_BQ < p.q_len) ? 2 : 1;
+  const int ntile = (QT == 2 && q_tile * (QT * ATT_BQ) + ATT_BQ < p.q_len) ? 2 : 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     mbar_init(q_full, 1);
-    for (int s = 0; s < ATT_KV_STAGES; ++s) {
+    for (int s = 0; s < KS; ++s) {
       mbar_init(&k_full[s], 1);
       mbar_init(&k_empty[s], ntile);  // one commit per tile's MMA issuer
       mbar_init(&v_full[s], 1);
       mbar_init(&v_empty[s], ntile);
     }
-    for (int t = 0; t < ATT_QT; ++t) {
+    for (int t = 0; t < QT; ++t) {
       mbar_init(&s_full[t], 1);
       mbar_init(&s_free[t], 4);  // one arrive per softmax warp of the tile
       mbar_init(&p_full[t], 4);
@@ -139,7 +152,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  if (warp == 1) tmem_alloc(tmem_slot, AttCfg<QT>::TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -148,10 +161,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   // broadcast through a shuffle so that the compiler knows the TMEM base is warp-uniform: otherwise every
   // tcgen05.mma is wrapped in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~100 cycles per instruction)
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
-  // TMEM columns: S_A @0, S_B @128, O_A @256, O_B @320, P_A @384, P_B @448 (bf16 pairs: 64 columns)
+  // TMEM columns (QT = 2): S_A @0, S_B @128, O_A @256, O_B @320, P_A @384, P_B @448 (bf16 pairs: 64
+  // columns); (QT = 1): S @0, O @128, P @192
   auto TM_S = [&](int t) { return tmem_base + t * 128; };
-  auto TM_O = [&](int t) { return tmem_base + 256 + t * 64; };
-  auto TM_P = [&](int t) { return tmem_base + 384 + t * 64; };
+  auto TM_O = [&](int t) { return tmem_base + QT * 128 + t * 64; };
+  auto TM_P = [&](int t) { return tmem_base + QT * 192 + t * 64; };
 
   if (warp == 0) {
     // ===================================== loader =========================================
@@ -160,8 +174,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       for (int t = 0; t < ntile; ++t)
         tma_load_2d(sQ + t * ATT_TILE_BYTES, &tmQ, q_full, p.q_col0 + head * ATT_D, q_row0 + t * ATT_BQ);
       for (int j = 0; j < nkv; ++j) {
-        const int st = j % ATT_KV_STAGES;
-        const uint32_t ph = (j / ATT_KV_STAGES) & 1;
+        const int st = j % KS;
+        const uint32_t ph = (j / KS) & 1;
         mbar_wait(&k_empty[st], ph ^ 1);
         mbar_arrive_expect_tx(&k_full[st], ATT_TILE_BYTES);
         tma_load_2d(sK + st * ATT_TILE_BYTES, &tmK, &k_full[st], p.k_col0 + head * ATT_D,
@@ -172,14 +186,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
                     kv_row0 + j * ATT_BKV);
       }
     }
-  } else if (warp == 1 || warp == 2) {
+  } else if (warp >= 1 && warp <= QT) {
     // ============================== MMA issuer of tile (warp - 1) ==============================
     const int t = warp - 1;
     constexpr uint32_t IDESC_QK = make_idesc_bf16(ATT_BQ, ATT_BKV, 0, 0);
     constexpr uint32_t IDESC_PV = make_idesc_bf16(ATT_BQ, ATT_D, 0, 1);  // B (=V) is MN-major
     auto issue_qk = [&](int j) {  // S_t(j) = Q_t K_j^T
       if (elect_one()) {
-        const int st = j % ATT_KV_STAGES;
+        const int st = j % KS;
         const uint32_t a = smem_u32(sQ + t * ATT_TILE_BYTES), b = smem_u32(sK + st * ATT_TILE_BYTES);
 #pragma unroll
         for (int k = 0; k < ATT_D / 16; ++k)
@@ -195,14 +209,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       tc_fence_after();
       issue_qk(0);
       for (int j = 0; j < nkv; ++j) {
-        const int st = j % ATT_KV_STAGES;
+        const int st = j % KS;
         if (j + 1 < nkv) {
-          mbar_wait(&k_full[(j + 1) % ATT_KV_STAGES], ((j + 1) / ATT_KV_STAGES) & 1);
+          mbar_wait(&k_full[(j + 1) % KS], ((j + 1) / KS) & 1);
           mbar_wait(&s_free[t], j & 1);  // S_t(j) has been read: the next Q K^T may overwrite it
           tc_fence_after();
           issue_qk(j + 1);
         }
-        mbar_wait(&v_full[st], (j / ATT_KV_STAGES) & 1);
+        mbar_wait(&v_full[st], (j / KS) & 1);
         mbar_wait(&p_full[t], j & 1);    // P_t(j) is in TMEM, O_t carries the right scale
         tc_fence_after();
         if (elect_one()) {
@@ -217,13 +231,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         __syncwarp();
       }
     }
-  } else if (warp >= 4) {
+  } else if (warp >= CTRL) {
     // ===================================== softmax ========================================
-    const int t = (warp - 4) >> 2;                      // Q tile of this warp
+    const int t = (warp - CTRL) >> 2;                      // Q tile of this warp
     const int q = warp & 3;                             // TMEM lane quarter (warp id % 4)
     const int row = q * 32 + lane;                      // query row within the tile
     const uint32_t lane_addr = uint32_t(q * 32) << 16;
-    const bool row_ok = q_tile * (ATT_QT * ATT_BQ) + t * ATT_BQ + row < p.q_len;
+    const bool row_ok = q_tile * (QT * ATT_BQ) + t * ATT_BQ + row < p.q_len;
     const long long grow = (long long)q_row0 + t * ATT_BQ + row;
     if (t < ntile) {
       const uint32_t ts = TM_S(t) + lane_addr, to = TM_O(t) + lane_addr, tp = TM_P(t) + lane_addr;
@@ -421,7 +435,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    tmem_dealloc(tmem_base, AttCfg<QT>::TMEM_COLS);
   }
 }
 

@@ -346,13 +346,29 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
   p.carry_o = carry_o; p.carry_ml = carry_ml; p.carry_in = carry_in; p.carry_out = carry_out;
   static bool attr_done = false;
   if (!attr_done) {
-    MAB_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  ATT_SMEM_BYTES));
+    MAB_CUDA(cudaFuncSetAttribute(attention_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  AttCfg<2>::SMEM_BYTES));
+    MAB_CUDA(cudaFuncSetAttribute(attention_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  AttCfg<1>::SMEM_BYTES));
     attr_done = true;
   }
-  dim3 grid((q_len + ATT_QT * ATT_BQ - 1) / (ATT_QT * ATT_BQ), heads, num_seqs);
   ProfScope ps(CAT_ATTENTION, 4.0 * q_len * (double)kv_len * 64.0 * heads * num_seqs, 0.0, st);
-  MAB_CUDA(launch_pdl(attention_kernel, grid, dim3(ATT_THREADS), ATT_SMEM_BYTES, st, 1, tQ, tKV, tKV, p));
+  // short sequences (frame / encoder attention: 9 K/V tiles): one Q tile per CTA, two CTAs per SM;
+  // long ones (global attention): two Q tiles per CTA sharing every K/V tile in shared memory
+  static int short_max = -1;
+  if (short_max < 0) {
+    const char* e = getenv("MAB_ATT_SHORT_MAX");
+    short_max = e ? atoi(e) : 6000;  // measured crossover between 4 and 8 views of global attention
+  }
+  if (kv_len <= short_max) {
+    dim3 grid((q_len + ATT_BQ - 1) / ATT_BQ, heads, num_seqs);
+    MAB_CUDA(launch_pdl(attention_kernel<1>, grid, dim3(AttCfg<1>::THREADS), AttCfg<1>::SMEM_BYTES, st, 1, tQ,
+                        tKV, tKV, p));
+    return 0;
+  }
+  dim3 grid((q_len + ATT_QT * ATT_BQ - 1) / (ATT_QT * ATT_BQ), heads, num_seqs);
+  MAB_CUDA(launch_pdl(attention_kernel<2>, grid, dim3(AttCfg<2>::THREADS), AttCfg<2>::SMEM_BYTES, st, 1, tQ,
+                      tKV, tKV, p));
   MAB_CUDA(cudaGetLastError());
   return 0;
 }
