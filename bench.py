@@ -152,6 +152,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-to-host leg (many-view sweeps)")
+    ap.add_argument("--multimodal", action="store_true",
+                    help="BASELINE.json configs[2]: images + intrinsics + poses + sparse depth (use with --views 32)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -191,7 +194,15 @@ def main():
     dev_imgs = torch.cat([v["img"] for v in host_views], 0).to(dev)
     V = hi - lo
 
+    mm_dev_views = None
+    if args.multimodal:
+        mm_all = synthetic.add_multimodal_inputs(all_views, seed=2)[lo:hi]  # poses follow the global view index
+        mm_dev_views = [{k: (t.to(dev) if torch.is_tensor(t) else t) for k, t in v.items()} for v in mm_all]
+        host_views = [{k: (t.pin_memory() if torch.is_tensor(t) else t) for k, t in v.items()} for v in mm_all]
+
     def step_resident():
+        if mm_dev_views is not None:  # geometric inputs resident on the device, public infer()
+            return model.infer([dict(v) for v in mm_dev_views], view_range=(lo, hi), total_views=n_views)
         outs, post = model.run_resident(dev_imgs, H_IMG, W_IMG, view_range=(lo, hi), total_views=n_views)
         return outs, post
 
@@ -242,7 +253,7 @@ def main():
     def e2e_fn():
         d2h[0] = step_e2e()
 
-    ms_e2e = timed(e2e_fn, max(3, args.steps // 2), 3)
+    ms_e2e = timed(e2e_fn, max(3, args.steps // 2), 3) if not args.no_e2e else float("nan")
     h2d_bytes = V * 3 * H_IMG * W_IMG * 4
 
     roof = None
@@ -304,12 +315,12 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"MapAnything image-only infer, {n_views} views 518x392 (WxH), one scene, random-init weights of the production architecture (DINOv2 ViT-L/14 + 24-layer alternating attention + DPT/pose/scale heads)",
+            "config": {"workload": f"MapAnything {'multi-modal (images + intrinsics + poses + sparse depth)' if args.multimodal else 'image-only'} infer, {n_views} views 518x392 (WxH), one scene, random-init weights of the production architecture (DINOv2 ViT-L/14 + 24-layer alternating attention + DPT/pose/scale heads)",
                        "views": n_views, "views_per_gpu": V, "parallelism": "single GPU" if world == 1 else f"one scene view-sharded x{world}; global attention: all-to-all K|V gather over NCCL/NVLink overlapped with the local block, carried online softmax",
                        "algorithmic_tflop_per_gpu_per_step": flops_per_scene(n_views) / 1e12 / world,
                        "note": "views per GPU are fixed but global attention is quadratic in the scene: algorithmic work per GPU grows as 10.95 + 2.53*N TFLOP with N GPUs (13.5 at N=1, 31.2 at N=8)",
                        "l2": "working set per step (activations of all views, > 1 GB) exceeds the 126 MB L2; no explicit flush"},
-            "tflops_per_gpu": flops_per_scene(n_views) / (ms_step * 1e-3) / 1e12 / world,
+            "tflops_per_gpu": (flops_per_scene(n_views) + (125.5e9 * n_views if args.multimodal else 0.0)) / (ms_step * 1e-3) / 1e12 / world,
             "e2e": {"value": n_views / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h[0],
                     "api": "MapAnything.infer(views, host_outputs=True): pinned host images in, all prediction tensors returned in pinned host memory"},
