@@ -206,6 +206,14 @@ int mab_conv3x3_tf32(const float* x, int batch, int H, int W, int C, const float
 int mab_resize_bilinear(const void* x, int batch, int Hi, int Wi, int C, int Hv, int Wv, int Ho,
                         int Wo, void* out, void* out_relu, void* stream);
 int mab_posembed_resize(const float* pos, int grid, int C, int h, int w, float* out, void* stream);
+/* RoPE2D in place -- the sm_100a equivalent of the reference tree's one native entry point,
+ * `rope_2d(tokens, positions, base, fwd)` (uniception/models/libs/croco/curope/curope.cpp:49-69,
+ * kernels.cu:17-108).  Token i, head h starts at tokens + i*token_pitch + h*head_dim (elements of
+ * `dtype`), so the q and k thirds of a packed [rows, 3*heads*head_dim] qkv buffer are rotated where
+ * they lie; positions [n_tokens, 2] int64 (y, x); fwd = -1 is the inverse rotation.
+ * head_dim % 16 == 0 (curope: % 4), token_pitch % 4 == 0, tokens 16-byte aligned. */
+int mab_rope2d(void* tokens, int dtype, long long n_tokens, int heads, int head_dim,
+               long long token_pitch, const long long* positions, float base, float fwd, void* stream);
 int mab_edge_mask(const float* pts3d, float* pts3d_cam, const unsigned char* fmask, int views, int H,
                   int W, float normal_tol_deg, float depth_rtol, void* workspace,
                   unsigned char* mask_out, void* stream);

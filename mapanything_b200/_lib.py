@@ -80,6 +80,7 @@ SYMBOLS = {
     "mab_conv3x3_tf32": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "mab_resize_bilinear": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "mab_posembed_resize": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "mab_rope2d": (_i, [_vp, _i, C.c_longlong, _i, _i, C.c_longlong, _vp, _f, _f, _vp]),
     "mab_edge_mask": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp, _vp]),
 }
 
@@ -93,7 +94,8 @@ def load(allow_build=True):
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB_PATH
+    # MAB_LIB: a differently-built libmab200 (kernel experiments under profiles/); the ABI is the same
+    path = os.environ.get("MAB_LIB") or _build.LIB_PATH
     if not os.path.exists(path):
         if not allow_build:
             raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")

@@ -23,22 +23,24 @@ def is_stale():
     return any(os.path.getmtime(s) > t for s in _sources())
 
 
-def build(force=False, verbose=False):
-    """Compile csrc/mab_api.cu -> libmab200.so.  Returns the library path."""
-    if not force and not is_stale():
+def build(force=False, verbose=False, out=None, defines=()):
+    """Compile csrc/mab_api.cu -> libmab200.so.  Returns the library path.  `out` / `defines` build a
+    kernel-experiment variant next to it (loaded with MAB_LIB=<path>, see profiles/)."""
+    if out is None and not force and not is_stale():
         return LIB_PATH
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
         raise RuntimeError("nvcc not found: cannot build libmab200.so")
     extra = os.environ.get("MAB_NVCC_EXTRA", "").split()
-    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + \
-          ["-o", LIB_PATH, os.path.join(CSRC, "mab_api.cu")]
+    target = out or LIB_PATH
+    cmd = [nvcc] + NVCC_FLAGS + extra + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else []) + \
+          ["-o", target, os.path.join(CSRC, "mab_api.cu")]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
     if verbose:
         print(res.stderr)
-    return LIB_PATH
+    return target
 
 
 if __name__ == "__main__":

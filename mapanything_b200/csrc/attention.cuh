@@ -36,8 +36,22 @@ constexpr int ATT_QT = 2;      // Q tiles per CTA (long sequences); short sequen
 constexpr int ATT_BKV = 128;
 constexpr int ATT_D = 64;
 constexpr int ATT_KV_STAGES = 4;
-#ifndef ATT_POLY_OF_8
-#define ATT_POLY_OF_8 0   // share (x/8) of the exponentials evaluated by polynomial on the FMA pipe
+#ifndef ATT_TURN_LATE
+#define ATT_TURN_LATE 1   // 1: the softmax turn barrier sits after the row max (0: before it)
+#endif
+// Which of the 16 element pairs of every 32 S columns take their exponentials from a polynomial on
+// the FMA pipe instead of the MUFU (bit k = pair k).  The exp pass is bound by the SM's 16 MUFU lanes;
+// measured (profiles/attn_variants.sh, 66 305 tokens): none 690, 4 adjacent pairs 812, 5 spread pairs
+// (0x1249) 836 TFLOP/s, 6 and more slower again (one warp per scheduler issues the whole pass, so the
+// extra FMA-pipe instructions must fit between its MUFU issues).
+#ifndef ATT_POLY_MASK
+#define ATT_POLY_MASK 0x1249   // long sequences (two Q tiles per CTA)
+#endif
+#ifndef ATT_POLY_MASK_SHORT
+#define ATT_POLY_MASK_SHORT 0x0101   // short sequences (one Q tile per CTA, two CTAs per SM)
+#endif
+#ifndef ATT_NO_TURNS
+#define ATT_NO_TURNS 0
 #endif
 // QT = 2: 4 control warps (one per scheduler partition) + 8 softmax warps, 4-stage K/V rings, 512 TMEM columns.
 // QT = 1: 2 control warps + 4 softmax warps, 2-stage rings, 256 TMEM columns -> two CTAs per SM whose
@@ -106,6 +120,7 @@ __global__ void __launch_bounds__(AttCfg<QT>::THREADS, QT == 2 ? 1 : 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, AttnParams p) {
   constexpr int KS = AttCfg<QT>::STAGES;
+  constexpr int POLY_MASK = QT == 2 ? ATT_POLY_MASK : ATT_POLY_MASK_SHORT;
   constexpr int CTRL = AttCfg<QT>::CTRL_WARPS;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -239,7 +254,20 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     const uint32_t lane_addr = uint32_t(q * 32) << 16;
     const bool row_ok = q_tile * (QT * ATT_BQ) + t * ATT_BQ + row < p.q_len;
     const long long grow = (long long)q_row0 + t * ATT_BQ + row;
-    if (t < ntile) {
+    // A warp whose 32 rows all lie beyond the sequence (1037 = 8 * 128 + 13: three of the four warps
+    // of every sequence's last tile) only keeps the barrier protocol going: no TMEM traffic, no
+    // exponentials, so the MUFU of the SM goes to the co-resident CTA.  Short-sequence kernel only:
+    // the turn barriers of the two-tile kernel count every softmax thread, and the mere presence of
+    // this branch costs its hot loop 17 % (840 -> 700 TFLOP/s measured).
+    const bool idle_warp = QT == 1 && q_tile * ATT_BQ + q * 32 >= p.q_len;
+    if (t < ntile && idle_warp) {
+      for (int j = 0; j < nkv; ++j) {
+        mbar_wait(&s_full[t], j & 1);  // one arrive per phase: never ahead of the tensor core
+        if (lane == 0) mbar_arrive(&s_free[t]);
+        if (j > 0) mbar_wait(&pv_done[t], (j - 1) & 1);
+        if (lane == 0) mbar_arrive(&p_full[t]);
+      }
+    } else if (t < ntile) {
       const uint32_t ts = TM_S(t) + lane_addr, to = TM_O(t) + lane_addr, tp = TM_P(t) + lane_addr;
       const float sc = p.scale_log2e;
       const uint64_t sc2 = pack_f2(sc, sc);
@@ -273,11 +301,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       // The exp pass is bound by the SM's 16 MUFU lanes: the two tiles take turns on it (named
       // barriers 1 = "A's turn", 2 = "B's turn") so that one tile's TMEM traffic, barrier waits and
       // MMA latency always sit under the other tile's exp pass.
-      const bool take_turns = ntile == 2;
+      const bool take_turns = ntile == 2 && !ATT_NO_TURNS;
       if (take_turns && t == 1) bar_arrive_named(1, 2 * ATT_BQ);  // tile A goes first
-      for (int j = 0; j < nkv; ++j) {
+      // One K/V tile of the softmax.  Full tiles and the partial last tile of a sequence are two
+      // separate instantiations, so that the hot (full) body stays one straight-line block.
+      auto kv_tile = [&](const int j, auto full_tag) {
+        constexpr bool full = decltype(full_tag)::value;
         const int valid = p.kv_len - j * ATT_BKV;  // columns >= valid are padding / next sequence
-        const bool full = valid >= ATT_BKV;
         mbar_wait(&s_full[t], j & 1);
         tc_fence_after();
         // ---- the whole S row into registers, then hand S_t back to the tensor core ----
@@ -290,8 +320,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&s_free[t]);
+#if !ATT_TURN_LATE
         if (take_turns) bar_sync_named(1 + t, 2 * ATT_BQ);
-        if (!full) {  // partial last tile: columns >= valid become -inf (exp2 -> 0), common path unmasked
+#endif
+        if (!full || (QT == 2 && valid < ATT_BKV)) {  // partial last tile: columns >= valid become -inf (exp2 -> 0), common path unmasked
 #pragma unroll
           for (int i = 0; i < 128; ++i)
             if (i >= valid) v[i] = 0xff800000u;
@@ -311,10 +343,16 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         const float m_new = grow_ref ? mx : m_ref;
         const float alpha = grow_ref ? fast_exp2((m_ref - m_new) * sc) : 1.0f;  // exp2(-inf) = 0
         const bool rescale = __any_sync(0xffffffffu, grow_ref) && (j > 0 || p.carry_in);
-        const float nmb = -m_new * sc;
+        float nmb = -m_new * sc;
+#if ATT_TURN_LATE
+        // the turn covers the exp pass only: the row max above (ALU pipe) runs under the other tile's
+        // exponentials, so the MUFU never waits for it.  nmb feeds every exponential: passing it
+        // through the barrier keeps the exp pass behind it and the max in front of it.
+        if (take_turns) bar_sync_named_dep(1 + t, 2 * ATT_BQ, nmb);
+#endif
         const uint64_t nmb2 = pack_f2(nmb, nmb);
         // ---- P = exp2(S*c - m*c) -> bf16 (registers), row sum ----
-        // ATT_POLY_OF_8 of every 8 groups of four exponentials are evaluated on the FMA/ALU pipes
+        // the pairs selected by ATT_POLY_MASK are evaluated on the FMA/ALU pipes
         // (round-to-nearest split x = n + f, |f| <= 0.5, degree-3 minimax 2^f, exponent add: relative
         // error 7.5e-5, far below the bf16 rounding of P) instead of the 16-lane MUFU, which is the
         // unit that bounds this loop.
@@ -337,24 +375,48 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           ea = __int_as_float(__float_as_int(pa) + (__float_as_int(ra) << 23));
           eb = __int_as_float(__float_as_int(pb) + (__float_as_int(rb) << 23));
         };
+        if constexpr (full) {
 #pragma unroll
-        for (int i = 0; i < 128; i += 4) {
-          float x0, x1, x2, x3;
-          unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])), sc2, nmb2), x0, x1);
-          unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i + 2]), __uint_as_float(v[i + 3])), sc2, nmb2), x2, x3);
-          float e0, e1, e2, e3;
-          if (((i >> 2) & 7) < ATT_POLY_OF_8) {
-            exp2_poly2(x0, x1, e0, e1);
-            exp2_poly2(x2, x3, e2, e3);
-          } else {
-            e0 = fast_exp2(x0); e1 = fast_exp2(x1); e2 = fast_exp2(x2); e3 = fast_exp2(x3);
+          for (int i = 0; i < 128; i += 2) {
+            float x0, x1, e0, e1;
+            unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])), sc2, nmb2), x0, x1);
+            if ((POLY_MASK >> ((i >> 1) & 15)) & 1) {
+              exp2_poly2(x0, x1, e0, e1);
+            } else {
+              e0 = fast_exp2(x0); e1 = fast_exp2(x1);
+            }
+            if (i & 2) sum_b = add_f2(sum_b, pack_f2(e0, e1));
+            else sum_a = add_f2(sum_a, pack_f2(e0, e1));
+            pk[i >> 1] = cvt_bf16x2(e0, e1);
           }
-          sum_a = add_f2(sum_a, pack_f2(e0, e1));
-          sum_b = add_f2(sum_b, pack_f2(e2, e3));
-          pk[i >> 1] = cvt_bf16x2(e0, e1);
-          pk[(i >> 1) + 1] = cvt_bf16x2(e2, e3);
+        } else {
+          // partial last K/V tile (1037 = 8 * 128 + 13): only the 32-column chunks that hold a valid
+          // column are evaluated (masked columns are -inf -> 0), the others are P = 0 outright
+#pragma unroll
+          for (int c = 0; c < 128; c += 32) {
+            if (c < valid) {
+#pragma unroll
+              for (int i = c; i < c + 32; i += 2) {
+                float x0, x1;
+                unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])), sc2, nmb2), x0, x1);
+                const float e0 = fast_exp2(x0), e1 = fast_exp2(x1);
+                sum_a = add_f2(sum_a, pack_f2(e0, e1));
+                pk[i >> 1] = cvt_bf16x2(e0, e1);
+              }
+            } else {
+#pragma unroll
+              for (int i = c; i < c + 32; i += 2) pk[i >> 1] = 0u;
+            }
+          }
         }
+        float s0, s1;
+        unpack_f2(add_f2(sum_a, sum_b), s0, s1);
+        const float row_sum = s0 + s1;  // depends on every exponential of the pass
+#if ATT_TURN_LATE
+        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named_dep(1 + (t ^ 1), 2 * ATT_BQ, row_sum);
+#else
         if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named(1 + (t ^ 1), 2 * ATT_BQ);
+#endif
         // ---- P_t and O_t are free once P_t(j-1) V has completed ----
         if (j > 0) {
           mbar_wait(&pv_done[t], (j - 1) & 1);
@@ -386,10 +448,19 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[t]);
-        float s0, s1;
-        unpack_f2(add_f2(sum_a, sum_b), s0, s1);
-        l_run = fmaf(l_run, alpha, s0 + s1);
+        l_run = fmaf(l_run, alpha, row_sum);
         m_ref = m_new;
+      };
+      if constexpr (QT == 2) {
+        // long sequences: one instantiation, the (single) partial tile is masked at run time and goes
+        // through the common pass -- a second copy of the body costs the hot loop its schedule
+        // (measured 836 -> 740 TFLOP/s at 66 305 tokens)
+        for (int j = 0; j < nkv; ++j) kv_tile(j, std::true_type{});
+      } else {
+        // short sequences (1037 tokens = 9 tiles): the partial tile is 1/9 of the work
+        const int nfull = p.kv_len / ATT_BKV;
+        for (int j = 0; j < nfull; ++j) kv_tile(j, std::true_type{});
+        if (nfull < nkv) kv_tile(nfull, std::false_type{});
       }
 
       // ---- epilogue: O_t out of TMEM once the last P V has completed ----

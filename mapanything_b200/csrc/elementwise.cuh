@@ -496,4 +496,58 @@ __global__ void scale_finalize_kernel(const float* __restrict__ raw, float* __re
   if (threadIdx.x == 0 && blockIdx.x == 0) scale[0] = fmaxf(expf(raw[0]), 1e-8f);
 }
 
+// ----------------------------------------------------------------------------------------------
+// RoPE2D, in place (the reference tree's one native kernel: uniception/models/libs/croco/curope/
+// kernels.cu:17-108, scalar loop curope.cpp:11-47; used by Attention.forward when a custom
+// positional encoding is configured, transformer_blocks.py:179-184).  A head vector of D elements
+// is [uY(Q) | vY(Q) | uX(Q) | vX(Q)], Q = D/4; for the y half (x half) the pair (u_d, v_d) is
+// rotated by the angle fwd * pos_y(x) / base^(d/Q).  Tokens are addressed as
+// base + token * pitch + head * D, so the q and k thirds of a packed [rows, 3*H*D] qkv buffer are
+// rotated where they lie (no head split / transposes).  Thread = 4 consecutive d of one half of
+// one (token, head): two 16-byte (fp32) or 8-byte (bf16) loads and stores, all lanes of a warp
+// touch one contiguous run of the row.  Bandwidth bound: D*sizeof(T) read + written per head.
+// ----------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void rope2d_kernel(T* __restrict__ tokens, long long n_tokens, int heads, int D, long long pitch,
+                              const long long* __restrict__ pos, float base, float fwd) {
+  const int Q = D >> 2, gq = Q >> 2;           // gq groups of 4 per quarter
+  const int per_head = 2 * gq;                 // threads per (token, head)
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long th = idx / per_head;         // token * heads + head
+  if (th >= n_tokens * heads) return;
+  const int sub = (int)(idx - th * per_head);
+  const int half = sub / gq, g = sub - half * gq;
+  const long long tok = th / heads;
+  const int head = (int)(th - tok * heads);
+  const float p = (float)pos[tok * 2 + half];
+  T* u_ptr = tokens + tok * pitch + (long long)head * D + half * 2 * Q + 4 * g;
+  T* v_ptr = u_ptr + Q;
+  float u[4], v[4];
+  if (sizeof(T) == 4) {
+    const float4 a = *reinterpret_cast<const float4*>(u_ptr), b = *reinterpret_cast<const float4*>(v_ptr);
+    u[0] = a.x; u[1] = a.y; u[2] = a.z; u[3] = a.w; v[0] = b.x; v[1] = b.y; v[2] = b.z; v[3] = b.w;
+  } else {
+    const uint2 a = *reinterpret_cast<const uint2*>(u_ptr), b = *reinterpret_cast<const uint2*>(v_ptr);
+    u[0] = bf16_lo(a.x); u[1] = bf16_hi(a.x); u[2] = bf16_lo(a.y); u[3] = bf16_hi(a.y);
+    v[0] = bf16_lo(b.x); v[1] = bf16_hi(b.x); v[2] = bf16_lo(b.y); v[3] = bf16_hi(b.y);
+  }
+  float ru[4], rv[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int d = 4 * g + i;
+    const float ang = fwd * p / powf(base, (float)d / (float)Q);  // curope.cpp:36
+    float s, c;
+    sincosf(ang, &s, &c);
+    ru[i] = u[i] * c - v[i] * s;
+    rv[i] = v[i] * c + u[i] * s;
+  }
+  if (sizeof(T) == 4) {
+    *reinterpret_cast<float4*>(u_ptr) = make_float4(ru[0], ru[1], ru[2], ru[3]);
+    *reinterpret_cast<float4*>(v_ptr) = make_float4(rv[0], rv[1], rv[2], rv[3]);
+  } else {
+    *reinterpret_cast<uint2*>(u_ptr) = make_uint2(pack_bf16(ru[0], ru[1]), pack_bf16(ru[2], ru[3]));
+    *reinterpret_cast<uint2*>(v_ptr) = make_uint2(pack_bf16(rv[0], rv[1]), pack_bf16(rv[2], rv[3]));
+  }
+}
+
 }  // namespace mab

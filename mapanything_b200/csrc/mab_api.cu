@@ -245,6 +245,34 @@ extern "C" int mab_posembed_resize(const float* pos, int grid, int C, int h, int
   return 0;
 }
 
+// RoPE2D in place (curope.cpp:49-69 `rope_2d(tokens, positions, base, fwd)`): tokens addressed as
+// tokens + token * token_pitch + head * head_dim (elements), positions [n_tokens, 2] int64 (y, x).
+extern "C" int mab_rope2d(void* tokens, int dtype, long long n_tokens, int heads, int head_dim,
+                          long long token_pitch, const long long* positions, float base, float fwd,
+                          void* stream) {
+  MAB_ARG(tokens && positions, "null argument");
+  MAB_ARG(dtype == 0 || dtype == 1, "dtype must be MAB_F32 or MAB_BF16");
+  MAB_ARG(n_tokens >= 0 && heads > 0, "bad sizes");
+  // curope requires D % 4 == 0 (kernels.cu:92); the vectorised kernel rotates 4 frequencies per thread
+  MAB_ARG(head_dim > 0 && head_dim % 16 == 0, "head_dim must be a multiple of 16");
+  MAB_ARG(token_pitch >= (long long)heads * head_dim && token_pitch % 4 == 0, "bad token pitch");
+  MAB_ARG(reinterpret_cast<uintptr_t>(tokens) % 16 == 0, "tokens must be 16-byte aligned");
+  if (n_tokens == 0) return 0;
+  const long long threads = n_tokens * heads * (head_dim / 8);
+  const double bytes = 2.0 * (double)n_tokens * heads * head_dim * (dtype == 0 ? 4 : 2) + 16.0 * n_tokens;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == 0)
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, bytes, st,
+               rope2d_kernel<float><<<ew_grid(threads), 256, 0, st>>>(
+                   reinterpret_cast<float*>(tokens), n_tokens, heads, head_dim, token_pitch, positions, base, fwd));
+  else
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, bytes, st,
+               rope2d_kernel<bf16><<<ew_grid(threads), 256, 0, st>>>(
+                   reinterpret_cast<bf16*>(tokens), n_tokens, heads, head_dim, token_pitch, positions, base, fwd));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // workspace: views*H*W*(3*4 + 1 + 4) bytes  (normals fp32x3, normal mask u8, angle fp32)
 extern "C" int mab_edge_mask(const float* pts3d, float* pts3d_cam, const unsigned char* fmask,
                              int views, int H, int W, float normal_tol_deg, float depth_rtol,
