@@ -214,6 +214,18 @@ int mab_posembed_resize(const float* pos, int grid, int C, int h, int w, float* 
  * head_dim % 16 == 0 (curope: % 4), token_pitch % 4 == 0, tokens 16-byte aligned. */
 int mab_rope2d(void* tokens, int dtype, long long n_tokens, int heads, int head_dim,
                long long token_pitch, const long long* positions, float base, float fwd, void* stream);
+/* Dense export.  depth_z [views,H,W], intrinsics [views,3,3], camera_poses
+ * [views,4,4] or NULL (camera frame) -> world_points [views,H,W,3] (optional; geometry.py:24-114
+ * depthmap_to_world_frame) and the mask-filtered cloud the demos build on the CPU
+ * (scripts/demo_local_weight.py:122-140, viz.py:233-239,275-279): pixels with mask != 0 (NULL = all)
+ * and depth > 0, in view-major / row-major order (numpy boolean-mask order), out_xyz [capacity,3]
+ * fp32 and out_rgb [capacity,3] u8 = (img_no_norm * 255).astype(uint8).  counts [views+1] int64 on
+ * the device: kept pixels per view, then the total (points beyond `capacity` are counted, not stored). */
+size_t mab_export_workspace_bytes(int views, int H, int W);
+int mab_export_points(const float* depth_z, const float* intrinsics, const float* camera_poses,
+                      const unsigned char* mask, const float* img_no_norm, int views, int H, int W,
+                      float* world_points, float* out_xyz, unsigned char* out_rgb, long long capacity,
+                      long long* counts, void* workspace, size_t workspace_bytes, void* stream);
 int mab_edge_mask(const float* pts3d, float* pts3d_cam, const unsigned char* fmask, int views, int H,
                   int W, float normal_tol_deg, float depth_rtol, void* workspace,
                   unsigned char* mask_out, void* stream);

@@ -81,6 +81,9 @@ SYMBOLS = {
     "mab_resize_bilinear": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "mab_posembed_resize": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "mab_rope2d": (_i, [_vp, _i, C.c_longlong, _i, _i, C.c_longlong, _vp, _f, _f, _vp]),
+    "mab_export_workspace_bytes": (C.c_size_t, [_i, _i, _i]),
+    "mab_export_points": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, C.c_longlong, _vp, _vp,
+                               C.c_size_t, _vp]),
     "mab_edge_mask": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp, _vp]),
 }
 

@@ -13,6 +13,7 @@
 #include "elementwise.cuh"
 #include "gemm.cuh"
 #include "postprocess.cuh"
+#include "export.cuh"
 
 namespace mab {
 

@@ -273,6 +273,42 @@ extern "C" int mab_rope2d(void* tokens, int dtype, long long n_tokens, int heads
   return 0;
 }
 
+// geometry.py:24-114 + the demos' mask-filtered cloud (see csrc/export.cuh).
+extern "C" size_t mab_export_workspace_bytes(int views, int H, int W) {
+  if (views <= 0 || H <= 0 || W <= 0) return 0;
+  const long long tiles = (long long)views * (((long long)H * W + EXP_TILE - 1) / EXP_TILE);
+  return (size_t)tiles * (sizeof(int) + sizeof(long long)) + 512;
+}
+
+extern "C" int mab_export_points(const float* depth_z, const float* intrinsics, const float* camera_poses,
+                                 const unsigned char* mask, const float* img_no_norm, int views, int H,
+                                 int W, float* world_points, float* out_xyz, unsigned char* out_rgb,
+                                 long long capacity, long long* counts, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+  MAB_ARG(depth_z && intrinsics && counts && workspace, "null argument");
+  MAB_ARG(views > 0 && H > 0 && W > 0 && capacity >= 0, "bad sizes");
+  MAB_ARG(!out_rgb || img_no_norm, "out_rgb needs img_no_norm");
+  MAB_ARG((long long)H * W < (1LL << 31), "view too large");
+  MAB_ARG(workspace_bytes >= mab_export_workspace_bytes(views, H, W), "workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int npix = H * W, tpv = (npix + EXP_TILE - 1) / EXP_TILE;
+  const long long tiles = (long long)views * tpv;
+  MAB_ARG(tiles < (1LL << 31), "too many tiles");
+  long long* tile_offsets = reinterpret_cast<long long*>(workspace);  // 8-byte aligned first
+  int* tile_counts = reinterpret_cast<int*>(tile_offsets + tiles);
+  const double px = (double)views * npix;
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, px * 5.0, st,
+             export_count_kernel<<<(int)tiles, EXP_THREADS, 0, st>>>(depth_z, mask, npix, tpv, tile_counts));
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, (double)tiles * 12.0, st,
+             export_scan_kernel<<<1, 1024, 0, st>>>(tile_counts, (int)tiles, tpv, views, tile_offsets, counts));
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, px * (5.0 + (world_points ? 12.0 : 0.0) + 27.0), st,
+             export_scatter_kernel<<<(int)tiles, EXP_THREADS, 0, st>>>(
+                 depth_z, intrinsics, camera_poses, mask, img_no_norm, W, npix, tpv, tile_offsets, capacity,
+                 world_points, out_xyz, out_rgb));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // workspace: views*H*W*(3*4 + 1 + 4) bytes  (normals fp32x3, normal mask u8, angle fp32)
 extern "C" int mab_edge_mask(const float* pts3d, float* pts3d_cam, const unsigned char* fmask,
                              int views, int H, int W, float normal_tol_deg, float depth_rtol,
