@@ -214,6 +214,25 @@ int mab_posembed_resize(const float* pos, int grid, int C, int h, int w, float* 
  * head_dim % 16 == 0 (curope: % 4), token_pitch % 4 == 0, tokens 16-byte aligned. */
 int mab_rope2d(void* tokens, int dtype, long long n_tokens, int heads, int head_dim,
                long long token_pitch, const long long* positions, float base, float fwd, void* stream);
+/* Image input path: what `load_images` (mapanything/utils/image.py:134-332)
+ * does per decoded image -- PIL LANCZOS/BICUBIC resize so that the image contains the target
+ * (mapanything/utils/cropping.py:230-244), centred crop (:441-447), ToTensor + Normalize
+ * (image.py:297-300) -- bit-exact with Pillow's 8-bit fixed-point resampling.  rgb: DEVICE u8
+ * [in_h,in_w,3]; mean/std: HOST float[3]; out: [3,out_h,out_w] fp32; out_u8 optional [out_h,out_w,3]
+ * (the resized + cropped 8-bit image).  File decoding stays on the host. */
+typedef struct {
+  int in_w, in_h;          /* decoded image */
+  int resize_w, resize_h;  /* floor(in * (max(target / in) + 1e-8)) */
+  int filter;              /* 0 LANCZOS (shrinking), 1 BICUBIC */
+  int crop_left, crop_top; /* (resize - target) // 2 */
+  int out_w, out_h;        /* target */
+} mab_image_plan;
+int mab_image_plan_make(int in_w, int in_h, int target_w, int target_h, mab_image_plan* plan);
+size_t mab_preprocess_workspace_bytes(const mab_image_plan* plan);
+int mab_preprocess_image(const unsigned char* rgb, const mab_image_plan* plan, const float* mean_host,
+                         const float* std_host, float* out, unsigned char* out_u8, void* workspace,
+                         size_t workspace_bytes, void* stream);
+
 /* Dense export.  depth_z [views,H,W], intrinsics [views,3,3], camera_poses
  * [views,4,4] or NULL (camera frame) -> world_points [views,H,W,3] (optional; geometry.py:24-114
  * depthmap_to_world_frame) and the mask-filtered cloud the demos build on the CPU

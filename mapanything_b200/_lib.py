@@ -39,6 +39,11 @@ class MabPostOptions(C.Structure):
                 ("apply_confidence_mask", C.c_int), ("confidence_percentile", C.c_float)]
 
 
+class MabImagePlan(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("in_w", "in_h", "resize_w", "resize_h", "filter", "crop_left", "crop_top",
+                                       "out_w", "out_h")]
+
+
 # every symbol include/mab200.h declares: (name, restype, argtypes)
 _vp, _i, _f = C.c_void_p, C.c_int, C.c_float
 SYMBOLS = {
@@ -81,6 +86,9 @@ SYMBOLS = {
     "mab_resize_bilinear": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "mab_posembed_resize": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "mab_rope2d": (_i, [_vp, _i, C.c_longlong, _i, _i, C.c_longlong, _vp, _f, _f, _vp]),
+    "mab_image_plan_make": (_i, [_i, _i, _i, _i, C.POINTER(MabImagePlan)]),
+    "mab_preprocess_workspace_bytes": (C.c_size_t, [C.POINTER(MabImagePlan)]),
+    "mab_preprocess_image": (_i, [_vp, C.POINTER(MabImagePlan), c_float_p, c_float_p, _vp, _vp, _vp, C.c_size_t, _vp]),
     "mab_export_workspace_bytes": (C.c_size_t, [_i, _i, _i]),
     "mab_export_points": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, C.c_longlong, _vp, _vp,
                                C.c_size_t, _vp]),

@@ -14,6 +14,7 @@
 #include "gemm.cuh"
 #include "postprocess.cuh"
 #include "export.cuh"
+#include "image.cuh"
 
 namespace mab {
 

@@ -273,6 +273,139 @@ extern "C" int mab_rope2d(void* tokens, int dtype, long long n_tokens, int heads
   return 0;
 }
 
+// ---- image input path (csrc/image.cuh) -------------------------------------------------------
+namespace {
+
+double img_sinc(double x) {
+  if (x == 0.0) return 1.0;
+  x *= M_PI;
+  return sin(x) / x;
+}
+double img_filter(int filter, double x) {  // Pillow Resample.c lanczos_filter / bicubic_filter (a = -0.5)
+  if (filter == 0) return (-3.0 <= x && x < 3.0) ? img_sinc(x) * img_sinc(x / 3) : 0.0;
+  const double a = -0.5;
+  if (x < 0.0) x = -x;
+  if (x < 1.0) return ((a + 2.0) * x - (a + 3.0)) * x * x + 1;
+  if (x < 2.0) return (((x - 5) * x + 8) * x - 4) * a;
+  return 0.0;
+}
+// Pillow precompute_coeffs + normalize_coeffs_8bpc for output samples [first, first + count) of a
+// resize in_size -> out_size; bounds (xmin, n) pairs and ksize coefficients per sample
+int img_coeffs(int in_size, int out_size, int filter, int first, int count, std::vector<int>* bounds,
+               std::vector<int>* kk) {
+  double scale = (double)((float)in_size - 0.0f) / out_size, filterscale = scale;
+  if (filterscale < 1.0) filterscale = 1.0;
+  const double support = (filter == 0 ? 3.0 : 2.0) * filterscale;
+  const int ksize = (int)ceil(support) * 2 + 1;
+  bounds->assign((size_t)count * 2, 0);
+  kk->assign((size_t)count * ksize, 0);
+  const double ss = 1.0 / filterscale;
+  std::vector<double> w(ksize);
+  for (int j = 0; j < count; ++j) {
+    const int xx = first + j;
+    const double center = 0.0 + (xx + 0.5) * scale;
+    int xmin = (int)(center - support + 0.5);
+    if (xmin < 0) xmin = 0;
+    int xmax = (int)(center + support + 0.5);
+    if (xmax > in_size) xmax = in_size;
+    xmax -= xmin;
+    double ww = 0.0;
+    for (int x = 0; x < xmax; ++x) {
+      w[x] = img_filter(filter, (x + xmin - center + 0.5) * ss);
+      ww += w[x];
+    }
+    for (int x = 0; x < xmax; ++x) {
+      const double v = ww != 0.0 ? w[x] / ww : w[x];
+      (*kk)[(size_t)j * ksize + x] = v < 0 ? (int)(-0.5 + v * (1 << IMG_PRECISION_BITS))
+                                           : (int)(0.5 + v * (1 << IMG_PRECISION_BITS));
+    }
+    (*bounds)[2 * j] = xmin;
+    (*bounds)[2 * j + 1] = xmax;
+  }
+  return ksize;
+}
+
+}  // namespace
+
+// cropping.py:230-244 (rescale so that the image contains the crop; LANCZOS when shrinking, BICUBIC
+// otherwise) and :441-447 (centred crop), evaluated in double like numpy does
+extern "C" int mab_image_plan_make(int in_w, int in_h, int target_w, int target_h, mab_image_plan* plan) {
+  MAB_ARG(plan && in_w > 0 && in_h > 0 && target_w > 0 && target_h > 0, "bad sizes");
+  const double sw = (double)target_w / in_w, sh = (double)target_h / in_h;
+  const double scale_final = (sw > sh ? sw : sh) + 1e-8;
+  plan->in_w = in_w; plan->in_h = in_h;
+  plan->resize_w = (int)floor(in_w * scale_final);
+  plan->resize_h = (int)floor(in_h * scale_final);
+  plan->filter = scale_final < 1 ? 0 : 1;
+  plan->out_w = target_w; plan->out_h = target_h;
+  // Python floor division (the crop offsets are >= 0 by construction of scale_final)
+  plan->crop_left = (int)floor((plan->resize_w - target_w) / 2.0);
+  plan->crop_top = (int)floor((plan->resize_h - target_h) / 2.0);
+  MAB_ARG(plan->crop_left >= 0 && plan->crop_top >= 0, "target larger than the rescaled image");
+  return 0;
+}
+
+extern "C" size_t mab_preprocess_workspace_bytes(const mab_image_plan* p) {
+  if (!p || p->out_w <= 0 || p->out_h <= 0) return 0;
+  auto ks = [](int in, int out, int filter) {
+    double fs = (double)in / out; if (fs < 1.0) fs = 1.0;
+    return (size_t)((int)ceil((filter == 0 ? 3.0 : 2.0) * fs) * 2 + 1);
+  };
+  const size_t tabs = (size_t)p->out_w * (2 + ks(p->in_w, p->resize_w, p->filter)) +
+                      (size_t)p->out_h * (2 + ks(p->in_h, p->resize_h, p->filter));
+  return tabs * sizeof(int) + (size_t)p->in_h * p->out_w * 3 + 1024;
+}
+
+extern "C" int mab_preprocess_image(const unsigned char* rgb, const mab_image_plan* p, const float* mean,
+                                    const float* std_, float* out, unsigned char* out_u8, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  MAB_ARG(rgb && p && mean && std_ && out && workspace, "null argument");
+  MAB_ARG(p->crop_left >= 0 && p->crop_top >= 0 && p->crop_left + p->out_w <= p->resize_w &&
+          p->crop_top + p->out_h <= p->resize_h, "crop outside the resized image");
+  MAB_ARG(workspace_bytes >= mab_preprocess_workspace_bytes(p), "workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  std::vector<int> hb, hk, vb, vk;
+  // a pass is skipped when that dimension is unchanged (ImagingResample need_horizontal / need_vertical)
+  const bool need_h = p->resize_w != p->in_w, need_v = p->resize_h != p->in_h;
+  int hks = 0, vks = 0;
+  if (need_h) hks = img_coeffs(p->in_w, p->resize_w, p->filter, p->crop_left, p->out_w, &hb, &hk);
+  else {  // identity taps: one coefficient of 1.0 per column
+    hks = 1; hb.resize((size_t)p->out_w * 2); hk.assign(p->out_w, 1 << IMG_PRECISION_BITS);
+    for (int x = 0; x < p->out_w; ++x) { hb[2 * x] = p->crop_left + x; hb[2 * x + 1] = 1; }
+  }
+  int y0 = p->crop_top, y1 = p->crop_top + p->out_h;  // source rows the vertical pass reads
+  if (need_v) {
+    vks = img_coeffs(p->in_h, p->resize_h, p->filter, p->crop_top, p->out_h, &vb, &vk);
+    y0 = vb[0]; y1 = vb[2 * (p->out_h - 1)] + vb[2 * (p->out_h - 1) + 1];
+    for (int y = 0; y < p->out_h; ++y) {  // bounds are monotone, but do not rely on it
+      if (vb[2 * y] < y0) y0 = vb[2 * y];
+      if (vb[2 * y] + vb[2 * y + 1] > y1) y1 = vb[2 * y] + vb[2 * y + 1];
+    }
+  }
+  const int rows = y1 - y0;
+  uint8_t* w8 = reinterpret_cast<uint8_t*>(workspace);
+  int* d_hb = reinterpret_cast<int*>(w8);
+  int* d_hk = d_hb + hb.size();
+  int* d_vb = d_hk + hk.size();
+  int* d_vk = d_vb + vb.size();
+  unsigned char* tmp = reinterpret_cast<unsigned char*>(d_vk + vk.size());
+  MAB_CUDA(cudaMemcpyAsync(d_hb, hb.data(), hb.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  MAB_CUDA(cudaMemcpyAsync(d_hk, hk.data(), hk.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  if (need_v) {
+    MAB_CUDA(cudaMemcpyAsync(d_vb, vb.data(), vb.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    MAB_CUDA(cudaMemcpyAsync(d_vk, vk.data(), vk.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  }
+  const double in_bytes = (double)rows * p->in_w * 3, tmp_bytes = (double)rows * p->out_w * 3;
+  dim3 gh((p->out_w + 127) / 128, rows), gv((p->out_w + 127) / 128, p->out_h);
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, in_bytes + tmp_bytes, st,
+             image_resample_h_kernel<<<gh, 128, 0, st>>>(rgb, p->in_w, y0, rows, p->out_w, d_hb, d_hk, hks, tmp));
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, tmp_bytes + (double)p->out_w * p->out_h * 12.0, st,
+             image_resample_v_norm_kernel<<<gv, 128, 0, st>>>(tmp, y0, p->out_w, p->out_h, d_vb, d_vk, vks, mean[0],
+                                                             mean[1], mean[2], std_[0], std_[1], std_[2], out, out_u8));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // geometry.py:24-114 + the demos' mask-filtered cloud (see csrc/export.cuh).
 extern "C" size_t mab_export_workspace_bytes(int views, int H, int W) {
   if (views <= 0 || H <= 0 || W <= 0) return 0;
