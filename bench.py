@@ -285,8 +285,19 @@ def main():
         kernel_name = {"gemm": "gemm_kernel<MODE_GEMM> (tcgen05 linear layers)",
                        "attention": "attention_kernel (tcgen05 flash attention)",
                        "conv3": "gemm_kernel<MODE_CONV3> (tcgen05 implicit-GEMM 3x3 conv)"}[dom]
+        # DRAM traffic per launch of that kernel class from the committed `ncu --set full` capture of the
+        # 8-view step (profiles/r1_traffic.json); only quoted for the workload it was captured on
+        traffic, traffic_src = None, None
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+                tj = json.load(f)
+            if n_views == VIEWS_PER_GPU and world == 1 and dom in tj:
+                traffic, traffic_src = tj[dom], tj["source"]
+        except Exception:
+            pass
         roof = {"bound": "tensor", "kernel": kernel_name, "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
-                "frac": ach / peak_tf, "traffic": None, "peak_source": peak_src,
+                "frac": ach / peak_tf, "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram read + write)",
+                "traffic_source": traffic_src, "peak_source": peak_src,
                 "launches_per_step": d["launches"], "avg_launch_ms": d["ms"] / max(d["launches"], 1),
                 "share_of_step": d["ms"] / total_ms if total_ms else None,
                 "how": "library-recorded CUDA events around every launch on the launch stream, K extra steps after the timed region",
