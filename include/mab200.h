@@ -233,6 +233,11 @@ int mab_preprocess_image(const unsigned char* rgb, const mab_image_plan* plan, c
                          const float* std_host, float* out, unsigned char* out_u8, void* workspace,
                          size_t workspace_bytes, void* stream);
 
+/* Depth maps of `preprocess_inputs` (image.py:335-675): cv2.INTER_NEAREST resize to
+ * (resize_w, resize_h) (cropping.py:246-253) + crop (cropping.py:345-349), one fp32 channel. */
+int mab_resize_nearest_crop(const float* src, int in_h, int in_w, int resize_w, int resize_h,
+                            int crop_left, int crop_top, int out_w, int out_h, float* out, void* stream);
+
 /* Dense export.  depth_z [views,H,W], intrinsics [views,3,3], camera_poses
  * [views,4,4] or NULL (camera frame) -> world_points [views,H,W,3] (optional; geometry.py:24-114
  * depthmap_to_world_frame) and the mask-filtered cloud the demos build on the CPU

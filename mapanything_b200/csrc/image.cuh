@@ -68,4 +68,18 @@ __global__ void image_resample_v_norm_kernel(const unsigned char* __restrict__ t
   if (out_u8) { out_u8[o * 3] = p0; out_u8[o * 3 + 1] = p1; out_u8[o * 3 + 2] = p2; }
 }
 
+// cv2.resize(..., INTER_NEAREST) of a one-channel fp32 map followed by the crop (cropping.py:246-253,
+// 345-349): out[y, x] = src[min(floor((y + top) * ify), in_h - 1), min(floor((x + left) * ifx), in_w - 1)]
+// with ifx = 1 / (resize_w / in_w) in double, as OpenCV's resizeNN computes its offset table.
+__global__ void resize_nearest_crop_kernel(const float* __restrict__ src, int in_h, int in_w, double ifx,
+                                           double ify, int left, int top, int out_w, int out_h,
+                                           float* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= out_w || y >= out_h) return;
+  int sx = (int)floor((double)(x + left) * ifx), sy = (int)floor((double)(y + top) * ify);
+  sx = sx < in_w - 1 ? sx : in_w - 1;
+  sy = sy < in_h - 1 ? sy : in_h - 1;
+  out[(long long)y * out_w + x] = src[(long long)sy * in_w + sx];
+}
+
 }  // namespace mab

@@ -406,6 +406,23 @@ extern "C" int mab_preprocess_image(const unsigned char* rgb, const mab_image_pl
   return 0;
 }
 
+// depth maps of preprocess_inputs (image.py:560-567 -> cropping.py:246-253,345-349)
+extern "C" int mab_resize_nearest_crop(const float* src, int in_h, int in_w, int resize_w, int resize_h,
+                                       int crop_left, int crop_top, int out_w, int out_h, float* out,
+                                       void* stream) {
+  MAB_ARG(src && out && in_h > 0 && in_w > 0 && resize_w > 0 && resize_h > 0 && out_w > 0 && out_h > 0, "bad sizes");
+  MAB_ARG(crop_left >= 0 && crop_top >= 0 && crop_left + out_w <= resize_w && crop_top + out_h <= resize_h,
+          "crop outside the resized map");
+  cudaStream_t st = (cudaStream_t)stream;
+  const double ifx = 1.0 / ((double)resize_w / in_w), ify = 1.0 / ((double)resize_h / in_h);
+  dim3 grid((out_w + 127) / 128, out_h);
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, (double)out_w * out_h * 8.0, st,
+             resize_nearest_crop_kernel<<<grid, 128, 0, st>>>(src, in_h, in_w, ifx, ify, crop_left, crop_top, out_w,
+                                                             out_h, out));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // geometry.py:24-114 + the demos' mask-filtered cloud (see csrc/export.cuh).
 extern "C" size_t mab_export_workspace_bytes(int views, int H, int W) {
   if (views <= 0 || H <= 0 || W <= 0) return 0;

@@ -151,3 +151,131 @@ def load_images(folder_or_list, resize_mode="fixed_mapping", size=None, norm_typ
     if not decoded:
         raise ValueError("No valid images found")
     return preprocess_decoded(decoded, resize_mode, size, norm_type, patch_size, resolution_set, device)
+
+
+# ---- preprocess_inputs (image.py:335-675): images + depth + intrinsics, cropped consistently ---------
+def _crop_plan(w1, h1, tw, th, intrinsics):
+    """cropping.py:230-283 (rescale) + :429-447 (crop that follows the principal point when intrinsics are
+    given, centred otherwise) + :360-363 (intrinsics of the crop).  3x3 host arithmetic in numpy, as the
+    reference does it.  -> (resize_w, resize_h, left, top, K_out or None)"""
+    inp = np.array([w1, h1])
+    scale_final = max(np.array([tw, th]) / inp) + 1e-8
+    out_res = np.floor(inp * scale_final).astype(int)
+    rw, rh = int(out_res[0]), int(out_res[1])
+    if intrinsics is None:
+        return rw, rh, (rw - tw) // 2, (rh - th) // 2, None
+
+    def matrix_of_crop(K, in_res, o_res, scaling=1, offset_factor=0.5):
+        margins = np.asarray(in_res) * scaling - o_res
+        assert np.all(margins >= 0.0)
+        Kc = K.copy()
+        Kc[0, 2] += 0.5; Kc[1, 2] += 0.5
+        Kc[:2, :] *= scaling
+        Kc[:2, 2] -= offset_factor * margins
+        Kc[0, 2] -= 0.5; Kc[1, 2] -= 0.5
+        return Kc
+
+    K = matrix_of_crop(np.asarray(intrinsics), inp, out_res, scaling=scale_final)
+    Knew = matrix_of_crop(K, (rw, rh), (tw, th))
+    left, top = (int(v) for v in np.int32(np.round(K[:2, 2] - Knew[:2, 2])))
+    Kout = K.copy()
+    Kout[0, 2] -= left; Kout[1, 2] -= top
+    return rw, rh, left, top, Kout
+
+
+def _to_u8(img, view_idx, dev):
+    """image.py:493-520 `to_pil_image`: tensor / array (H, W, 3) in [0, 1] or [0, 255], or a PIL image."""
+    import PIL.Image
+
+    if isinstance(img, PIL.Image.Image):
+        return torch.from_numpy(np.asarray(img.convert("RGB") if img.mode != "RGB" else img)).to(dev)
+    if isinstance(img, torch.Tensor):
+        if img.ndim != 3 or img.shape[2] != 3:
+            raise ValueError(f"Expected tensor shape (H, W, 3) for img in view {view_idx}, got {img.shape}")
+        img = img.to(dev)
+        return ((img * 255) if img.max() <= 1.0 else img).clamp(0, 255).byte()
+    if isinstance(img, np.ndarray):
+        if img.ndim != 3 or img.shape[2] != 3:
+            raise ValueError(f"Expected array shape (H, W, 3) for img in view {view_idx}, got {img.shape}")
+        if img.dtype != np.uint8:
+            img = (img * 255).clip(0, 255).astype(np.uint8)
+        return torch.from_numpy(img).to(dev)
+    raise ValueError(f"Unsupported image type in view {view_idx}: {type(img)}")
+
+
+def preprocess_inputs(input_views, resize_mode="fixed_mapping", size=None, norm_type="dinov2", patch_size=14,
+                      resolution_set=518, verbose=False, device="cuda") -> List[dict]:
+    """`mapanything.utils.image.preprocess_inputs` (image.py:335-675): same arguments, same view dicts;
+    images (Pillow-exact resize + crop + normalise) and depth maps (cv2.INTER_NEAREST + crop) on the device.
+    `ray_directions` inputs (intrinsics recovered by least squares, image.py:572-590) are not supported
+    here: pass `intrinsics`."""
+    _validate(resize_mode, size)
+    if not input_views:
+        raise ValueError("input_views cannot be empty")
+    if norm_type not in IMAGE_NORMALIZATION_DICT:
+        raise ValueError(f"Unknown image normalization type: {norm_type}. "
+                         f"Available options: {list(IMAGE_NORMALIZATION_DICT.keys())}")
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError("mapanything_b200.image runs on a CUDA device only (no CPU path)")
+    for i, v in enumerate(input_views):
+        if "img" not in v:
+            raise ValueError(f"View {i} missing required 'img' key")
+        if "intrinsics" in v and "ray_directions" in v:
+            raise ValueError(f"View {i} cannot have both 'intrinsics' and 'ray_directions'. Please provide only one "
+                             "as they are redundant (ray_directions can be used to recover intrinsics).")
+        if "ray_directions" in v:
+            raise NotImplementedError("preprocess_inputs: pass 'intrinsics' instead of 'ray_directions'")
+    lib = _lib.load()
+    u8s = [_to_u8(v["img"], i, dev).contiguous() for i, v in enumerate(input_views)]
+    tw, th = _target_size([(int(t.shape[1]), int(t.shape[0])) for t in u8s], resize_mode, size, patch_size,
+                          resolution_set)
+    mean, std = IMAGE_NORMALIZATION_DICT[norm_type]
+    c_mean, c_std = (C.c_float * 3)(*mean), (C.c_float * 3)(*std)
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    out = []
+    for i, (view, u8) in enumerate(zip(input_views, u8s)):
+        h1, w1 = int(u8.shape[0]), int(u8.shape[1])
+        K = view.get("intrinsics")
+        if K is not None:
+            K = K.cpu().numpy() if isinstance(K, torch.Tensor) else K
+            if not isinstance(K, np.ndarray) or K.shape != (3, 3):
+                raise ValueError(f"Expected shape (3, 3) for intrinsics in view {i}, got {getattr(K, 'shape', type(K))}")
+        rw, rh, left, top, Kout = _crop_plan(w1, h1, tw, th, K)
+        plan = _lib.MabImagePlan()
+        _lib.check(lib.mab_image_plan_make(w1, h1, tw, th, C.byref(plan)), "mab_image_plan_make")
+        assert (plan.resize_w, plan.resize_h) == (rw, rh)
+        plan.crop_left, plan.crop_top = left, top   # the crop follows the principal point (cropping.py:429-440)
+        ws = torch.empty(lib.mab_preprocess_workspace_bytes(C.byref(plan)), dtype=torch.uint8, device=dev)
+        img = torch.empty((1, 3, th, tw), dtype=torch.float32, device=dev)
+        _lib.check(lib.mab_preprocess_image(C.c_void_p(u8.data_ptr()), C.byref(plan), c_mean, c_std,
+                                            C.c_void_p(img.data_ptr()), None, C.c_void_p(ws.data_ptr()), ws.numel(), st),
+                   "mab_preprocess_image")
+        pv = {"img": img, "data_norm_type": [norm_type]}
+        if "depth_z" in view:
+            d = view["depth_z"]
+            d = torch.as_tensor(d)
+            if d.ndim != 2:
+                raise ValueError(f"Expected shape (H, W) for depth_z in view {i}, got {tuple(d.shape)}")
+            assert tuple(d.shape) == (h1, w1)  # cropping.py:221
+            d = d.to(dev, torch.float32).contiguous()
+            dz = torch.empty((1, th, tw), dtype=torch.float32, device=dev)
+            _lib.check(lib.mab_resize_nearest_crop(C.c_void_p(d.data_ptr()), h1, w1, rw, rh, left, top, tw, th,
+                                                   C.c_void_p(dz.data_ptr()), st), "mab_resize_nearest_crop")
+            pv["depth_z"] = dz
+        if Kout is not None:
+            pv["intrinsics"] = torch.from_numpy(Kout)[None].to(dev)
+        if "camera_poses" in view:  # image.py:621-652: batch dimension only
+            cp = view["camera_poses"]
+            if isinstance(cp, tuple):
+                pv["camera_poses"] = tuple(torch.as_tensor(c)[None] for c in cp)
+            elif isinstance(cp, (torch.Tensor, np.ndarray)):
+                pv["camera_poses"] = torch.as_tensor(cp)[None]
+            else:
+                raise ValueError(f"Unsupported camera_poses format: {type(cp)}. Expected tuple (quats, trans) or "
+                                 "matrix (tensor/array).")
+        for k, val in view.items():
+            if k not in ("img", "depth_z", "intrinsics", "ray_directions", "camera_poses"):
+                pv[k] = val
+        out.append(pv)
+    return out

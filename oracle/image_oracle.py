@@ -141,3 +141,55 @@ def preprocess_image(img, target_w, target_h, mean=DINOV2_MEAN, std=DINOV2_STD):
     m = np.asarray(mean, np.float32).reshape(3, 1, 1)
     s = np.asarray(std, np.float32).reshape(3, 1, 1)
     return crop, ((x - m) / s).astype(np.float32)                            # Normalize
+
+
+# ---- multi-modal inputs: preprocess_inputs (image.py:335-675) --------------------------------------
+def cv2_resize_nearest(src, out_w, out_h):
+    """cv2.resize(src, (out_w, out_h), interpolation=cv2.INTER_NEAREST) -- a THIRD-PARTY dependency
+    (opencv-python, unpinned by the reference): OpenCV imgproc resize.cpp `resizeNN`: source index
+    min(floor(dst * (1 / (dsize / ssize))), ssize - 1) per axis, in double.  Pinned against the live cv2."""
+    h, w = src.shape[:2]
+    ifx, ify = 1.0 / (out_w / w), 1.0 / (out_h / h)
+    xs = np.minimum(np.floor(np.arange(out_w) * ifx).astype(np.int64), w - 1)
+    ys = np.minimum(np.floor(np.arange(out_h) * ify).astype(np.int64), h - 1)
+    return src[ys][:, xs]
+
+
+def crop_plan(w1, h1, target_w, target_h, intrinsics=None):
+    """cropping.py:230-283 + :429-447 -> (resize_w, resize_h, filter, left, top, new_intrinsics or None)."""
+    inp = np.array([w1, h1])
+    scale_final = max(np.array([target_w, target_h]) / inp) + 1e-8
+    out_res = np.floor(inp * scale_final).astype(int)
+    rw, rh = int(out_res[0]), int(out_res[1])
+    filt = "lanczos" if scale_final < 1 else "bicubic"
+    if intrinsics is None:
+        return rw, rh, filt, (rw - target_w) // 2, (rh - target_h) // 2, None
+
+    def matrix_of_crop(K, in_res, o_res, scaling=1, offset_factor=0.5):  # cropping.py:283-318
+        margins = np.asarray(in_res) * scaling - o_res
+        assert np.all(margins >= 0.0)
+        offset = offset_factor * margins
+        Kc = K.copy(); Kc[0, 2] += 0.5; Kc[1, 2] += 0.5         # opencv_to_colmap_intrinsics
+        Kc[:2, :] *= scaling
+        Kc[:2, 2] -= offset
+        Kc[0, 2] -= 0.5; Kc[1, 2] -= 0.5                         # colmap_to_opencv_intrinsics
+        return Kc
+
+    K = matrix_of_crop(np.asarray(intrinsics), inp, out_res, scaling=scale_final)      # rescale, :268-272
+    Knew = matrix_of_crop(K, (rw, rh), (target_w, target_h), offset_factor=0.5)         # :430-435
+    left, top = (int(v) for v in np.int32(np.round(K[:2, 2] - Knew[:2, 2])))            # :375-378
+    Kout = K.copy(); Kout[0, 2] -= left; Kout[1, 2] -= top                              # :360-363
+    return rw, rh, filt, left, top, Kout
+
+
+def preprocess_view(img, target_w, target_h, depth=None, intrinsics=None, mean=DINOV2_MEAN, std=DINOV2_STD):
+    """one view of preprocess_inputs: -> (normalised img [3,th,tw], depth [th,tw] or None, K or None)"""
+    h1, w1 = img.shape[:2]
+    rw, rh, filt, left, top, K = crop_plan(w1, h1, target_w, target_h, intrinsics)
+    crop = pil_resize(img, rw, rh, filt)[top:top + target_h, left:left + target_w]
+    x = crop.astype(np.float32).transpose(2, 0, 1) / np.float32(255)
+    out = ((x - np.asarray(mean, np.float32).reshape(3, 1, 1)) / np.asarray(std, np.float32).reshape(3, 1, 1))
+    d = None
+    if depth is not None:
+        d = cv2_resize_nearest(np.asarray(depth), rw, rh)[top:top + target_h, left:left + target_w]
+    return out.astype(np.float32), d, K

@@ -92,3 +92,48 @@ def test_argument_errors_mirror_reference():
             image.preprocess_decoded([np.zeros((4, 4, 3), np.uint8)], **kw)
     with pytest.raises(ValueError):
         image.preprocess_decoded([np.zeros((4, 4, 3), np.uint8)], norm_type="unknown")
+
+
+# ---- preprocess_inputs: image + depth + intrinsics ------------------------------------------------
+from oracle.make_golden_inputs import CASES as IN_CASES, case_views  # noqa: E402
+
+
+@pytest.mark.parametrize("shape", [((480, 640), (518, 388)), ((100, 150), (518, 777)), ((37, 53), (20, 53)),
+                                   ((7, 9), (100, 50))])
+def test_oracle_nearest_equals_live_cv2(shape):
+    cv2 = pytest.importorskip("cv2")
+    (h, w), (ow, oh) = shape
+    src = np.random.default_rng(h).random((h, w)).astype(np.float32)
+    ref = cv2.resize(src, (ow, oh), fx=ow / w, fy=oh / h, interpolation=cv2.INTER_NEAREST)
+    assert np.array_equal(io.cv2_resize_nearest(src, ow, oh), ref)
+
+
+@pytest.mark.parametrize("name", list(IN_CASES))
+def test_oracle_inputs_match_reference_golden(name):
+    g = _golden(name)
+    specs, kw = IN_CASES[name]
+    tw, th = io.target_size([(s[1], s[0]) for s in specs], kw["resize_mode"], kw["size"])
+    for i in range(len(specs)):
+        K = g[f"K{i}"] if f"K{i}" in g else None
+        img, d, Ko = io.preprocess_view(g[f"img{i}"], tw, th, g[f"depth{i}"], K)
+        assert np.array_equal(img, g[f"out_img{i}"]) and np.array_equal(d, g[f"out_depth{i}"])
+        if K is not None:
+            assert np.array_equal(Ko, g[f"out_K{i}"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(IN_CASES))
+def test_cuda_inputs_match_golden(name):
+    from mapanything_b200 import image
+
+    g = _golden(name)
+    specs, kw = IN_CASES[name]
+    views = case_views(name)
+    assert all(np.array_equal(v["img"].numpy(), g[f"img{i}"]) for i, v in enumerate(views))
+    out = image.preprocess_inputs(views, **kw)
+    for i, o in enumerate(out):
+        assert np.array_equal(o["img"][0].cpu().numpy(), g[f"out_img{i}"]), (name, i)
+        assert np.array_equal(o["depth_z"][0].cpu().numpy(), g[f"out_depth{i}"]), (name, i)
+        if f"K{i}" in g:
+            assert np.array_equal(o["intrinsics"][0].cpu().numpy(), g[f"out_K{i}"])
+        assert o["data_norm_type"] == ["dinov2"]
