@@ -40,6 +40,9 @@ typedef struct {
   int aat_tap0;       /* 11 */
   int aat_tap1;       /* 17 */
   int head_chunk;     /* views per dense-head pass (workspace knob; outputs do not depend on it) */
+  /* info_sharing module_args variants (configs/model/info_sharing/aat_ifr_24_layers_*.yaml) */
+  int aat_ref_view_pe;      /* 1: distinguish_ref_and_non_ref_views (production); 0: *_no_ref_view.yaml */
+  int aat_entropy_scaling;  /* 1: use_entropy_scaling (*_escaling.yaml): q *= sqrt(1.4 log N / log 444) */
 } mab_config;
 
 /* One scene, `views` views of H x W pixels held by this rank. */

@@ -829,11 +829,13 @@ extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
   }
   // required fp32 tensors that are used as-is
   for (const char* k : {"encoder.model.cls_token", "encoder.model.pos_embed", "encoder.model.norm.weight",
-                        "fusion_norm_layer.weight", "scale_token", "info_sharing.view_pos_table",
-                        "info_sharing.norm.weight", "dpt_regressor_head.conv2.2.weight",
+                        "fusion_norm_layer.weight", "scale_token", "info_sharing.norm.weight", "dpt_regressor_head.conv2.2.weight",
                         "pose_head.more_mlps.0.weight", "pose_head.fc_t.weight", "pose_head.fc_rot.weight",
                         "scale_head.proj.weight", "scale_head.output_proj.weight"})
     if (!h->F(k)) return fail(-4, "missing weight %s", k);
+  // the buffer only exists in checkpoints with the reference-view PE (aat.py:160-172)
+  if (h->cfg.aat_ref_view_pe && !h->F("info_sharing.view_pos_table"))
+    return fail(-4, "missing weight %s", "info_sharing.view_pos_table");
   // fc_t | fc_rot fused into one [7,784] matrix + [7] bias for the pose tail
   {
     float* w7; float* b7;
@@ -1161,7 +1163,7 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
   // proj_embed (aat.py:121-124,600) + reference-view PE on view 0's tokens (aat.py:618-626)
   MAB_TRY(c.linear(p.fused, (int)p.L, D, D, "info_sharing.proj_embed.weight", cf.aat_dim,
                    h->F("info_sharing.proj_embed.bias"), ACT_NONE, nullptr, nullptr, p.ys, nullptr));
-  if (p.has_ref) {
+  if (p.has_ref && cf.aat_ref_view_pe) {  // distinguish_ref_and_non_ref_views (aat.py:618-626)
     MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
                add_row_vector_kernel<<<ew_grid((long long)T * cf.aat_dim), 256, 0, c.st>>>(
         p.ys, h->F("info_sharing.view_pos_table"), T, cf.aat_dim));
@@ -1183,6 +1185,16 @@ extern "C" int mab_stage_aat_qkv(mab_handle* h, int layer, void** qkv_out, int* 
   return 0;
 }
 
+// softmax scale of the info-sharing attention: head_dim^-0.5, times the entropy scaling of q
+// sqrt(1.4 * log(N) / log(444)) when configured (transformer_blocks.py:108-110,190-196; N = tokens of
+// the attention call: the whole scene + scale token for a global layer, T for a frame layer),
+// evaluated in fp32 like the reference's 0-dim tensors
+static float aat_softmax_scale(const mab_config& cf, long long n_tokens) {
+  if (!cf.aat_entropy_scaling) return 0.125f;
+  const float f = sqrtf((1.4f * logf((float)n_tokens)) / logf(444.0f));
+  return 0.125f * f;
+}
+
 // Attention of block `layer` against one K/V block.  Odd (frame) layers and single-GPU global
 // layers take one call (flags = FIRST|LAST, kv = NULL).  View-sharded global layers call it once
 // per ring step with the qkv rows of the rank whose block is currently held: the online-softmax
@@ -1200,12 +1212,15 @@ extern "C" int mab_stage_aat_attend(mab_handle* h, int layer, const void* kv, in
     const void* kvp = kv ? kv : p.qkv;
     const int kvr = kv ? kv_rows : (int)rows;
     MAB_ARG((first && last) || p.carry_o, "ring attention needs views_total > views at mab_stage_encode");
-    return launch_attention(p.qkv, rows, kvp, kvr, cf.aat_heads, 1, (int)rows, kvr, 0, 0, 0.125f,
-                            p.att, nullptr, c.st, p.carry_o, p.carry_ml, first ? 0 : 1, last ? 0 : 1);
+    // sharded scenes: every rank sees Vtot * T + 1 tokens in total (the scale token lives on one rank)
+    const long long n_scene = (long long)p.Vtot * T + 1;
+    return launch_attention(p.qkv, rows, kvp, kvr, cf.aat_heads, 1, (int)rows, kvr, 0, 0,
+                            aat_softmax_scale(cf, n_scene), p.att, nullptr, c.st, p.carry_o, p.carry_ml,
+                            first ? 0 : 1, last ? 0 : 1);
   }
   MAB_ARG(first && last && !kv, "frame attention is local to a view: one step");
   const long long rows = (long long)V * T;  // frame attention inside each view (aat.py:662-705)
-  return launch_attention(p.qkv, rows, p.qkv, rows, cf.aat_heads, V, T, T, T, T, 0.125f, p.att,
+  return launch_attention(p.qkv, rows, p.qkv, rows, cf.aat_heads, V, T, T, T, T, aat_softmax_scale(cf, T), p.att,
                           nullptr, c.st);
 }
 
@@ -1230,8 +1245,9 @@ extern "C" int mab_stage_aat_attend_kv(mab_handle* h, int layer, const void* kv,
   Plan& p = h->plan;
   const int first = flags & MAB_RING_FIRST, last = flags & MAB_RING_LAST;
   MAB_ARG((first && last) || p.carry_o, "carried attention needs views_total > views at mab_stage_encode");
-  return launch_attention(p.qkv, p.L, kv, kv_rows, cf.aat_heads, 1, (int)p.L, kv_rows, 0, 0, 0.125f, p.att,
-                          nullptr, (cudaStream_t)stream, p.carry_o, p.carry_ml, first ? 0 : 1, last ? 0 : 1, 1);
+  return launch_attention(p.qkv, p.L, kv, kv_rows, cf.aat_heads, 1, (int)p.L, kv_rows, 0, 0,
+                          aat_softmax_scale(cf, (long long)p.Vtot * p.T + 1), p.att, nullptr, (cudaStream_t)stream,
+                          p.carry_o, p.carry_ml, first ? 0 : 1, last ? 0 : 1, 1);
 }
 
 // proj + residual, LN2, MLP + residual of block `layer`, intermediate taps and the final norm

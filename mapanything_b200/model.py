@@ -61,7 +61,8 @@ def validate_input_views_for_inference(views):
 def default_config():
     """Architecture of the production model (configs/model/mapanything.yaml)."""
     return dict(patch=14, enc_dim=1024, enc_depth=24, enc_heads=16, enc_pos_grid=37, aat_dim=768,
-                aat_depth=24, aat_heads=12, aat_tap0=11, aat_tap1=17, head_chunk=8)
+                aat_depth=24, aat_heads=12, aat_tap0=11, aat_tap1=17, head_chunk=8,
+                aat_ref_view_pe=1, aat_entropy_scaling=0)
 
 
 class MapAnything(torch.nn.Module):
@@ -93,6 +94,9 @@ class MapAnything(torch.nn.Module):
             cfg["aat_depth"] = int(margs["depth"])
         if "indices" in margs:
             cfg["aat_tap0"], cfg["aat_tap1"] = [int(i) for i in margs["indices"]]
+        # info_sharing variants: aat_ifr_24_layers_no_ref_view.yaml / aat_ifr_24_layers_escaling.yaml
+        cfg["aat_ref_view_pe"] = int(bool(margs.get("distinguish_ref_and_non_ref_views", True)))
+        cfg["aat_entropy_scaling"] = int(bool(margs.get("use_entropy_scaling", False)))
         cfg["head_chunk"] = int(head_chunk)
         self._cfg = _lib.MabConfig(**cfg)
         self._handle = C.c_void_p()
@@ -116,6 +120,12 @@ class MapAnything(torch.nn.Module):
             raise NotImplementedError("only the alternating-attention info-sharing model is built")
         if ic and ic.get("custom_positional_encoding") is not None:
             raise NotImplementedError("custom positional encodings are not part of the default path")
+        margs = (ic or {}).get("module_args", {})
+        if margs.get("use_pe_for_non_reference_views", False):
+            # aat.py:628-645 draws the non-reference view indices with torch.randint at every call
+            raise NotImplementedError("view positional encodings of non-reference views are not built")
+        if int(margs.get("dim", 768)) != 768 or int(margs.get("num_heads", 12)) != 12:
+            raise NotImplementedError("only the dim-768 / 12-head info-sharing transformer is built")
         pc = self.pred_head_config
         if pc and pc.get("type", "dpt+pose") != "dpt+pose":
             raise NotImplementedError("only the dpt+pose head is built")

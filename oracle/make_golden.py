@@ -42,6 +42,16 @@ CASES = {
 }
 
 
+# info_sharing module_args of the variant cases (configs/model/info_sharing/aat_ifr_24_layers_escaling.yaml,
+# aat_ifr_24_layers_no_ref_view.yaml); every other case runs the production config
+CASE_MODULE_ARGS = {
+    "small_escaling_n3_70x98": dict(use_entropy_scaling=True),
+    "small_noref_n3_70x98": dict(distinguish_ref_and_non_ref_views=False),
+}
+CASES["small_escaling_n3_70x98"] = (3, 70, 98, False, 1, {})
+CASES["small_noref_n3_70x98"] = (3, 70, 98, False, 1, {})
+
+
 def case_views(name):
     n, H, W, mm, _, _ = CASES[name]
     views = weights.synthetic_views(n, H, W, seed=1)
@@ -71,10 +81,15 @@ def main(only=None):
 
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     sd = weights.synthetic_state_dict()
-    model = ref_shim.build_reference_model(sd)
+    models = {}
     for name, (n, H, W, mm, stride, kw) in CASES.items():
         if only and name not in only:
             continue
+        margs = CASE_MODULE_ARGS.get(name, {})
+        mkey = tuple(sorted(margs.items()))
+        if mkey not in models:
+            models[mkey] = ref_shim.build_reference_model(sd, margs)
+        model = models[mkey]
         views = case_views(name)
         t0 = time.time()
         ref = model.infer([dict(v) for v in views], use_amp=False, amp_dtype="fp32", **kw)
@@ -82,7 +97,7 @@ def main(only=None):
         gold = pack_outputs(ref, stride)
         np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"), **gold)
         t0 = time.time()
-        mine = pack_outputs(orc.infer(sd, [dict(v) for v in views], **kw), stride)
+        mine = pack_outputs(orc.infer(sd, [dict(v) for v in views], aat_opts=margs, **kw), stride)
         t_orc = time.time() - t0
         print(f"== {name}: reference {t_ref:.1f}s, restatement {t_orc:.1f}s")
         worst = 0.0

@@ -37,12 +37,16 @@ def _conv(x, sd, prefix, stride=1, padding=0):
     return F.conv2d(x, sd[prefix + ".weight"], sd.get(prefix + ".bias"), stride=stride, padding=padding)
 
 
-def _attention(x, sd, prefix, num_heads):
-    """transformer_blocks.py:174-212 / encoders/dinov2.py:128-141 (SDPA, scale = head_dim**-0.5)."""
+def _attention(x, sd, prefix, num_heads, entropy_scaling=False):
+    """transformer_blocks.py:174-212 / encoders/dinov2.py:128-141 (SDPA, scale = head_dim**-0.5).
+    entropy_scaling: q *= sqrt(1.4 * log(N) / log(444)) (transformer_blocks.py:108-110,190-196)."""
     B, N, C = x.shape
     hd = C // num_heads
     qkv = _lin(x, sd, prefix + ".qkv").reshape(B, N, 3, num_heads, hd).permute(2, 0, 3, 1, 4)
     q, k, v = qkv[0], qkv[1], qkv[2]
+    if entropy_scaling:
+        q = q * torch.sqrt((1.4 * torch.log(torch.tensor(N, device=q.device))) /
+                           torch.log(torch.tensor(444, device=q.device)))
     o = F.scaled_dot_product_attention(q, k, v, scale=hd ** -0.5)
     o = o.transpose(1, 2).reshape(B, N, C)
     return _lin(o, sd, prefix + ".proj")
@@ -310,10 +314,16 @@ def fuse_geometric_inputs(feats, views, sd, flags):
 # --------------------------------------------------------------------------------------------
 # a7-a9: multi-view alternating-attention transformer (IFR)
 # --------------------------------------------------------------------------------------------
-def _block(x, sd, p, heads):
+def _block(x, sd, p, heads, entropy_scaling=False):
     """transformer_blocks.py:467-468 (no LayerScale: init_values=None)."""
-    x = x + _attention(_ln(x, sd, p + ".norm1"), sd, p + ".attn", heads)
+    x = x + _attention(_ln(x, sd, p + ".norm1"), sd, p + ".attn", heads, entropy_scaling)
     return x + _mlp(_ln(x, sd, p + ".norm2"), sd, p + ".mlp")
+
+
+# info_sharing module_args that change the arithmetic (configs/model/info_sharing/*.yaml):
+#   use_entropy_scaling (aat_ifr_24_layers_escaling.yaml), distinguish_ref_and_non_ref_views
+#   (aat_ifr_24_layers_no_ref_view.yaml).  Set by infer(..., aat_opts=...).
+AAT_OPTS = {"use_entropy_scaling": False, "distinguish_ref_and_non_ref_views": True}
 
 
 def alternating_attention_transformer(feats, sd, indices=(11, 17), prefix="info_sharing", taps=None):
@@ -322,7 +332,9 @@ def alternating_attention_transformer(feats, sd, indices=(11, 17), prefix="info_
     V, T, _ = feats.shape
     x = torch.cat([feats.reshape(1, V * T, -1), sd["scale_token"].view(1, 1, -1)], dim=1)
     x = _lin(x, sd, prefix + ".proj_embed")
-    x = torch.cat([x[:, :T] + sd[prefix + ".view_pos_table"][0].view(1, 1, -1), x[:, T:]], dim=1)
+    if AAT_OPTS["distinguish_ref_and_non_ref_views"]:  # aat.py:618-626
+        x = torch.cat([x[:, :T] + sd[prefix + ".view_pos_table"][0].view(1, 1, -1), x[:, T:]], dim=1)
+    es = AAT_OPTS["use_entropy_scaling"]
     if taps is not None:
         taps["aat_in"] = x[0]
     depth = 1 + max(int(k.split(".")[2]) for k in sd if k.startswith(prefix + ".self_attention_blocks."))
@@ -330,10 +342,10 @@ def alternating_attention_transformer(feats, sd, indices=(11, 17), prefix="info_
     for i in range(depth):
         p = f"{prefix}.self_attention_blocks.{i}"
         if i % 2 == 0:
-            x = _block(x, sd, p, 12)
+            x = _block(x, sd, p, 12, es)
         else:
             extra = x[:, V * T:]
-            y = _block(x[:, :V * T].reshape(V, T, -1), sd, p, 12)
+            y = _block(x[:, :V * T].reshape(V, T, -1), sd, p, 12, es)
             x = torch.cat([y.reshape(1, V * T, -1), extra], dim=1)
         if taps is not None and i in (0, 1):
             taps[f"aat_block{i}"] = x[0]
@@ -682,9 +694,26 @@ def validate_views(views):
 def infer(sd, views, apply_mask=True, mask_edges=True, edge_normal_threshold=5.0,
           edge_depth_threshold=0.03, apply_confidence_mask=False, confidence_percentile=10,
           ignore_calibration_inputs=False, ignore_depth_inputs=False, ignore_pose_inputs=False,
-          ignore_depth_scale_inputs=False, ignore_pose_scale_inputs=False, taps=None, amp=False):
+          ignore_depth_scale_inputs=False, ignore_pose_scale_inputs=False, taps=None, amp=False,
+          aat_opts=None):
     """model.py:2206-2355; fp32 (use_amp=False) unless amp=True (see forward).  Tensors may live on
-    any device; post-processing runs on the CPU like the reference's numpy code."""
+    any device; post-processing runs on the CPU like the reference's numpy code.  aat_opts: the
+    info_sharing module_args that change the arithmetic (see AAT_OPTS)."""
+    saved = dict(AAT_OPTS)
+    AAT_OPTS.update(aat_opts or {})
+    try:
+        return _infer(sd, views, apply_mask, mask_edges, edge_normal_threshold, edge_depth_threshold,
+                      apply_confidence_mask, confidence_percentile, ignore_calibration_inputs,
+                      ignore_depth_inputs, ignore_pose_inputs, ignore_depth_scale_inputs,
+                      ignore_pose_scale_inputs, taps, amp)
+    finally:
+        AAT_OPTS.clear()
+        AAT_OPTS.update(saved)
+
+
+def _infer(sd, views, apply_mask, mask_edges, edge_normal_threshold, edge_depth_threshold,
+           apply_confidence_mask, confidence_percentile, ignore_calibration_inputs, ignore_depth_inputs,
+           ignore_pose_inputs, ignore_depth_scale_inputs, ignore_pose_scale_inputs, taps, amp):
     with torch.inference_mode():
         pv = preprocess_views(validate_views(views))
         flags = dict(use_calibration=not ignore_calibration_inputs, use_depth=not ignore_depth_inputs,

@@ -149,13 +149,20 @@ def reference_config():
     return cfg
 
 
-def build_reference_model(state_dict=None):
-    """Construct the reference MapAnything (CPU, fp32, eval); optionally load a state dict."""
+def build_reference_model(state_dict=None, module_args=None):
+    """Construct the reference MapAnything (CPU, fp32, eval); optionally load a state dict.
+    module_args: overrides of info_sharing_config.module_args (the configs/model/info_sharing/*.yaml
+    variants, e.g. use_entropy_scaling=True, distinguish_ref_and_non_ref_views=False)."""
     install()
     from mapanything.models.mapanything.model import MapAnything
 
-    model = MapAnything(**copy.deepcopy(reference_config())).eval()
+    cfg = copy.deepcopy(reference_config())
+    cfg["info_sharing_config"]["module_args"].update(module_args or {})
+    model = MapAnything(**cfg).eval()
     if state_dict is not None:
-        missing, unexpected = model.load_state_dict(state_dict, strict=True)
+        sd = dict(state_dict)
+        if not cfg["info_sharing_config"]["module_args"]["distinguish_ref_and_non_ref_views"]:
+            sd.pop("info_sharing.view_pos_table", None)  # the buffer only exists with the reference-view PE
+        missing, unexpected = model.load_state_dict(sd, strict=True)
         assert not missing and not unexpected
     return model

@@ -78,6 +78,47 @@ def test_infer_matches_reference_golden(name, model, sd_cuda):
     assert all(t.device.type == "cuda" for t in p.values())
 
 
+@pytest.mark.parametrize("name", ["small_escaling_n3_70x98", "small_noref_n3_70x98"])
+def test_info_sharing_variants_match_reference_golden(name, synthetic_sd, sd_cuda):
+    """configs/model/info_sharing/aat_ifr_24_layers_escaling.yaml (entropy-scaled attention) and
+    aat_ifr_24_layers_no_ref_view.yaml (no reference-view PE) against goldens of the LIVE reference built
+    with those module_args; same tolerances and bf16 yardstick as the production config."""
+    from mapanything_b200 import MapAnything
+    from oracle import make_golden
+    from oracle import mapanything_oracle as orc
+    from tests import helpers
+
+    margs = make_golden.CASE_MODULE_ARGS[name]
+    m = MapAnything(device="cuda:0", head_chunk=2,
+                    info_sharing_config={"model_type": "alternating_attention", "module_args": dict(margs)})
+    sd = dict(synthetic_sd)
+    if not margs.get("distinguish_ref_and_non_ref_views", True):
+        sd.pop("info_sharing.view_pos_table")  # such a checkpoint has no view_pos_table buffer
+    m.load_state_dict(sd)
+    n, H, W, mm, stride, kw = make_golden.CASES[name]
+    views = make_golden.case_views(name)
+    preds = m.infer([dict(v) for v in views], **kw)
+    torch.cuda.synchronize()
+    g = helpers.load_golden(name)
+    rep = helpers.compare_with_golden(preds, g, stride, None, None)
+    yard = helpers.compare_with_golden(orc.infer(sd_cuda, _to_cuda(views), amp=True, aat_opts=margs, **kw), g,
+                                       stride, None, None)
+    print("libmab200  :", {k: round(v, 5) for k, v in rep.items()})
+    print("ref bf16   :", {k: round(v, 5) for k, v in yard.items()})
+    cam_frame = {k: v for k, v in rep.items() if k.split(".", 1)[1] not in helpers.POSE_DEPENDENT_KEYS
+                 and k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
+    bad = helpers.out_of_tolerance(cam_frame, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97)
+    assert not bad, f"camera-frame keys out of absolute tolerance: {bad}"
+    rest = {k: v for k, v in rep.items() if k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
+    bad = helpers.out_of_tolerance(rest, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97,
+                                   yardstick=yard, slack=3.0)
+    assert not bad, f"further from the fp32 reference than the reference's bf16 path: {bad}\nyardstick {yard}"
+    # and the variant really is a different function: the production config misses this golden
+    base = helpers.compare_with_golden(orc.infer(sd_cuda, _to_cuda(views), **kw), g, stride, None, None)
+    worst = lambda r: max(v for k, v in r.items() if k.endswith("pts3d_cam"))
+    assert worst(base) > 5 * worst(rep), (worst(base), worst(rep))
+
+
 def test_forward_raw_matches_oracle(model, synthetic_sd, sd_cuda):
     """raw forward dicts (model.py:1907-1923) vs the fp32 oracle, incl. the views-chunked dense head"""
     from oracle import mapanything_oracle as orc, weights
