@@ -200,8 +200,7 @@ class MapAnything(torch.nn.Module):
         B, Cc, H, W = views[0]["img"].shape
         assert Cc == 3, "Input must have 3 channels"
         assert H % 14 == 0 and W % 14 == 0, "Input shape must be divisible by patch size: 14"
-        if B != 1:
-            raise NotImplementedError("batch size per view > 1 (every reference config uses 1)")
+        assert B == 1, "a batch of B scenes is split into scenes by infer() / forward()"
         imgs = torch.empty((len(views), 3, H, W), dtype=torch.float32, device=self._device)
         for i, v in enumerate(views):
             imgs[i].copy_(v["img"][0], non_blocking=True)
@@ -587,6 +586,16 @@ class MapAnything(torch.nn.Module):
         no-op here (the dense head always streams `head_chunk` views through a fixed workspace)."""
         if not self._finalized:
             raise RuntimeError("load_state_dict() / from_pretrained() must be called before inference")
+        B = int(views[0]["img"].shape[0])
+        if B > 1:  # B independent scenes (see infer)
+            per_scene = []
+            for b in range(B):
+                scene = [{k: (t[b:b + 1] if torch.is_tensor(t) and t.dim() > 0 and t.shape[0] == B else
+                              (tuple(c[b:b + 1] for c in t) if isinstance(t, tuple) else t))
+                          for k, t in v.items()} for v in views]
+                per_scene.append(self.forward(scene, memory_efficient_inference))
+            return [{k: torch.cat([per_scene[b][i][k] for b in range(B)], 0) for k in per_scene[0][i]}
+                    for i in range(len(views))]
         imgs, H, W = self._pack_images(views)
         geo = self._pack_geometry(views, dict(_ALL_INPUTS), H, W)
         outs = self._run_forward(imgs, H, W, geo=geo)
@@ -622,6 +631,33 @@ class MapAnything(torch.nn.Module):
         for v in views:
             if v["data_norm_type"][0] != self.data_norm_type:  # encoders/base.py:83-96
                 raise AssertionError(f"data_norm_type {v['data_norm_type']} != encoder's {self.data_norm_type}")
+        B = int(views[0]["img"].shape[0])
+        if B > 1:
+            # A per-view batch is B independent scenes (sample b of every view; shown on the live
+            # reference by oracle/check_batch_independence.py): run them one after the other and
+            # concatenate every prediction along dim 0, which is what the reference returns.
+            kw = dict(memory_efficient_inference=memory_efficient_inference, use_amp=use_amp, amp_dtype=amp_dtype,
+                      apply_mask=apply_mask, mask_edges=mask_edges, edge_normal_threshold=edge_normal_threshold,
+                      edge_depth_threshold=edge_depth_threshold, apply_confidence_mask=apply_confidence_mask,
+                      confidence_percentile=confidence_percentile, ignore_calibration_inputs=ignore_calibration_inputs,
+                      ignore_depth_inputs=ignore_depth_inputs, ignore_pose_inputs=ignore_pose_inputs,
+                      ignore_depth_scale_inputs=ignore_depth_scale_inputs,
+                      ignore_pose_scale_inputs=ignore_pose_scale_inputs, view_range=view_range,
+                      total_views=total_views, host_outputs=host_outputs, stream_chunk=stream_chunk)
+            per_scene = []
+            for b in range(B):
+                scene = [{k: (t[b:b + 1] if torch.is_tensor(t) and t.dim() > 0 and t.shape[0] == B else
+                              (tuple(c[b:b + 1] for c in t) if isinstance(t, tuple) else t))
+                          for k, t in v.items()} for v in views]
+                preds = self.infer(scene, **kw)
+                # host_outputs reuses one pinned pool per call: detach the scene's results from it
+                per_scene.append([{k: t.clone() for k, t in p.items()} for p in preds] if host_outputs else preds)
+            for v in views:  # model.py:2316-2320: the caller's tensors end up on the model device
+                for name in list(v.keys()):
+                    if name not in _PASS_THROUGH and torch.is_tensor(v[name]):
+                        v[name] = v[name].to(self._device, non_blocking=True)
+            return [{k: torch.cat([per_scene[b][i][k] for b in range(B)], 0) for k in per_scene[0][i]}
+                    for i in range(len(views))]
         flags = dict(use_calibration=not ignore_calibration_inputs, use_depth=not ignore_depth_inputs,
                      use_pose=not ignore_pose_inputs, use_depth_scale=not ignore_depth_scale_inputs,
                      use_pose_scale=not ignore_pose_scale_inputs)  # model.py:2154-2197

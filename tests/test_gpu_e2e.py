@@ -119,6 +119,63 @@ def test_info_sharing_variants_match_reference_golden(name, synthetic_sd, sd_cud
     assert worst(base) > 5 * worst(rep), (worst(base), worst(rep))
 
 
+@pytest.mark.parametrize("H,W", [(518, 518), (518, 294), (168, 518)])
+def test_other_resolution_mappings_match_oracle(H, W, model, sd_cuda):
+    """The other entries of RESOLUTION_MAPPINGS[518] (image.py:40-52): square (37 x 37 patches: the
+    pos-embed is used as stored, vision_transformer.py:214-215), portrait 9:16 and 3.2:1 panorama, against
+    the fp32 oracle on the same GPU; camera-frame geometry within BASELINE.json's bf16 tolerance."""
+    from oracle import mapanything_oracle as orc, weights
+    from tests import helpers
+
+    views = weights.synthetic_views(2, H, W, seed=9)
+    preds = model.infer([dict(v) for v in views])
+    torch.cuda.synchronize()
+    with helpers.strict_fp32():
+        ref = orc.infer(sd_cuda, _to_cuda(views))
+    for p, r in zip(preds, ref):
+        assert p["pts3d"].shape == (1, H, W, 3) and p["mask"].shape == (1, H, W, 1)
+        both = (p["mask"].cpu() & r["mask"]).float()
+        for k in ("ray_directions", "conf", "depth_along_ray", "pts3d_cam"):
+            a, b = p[k].float().cpu(), r[k].float().cpu()
+            if k in ("depth_along_ray", "pts3d_cam"):  # infer() zeroes masked pixels
+                a, b = a * both, b * both
+            err = float((a - b).norm() / (b.norm() + 1e-30))
+            assert err < TOL_DENSE, (H, W, k, err)
+        assert float((p["mask"].cpu() == r["mask"]).float().mean()) > 0.95
+
+
+def test_batched_views_are_independent_scenes(model):
+    """img (B,3,H,W) with B = 2: the reference treats the batch as two independent scenes
+    (oracle/check_batch_independence.py, live reference); predictions come back as (B, ...) tensors."""
+    from oracle import weights
+
+    H, W = 56, 84
+    va = weights.synthetic_views(3, H, W, seed=1)
+    vb = weights.add_multimodal_inputs(weights.synthetic_views(3, H, W, seed=5), seed=6)
+    va = weights.add_multimodal_inputs(va, seed=2)
+    batched = []
+    for a, b in zip(va, vb):
+        d = {}
+        for k in a:
+            d[k] = torch.cat([a[k], b[k]], 0) if torch.is_tensor(a[k]) else a[k]
+        batched.append(d)
+    pa = model.infer([dict(v) for v in va])
+    pb = model.infer([dict(v) for v in vb])
+    pp = model.infer([dict(v) for v in batched])
+    raw = model.forward([dict(v) for v in batched])
+    torch.cuda.synchronize()
+    assert len(pp) == 3 and raw[0]["pts3d"].shape == (2, H, W, 3)
+    for i in range(3):
+        assert set(pp[i]) == set(pa[i])
+        for k in pp[i]:
+            ref = torch.cat([pa[i][k], pb[i][k]], 0)
+            assert pp[i][k].shape == ref.shape and pp[i][k].dtype == ref.dtype, k
+            assert torch.equal(pp[i][k], ref), k
+    assert pp[0]["metric_scaling_factor"].shape == (2, 1) and pp[0]["mask"].shape == (2, H, W, 1)
+    hp = model.infer([dict(v) for v in batched], host_outputs=True)
+    assert all(torch.equal(hp[i][k], pp[i][k].cpu()) for i in range(3) for k in pp[i])
+
+
 def test_forward_raw_matches_oracle(model, synthetic_sd, sd_cuda):
     """raw forward dicts (model.py:1907-1923) vs the fp32 oracle, incl. the views-chunked dense head"""
     from oracle import mapanything_oracle as orc, weights
