@@ -144,6 +144,30 @@ def test_other_resolution_mappings_match_oracle(H, W, model, sd_cuda):
         assert float((p["mask"].cpu() == r["mask"]).float().mean()) > 0.95
 
 
+def test_from_pretrained_local_directory(tmp_path, model, synthetic_sd):
+    """MapAnything.from_pretrained(dir) (PyTorchModelHubMixin layout: config.json + model.safetensors,
+    model.py:96) builds the same model as constructor + load_state_dict."""
+    import json
+
+    from safetensors.torch import save_file
+
+    from mapanything_b200 import MapAnything
+    from oracle import ref_shim, weights
+
+    cfg = ref_shim.reference_config()
+    with open(tmp_path / "config.json", "w") as f:
+        json.dump(cfg, f)  # the adaptor bounds are +-inf: "Infinity" in the file, as huggingface_hub writes them
+    save_file({k: v.detach().clone().contiguous() for k, v in synthetic_sd.items()}, str(tmp_path / "model.safetensors"))
+    m = MapAnything.from_pretrained(str(tmp_path), device="cuda:0", head_chunk=2)
+    views = weights.synthetic_views(2, 56, 84, seed=3)
+    a = m.infer([dict(v) for v in views])
+    b = model.infer([dict(v) for v in views])
+    torch.cuda.synchronize()
+    assert all(torch.equal(a[i][k], b[i][k]) for i in range(2) for k in b[i])
+    with pytest.raises(FileNotFoundError):
+        MapAnything.from_pretrained("facebook/map-anything")  # hub ids need network access
+
+
 def test_batched_views_are_independent_scenes(model):
     """img (B,3,H,W) with B = 2: the reference treats the batch as two independent scenes
     (oracle/check_batch_independence.py, live reference); predictions come back as (B, ...) tensors."""
