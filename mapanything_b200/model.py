@@ -355,9 +355,7 @@ class MapAnything(torch.nn.Module):
                     self._trunk_single(inp, outs, ws)
                 else:
                     self._forward_sharded(inp, ost, outs, ws, V, H, W, view_lo, total, heads=False)
-                step = max(1, int(stream_chunk) or self._cfg.head_chunk)
-                for v0 in range(0, V, step):
-                    v1 = min(V, v0 + step)
+                for v0, v1 in self._head_ranges(V, stream_chunk):
                     _lib.check(self._lib.mab_stage_heads_range(self._handle, C.byref(inp), C.byref(ost), v0, v1,
                                                                self._stream_ptr()), "mab_stage_heads_range")
                     on_views(outs, v0, v1)
@@ -367,6 +365,21 @@ class MapAnything(torch.nn.Module):
             else:
                 self._forward_sharded(inp, ost, outs, ws, V, H, W, view_lo, total)
         return outs
+
+    def _head_ranges(self, V, stream_chunk):
+        """View ranges of the streamed heads.  int: equal ranges of that many views.  Sequence: range sizes
+        in order, the last size repeating (e.g. (4, 2, 1): 4, 2, 1, 1, ...): the tail of the call is the
+        device-to-host copy of the LAST range, so the ranges shrink towards the end."""
+        if isinstance(stream_chunk, (tuple, list)):
+            sizes = [max(1, int(c)) for c in stream_chunk] or [self._cfg.head_chunk]
+        else:
+            sizes = [max(1, int(stream_chunk) or self._cfg.head_chunk)]
+        out, v0, i = [], 0, 0
+        while v0 < V:
+            v1 = min(V, v0 + sizes[min(i, len(sizes) - 1)])
+            out.append((v0, v1))
+            v0, i = v1, i + 1
+        return out
 
     def _trunk_single(self, inp, outs, ws):
         """Encoder + info sharing + scale head of a whole scene on this GPU through the staged ABI
@@ -623,8 +636,11 @@ class MapAnything(torch.nn.Module):
         The heads then run `stream_chunk` views at a time and every finished range is post-processed
         and copied out on a second stream while the heads of the later views compute, so the
         107 MB of predictions per 8 views leave the device under the dense head instead of after
-        it.  The returned tensors are views into a buffer the model reuses: valid until the next
-        `infer(host_outputs=True)` call on this model."""
+        it.  `stream_chunk` may also be a sequence of range sizes (last one repeating); measured at
+        8 views (profiles/e2e_variants.py): 4|4 20.28 ms, 4|3|1 20.40, 4|2|2 20.70, 8 20.87, 2|2|2|2
+        21.44 -- shrinking the last range shortens the copy-out tail by less than small ranges cost
+        the dense head.  The returned tensors are views into a buffer the model reuses: valid until
+        the next `infer(host_outputs=True)` call on this model."""
         if not self._finalized:
             raise RuntimeError("load_state_dict() / from_pretrained() must be called before inference")
         views = validate_input_views_for_inference(views)

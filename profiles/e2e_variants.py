@@ -19,7 +19,7 @@ def timed(fn, n=10):
     for _ in range(n): fn()
     torch.cuda.synchronize(); return (time.perf_counter() - t0) / n * 1e3
 print(f"device outputs + copies afterwards: {timed(old_way):.2f} ms")
-for c in (1, 2, 4, 8):
+for c in (1, 2, 4, 8, (4, 2, 2), (4, 2, 1), (3, 3, 2), (5, 2, 1), (4, 3, 1), (6, 1), (2, 2, 2, 1)):
     print(f"host_outputs stream_chunk={c}: {timed(lambda: model.infer([dict(v) for v in views], host_outputs=True, stream_chunk=c)):.2f} ms")
 imgs = torch.cat([v["img"] for v in views], 0).to(dev)
 print(f"resident forward+post: {timed(lambda: model.run_resident(imgs, 392, 518)):.2f} ms")
