@@ -236,6 +236,11 @@ int mab_preprocess_image(const unsigned char* rgb, const mab_image_plan* plan, c
                          const float* std_host, float* out, unsigned char* out_u8, void* workspace,
                          size_t workspace_bytes, void* stream);
 
+/* `recover_pinhole_intrinsics_from_ray_directions` (mapanything/utils/geometry.py:304-447, least-squares
+ * branch): rays [views,H,W,3] -> K [views,3,3]; used by preprocess_inputs for views that carry
+ * ray_directions instead of intrinsics (image.py:572-590). */
+int mab_recover_intrinsics(const float* rays, int views, int H, int W, float* K_out, void* stream);
+
 /* Depth maps of `preprocess_inputs` (image.py:335-675): cv2.INTER_NEAREST resize to
  * (resize_w, resize_h) (cropping.py:246-253) + crop (cropping.py:345-349), one fp32 channel. */
 int mab_resize_nearest_crop(const float* src, int in_h, int in_w, int resize_w, int resize_h,

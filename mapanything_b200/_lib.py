@@ -89,6 +89,7 @@ SYMBOLS = {
     "mab_image_plan_make": (_i, [_i, _i, _i, _i, C.POINTER(MabImagePlan)]),
     "mab_preprocess_workspace_bytes": (C.c_size_t, [C.POINTER(MabImagePlan)]),
     "mab_preprocess_image": (_i, [_vp, C.POINTER(MabImagePlan), c_float_p, c_float_p, _vp, _vp, _vp, C.c_size_t, _vp]),
+    "mab_recover_intrinsics": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "mab_resize_nearest_crop": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "mab_export_workspace_bytes": (C.c_size_t, [_i, _i, _i]),
     "mab_export_points": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, C.c_longlong, _vp, _vp,

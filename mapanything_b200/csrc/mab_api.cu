@@ -406,6 +406,19 @@ extern "C" int mab_preprocess_image(const unsigned char* rgb, const mab_image_pl
   return 0;
 }
 
+// recover_pinhole_intrinsics_from_ray_directions (geometry.py:304-447, regression branch): least squares
+// of x = cx + fx * (dx / dz) on the stride-max(1, H//50) x max(1, W//50) grid, one block per view
+extern "C" int mab_recover_intrinsics(const float* rays, int views, int H, int W, float* K_out, void* stream) {
+  MAB_ARG(rays && K_out && views > 0 && H > 0 && W > 0, "bad arguments");
+  MAB_ARG((long long)H * W <= 1000000, "the reference switches to its geometric branch above 1e6 pixels");
+  cudaStream_t st = (cudaStream_t)stream;
+  MAB_LAUNCH(CAT_POSTPROCESS, 0.0, 0.0, st,
+             intrinsics_pose_kernel<<<views, 256, 0, st>>>(rays, H, W, nullptr, nullptr, K_out, nullptr, nullptr,
+                                                          nullptr));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // depth maps of preprocess_inputs (image.py:560-567 -> cropping.py:246-253,345-349)
 extern "C" int mab_resize_nearest_crop(const float* src, int in_h, int in_w, int resize_w, int resize_h,
                                        int crop_left, int crop_top, int out_w, int out_h, float* out,

@@ -64,6 +64,7 @@ __global__ void intrinsics_pose_kernel(const float* __restrict__ rays, int H, in
     float* K = K_out + v * 9;
     K[0] = (float)fx; K[1] = 0; K[2] = (float)cx; K[3] = 0; K[4] = (float)fy; K[5] = (float)cy;
     K[6] = 0; K[7] = 0; K[8] = 1.f;
+    if (!pose) return;  // intrinsics only (mab_recover_intrinsics)
     const float* p = pose + v * 8;
     const float s = scale[0];
     // quaternion_to_rotation_matrix re-normalises (geometry.py:617)

@@ -206,9 +206,9 @@ def _to_u8(img, view_idx, dev):
 def preprocess_inputs(input_views, resize_mode="fixed_mapping", size=None, norm_type="dinov2", patch_size=14,
                       resolution_set=518, verbose=False, device="cuda") -> List[dict]:
     """`mapanything.utils.image.preprocess_inputs` (image.py:335-675): same arguments, same view dicts;
-    images (Pillow-exact resize + crop + normalise) and depth maps (cv2.INTER_NEAREST + crop) on the device.
-    `ray_directions` inputs (intrinsics recovered by least squares, image.py:572-590) are not supported
-    here: pass `intrinsics`."""
+    images (Pillow-exact resize + crop + normalise) and depth maps (cv2.INTER_NEAREST + crop) on the device;
+    views that carry `ray_directions` get their intrinsics recovered by least squares (image.py:572-590,
+    `mab_recover_intrinsics`)."""
     _validate(resize_mode, size)
     if not input_views:
         raise ValueError("input_views cannot be empty")
@@ -224,8 +224,6 @@ def preprocess_inputs(input_views, resize_mode="fixed_mapping", size=None, norm_
         if "intrinsics" in v and "ray_directions" in v:
             raise ValueError(f"View {i} cannot have both 'intrinsics' and 'ray_directions'. Please provide only one "
                              "as they are redundant (ray_directions can be used to recover intrinsics).")
-        if "ray_directions" in v:
-            raise NotImplementedError("preprocess_inputs: pass 'intrinsics' instead of 'ray_directions'")
     lib = _lib.load()
     u8s = [_to_u8(v["img"], i, dev).contiguous() for i, v in enumerate(input_views)]
     tw, th = _target_size([(int(t.shape[1]), int(t.shape[0])) for t in u8s], resize_mode, size, patch_size,
@@ -237,6 +235,15 @@ def preprocess_inputs(input_views, resize_mode="fixed_mapping", size=None, norm_
     for i, (view, u8) in enumerate(zip(input_views, u8s)):
         h1, w1 = int(u8.shape[0]), int(u8.shape[1])
         K = view.get("intrinsics")
+        if "ray_directions" in view:  # image.py:572-590: intrinsics recovered from the rays by least squares
+            rays = torch.as_tensor(view["ray_directions"])
+            if rays.ndim != 3 or rays.shape[2] != 3:
+                raise ValueError(f"Expected shape (H, W, 3) for ray_directions in view {i}, got {tuple(rays.shape)}")
+            rays = rays.to(dev, torch.float32).contiguous()
+            Kd = torch.empty((1, 3, 3), dtype=torch.float32, device=dev)
+            _lib.check(lib.mab_recover_intrinsics(C.c_void_p(rays.data_ptr()), 1, int(rays.shape[0]), int(rays.shape[1]),
+                                                  C.c_void_p(Kd.data_ptr()), st), "mab_recover_intrinsics")
+            K = Kd[0].cpu().numpy()
         if K is not None:
             K = K.cpu().numpy() if isinstance(K, torch.Tensor) else K
             if not isinstance(K, np.ndarray) or K.shape != (3, 3):

@@ -21,7 +21,11 @@ CASES = {  # name -> (list of (h, w, fx, fy, cx, cy)), kwargs
                                  dict(resize_mode="fixed_size", size=(196, 140))),
     "inputs_up_intrinsics": ([(60, 96, 80.0, 82.0, 50.2, 27.7)], dict(resize_mode="longest_side", size=126)),
     "inputs_depth_no_intrinsics": ([(200, 260, 0, 0, 0, 0)], dict(resize_mode="square", size=112)),
+    # ray_directions instead of intrinsics (image.py:572-590); the margin of the crop is even, so the
+    # crop offset does not sit on a rounding tie of the recovered principal point
+    "inputs_rays": ([(120, 200, 150.0, 148.0, 101.3, 58.6)], dict(resize_mode="fixed_size", size=(98, 70))),
 }
+RAY_CASES = {"inputs_rays"}
 
 
 def case_views(name):
@@ -32,7 +36,13 @@ def case_views(name):
         v = {"img": torch.from_numpy(synthetic_photo(h, w, 40 + i)),
              "depth_z": torch.from_numpy((rng.random((h, w)) * 5 + 0.5).astype(np.float32))}
         if fx:
-            v["intrinsics"] = torch.tensor([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], dtype=torch.float32)
+            K = torch.tensor([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], dtype=torch.float32)
+            if name in RAY_CASES:  # unit rays of that pinhole camera (geometry.py:186-241), restated
+                ys, xs = torch.meshgrid(torch.arange(h).float(), torch.arange(w).float(), indexing="ij")
+                d = torch.stack([(xs - cx) / fx, (ys - cy) / fy, torch.ones_like(xs)], -1)
+                v["ray_directions"] = d / d.norm(dim=-1, keepdim=True)
+            else:
+                v["intrinsics"] = K
         views.append(v)
     return views
 
@@ -49,6 +59,8 @@ def main():
             store[f"img{i}"] = v["img"].numpy(); store[f"depth{i}"] = v["depth_z"].numpy()
             if "intrinsics" in v:
                 store[f"K{i}"] = v["intrinsics"].numpy(); store[f"out_K{i}"] = o["intrinsics"][0].numpy()
+            if "ray_directions" in v:
+                store[f"out_K{i}"] = o["intrinsics"][0].numpy()
             store[f"out_img{i}"] = o["img"][0].numpy(); store[f"out_depth{i}"] = o["depth_z"][0].numpy()
         path = os.path.join(ROOT, "tests", "golden", name + ".npz")
         np.savez_compressed(path, **store)
