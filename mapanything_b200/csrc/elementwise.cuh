@@ -353,38 +353,38 @@ __global__ void resize_bilinear_ac_kernel(const __nv_bfloat16* __restrict__ in, 
                                           int Wi, int C, int Hv, int Wv, int Ho, int Wo,
                                           __nv_bfloat16* __restrict__ out,
                                           __nv_bfloat16* __restrict__ out_relu) {
+  // grid = (ceil(Wo * C/8 / 256), Ho, views): the output row and view come from the block index, so the
+  // per-thread index arithmetic is one 32-bit division (the flat grid-stride version spent its time in
+  // four 64-bit divisions per 16-byte store)
   const int c8n = C / 8;
-  const long long total = (long long)views * Ho * Wo * c8n;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= Wo * c8n) return;
+  const int ox = idx / c8n, c8 = idx - ox * c8n;
+  const int oy = blockIdx.y, v = blockIdx.z;
   const float ry = Hv > 1 ? float(Hi - 1) / float(Hv - 1) : 0.f;
   const float rx = Wv > 1 ? float(Wi - 1) / float(Wv - 1) : 0.f;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = i % c8n;
-    const int ox = (i / c8n) % Wo;
-    const int oy = (i / ((long long)c8n * Wo)) % Ho;
-    const int v = i / ((long long)c8n * Wo * Ho);
-    const float sy = ry * oy, sx = rx * ox;
-    const int y0 = min((int)sy, Hi - 1), x0 = min((int)sx, Wi - 1);
-    const int y1 = min(y0 + 1, Hi - 1), x1 = min(x0 + 1, Wi - 1);
-    const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
-    const uint4* base = reinterpret_cast<const uint4*>(in) + (long long)v * Hi * Wi * c8n + c8;
-    const uint4 a = base[((long long)y0 * Wi + x0) * c8n], b = base[((long long)y0 * Wi + x1) * c8n];
-    const uint4 c = base[((long long)y1 * Wi + x0) * c8n], d = base[((long long)y1 * Wi + x1) * c8n];
-    const uint32_t* pa = &a.x; const uint32_t* pb = &b.x; const uint32_t* pc = &c.x; const uint32_t* pd = &d.x;
-    uint32_t o[4], orl[4];
+  const float sy = ry * oy, sx = rx * ox;
+  const int y0 = min((int)sy, Hi - 1), x0 = min((int)sx, Wi - 1);
+  const int y1 = min(y0 + 1, Hi - 1), x1 = min(x0 + 1, Wi - 1);
+  const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
+  const uint4* base = reinterpret_cast<const uint4*>(in) + (long long)v * Hi * Wi * c8n + c8;
+  const uint4 a = base[((long long)y0 * Wi + x0) * c8n], b = base[((long long)y0 * Wi + x1) * c8n];
+  const uint4 c = base[((long long)y1 * Wi + x0) * c8n], d = base[((long long)y1 * Wi + x1) * c8n];
+  const uint32_t* pa = &a.x; const uint32_t* pb = &b.x; const uint32_t* pc = &c.x; const uint32_t* pd = &d.x;
+  uint32_t o[4], orl[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      // ATen: hy*(hx*a + lx*b) + ly*(hx*c + lx*d)
-      const float lo = hy * (hx * bf16_lo(pa[k]) + lx * bf16_lo(pb[k])) +
-                       ly * (hx * bf16_lo(pc[k]) + lx * bf16_lo(pd[k]));
-      const float hi = hy * (hx * bf16_hi(pa[k]) + lx * bf16_hi(pb[k])) +
-                       ly * (hx * bf16_hi(pc[k]) + lx * bf16_hi(pd[k]));
-      o[k] = pack_bf16(lo, hi);
-      orl[k] = pack_bf16(fmaxf(lo, 0.f), fmaxf(hi, 0.f));
-    }
-    if (out) reinterpret_cast<uint4*>(out)[i] = make_uint4(o[0], o[1], o[2], o[3]);
-    if (out_relu) reinterpret_cast<uint4*>(out_relu)[i] = make_uint4(orl[0], orl[1], orl[2], orl[3]);
+  for (int k = 0; k < 4; ++k) {
+    // ATen: hy*(hx*a + lx*b) + ly*(hx*c + lx*d)
+    const float lo = hy * (hx * bf16_lo(pa[k]) + lx * bf16_lo(pb[k])) +
+                     ly * (hx * bf16_lo(pc[k]) + lx * bf16_lo(pd[k]));
+    const float hi = hy * (hx * bf16_hi(pa[k]) + lx * bf16_hi(pb[k])) +
+                     ly * (hx * bf16_hi(pc[k]) + lx * bf16_hi(pd[k]));
+    o[k] = pack_bf16(lo, hi);
+    orl[k] = pack_bf16(fmaxf(lo, 0.f), fmaxf(hi, 0.f));
   }
+  const long long i = (((long long)v * Ho + oy) * Wo + ox) * c8n + c8;
+  if (out) reinterpret_cast<uint4*>(out)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  if (out_relu) reinterpret_cast<uint4*>(out_relu)[i] = make_uint4(orl[0], orl[1], orl[2], orl[3]);
 }
 
 // ConvTranspose2d with kernel == stride (dpt.py:117-127,139-149) = GEMM + pixel shuffle.

@@ -218,9 +218,10 @@ extern "C" int mab_conv3x3_tf32(const float* x, int batch, int H, int W, int C, 
 extern "C" int mab_resize_bilinear(const void* x, int batch, int Hi, int Wi, int C, int Hv, int Wv,
                                    int Ho, int Wo, void* out, void* out_relu, void* stream) {
   MAB_ARG(C % 8 == 0, "C must be a multiple of 8");
+  MAB_ARG(batch > 0 && batch <= 65535 && Ho > 0 && Ho <= 65535 && Wo > 0, "resize: bad sizes");
+  const dim3 grid((Wo * (C / 8) + 255) / 256, Ho, batch);
   MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, (cudaStream_t)stream,
-             resize_bilinear_ac_kernel<<<ew_grid((long long)batch * Ho * Wo * (C / 8)), 256, 0,
-                              (cudaStream_t)stream>>>(
+             resize_bilinear_ac_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const bf16*>(x), batch, Hi, Wi, C, Hv, Wv, Ho, Wo,
       reinterpret_cast<bf16*>(out), reinterpret_cast<bf16*>(out_relu)));
   MAB_CUDA(cudaGetLastError());
