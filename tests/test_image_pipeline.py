@@ -145,3 +145,27 @@ def test_cuda_inputs_match_golden(name):
         elif f"out_K{i}" in g:  # from ray_directions: least squares in double here, fp32 in the reference
             assert np.abs(o["intrinsics"][0].cpu().numpy() - g[f"out_K{i}"]).max() < 1e-3 * np.abs(g[f"out_K{i}"]).max()
         assert o["data_norm_type"] == ["dinov2"]
+
+
+def test_oracle_resize_equals_live_pillow_random_sizes():
+    """Seeded sweep over odd sizes and scale factors (shrink -> LANCZOS, enlarge -> BICUBIC), both passes,
+    single-pass cases (one dimension unchanged) and extreme aspect ratios."""
+    PIL = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(2024)
+    for _ in range(40):
+        h, w = int(rng.integers(3, 120)), int(rng.integers(3, 160))
+        if rng.random() < 0.5:   # shrink
+            oh, ow, f = int(rng.integers(1, h + 1)), int(rng.integers(1, w + 1)), "lanczos"
+        else:                    # enlarge
+            oh, ow, f = int(rng.integers(h, 3 * h + 1)), int(rng.integers(w, 3 * w + 1)), "bicubic"
+        img = rng.integers(0, 256, (h, w, 3)).astype(np.uint8)
+        res = PIL.Resampling.LANCZOS if f == "lanczos" else PIL.Resampling.BICUBIC
+        ref = np.asarray(PIL.fromarray(img).resize((ow, oh), resample=res))
+        assert np.array_equal(io.pil_resize(img, ow, oh, f), ref), (h, w, oh, ow, f)
+
+
+def test_oracle_crop_plan_matches_resize_plan_without_intrinsics():
+    for (w1, h1, tw, th) in [(640, 480, 518, 392), (1920, 1080, 518, 294), (90, 60, 126, 84), (333, 777, 294, 518)]:
+        rw, rh, filt, left, top = io.resize_plan(w1, h1, tw, th)
+        assert io.crop_plan(w1, h1, tw, th)[:5] == (rw, rh, filt, left, top)
+        assert rw >= tw and rh >= th and 0 <= left <= rw - tw and 0 <= top <= rh - th
