@@ -193,15 +193,22 @@ inline int make_tmap_nhwc(CUtensorMap* m, const void* ptr, int batch, int H, int
   return 0;
 }
 
+// Per-device caches: one process may hold handles on several GPUs (function attributes and the SM
+// count belong to the current device's context).
+constexpr int MAB_MAX_DEVICES = 64;
+inline int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev >= 0 && dev < MAB_MAX_DEVICES ? dev : 0;
+}
 inline int sm_count() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
+  static int n[MAB_MAX_DEVICES] = {0};
+  const int dev = current_device();
+  if (!n[dev]) {
+    cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (n[dev] <= 0) n[dev] = 148;
   }
-  return n;
+  return n[dev];
 }
 inline int ew_grid(long long total, int block = 256) {
   long long g = (total + block - 1) / block;
@@ -217,10 +224,10 @@ inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const Gem
                          const GemmEpilogue& ep, const RegressEpilogue& rg, cudaStream_t st) {
   using SM = GemmSmem<BN, STAGES>;
   auto kern = gemm_kernel<BN, STAGES, MODE, EPI, CL, TF>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static bool attr_done[MAB_MAX_DEVICES] = {false};
+  if (!attr_done[current_device()]) {
     MAB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::TOTAL));
-    attr_done = true;
+    attr_done[current_device()] = true;
   }
   int num_m;
   if (MODE == MODE_CONV3)
@@ -346,13 +353,13 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
   p.scale_log2e = scale * 1.4426950408889634f;
   p.lse = lse;
   p.carry_o = carry_o; p.carry_ml = carry_ml; p.carry_in = carry_in; p.carry_out = carry_out;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static bool attr_done[MAB_MAX_DEVICES] = {false};
+  if (!attr_done[current_device()]) {
     MAB_CUDA(cudaFuncSetAttribute(attention_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   AttCfg<2>::SMEM_BYTES));
     MAB_CUDA(cudaFuncSetAttribute(attention_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   AttCfg<1>::SMEM_BYTES));
-    attr_done = true;
+    attr_done[current_device()] = true;
   }
   ProfScope ps(CAT_ATTENTION, 4.0 * q_len * (double)kv_len * 64.0 * heads * num_seqs, 0.0, st);
   // short sequences (frame / encoder attention: 9 K/V tiles): one Q tile per CTA, two CTAs per SM;
