@@ -463,6 +463,7 @@ __global__ void small_linear_kernel(const float* __restrict__ x, const float* __
   float acc[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll 4  // independent loads in flight (the loop is latency-bound: one warp per output column)
   for (int k = lane; k < K; k += 32) {
     const float wv = __ldg(w + (long long)n * K + k);
 #pragma unroll
