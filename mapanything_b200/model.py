@@ -65,6 +65,22 @@ def default_config():
                 aat_ref_view_pe=1, aat_entropy_scaling=0)
 
 
+def head_ranges(V, stream_chunk, default_chunk):
+    """View ranges of the streamed heads.  int: equal ranges of that many views (0: default_chunk).
+    Sequence: range sizes in order, the last size repeating (e.g. (4, 2, 1): 4, 2, 1, 1, ...): the tail
+    of the call is the device-to-host copy of the LAST range, so the ranges may shrink towards the end."""
+    if isinstance(stream_chunk, (tuple, list)):
+        sizes = [max(1, int(c)) for c in stream_chunk] or [default_chunk]
+    else:
+        sizes = [max(1, int(stream_chunk) or default_chunk)]
+    out, v0, i = [], 0, 0
+    while v0 < V:
+        v1 = min(V, v0 + sizes[min(i, len(sizes) - 1)])
+        out.append((v0, v1))
+        v0, i = v1, i + 1
+    return out
+
+
 class MapAnything(torch.nn.Module):
     """Drop-in for the reference class on the inference path (no trainable state on the torch side:
     the weights live in packed device buffers owned by libmab200)."""
@@ -367,19 +383,7 @@ class MapAnything(torch.nn.Module):
         return outs
 
     def _head_ranges(self, V, stream_chunk):
-        """View ranges of the streamed heads.  int: equal ranges of that many views.  Sequence: range sizes
-        in order, the last size repeating (e.g. (4, 2, 1): 4, 2, 1, 1, ...): the tail of the call is the
-        device-to-host copy of the LAST range, so the ranges shrink towards the end."""
-        if isinstance(stream_chunk, (tuple, list)):
-            sizes = [max(1, int(c)) for c in stream_chunk] or [self._cfg.head_chunk]
-        else:
-            sizes = [max(1, int(stream_chunk) or self._cfg.head_chunk)]
-        out, v0, i = [], 0, 0
-        while v0 < V:
-            v1 = min(V, v0 + sizes[min(i, len(sizes) - 1)])
-            out.append((v0, v1))
-            v0, i = v1, i + 1
-        return out
+        return head_ranges(V, stream_chunk, self._cfg.head_chunk)
 
     def _trunk_single(self, inp, outs, ws):
         """Encoder + info sharing + scale head of a whole scene on this GPU through the staged ABI

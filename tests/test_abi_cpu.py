@@ -45,3 +45,19 @@ def test_product_fails_loudly_without_gpu():
 
     with pytest.raises(RuntimeError):
         MapAnything()
+
+
+def test_head_ranges_cover_all_views_in_order():
+    from mapanything_b200.model import head_ranges
+
+    assert head_ranges(8, 4, 4) == [(0, 4), (4, 8)]
+    assert head_ranges(8, 0, 4) == [(0, 4), (4, 8)]          # 0: the library's head_chunk
+    assert head_ranges(7, 3, 4) == [(0, 3), (3, 6), (6, 7)]  # ragged last range
+    assert head_ranges(9, (4, 2, 1), 4) == [(0, 4), (4, 6), (6, 7), (7, 8), (8, 9)]  # last size repeats
+    assert head_ranges(3, (), 2) == [(0, 2), (2, 3)]
+    assert head_ranges(0, 4, 4) == []
+    for V in (1, 5, 32, 33):
+        for chunk in (1, 4, 64, (8, 4), (3,), (0, -2)):
+            r = head_ranges(V, chunk, 4)
+            assert r[0][0] == 0 and r[-1][1] == V
+            assert all(a[1] == b[0] for a, b in zip(r, r[1:])) and all(lo < hi for lo, hi in r)
