@@ -61,3 +61,27 @@ def test_head_ranges_cover_all_views_in_order():
             r = head_ranges(V, chunk, 4)
             assert r[0][0] == 0 and r[-1][1] == V
             assert all(a[1] == b[0] for a, b in zip(r, r[1:])) and all(lo < hi for lo, hi in r)
+
+
+def test_constructor_rejects_unbuilt_trunk_configs_before_touching_the_gpu():
+    """The configs/model/info_sharing/*.yaml variants: the unbuilt ones are refused by name, the built
+    ones get as far as the device check (RuntimeError here: this container has no GPU)."""
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from mapanything_b200 import MapAnything
+
+    def cfg(**margs):
+        return {"model_type": "alternating_attention", "custom_positional_encoding": None,
+                "module_args": dict(depth=24, indices=[11, 17], **margs)}
+
+    for bad in (cfg(dim=1024, num_heads=16), cfg(use_pe_for_non_reference_views=True),
+                dict(cfg(), model_type="global_attention"), dict(cfg(), custom_positional_encoding="RoPE100")):
+        with pytest.raises(NotImplementedError):
+            MapAnything(info_sharing_config=bad)
+    with pytest.raises(NotImplementedError):
+        MapAnything(pred_head_config={"type": "dpt"})
+    for ok in (cfg(), cfg(use_entropy_scaling=True), cfg(distinguish_ref_and_non_ref_views=False),
+               cfg(distinguish_ref_and_non_ref_views=True, max_num_views_for_pe=1000,
+                   use_rand_idx_pe_for_non_reference_views=True)):   # aat_ifr_24_layers_w_view_pe.yaml
+        with pytest.raises(RuntimeError, match="CUDA device"):
+            MapAnything(info_sharing_config=ok)
