@@ -144,6 +144,7 @@ extern "C" int mab_depth_z_to_along_ray(const void* depth_z, const void* rays, l
 
 extern "C" int mab_layernorm(const float* x, int rows, int C, const float* w, const float* b,
                              float eps, void* out_bf16, float* out_f32, void* stream) {
+  MAB_ARG(x && w && b && (out_bf16 || out_f32), "null argument");
   return launch_layernorm(x, rows, C, rows > 0 ? rows : 1, rows > 0 ? rows : 1, 0, w, b, nullptr,
                           nullptr, eps, out_bf16, out_f32, nullptr, (cudaStream_t)stream);
 }
@@ -151,6 +152,7 @@ extern "C" int mab_layernorm(const float* x, int rows, int C, const float* w, co
 extern "C" int mab_gemm(const void* A, const void* B, int M, int N, int K, const float* bias,
                         const float* gamma, const float* res_f32, int act, float* out_f32,
                         void* out_bf16, void* stream) {
+  MAB_ARG(A && B && (out_f32 || out_bf16), "null argument");
   GemmEpilogue ep{};
   ep.bias = bias; ep.gamma = gamma; ep.res_f32 = res_f32; ep.out_f32 = out_f32;
   ep.out_bf16 = reinterpret_cast<bf16*>(out_bf16); ep.ldo = N; ep.act = act;
@@ -161,6 +163,11 @@ extern "C" int mab_attention(const void* q_src, int q_rows_total, const void* kv
                              int kv_rows_total, int heads, int num_seqs, int q_len, int kv_len,
                              int q_seq_stride, int kv_seq_stride, float scale, void* out, float* lse,
                              void* stream) {
+  MAB_ARG(q_src && kv_src && out, "null argument");
+  MAB_ARG(q_seq_stride >= 0 && kv_seq_stride >= 0 &&
+          (long long)(num_seqs - 1) * q_seq_stride + q_len <= q_rows_total &&
+          (long long)(num_seqs - 1) * kv_seq_stride + kv_len <= kv_rows_total,
+          "sequences reach past the end of the buffers");
   return launch_attention(q_src, q_rows_total, kv_src, kv_rows_total, heads, num_seqs, q_len, kv_len,
                           q_seq_stride, kv_seq_stride, scale, out, lse, (cudaStream_t)stream);
 }
@@ -170,12 +177,18 @@ extern "C" int mab_attention_carry(const void* q_src, int q_rows_total, const vo
                                    int q_seq_stride, int kv_seq_stride, float scale, void* out,
                                    float* carry_o, float* carry_ml, int carry_in, int carry_out,
                                    void* stream) {
+  MAB_ARG(q_src && kv_src && (out || carry_out), "null argument");
+  MAB_ARG(q_seq_stride >= 0 && kv_seq_stride >= 0 &&
+          (long long)(num_seqs - 1) * q_seq_stride + q_len <= q_rows_total &&
+          (long long)(num_seqs - 1) * kv_seq_stride + kv_len <= kv_rows_total,
+          "sequences reach past the end of the buffers");
   return launch_attention(q_src, q_rows_total, kv_src, kv_rows_total, heads, num_seqs, q_len, kv_len,
                           q_seq_stride, kv_seq_stride, scale, out, nullptr, (cudaStream_t)stream,
                           carry_o, carry_ml, carry_in, carry_out);
 }
 
 extern "C" int mab_pack_conv3_weight(const float* w, int Cout, int Cin, void* out, void* stream) {
+  MAB_ARG(w && out && Cout > 0 && Cin > 0, "bad arguments");
   const int Cpad = (Cin + 63) / 64 * 64;
   pack_conv3_kernel<<<ew_grid((long long)Cout * 9 * Cpad), 256, 0, (cudaStream_t)stream>>>(
       w, Cout, Cin, Cpad, reinterpret_cast<bf16*>(out));
@@ -186,6 +199,8 @@ extern "C" int mab_pack_conv3_weight(const float* w, int Cout, int Cin, void* ou
 extern "C" int mab_conv3x3(const void* x, int batch, int H, int W, int C, const void* w_packed,
                            int Cout, const float* bias, const void* res1, const void* res2, int act,
                            void* out_bf16, void* out_relu, void* stream) {
+  MAB_ARG(x && w_packed && (out_bf16 || out_relu), "null argument");
+  MAB_ARG(batch > 0 && H > 0 && W > 0 && C > 0 && Cout > 0 && Cout % 4 == 0, "bad conv shape");
   GemmEpilogue ep{};
   ep.bias = bias; ep.res1 = reinterpret_cast<const bf16*>(res1);
   ep.res2 = reinterpret_cast<const bf16*>(res2); ep.out_bf16 = reinterpret_cast<bf16*>(out_bf16);
@@ -196,11 +211,13 @@ extern "C" int mab_conv3x3(const void* x, int batch, int H, int W, int C, const 
 // ---- TF32 variants (fp32 operands) used by the geometric-input encoders ---------------------------
 extern "C" int mab_gemm_tf32(const float* A, const float* B, int M, int N, int K, const float* bias,
                              const float* res_f32, int act, int act_post, float* out_f32, void* stream) {
+  MAB_ARG(A && B && out_f32, "null argument");
   GemmEpilogue ep{};
   ep.bias = bias; ep.res_f32 = res_f32; ep.out_f32 = out_f32; ep.ldo = N; ep.act = act; ep.act_post = act_post;
   return launch_gemm_tf32(A, K, B, K, M, N, K, ep, (cudaStream_t)stream);
 }
 extern "C" int mab_pack_conv3_weight_f32(const float* w, int Cout, int Cin, int Cpad, float* out, void* stream) {
+  MAB_ARG(w && out && Cout > 0 && Cin > 0, "bad arguments");
   MAB_ARG(Cpad >= Cin && Cpad % 32 == 0, "Cpad must be a multiple of 32 and >= Cin");
   pack_conv3_kernel<<<ew_grid((long long)Cout * 9 * Cpad), 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, Cpad, out);
   MAB_CUDA(cudaGetLastError());
@@ -209,7 +226,9 @@ extern "C" int mab_pack_conv3_weight_f32(const float* w, int Cout, int Cin, int 
 extern "C" int mab_conv3x3_tf32(const float* x, int batch, int H, int W, int C, const float* w_packed,
                                 int Cout, const float* bias, const float* res_f32, int act, int act_post,
                                 float* out_f32, void* stream) {
-  MAB_ARG(C % 32 == 0, "C must be a multiple of 32 (pad the channels)");
+  MAB_ARG(x && w_packed && out_f32, "null argument");
+  MAB_ARG(batch > 0 && H > 0 && W > 0 && Cout > 0 && Cout % 4 == 0, "bad conv shape");
+  MAB_ARG(C > 0 && C % 32 == 0, "C must be a multiple of 32 (pad the channels)");
   GemmEpilogue ep{};
   ep.bias = bias; ep.res_f32 = res_f32; ep.out_f32 = out_f32; ep.ldo = Cout; ep.act = act; ep.act_post = act_post;
   return launch_conv3_tf32(x, batch, H, W, C, C, w_packed, Cout, ep, (cudaStream_t)stream);
@@ -217,7 +236,9 @@ extern "C" int mab_conv3x3_tf32(const float* x, int batch, int H, int W, int C, 
 
 extern "C" int mab_resize_bilinear(const void* x, int batch, int Hi, int Wi, int C, int Hv, int Wv,
                                    int Ho, int Wo, void* out, void* out_relu, void* stream) {
-  MAB_ARG(C % 8 == 0, "C must be a multiple of 8");
+  MAB_ARG(x && (out || out_relu), "null argument");
+  MAB_ARG(C > 0 && C % 8 == 0, "C must be a multiple of 8");
+  MAB_ARG(Hi > 0 && Wi > 0 && Hv >= Ho && Wv >= Wo, "resize: bad sizes");
   MAB_ARG(batch > 0 && batch <= 65535 && Ho > 0 && Ho <= 65535 && Wo > 0, "resize: bad sizes");
   const dim3 grid((Wo * (C / 8) + 255) / 256, Ho, batch);
   MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, (cudaStream_t)stream,
@@ -230,6 +251,7 @@ extern "C" int mab_resize_bilinear(const void* x, int batch, int Hi, int Wi, int
 
 extern "C" int mab_posembed_resize(const float* pos, int grid, int C, int h, int w, float* out,
                                    void* stream) {
+  MAB_ARG(pos && out && grid > 0 && C > 0 && h > 0 && w > 0, "bad arguments");
   // vision_transformer.py:223-228: scale_factor = ((h + 0.1)/M, (w + 0.1)/M); ATen then uses
   // 1/scale_factor as the source step
   if (h == grid && w == grid) {  // vision_transformer.py:214-215: same grid -> returned unchanged
@@ -361,6 +383,8 @@ extern "C" int mab_preprocess_image(const unsigned char* rgb, const mab_image_pl
                                     const float* std_, float* out, unsigned char* out_u8, void* workspace,
                                     size_t workspace_bytes, void* stream) {
   MAB_ARG(rgb && p && mean && std_ && out && workspace, "null argument");
+  MAB_ARG(p->in_w > 0 && p->in_h > 0 && p->resize_w > 0 && p->resize_h > 0 && p->out_w > 0 && p->out_h > 0 &&
+          (p->filter == 0 || p->filter == 1), "bad image plan");
   MAB_ARG(p->crop_left >= 0 && p->crop_top >= 0 && p->crop_left + p->out_w <= p->resize_w &&
           p->crop_top + p->out_h <= p->resize_h, "crop outside the resized image");
   MAB_ARG(workspace_bytes >= mab_preprocess_workspace_bytes(p), "workspace too small");
@@ -477,6 +501,8 @@ extern "C" int mab_export_points(const float* depth_z, const float* intrinsics, 
 extern "C" int mab_edge_mask(const float* pts3d, float* pts3d_cam, const unsigned char* fmask,
                              int views, int H, int W, float normal_tol_deg, float depth_rtol,
                              void* workspace, unsigned char* mask_out, void* stream) {
+  MAB_ARG(pts3d && pts3d_cam && fmask && workspace && mask_out, "null argument");
+  MAB_ARG(views > 0 && H > 0 && W > 0, "bad sizes");
   cudaStream_t st = (cudaStream_t)stream;
   const long long npix = (long long)views * H * W;
   float* normals = reinterpret_cast<float*>(workspace);
@@ -649,6 +675,11 @@ extern "C" int mab_create(const mab_config* cfg, int device, mab_handle** out) {
   MAB_ARG(cfg && out, "null argument");
   MAB_ARG(cfg->patch == 14 && cfg->enc_dim == 1024 && cfg->aat_dim == 768, "unsupported architecture");
   MAB_ARG(cfg->enc_heads * 64 == cfg->enc_dim && cfg->aat_heads * 64 == cfg->aat_dim, "head_dim must be 64");
+  MAB_ARG(cfg->enc_depth > 0 && cfg->enc_pos_grid > 0 && cfg->aat_depth > 0 && cfg->head_chunk > 0,
+          "depths, position grid and head_chunk must be positive");
+  MAB_ARG(cfg->aat_tap0 >= 0 && cfg->aat_tap0 < cfg->aat_tap1 && cfg->aat_tap1 < cfg->aat_depth,
+          "intermediate feature indices must satisfy 0 <= tap0 < tap1 < depth");
+  MAB_ARG(device >= 0, "bad device");
   MAB_CUDA(cudaSetDevice(device));
   mab_handle* h = new mab_handle();
   h->cfg = *cfg;
@@ -670,10 +701,14 @@ extern "C" int mab_set_weight(mab_handle* h, const char* ref_key, const void* pt
   MAB_ARG(h && ref_key && ptr && shape, "null argument");
   MAB_ARG(dtype == MAB_F32, "weights must be fp32");
   MAB_ARG(!h->finalized, "weights are frozen after mab_finalize_weights");
+  MAB_ARG(ndim >= 1 && ndim <= 8, "ndim must be in 1..8");
+  long long n = 1;
+  for (int i = 0; i < ndim; ++i) {
+    MAB_ARG(shape[i] > 0 && shape[i] < (1LL << 31), "every dimension must be positive");
+    n *= shape[i];
+  }
   MAB_CUDA(cudaSetDevice(h->device));
   const std::string key = canonical_key(ref_key);
-  long long n = 1;
-  for (int i = 0; i < ndim; ++i) n *= shape[i];
   RawTensor& t = h->raw[key];
   if (t.p && t.numel != n) { cudaFree(t.p); t.p = nullptr; }
   if (!t.p) MAB_CUDA(cudaMalloc(&t.p, (size_t)n * sizeof(float)));
@@ -788,6 +823,7 @@ int pack_convT(mab_handle* h, const std::string& wkey, const std::string& bkey, 
 
 extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
   MAB_ARG(h, "null handle");
+  if (h->finalized) return 0;  // the weights are frozen: nothing new to pack
   MAB_CUDA(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   const mab_config& c = h->cfg;
@@ -1122,7 +1158,8 @@ int encode_geometric_inputs(Ctx& c, const mab_inputs* in) {
 extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_total, void* workspace,
                                 size_t workspace_bytes, int has_scale_token, void* stream) {
   MAB_ARG(h && in && workspace && h->finalized, "handle not ready");
-  MAB_ARG(in->views > 0 && in->H % 14 == 0 && in->W % 14 == 0 && in->images, "bad inputs");
+  MAB_ARG(in->views > 0 && in->H > 0 && in->W > 0 && in->H % 14 == 0 && in->W % 14 == 0 && in->images,
+          "bad inputs");
   MAB_CUDA(cudaSetDevice(h->device));
   const mab_config& cf = h->cfg;
   Ctx c{h, (cudaStream_t)stream};
@@ -1189,6 +1226,7 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
 extern "C" int mab_stage_aat_qkv(mab_handle* h, int layer, void** qkv_out, int* rows_out,
                                  void* stream) {
   MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");
+  MAB_ARG(layer >= 0 && layer < h->cfg.aat_depth, "layer out of range");
   Ctx c{h, (cudaStream_t)stream};
   Plan& p = h->plan;
   const long long rows = (layer % 2 == 0) ? p.L : (long long)p.V * p.T;  // odd: scale token skips
@@ -1216,6 +1254,7 @@ static float aat_softmax_scale(const mab_config& cf, long long n_tokens) {
 extern "C" int mab_stage_aat_attend(mab_handle* h, int layer, const void* kv, int kv_rows, int flags,
                                     void* stream) {
   MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");
+  MAB_ARG(layer >= 0 && layer < h->cfg.aat_depth, "layer out of range");
   const mab_config& cf = h->cfg;
   Ctx c{h, (cudaStream_t)stream};
   Plan& p = h->plan;
@@ -1254,6 +1293,7 @@ extern "C" int mab_stage_aat_export_kv(mab_handle* h, void* dst, void* stream) {
 extern "C" int mab_stage_aat_attend_kv(mab_handle* h, int layer, const void* kv, int kv_rows, int flags,
                                        void* stream) {
   MAB_ARG(h && h->plan.V > 0 && kv && kv_rows > 0, "mab_stage_encode must run first");
+  MAB_ARG(layer >= 0 && layer < h->cfg.aat_depth, "layer out of range");
   MAB_ARG(layer % 2 == 0, "only the global (even) layers attend across ranks");
   const mab_config& cf = h->cfg;
   Plan& p = h->plan;
@@ -1267,6 +1307,7 @@ extern "C" int mab_stage_aat_attend_kv(mab_handle* h, int layer, const void* kv,
 // proj + residual, LN2, MLP + residual of block `layer`, intermediate taps and the final norm
 extern "C" int mab_stage_aat_finish(mab_handle* h, int layer, void* stream) {
   MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");
+  MAB_ARG(layer >= 0 && layer < h->cfg.aat_depth, "layer out of range");
   const mab_config& cf = h->cfg;
   Ctx c{h, (cudaStream_t)stream};
   Plan& p = h->plan;
@@ -1340,11 +1381,17 @@ extern "C" int mab_stage_scale_head(mab_handle* h, float* metric_scale_out, void
 namespace {
 int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, const float* metric_scale_in,
                       int view_lo, int view_hi, bool with_scale, void* stream);
+// every array of mab_outputs except logits6 is written by the heads
+bool outputs_complete(const mab_outputs* o) {
+  return o->pts3d && o->pts3d_cam && o->ray_directions && o->depth_along_ray && o->conf && o->mask_logits &&
+         o->non_ambiguous_mask && o->pose && o->metric_scale;
+}
 }
 
 extern "C" int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out,
                                const float* metric_scale_in, void* stream) {
   MAB_ARG(h && in && out && h->plan.V > 0, "mab_stage_encode must run first");
+  MAB_ARG(outputs_complete(out), "only mab_outputs.logits6 may be NULL");
   return stage_heads_range(h, in, out, metric_scale_in, 0, h->plan.V, true, stream);
 }
 
@@ -1355,6 +1402,7 @@ extern "C" int mab_stage_heads_range(mab_handle* h, const mab_inputs* in, mab_ou
                                      int view_hi, void* stream) {
   MAB_ARG(h && in && out && h->plan.V > 0, "mab_stage_encode must run first");
   MAB_ARG(view_lo >= 0 && view_lo < view_hi && view_hi <= h->plan.V, "bad view range");
+  MAB_ARG(outputs_complete(out), "only mab_outputs.logits6 may be NULL");
   return stage_heads_range(h, in, out, out->metric_scale, view_lo, view_hi, false, stream);
 }
 
@@ -1500,9 +1548,13 @@ extern "C" int mab_forward(mab_handle* h, const mab_inputs* in, mab_outputs* out
 extern "C" int mab_postprocess(mab_handle* h, const mab_inputs* in, mab_outputs* raw,
                                mab_post_outputs* post, const mab_post_options* opt, void* workspace,
                                size_t workspace_bytes, void* stream) {
-  MAB_ARG(h && in && raw && post && opt, "null argument");
+  MAB_ARG(h && in && raw && post && opt && workspace, "null argument");
   cudaStream_t st = (cudaStream_t)stream;
   const int V = in->views, H = in->H, W = in->W;
+  MAB_ARG(V > 0 && H > 0 && W > 0 && in->images, "bad inputs");
+  MAB_ARG(outputs_complete(raw), "only mab_outputs.logits6 may be NULL");
+  MAB_ARG(post->img_no_norm && post->depth_z && post->intrinsics && post->camera_poses && post->cam_trans &&
+          post->cam_quats && post->mask, "every mab_post_outputs array is written");
   const long long npix = (long long)V * H * W;
   MAB_ARG(workspace_bytes >= (size_t)npix * 18 + (size_t)V * 8 + 512, "post-process workspace too small");
   const unsigned char* fmask = raw->non_ambiguous_mask;

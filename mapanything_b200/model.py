@@ -81,6 +81,38 @@ def head_ranges(V, stream_chunk, default_chunk):
     return out
 
 
+def check_state_dict(state_dict, aat_depth=24, ref_view_pe=True):
+    """torch.nn.Module.load_state_dict's key / shape bookkeeping for the reference key space
+    (state_dict_manifest.json: the reference's own `state_dict()` of the default configuration, aliases
+    of shared modules included).  Returns (missing, unexpected, size_mismatch_messages).  A key and its
+    aliases (dense_head.0.* / dpt_feature_head.*) count as one tensor; the
+    info-sharing blocks of a deeper or shallower trunk take the shapes of block 0; a checkpoint without
+    the reference-view PE has no info_sharing.view_pos_table buffer (aat.py:160-172)."""
+    import re
+
+    from .synthetic import canonical_key, load_manifest
+
+    block = re.compile(r"^info_sharing\.self_attention_blocks\.(\d+)\.(.*)$")
+    expected = {}
+    for key, shape in load_manifest().items():
+        m = block.match(key)
+        if m:
+            if int(m.group(1)) == 0:
+                for i in range(aat_depth):
+                    expected[f"info_sharing.self_attention_blocks.{i}.{m.group(2)}"] = tuple(shape)
+            continue
+        if key == "info_sharing.view_pos_table" and not ref_view_pe:
+            continue
+        expected[key] = tuple(shape)
+    unexpected = [k for k in state_dict if k not in expected]
+    mismatch = [f"size mismatch for {k}: copying a param with shape {tuple(v.shape)} from checkpoint, "
+                f"the shape in current model is {expected[k]}."
+                for k, v in state_dict.items() if k in expected and tuple(v.shape) != expected[k]]
+    have = {canonical_key(k) for k in state_dict if k in expected}
+    missing = [k for k in expected if canonical_key(k) == k and k not in have]
+    return missing, unexpected, mismatch
+
+
 class MapAnything(torch.nn.Module):
     """Drop-in for the reference class on the inference path (no trainable state on the torch side:
     the weights live in packed device buffers owned by libmab200)."""
@@ -142,6 +174,9 @@ class MapAnything(torch.nn.Module):
             raise NotImplementedError("view positional encodings of non-reference views are not built")
         if int(margs.get("dim", 768)) != 768 or int(margs.get("num_heads", 12)) != 12:
             raise NotImplementedError("only the dim-768 / 12-head info-sharing transformer is built")
+        if len(margs.get("indices", (11, 17))) != 2:
+            raise NotImplementedError("the dense head takes two intermediate info-sharing features "
+                                      "(the 48-layer configs return three)")
         pc = self.pred_head_config
         if pc and pc.get("type", "dpt+pose") != "dpt+pose":
             raise NotImplementedError("only the dpt+pose head is built")
@@ -181,8 +216,19 @@ class MapAnything(torch.nn.Module):
         """Accepts the reference key space unchanged, aliases included."""
         if self._finalized:
             raise RuntimeError("weights are already finalized for this instance")
+        missing, unexpected, mismatch = check_state_dict(state_dict, self._cfg.aat_depth,
+                                                         bool(self._cfg.aat_ref_view_pe))
+        errors = list(mismatch)  # a size mismatch is an error with strict=False as well (torch)
+        if strict and unexpected:
+            errors.insert(0, "Unexpected key(s) in state_dict: " + ", ".join(f'"{k}"' for k in unexpected) + ". ")
+        if missing:  # every weight is needed to run: no partially initialised model on this path
+            errors.insert(0, "Missing key(s) in state_dict: " + ", ".join(f'"{k}"' for k in missing) + ". ")
+        if errors:
+            raise RuntimeError("Error(s) in loading state_dict for MapAnything:\n\t" + "\n\t".join(errors))
         with torch.cuda.device(self._device):
             for key, t in state_dict.items():
+                if key in unexpected:
+                    continue
                 t = t.detach().to(dtype=torch.float32).contiguous()
                 shape = (C.c_int64 * max(t.dim(), 1))(*(list(t.shape) or [1]))
                 _lib.check(self._lib.mab_set_weight(self._handle, key.encode(), t.data_ptr(), 0,
@@ -190,7 +236,7 @@ class MapAnything(torch.nn.Module):
             _lib.check(self._lib.mab_finalize_weights(self._handle, self._stream_ptr()),
                        "mab_finalize_weights")
         self._finalized = True
-        return torch.nn.modules.module._IncompatibleKeys([], [])
+        return torch.nn.modules.module._IncompatibleKeys([], unexpected)
 
     def __del__(self):
         try:

@@ -75,6 +75,7 @@ def test_constructor_rejects_unbuilt_trunk_configs_before_touching_the_gpu():
                 "module_args": dict(depth=24, indices=[11, 17], **margs)}
 
     for bad in (cfg(dim=1024, num_heads=16), cfg(use_pe_for_non_reference_views=True),
+                dict(cfg(), module_args=dict(depth=48, indices=[11, 23, 35])),
                 dict(cfg(), model_type="global_attention"), dict(cfg(), custom_positional_encoding="RoPE100")):
         with pytest.raises(NotImplementedError):
             MapAnything(info_sharing_config=bad)
@@ -85,3 +86,85 @@ def test_constructor_rejects_unbuilt_trunk_configs_before_touching_the_gpu():
                    use_rand_idx_pe_for_non_reference_views=True)):   # aat_ifr_24_layers_w_view_pe.yaml
         with pytest.raises(RuntimeError, match="CUDA device"):
             MapAnything(info_sharing_config=ok)
+
+
+def test_entry_points_refuse_bad_arguments_before_any_cuda_call():
+    """Argument errors come back as status -1 with a message from mab_last_error, before the first
+    CUDA call (so this runs without a GPU and computes nothing)."""
+    import ctypes as C
+
+    from mapanything_b200 import _lib
+
+    lib = _lib.load()
+    one = C.c_void_p(16)  # a non-null, 16-byte aligned address that is never dereferenced
+    calls = {
+        "mab_gemm": (None, one, 8, 8, 8, None, None, None, 0, None, one, None),
+        "mab_gemm_tf32": (one, one, 8, 8, 8, None, None, 0, 0, None, None),
+        "mab_layernorm": (None, 4, 768, one, one, 1e-6, one, None, None),
+        "mab_attention": (one, 10, one, 10, 12, 2, 8, 8, 8, 8, 0.125, one, None, None),  # 2 x 8 rows > 10
+        "mab_attention_carry": (one, 8, None, 8, 12, 1, 8, 8, 0, 0, 0.125, one, None, None, 0, 0, None),
+        "mab_conv3x3": (one, 1, 8, 8, 64, one, 64, None, None, None, 0, None, None, None),
+        "mab_conv3x3_tf32": (one, 1, 8, 8, 48, one, 64, None, None, 0, 0, one, None),
+        "mab_pack_conv3_weight": (None, 64, 64, one, None),
+        "mab_pack_conv3_weight_f32": (one, 64, 40, 32, one, None),
+        "mab_resize_bilinear": (one, 1, 8, 8, 12, 16, 16, 16, 16, one, None, None),
+        "mab_posembed_resize": (None, 37, 1024, 28, 37, one, None),
+        "mab_rope2d": (one, 7, 4, 2, 64, 128, one, 100.0, 1.0, None),
+        "mab_rays_from_intrinsics": (one, 0, 8, 8, one, None),
+        "mab_normalize_rays": (one, 0, one, None),
+        "mab_recover_intrinsics": (None, 1, 8, 8, one, None),
+        "mab_resize_nearest_crop": (None, 8, 8, 4, 4, 0, 0, 4, 4, one, None),
+        "mab_edge_mask": (None, one, one, 1, 8, 8, 5.0, 0.03, one, one, None),
+    }
+    for name, args in calls.items():
+        st = getattr(lib, name)(*args)
+        msg = lib.mab_last_error().decode()
+        assert st == -1 and msg.startswith("argument error"), (name, st, msg)
+    with pytest.raises(RuntimeError, match="argument error"):
+        _lib.check(lib.mab_normalize_rays(one, 0, one, None), "mab_normalize_rays")
+
+
+def test_create_refuses_inconsistent_configs():
+    import ctypes as C
+
+    from mapanything_b200 import _lib
+    from mapanything_b200.model import default_config
+
+    lib = _lib.load()
+    for change in (dict(aat_tap1=24), dict(aat_tap0=17), dict(aat_dim=1024), dict(enc_heads=12),
+                   dict(head_chunk=0), dict(patch=16), dict(enc_depth=0)):
+        cfg = _lib.MabConfig(**dict(default_config(), **change))
+        handle = C.c_void_p()
+        assert lib.mab_create(C.byref(cfg), 0, C.byref(handle)) == -1, change
+        assert lib.mab_last_error().decode().startswith("argument error") and not handle.value
+
+
+def test_state_dict_bookkeeping_mirrors_torch_strict_loading():
+    from mapanything_b200 import synthetic
+    from mapanything_b200.model import check_state_dict
+
+    sd = synthetic.synthetic_state_dict()
+    assert check_state_dict(sd) == ([], [], [])
+    # either name of an aliased tensor satisfies the model (dense_head.0.* == dpt_feature_head.*)
+    canonical = {k: v for k, v in sd.items() if synthetic.canonical_key(k) == k}
+    aliases = {k: v for k, v in sd.items() if synthetic.canonical_key(k) != k or not k.startswith("dpt_")}
+    assert len(canonical) < len(sd) and check_state_dict(canonical) == ([], [], [])
+    assert check_state_dict(aliases) == ([], [], [])
+
+    bad = dict(sd)
+    del bad["encoder.model.blocks.3.attn.qkv.weight"]
+    bad["encoder.model.blocks.3.attn.qkv.wieght"] = sd["encoder.model.blocks.3.attn.qkv.weight"]
+    bad["pose_head.fc_rot.weight"] = torch.zeros(3, 784)
+    missing, unexpected, mismatch = check_state_dict(bad)
+    assert missing == ["encoder.model.blocks.3.attn.qkv.weight"]
+    assert unexpected == ["encoder.model.blocks.3.attn.qkv.wieght"]
+    assert len(mismatch) == 1 and "pose_head.fc_rot.weight" in mismatch[0] and "(4, 784)" in mismatch[0]
+
+    # aat_ifr_24_layers_no_ref_view.yaml: such a checkpoint has no view_pos_table buffer
+    noref = {k: v for k, v in sd.items() if k != "info_sharing.view_pos_table"}
+    assert check_state_dict(noref, ref_view_pe=False) == ([], [], [])
+    assert check_state_dict(noref)[0] == ["info_sharing.view_pos_table"]
+    assert check_state_dict(sd, ref_view_pe=False)[1] == ["info_sharing.view_pos_table"]
+    # a shallower trunk: the extra blocks of a 24-layer checkpoint are unexpected, none is missing
+    missing, unexpected, _ = check_state_dict(sd, aat_depth=20)
+    assert not missing and unexpected and all(k.startswith("info_sharing.self_attention_blocks.2") for k in unexpected)
