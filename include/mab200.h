@@ -34,15 +34,20 @@ typedef struct {
   int enc_depth;      /* 24 */
   int enc_heads;      /* 16 */
   int enc_pos_grid;   /* 37 (pos_embed is 1 + 37*37 rows) */
-  int aat_dim;        /* 768 */
+  int aat_dim;        /* 768 (1024 in the 48-layer configs) */
   int aat_depth;      /* 24 */
-  int aat_heads;      /* 12 */
+  int aat_heads;      /* 12 = aat_dim / 64 */
   int aat_tap0;       /* 11 */
   int aat_tap1;       /* 17 */
   int head_chunk;     /* views per dense-head pass (workspace knob; outputs do not depend on it) */
   /* info_sharing module_args variants (configs/model/info_sharing/aat_ifr_24_layers_*.yaml) */
   int aat_ref_view_pe;      /* 1: distinguish_ref_and_non_ref_views (production); 0: *_no_ref_view.yaml */
   int aat_entropy_scaling;  /* 1: use_entropy_scaling (*_escaling.yaml): q *= sqrt(1.4 log N / log 444) */
+  /* aat_ifr_48_layers*.yaml: aat_dim 1024 / aat_heads 16 / aat_depth 48 (no proj_embed at that width,
+   * alternating_attention_transformer.py:121-124) and a third intermediate feature, indices [11,23,35]:
+   * the dense head then takes [tap0, tap1, tap2, final] instead of [encoder, tap0, tap1, final]
+   * (model.py:324-327,1724-1768).  <= 0: two intermediate features. */
+  int aat_tap2;
 } mab_config;
 
 /* One scene, `views` views of H x W pixels held by this rank. */
@@ -171,7 +176,7 @@ int mab_prof_query(int cat, long long* launches, double* ms, double* flops, doub
 
 /* Diagnostic hook for the parity tests: device pointer, element count and dtype (MAB_F32 /
  * MAB_BF16) of a named intermediate of the last forward ("enc_tokens", "fused", "aat_stream",
- * "tap0", "tap1", "final", "scale_token", "pose_raw", "pose_pool", "feat8"). */
+ * "tap0", "tap1", "tap2", "final", "scale_token", "pose_raw", "pose_pool", "feat8"). */
 int mab_debug_buffer(mab_handle* h, const char* name, void** ptr, long long* numel, int* dtype);
 
 /* ---- per-kernel entry points (parity tests call these through the same ABI) ---- */

@@ -225,12 +225,13 @@ __global__ void geo_prepare_kernel(int views, const float* __restrict__ depth_no
 }
 
 // fused = LayerNorm(enc[row] + dense[row] + vec[view(row)])  -> bf16   (model.py:1423-1431)
-// one warp per row, C = 128 * VPL
+// one warp per row, C = 128 * VPL.  out_f32 (optional): the same rows in fp32, the residual stream of
+// an info-sharing trunk without proj_embed (width 1024, aat.py:121-124)
 template <int VPL>
 __global__ void fuse_norm_kernel(const float* __restrict__ enc, const float* __restrict__ dense,
                                  const float* __restrict__ vec, int rows, int T,
                                  const float* __restrict__ w, const float* __restrict__ b, float eps,
-                                 __nv_bfloat16* __restrict__ out) {
+                                 __nv_bfloat16* __restrict__ out, float* __restrict__ out_f32) {
   constexpr int C = 128 * VPL;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= rows) return;
@@ -258,9 +259,11 @@ __global__ void fuse_norm_kernel(const float* __restrict__ enc, const float* __r
   for (int i = 0; i < VPL; ++i) {
     const float4 g = __ldg(reinterpret_cast<const float4*>(w) + lane + 32 * i);
     const float4 h = __ldg(reinterpret_cast<const float4*>(b) + lane + 32 * i);
+    const float4 y = make_float4((v[i].x - mean) * rstd * g.x + h.x, (v[i].y - mean) * rstd * g.y + h.y,
+                                 (v[i].z - mean) * rstd * g.z + h.z, (v[i].w - mean) * rstd * g.w + h.w);
     reinterpret_cast<uint2*>(out + (long long)warp * C)[lane + 32 * i] =
-        make_uint2(pack_bf16((v[i].x - mean) * rstd * g.x + h.x, (v[i].y - mean) * rstd * g.y + h.y),
-                   pack_bf16((v[i].z - mean) * rstd * g.z + h.z, (v[i].w - mean) * rstd * g.w + h.w));
+        make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
+    if (out_f32) reinterpret_cast<float4*>(out_f32 + (long long)warp * C)[lane + 32 * i] = y;
   }
 }
 

@@ -569,7 +569,7 @@ struct Plan {  // every workspace pointer of one forward
   bf16* im2col; float* patch; float* pos; float* xs; bf16* ln; bf16* qkv; bf16* att; bf16* hid;
   float* enc_out; bf16* fused; float* geo_sum; float* geo_vec; float* geo_small;
   // info sharing
-  float* ys; bf16* tap[2]; bf16* fin; float* scale_tok; float* carry_o; float* carry_ml;
+  float* ys; bf16* tap[3]; bf16* fin; float* scale_tok; float* carry_o; float* carry_ml;
   // heads (small)
   float* scale_tmp; float* pose_pool; float* pose_tmp; float* pose_raw; bf16* ph_in; bf16* ph_a; bf16* ph_b; bf16* ph_c; bf16* ph_d;
   // dense head chunk buffers
@@ -635,6 +635,7 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
   p.ys = b.take<float>((VT + 1) * A);
   p.tap[0] = b.take<bf16>(VT * A);
   p.tap[1] = b.take<bf16>(VT * A);
+  p.tap[2] = c.aat_tap2 > 0 ? b.take<bf16>(VT * A) : nullptr;  // third intermediate feature (48-layer configs)
   p.fin = b.take<bf16>(VT * A);
   p.scale_tok = b.take<float>(A);
   p.carry_o = Vtot > V ? b.take<float>((VT + 1) * A) : nullptr;   // ring attention state
@@ -673,12 +674,15 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
 
 extern "C" int mab_create(const mab_config* cfg, int device, mab_handle** out) {
   MAB_ARG(cfg && out, "null argument");
-  MAB_ARG(cfg->patch == 14 && cfg->enc_dim == 1024 && cfg->aat_dim == 768, "unsupported architecture");
+  MAB_ARG(cfg->patch == 14 && cfg->enc_dim == 1024 && (cfg->aat_dim == 768 || cfg->aat_dim == 1024),
+          "unsupported architecture");
   MAB_ARG(cfg->enc_heads * 64 == cfg->enc_dim && cfg->aat_heads * 64 == cfg->aat_dim, "head_dim must be 64");
   MAB_ARG(cfg->enc_depth > 0 && cfg->enc_pos_grid > 0 && cfg->aat_depth > 0 && cfg->head_chunk > 0,
           "depths, position grid and head_chunk must be positive");
   MAB_ARG(cfg->aat_tap0 >= 0 && cfg->aat_tap0 < cfg->aat_tap1 && cfg->aat_tap1 < cfg->aat_depth,
           "intermediate feature indices must satisfy 0 <= tap0 < tap1 < depth");
+  MAB_ARG(cfg->aat_tap2 <= 0 || (cfg->aat_tap1 < cfg->aat_tap2 && cfg->aat_tap2 < cfg->aat_depth),
+          "a third intermediate feature index must satisfy tap1 < tap2 < depth");
   MAB_ARG(device >= 0, "bad device");
   MAB_CUDA(cudaSetDevice(device));
   mab_handle* h = new mab_handle();
@@ -833,7 +837,8 @@ extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
     for (const char* s : {".attn.qkv.weight", ".attn.proj.weight", ".mlp.fc1.weight", ".mlp.fc2.weight"})
       MAB_TRY(pack_linear(h, p + s, 0, st));
   }
-  MAB_TRY(pack_linear(h, "info_sharing.proj_embed.weight", 0, st));
+  // aat.py:121-124: nn.Identity when the trunk is as wide as the encoder
+  if (c.aat_dim != c.enc_dim) MAB_TRY(pack_linear(h, "info_sharing.proj_embed.weight", 0, st));
   for (int i = 0; i < c.aat_depth; ++i) {
     const std::string p = "info_sharing.self_attention_blocks." + std::to_string(i);
     for (const char* s : {".attn.qkv.weight", ".attn.proj.weight", ".mlp.fc1.weight", ".mlp.fc2.weight"})
@@ -917,6 +922,7 @@ extern "C" int mab_debug_buffer(mab_handle* h, const char* name, void** ptr, lon
   else if (n == "aat_stream") { *ptr = p.ys; *numel = p.L * A; *dtype = MAB_F32; }
   else if (n == "tap0") { *ptr = p.tap[0]; *numel = VT * A; *dtype = MAB_BF16; }
   else if (n == "tap1") { *ptr = p.tap[1]; *numel = VT * A; *dtype = MAB_BF16; }
+  else if (n == "tap2" && p.tap[2]) { *ptr = p.tap[2]; *numel = VT * A; *dtype = MAB_BF16; }
   else if (n == "final") { *ptr = p.fin; *numel = VT * A; *dtype = MAB_BF16; }
   else if (n == "scale_token") { *ptr = p.scale_tok; *numel = A; *dtype = MAB_F32; }
   else if (n == "pose_raw") { *ptr = p.pose_raw; *numel = (long long)p.V * 7; *dtype = MAB_F32; }
@@ -1147,7 +1153,8 @@ int encode_geometric_inputs(Ctx& c, const mab_inputs* in) {
   MAB_LAUNCH(CAT_LAYERNORM, 0.0, (double)VT * D * 6.0, c.st,
              fuse_norm_kernel<8><<<(int)((VT + 7) / 8), 256, 0, c.st>>>(
                  p.enc_out, first_dense ? nullptr : p.geo_sum, first_vec ? nullptr : p.geo_vec, (int)VT, T,
-                 h->F("fusion_norm_layer.weight"), h->F("fusion_norm_layer.bias"), 1e-6f, p.fused));
+                 h->F("fusion_norm_layer.weight"), h->F("fusion_norm_layer.bias"), 1e-6f, p.fused,
+                 c.h->cfg.aat_dim == D ? p.ys : nullptr));
   MAB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -1172,6 +1179,7 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
   const int V = p.V, T = p.T, D = cf.enc_dim;
   const long long VT = (long long)V * T;
   const bool multimodal = in->ray_dirs || in->depth_along_ray || in->cam_quats;
+  const bool identity_embed = cf.aat_dim == D;  // no proj_embed: the fused tokens ARE the residual stream
   if (multimodal && !h->P32("ray_dirs_encoder.conv_in.weight"))
     return fail(-4, "geometric inputs given but the checkpoint has no geometric encoders");
 
@@ -1199,21 +1207,30 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
     // (image-only: the geometric features are exactly zero, model.py:931-968 / SURVEY 8a a6)
     MAB_TRY(launch_layernorm(p.xs, (int)VT, D, T, T + 1, 1, h->F("encoder.model.norm.weight"),
                              h->F("encoder.model.norm.bias"), h->F("fusion_norm_layer.weight"),
-                             h->F("fusion_norm_layer.bias"), 1e-6f, p.fused, nullptr, nullptr, c.st));
+                             h->F("fusion_norm_layer.bias"), 1e-6f, p.fused, identity_embed ? p.ys : nullptr,
+                             nullptr, c.st));
   } else {
     MAB_TRY(launch_layernorm(p.xs, (int)VT, D, T, T + 1, 1, h->F("encoder.model.norm.weight"),
                              h->F("encoder.model.norm.bias"), nullptr, nullptr, 1e-6f, nullptr, p.enc_out,
                              nullptr, c.st));
     MAB_TRY(encode_geometric_inputs(c, in));
   }
-  if (p.has_scale) {
-    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
-               f32_to_bf16_kernel<<<4, 256, 0, c.st>>>(h->F("scale_token"), p.fused + VT * D, D));
-    MAB_CUDA(cudaGetLastError());
+  if (identity_embed) {
+    // the fp32 fused tokens were written straight into the stream; the scale token joins them as is
+    if (p.has_scale)
+      MAB_CUDA(cudaMemcpyAsync(p.ys + VT * D, h->F("scale_token"), (size_t)D * sizeof(float),
+                               cudaMemcpyDeviceToDevice, c.st));
+  } else {
+    if (p.has_scale) {
+      MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+                 f32_to_bf16_kernel<<<4, 256, 0, c.st>>>(h->F("scale_token"), p.fused + VT * D, D));
+      MAB_CUDA(cudaGetLastError());
+    }
+    // proj_embed (aat.py:121-124,600)
+    MAB_TRY(c.linear(p.fused, (int)p.L, D, D, "info_sharing.proj_embed.weight", cf.aat_dim,
+                     h->F("info_sharing.proj_embed.bias"), ACT_NONE, nullptr, nullptr, p.ys, nullptr));
   }
-  // proj_embed (aat.py:121-124,600) + reference-view PE on view 0's tokens (aat.py:618-626)
-  MAB_TRY(c.linear(p.fused, (int)p.L, D, D, "info_sharing.proj_embed.weight", cf.aat_dim,
-                   h->F("info_sharing.proj_embed.bias"), ACT_NONE, nullptr, nullptr, p.ys, nullptr));
+  // reference-view PE on view 0's tokens (aat.py:618-626)
   if (p.has_ref && cf.aat_ref_view_pe) {  // distinguish_ref_and_non_ref_views (aat.py:618-626)
     MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
                add_row_vector_kernel<<<ew_grid((long long)T * cf.aat_dim), 256, 0, c.st>>>(
@@ -1322,6 +1339,7 @@ extern "C" int mab_stage_aat_finish(mab_handle* h, int layer, void* stream) {
   bf16* dst = nullptr;
   if (layer == cf.aat_tap0) dst = p.tap[0];
   else if (layer == cf.aat_tap1) dst = p.tap[1];
+  else if (cf.aat_tap2 > 0 && layer == cf.aat_tap2) dst = p.tap[2];
   if (dst)
     MAB_TRY(launch_layernorm(p.ys, (int)VT, A, (int)VT, (int)VT, 0, nw, nb, nullptr, nullptr, 1e-6f,
                              dst, nullptr, nullptr, c.st));
@@ -1434,9 +1452,13 @@ int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, con
   for (int v0 = view_lo; v0 < view_hi; v0 += p.vc) {
     const int vc = (view_hi - v0 < p.vc) ? view_hi - v0 : p.vc;
     const int M = vc * T;
-    const bf16* f0 = p.fused + (long long)v0 * T * cf.enc_dim;
-    const bf16* f1 = p.tap[0] + (long long)v0 * T * A;
-    const bf16* f2 = p.tap[1] + (long long)v0 * T * A;
+    // model.py:1724-1768: [encoder features, 2 intermediate, final] or, with three intermediate
+    // features (48-layer configs), [3 intermediate, final] and no encoder features
+    const bool three = cf.aat_tap2 > 0;
+    const int K0 = three ? A : cf.enc_dim;
+    const bf16* f0 = three ? p.tap[0] + (long long)v0 * T * A : p.fused + (long long)v0 * T * cf.enc_dim;
+    const bf16* f1 = p.tap[three ? 1 : 0] + (long long)v0 * T * A;
+    const bf16* f2 = p.tap[three ? 2 : 1] + (long long)v0 * T * A;
     const bf16* f3 = p.fin + (long long)v0 * T * A;
     // ---- pose head (pose_head.py:115-159, adaptors.py:714-732) in bf16x3 (~fp32) arithmetic:
     // final norm of this chunk's tokens as a split value, 7 token-wise GEMMs, mean over tokens
@@ -1472,7 +1494,7 @@ int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, con
       MAB_CUDA(cudaGetLastError());
     }
     // layer 0: 1x1 (1024->96) -> convT 4x4/s4 -> 3x3 (96->256, no bias)           dpt.py:107-128
-    MAB_TRY(c.linear(f0, M, cf.enc_dim, cf.enc_dim, ip + "0.0.0.weight", 96, h->F(ip + "0.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
+    MAB_TRY(c.linear(f0, M, K0, K0, ip + "0.0.0.weight", 96, h->F(ip + "0.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
     MAB_TRY(c.linear(p.d_a, M, 96, 96, ip + "0.0.1.weight", 16 * 96, h->extra[ip + "0.0.1.bias.tiled"], ACT_NONE, nullptr, nullptr, nullptr, p.d_s));
     MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
                pixel_shuffle_kernel<<<ew_grid((long long)M * 16 * 12), 256, 0, c.st>>>(p.d_s, vc, hh, ww, 4, 96, p.d_u));

@@ -62,7 +62,7 @@ def default_config():
     """Architecture of the production model (configs/model/mapanything.yaml)."""
     return dict(patch=14, enc_dim=1024, enc_depth=24, enc_heads=16, enc_pos_grid=37, aat_dim=768,
                 aat_depth=24, aat_heads=12, aat_tap0=11, aat_tap1=17, head_chunk=8,
-                aat_ref_view_pe=1, aat_entropy_scaling=0)
+                aat_ref_view_pe=1, aat_entropy_scaling=0, aat_tap2=0)
 
 
 def head_ranges(V, stream_chunk, default_chunk):
@@ -81,29 +81,16 @@ def head_ranges(V, stream_chunk, default_chunk):
     return out
 
 
-def check_state_dict(state_dict, aat_depth=24, ref_view_pe=True):
+def check_state_dict(state_dict, aat_depth=24, ref_view_pe=True, aat_dim=768):
     """torch.nn.Module.load_state_dict's key / shape bookkeeping for the reference key space
-    (state_dict_manifest.json: the reference's own `state_dict()` of the default configuration, aliases
-    of shared modules included).  Returns (missing, unexpected, size_mismatch_messages).  A key and its
-    aliases (dense_head.0.* / dpt_feature_head.*) count as one tensor; the
-    info-sharing blocks of a deeper or shallower trunk take the shapes of block 0; a checkpoint without
-    the reference-view PE has no info_sharing.view_pos_table buffer (aat.py:160-172)."""
-    import re
+    (synthetic.manifest_for: the reference's own `state_dict()` of the default configuration, aliases
+    of shared modules included, re-shaped for the trunk's width and depth).  Returns (missing,
+    unexpected, size_mismatch_messages).  A key and its aliases (dense_head.0.* / dpt_feature_head.*,
+    SURVEY.md Appendix B) count as one tensor; a checkpoint without the reference-view PE has no
+    info_sharing.view_pos_table buffer (aat.py:160-172)."""
+    from .synthetic import canonical_key, manifest_for
 
-    from .synthetic import canonical_key, load_manifest
-
-    block = re.compile(r"^info_sharing\.self_attention_blocks\.(\d+)\.(.*)$")
-    expected = {}
-    for key, shape in load_manifest().items():
-        m = block.match(key)
-        if m:
-            if int(m.group(1)) == 0:
-                for i in range(aat_depth):
-                    expected[f"info_sharing.self_attention_blocks.{i}.{m.group(2)}"] = tuple(shape)
-            continue
-        if key == "info_sharing.view_pos_table" and not ref_view_pe:
-            continue
-        expected[key] = tuple(shape)
+    expected = {k: tuple(v) for k, v in manifest_for(aat_dim, aat_depth, ref_view_pe).items()}
     unexpected = [k for k in state_dict if k not in expected]
     mismatch = [f"size mismatch for {k}: copying a param with shape {tuple(v.shape)} from checkpoint, "
                 f"the shape in current model is {expected[k]}."
@@ -140,8 +127,12 @@ class MapAnything(torch.nn.Module):
         margs = self.info_sharing_config.get("module_args", {})
         if "depth" in margs:
             cfg["aat_depth"] = int(margs["depth"])
-        if "indices" in margs:
-            cfg["aat_tap0"], cfg["aat_tap1"] = [int(i) for i in margs["indices"]]
+        if "indices" in margs:  # two or three intermediate features (model.py:324-327)
+            taps = [int(i) for i in margs["indices"]]
+            cfg["aat_tap0"], cfg["aat_tap1"], cfg["aat_tap2"] = (taps + [0])[:3]
+        # aat_ifr_48_layers*.yaml: width 1024, 16 heads
+        cfg["aat_dim"] = int(margs.get("dim", 768))
+        cfg["aat_heads"] = int(margs.get("num_heads", cfg["aat_dim"] // 64))
         # info_sharing variants: aat_ifr_24_layers_no_ref_view.yaml / aat_ifr_24_layers_escaling.yaml
         cfg["aat_ref_view_pe"] = int(bool(margs.get("distinguish_ref_and_non_ref_views", True)))
         cfg["aat_entropy_scaling"] = int(bool(margs.get("use_entropy_scaling", False)))
@@ -172,11 +163,13 @@ class MapAnything(torch.nn.Module):
         if margs.get("use_pe_for_non_reference_views", False):
             # aat.py:628-645 draws the non-reference view indices with torch.randint at every call
             raise NotImplementedError("view positional encodings of non-reference views are not built")
-        if int(margs.get("dim", 768)) != 768 or int(margs.get("num_heads", 12)) != 12:
-            raise NotImplementedError("only the dim-768 / 12-head info-sharing transformer is built")
-        if len(margs.get("indices", (11, 17))) != 2:
-            raise NotImplementedError("the dense head takes two intermediate info-sharing features "
-                                      "(the 48-layer configs return three)")
+        dim = int(margs.get("dim", 768))
+        if dim not in (768, 1024) or int(margs.get("num_heads", dim // 64)) * 64 != dim:
+            raise NotImplementedError("the info-sharing transformer is built for widths 768 and 1024 with "
+                                      "64-wide heads (aat_ifr_24_layers*.yaml, aat_ifr_48_layers*.yaml)")
+        if len(margs.get("indices", (11, 17))) not in (2, 3):
+            raise ValueError("Invalid number of indices provided for info sharing feature returner. "
+                             "Please provide 2 or 3 indices.")  # model.py:328-331
         pc = self.pred_head_config
         if pc and pc.get("type", "dpt+pose") != "dpt+pose":
             raise NotImplementedError("only the dpt+pose head is built")
@@ -217,7 +210,7 @@ class MapAnything(torch.nn.Module):
         if self._finalized:
             raise RuntimeError("weights are already finalized for this instance")
         missing, unexpected, mismatch = check_state_dict(state_dict, self._cfg.aat_depth,
-                                                         bool(self._cfg.aat_ref_view_pe))
+                                                         bool(self._cfg.aat_ref_view_pe), self._cfg.aat_dim)
         errors = list(mismatch)  # a size mismatch is an error with strict=False as well (torch)
         if strict and unexpected:
             errors.insert(0, "Unexpected key(s) in state_dict: " + ", ".join(f'"{k}"' for k in unexpected) + ". ")

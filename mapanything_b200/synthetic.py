@@ -35,6 +35,49 @@ def load_manifest():
         return json.load(f)
 
 
+def manifest_for(aat_dim: int = 768, aat_depth: int = 24, ref_view_pe: bool = True):
+    """Key -> shape of the reference `state_dict()` for an info-sharing trunk of width `aat_dim` and
+    `aat_depth` blocks (configs/model/info_sharing/aat_ifr_{24,48}_layers*.yaml), derived from the
+    manifest of the default configuration: the blocks take the shapes of block 0 at the new width, the
+    tensors that consume trunk tokens (norm, view_pos_table, DPT input_process 1-3, pose / scale head
+    projections) follow it, and proj_embed only exists when the width differs from the encoder's 1024
+    (aat.py:121-124: nn.Identity otherwise).  oracle/make_golden.py checks the derived manifest against
+    the live reference's state_dict() for every variant it builds."""
+    base = load_manifest()
+    block = re.compile(r"^info_sharing\.self_attention_blocks\.(\d+)\.(.*)$")
+    follows = re.compile(r"^(info_sharing\.(norm\.(weight|bias)|view_pos_table)|"
+                         r"(dpt_feature_head|dense_head\.0)\.input_process\.[123]\.0\.0\.weight|"
+                         r"pose_head\.proj\.weight|scale_head\.proj\.weight)$")
+    # every dimension of a block tensor is a multiple of the width
+    block0 = [(m.group(2), [d * aat_dim // 768 for d in shape]) for key, shape in base.items()
+              for m in [block.match(key)] if m and int(m.group(1)) == 0]
+    out = {}
+    for key, shape in base.items():
+        if block.match(key):
+            if key == "info_sharing.self_attention_blocks.0." + block0[0][0]:
+                for i in range(aat_depth):
+                    for suffix, shp in block0:
+                        out[f"info_sharing.self_attention_blocks.{i}.{suffix}"] = list(shp)
+            continue
+        if key.startswith("info_sharing.proj_embed.") and aat_dim == 1024:
+            continue
+        if key == "info_sharing.view_pos_table" and not ref_view_pe:
+            continue
+        if key == "info_sharing.proj_embed.weight":
+            shape = [aat_dim, shape[1]]
+        elif key == "info_sharing.proj_embed.bias":
+            shape = [aat_dim]
+        elif follows.match(key):
+            if key.endswith("norm.weight") or key.endswith("norm.bias"):
+                shape = [aat_dim]
+            elif key.endswith("view_pos_table"):
+                shape = [shape[0], aat_dim]
+            else:
+                shape = [shape[0], aat_dim] + list(shape[2:])
+        out[key] = list(shape)
+    return out
+
+
 def canonical_key(key: str) -> str:
     """Map aliased state-dict keys onto one canonical name."""
     key = re.sub(r"^dense_head\.0\.", "dpt_feature_head.", key)
@@ -113,9 +156,9 @@ def _gen(key, shape, seed_salt=0):
     return uniform(HEAD_GAIN.get(key, HEAD_GAIN_DEFAULT) * math.sqrt(3.0 / fi))
 
 
-def synthetic_state_dict(seed_salt: int = 0, keys=None):
+def synthetic_state_dict(seed_salt: int = 0, keys=None, aat_dim: int = 768, aat_depth: int = 24):
     """Return {key: fp32 CPU tensor} for every key of the manifest (aliases share storage)."""
-    man = load_manifest()
+    man = manifest_for(aat_dim, aat_depth)
     cache = {}
     out = {}
     for k, shape in man.items():

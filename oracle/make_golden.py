@@ -50,6 +50,17 @@ CASE_MODULE_ARGS = {
 }
 CASES["small_escaling_n3_70x98"] = (3, 70, 98, False, 1, {})
 CASES["small_noref_n3_70x98"] = (3, 70, 98, False, 1, {})
+# aat_ifr_48_layers.yaml: 48 blocks of width 1024 / 16 heads, three intermediate features (the DPT head
+# then takes no encoder features, model.py:324-327) and no proj_embed (aat.py:121-124)
+CASE_MODULE_ARGS["small_48l_n2_56x84"] = dict(name="aat_48_layers_ifr", indices=[11, 23, 35], size="48_layers",
+                                              depth=48, dim=1024, num_heads=16)
+CASES["small_48l_n2_56x84"] = (2, 56, 84, False, 1, {})
+
+
+def case_state_dict(name):
+    """The synthetic checkpoint of a case: same generator, shapes of that case's trunk."""
+    margs = CASE_MODULE_ARGS.get(name, {})
+    return weights.synthetic_state_dict(aat_dim=margs.get("dim", 768), aat_depth=margs.get("depth", 24))
 
 
 def case_views(name):
@@ -80,15 +91,21 @@ def main(only=None):
     from oracle import ref_shim
 
     os.makedirs(GOLDEN_DIR, exist_ok=True)
-    sd = weights.synthetic_state_dict()
     models = {}
     for name, (n, H, W, mm, stride, kw) in CASES.items():
         if only and name not in only:
             continue
         margs = CASE_MODULE_ARGS.get(name, {})
-        mkey = tuple(sorted(margs.items()))
+        sd = case_state_dict(name)
+        mkey = repr(sorted(margs.items()))
         if mkey not in models:
             models[mkey] = ref_shim.build_reference_model(sd, margs)
+            # the derived manifest is the live reference's key space and shapes for this variant
+            live = {k: list(v.shape) for k, v in models[mkey].state_dict().items()}
+            mine = {k: list(v.shape) for k, v in sd.items()}
+            if not margs.get("distinguish_ref_and_non_ref_views", True):
+                mine.pop("info_sharing.view_pos_table")
+            assert live == mine, sorted(set(live.items()) ^ set(mine.items()))[:8]
         model = models[mkey]
         views = case_views(name)
         t0 = time.time()

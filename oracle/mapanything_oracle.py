@@ -323,15 +323,19 @@ def _block(x, sd, p, heads, entropy_scaling=False):
 # info_sharing module_args that change the arithmetic (configs/model/info_sharing/*.yaml):
 #   use_entropy_scaling (aat_ifr_24_layers_escaling.yaml), distinguish_ref_and_non_ref_views
 #   (aat_ifr_24_layers_no_ref_view.yaml).  Set by infer(..., aat_opts=...).
-AAT_OPTS = {"use_entropy_scaling": False, "distinguish_ref_and_non_ref_views": True}
+AAT_OPTS = {"use_entropy_scaling": False, "distinguish_ref_and_non_ref_views": True, "indices": (11, 17)}
 
 
-def alternating_attention_transformer(feats, sd, indices=(11, 17), prefix="info_sharing", taps=None):
+def alternating_attention_transformer(feats, sd, indices=None, prefix="info_sharing", taps=None):
     """alternating_attention_transformer.py:530-771.  feats (V, T, 1024) fused tokens of one scene
-    (B=1).  Returns (final (V,T,768), [tap (V,T,768)...], scale_token_final (768,))."""
+    (B=1).  Returns (final (V,T,dim), [tap (V,T,dim)...], scale_token_final (dim,)).  Width, head
+    count (dim / 64: 768 / 12 and 1024 / 16 in the shipped configs) and depth come from the state dict."""
     V, T, _ = feats.shape
+    indices = AAT_OPTS["indices"] if indices is None else indices
     x = torch.cat([feats.reshape(1, V * T, -1), sd["scale_token"].view(1, 1, -1)], dim=1)
-    x = _lin(x, sd, prefix + ".proj_embed")
+    if prefix + ".proj_embed.weight" in sd:  # aat.py:121-124: nn.Identity when the widths agree
+        x = _lin(x, sd, prefix + ".proj_embed")
+    heads = sd[prefix + ".norm.weight"].numel() // 64
     if AAT_OPTS["distinguish_ref_and_non_ref_views"]:  # aat.py:618-626
         x = torch.cat([x[:, :T] + sd[prefix + ".view_pos_table"][0].view(1, 1, -1), x[:, T:]], dim=1)
     es = AAT_OPTS["use_entropy_scaling"]
@@ -342,10 +346,10 @@ def alternating_attention_transformer(feats, sd, indices=(11, 17), prefix="info_
     for i in range(depth):
         p = f"{prefix}.self_attention_blocks.{i}"
         if i % 2 == 0:
-            x = _block(x, sd, p, 12, es)
+            x = _block(x, sd, p, heads, es)
         else:
             extra = x[:, V * T:]
-            y = _block(x[:, :V * T].reshape(V, T, -1), sd, p, 12, es)
+            y = _block(x[:, :V * T].reshape(V, T, -1), sd, p, heads, es)
             x = torch.cat([y.reshape(1, V * T, -1), extra], dim=1)
         if taps is not None and i in (0, 1):
             taps[f"aat_block{i}"] = x[0]
@@ -488,12 +492,16 @@ def _forward_impl(sd, views, flags=None, taps=None, amp=False):
     final, inter, scale_tok = final.float(), [t.float() for t in inter], scale_tok.float()
     if taps is not None:
         taps["aat_tap11"], taps["aat_tap17"], taps["aat_final"] = inter[0], inter[1], final
+        taps["aat_inter"] = list(inter)
         taps["scale_token_final"] = scale_tok
 
     def nchw(t):
         return t.reshape(V, h, w, -1).permute(0, 3, 1, 2).contiguous()
 
-    layers = [nchw(fused), nchw(inter[0]), nchw(inter[1]), nchw(final)]  # model.py:1724-1747
+    if len(inter) == 2:
+        layers = [nchw(fused), nchw(inter[0]), nchw(inter[1]), nchw(final)]  # model.py:1724-1747
+    else:  # three intermediate features: the DPT head does not see the encoder output (model.py:324-327,1748-1768)
+        layers = [nchw(inter[0]), nchw(inter[1]), nchw(inter[2]), nchw(final)]
     feat8 = dpt_feature(layers, sd)
     logits = dpt_regressor(feat8, sd, (H, W))  # (V,6,H,W)
     cam_t, cam_q = pose_head(layers[3], sd)

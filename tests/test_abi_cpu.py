@@ -74,16 +74,18 @@ def test_constructor_rejects_unbuilt_trunk_configs_before_touching_the_gpu():
         return {"model_type": "alternating_attention", "custom_positional_encoding": None,
                 "module_args": dict(depth=24, indices=[11, 17], **margs)}
 
-    for bad in (cfg(dim=1024, num_heads=16), cfg(use_pe_for_non_reference_views=True),
-                dict(cfg(), module_args=dict(depth=48, indices=[11, 23, 35])),
+    for bad in (cfg(dim=512, num_heads=8), cfg(dim=1024, num_heads=12), cfg(use_pe_for_non_reference_views=True),
                 dict(cfg(), model_type="global_attention"), dict(cfg(), custom_positional_encoding="RoPE100")):
         with pytest.raises(NotImplementedError):
             MapAnything(info_sharing_config=bad)
     with pytest.raises(NotImplementedError):
         MapAnything(pred_head_config={"type": "dpt"})
+    with pytest.raises(ValueError, match="2 or 3 indices"):   # model.py:328-331
+        MapAnything(info_sharing_config=dict(cfg(), module_args=dict(depth=24, indices=[5, 11, 17, 23])))
     for ok in (cfg(), cfg(use_entropy_scaling=True), cfg(distinguish_ref_and_non_ref_views=False),
                cfg(distinguish_ref_and_non_ref_views=True, max_num_views_for_pe=1000,
-                   use_rand_idx_pe_for_non_reference_views=True)):   # aat_ifr_24_layers_w_view_pe.yaml
+                   use_rand_idx_pe_for_non_reference_views=True),    # aat_ifr_24_layers_w_view_pe.yaml
+               dict(cfg(), module_args=dict(depth=48, indices=[11, 23, 35], dim=1024, num_heads=16))):  # aat_ifr_48_layers.yaml
         with pytest.raises(RuntimeError, match="CUDA device"):
             MapAnything(info_sharing_config=ok)
 
@@ -131,7 +133,8 @@ def test_create_refuses_inconsistent_configs():
     from mapanything_b200.model import default_config
 
     lib = _lib.load()
-    for change in (dict(aat_tap1=24), dict(aat_tap0=17), dict(aat_dim=1024), dict(enc_heads=12),
+    for change in (dict(aat_tap1=24), dict(aat_tap0=17), dict(aat_dim=1024), dict(aat_dim=512, aat_heads=8),
+                   dict(aat_tap2=17), dict(aat_tap2=24), dict(enc_heads=12),
                    dict(head_chunk=0), dict(patch=16), dict(enc_depth=0)):
         cfg = _lib.MabConfig(**dict(default_config(), **change))
         handle = C.c_void_p()
@@ -168,3 +171,22 @@ def test_state_dict_bookkeeping_mirrors_torch_strict_loading():
     # a shallower trunk: the extra blocks of a 24-layer checkpoint are unexpected, none is missing
     missing, unexpected, _ = check_state_dict(sd, aat_depth=20)
     assert not missing and unexpected and all(k.startswith("info_sharing.self_attention_blocks.2") for k in unexpected)
+
+
+def test_state_dict_bookkeeping_follows_the_trunk_width_and_depth():
+    """aat_ifr_48_layers.yaml: 48 blocks of width 1024, no proj_embed (aat.py:121-124), the consumers of
+    trunk tokens follow the width.  oracle/make_golden.py pins manifest_for against the live reference."""
+    from mapanything_b200 import synthetic
+    from mapanything_b200.model import check_state_dict
+
+    man = synthetic.manifest_for(1024, 48)
+    assert len(man) == 1166 and "info_sharing.proj_embed.weight" not in man
+    assert man["info_sharing.self_attention_blocks.47.attn.qkv.weight"] == [3072, 1024]
+    assert man["pose_head.proj.weight"] == [784, 1024, 1, 1] and man["scale_head.proj.weight"] == [196, 1024]
+    assert man["dpt_feature_head.input_process.0.0.0.weight"] == [96, 1024, 1, 1]   # tap0 instead of the encoder
+    assert man["dense_head.0.input_process.3.0.0.weight"] == [768, 1024, 1, 1]
+    assert synthetic.manifest_for() == synthetic.load_manifest()
+    shapes = {k: torch.empty(v, device="meta") for k, v in man.items()}
+    assert check_state_dict(shapes, aat_depth=48, aat_dim=1024) == ([], [], [])
+    missing, unexpected, mismatch = check_state_dict(shapes)      # into the production configuration
+    assert "info_sharing.proj_embed.weight" in missing and unexpected and mismatch

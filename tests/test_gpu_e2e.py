@@ -119,6 +119,53 @@ def test_info_sharing_variants_match_reference_golden(name, synthetic_sd, sd_cud
     assert worst(base) > 5 * worst(rep), (worst(base), worst(rep))
 
 
+def test_48_layer_trunk_matches_reference_golden():
+    """configs/model/info_sharing/aat_ifr_48_layers.yaml: 48 blocks of width 1024 / 16 heads, no
+    proj_embed, three intermediate features feeding the dense head instead of the encoder features
+    (model.py:324-327,1748-1768), against a golden of the LIVE reference built with those module_args.
+    Same criteria as the production config; the trunk's stage taps are compared first so that a
+    failure names the stage."""
+    from mapanything_b200 import MapAnything
+    from oracle import make_golden
+    from oracle import mapanything_oracle as orc
+    from tests import helpers
+    from tests.diag_stages import debug_buffer
+
+    name = "small_48l_n2_56x84"
+    margs = make_golden.CASE_MODULE_ARGS[name]
+    sd = make_golden.case_state_dict(name)
+    m = MapAnything(device="cuda:0", head_chunk=2,
+                    info_sharing_config={"model_type": "alternating_attention", "module_args": dict(margs)})
+    m.load_state_dict(sd)
+    sd_dev = {k: v.cuda() for k, v in sd.items()}
+    n, H, W, mm, stride, kw = make_golden.CASES[name]
+    views = make_golden.case_views(name)
+    preds = m.infer([dict(v) for v in views], **kw)
+    torch.cuda.synchronize()
+    taps = {}
+    orc.infer(sd_dev, _to_cuda(views), taps=taps, aat_opts=margs, **kw)
+    stages = {"tap0": taps["aat_inter"][0], "tap1": taps["aat_inter"][1], "tap2": taps["aat_inter"][2],
+              "final": taps["aat_final"], "scale_token": taps["scale_token_final"]}
+    stage_err = {k: helpers.rel_l2(debug_buffer(m, k).cpu()[: v.numel()], v.float().reshape(-1).cpu())
+                 for k, v in stages.items()}
+    print("stage rel-L2 vs fp32 oracle:", {k: round(v, 5) for k, v in stage_err.items()})
+    assert max(stage_err.values()) < 2e-2, stage_err
+    g = helpers.load_golden(name)
+    rep = helpers.compare_with_golden(preds, g, stride, None, None)
+    yard = helpers.compare_with_golden(orc.infer(sd_dev, _to_cuda(views), amp=True, aat_opts=margs, **kw), g,
+                                       stride, None, None)
+    print("libmab200  :", {k: round(v, 5) for k, v in rep.items()})
+    print("ref bf16   :", {k: round(v, 5) for k, v in yard.items()})
+    cam_frame = {k: v for k, v in rep.items() if k.split(".", 1)[1] not in helpers.POSE_DEPENDENT_KEYS
+                 and k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
+    bad = helpers.out_of_tolerance(cam_frame, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97)
+    assert not bad, f"camera-frame keys out of absolute tolerance: {bad}"
+    rest = {k: v for k, v in rep.items() if k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
+    bad = helpers.out_of_tolerance(rest, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97,
+                                   yardstick=yard, slack=3.0)
+    assert not bad, f"further from the fp32 reference than the reference's bf16 path: {bad}\nyardstick {yard}"
+
+
 @pytest.mark.parametrize("H,W", [(518, 518), (518, 294), (168, 518)])
 def test_other_resolution_mappings_match_oracle(H, W, model, sd_cuda):
     """The other entries of RESOLUTION_MAPPINGS[518] (image.py:40-52): square (37 x 37 patches: the
