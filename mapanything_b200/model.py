@@ -157,8 +157,14 @@ class MapAnything(torch.nn.Module):
         ic = self.info_sharing_config
         if ic and ic.get("model_type", "alternating_attention") != "alternating_attention":
             raise NotImplementedError("only the alternating-attention info-sharing model is built")
-        if ic and ic.get("custom_positional_encoding") is not None:
-            raise NotImplementedError("custom positional encodings are not part of the default path")
+        cpe = (ic or {}).get("custom_positional_encoding")
+        if isinstance(cpe, str):  # model.py:259-267: the reference implements none of the named encodings
+            raise ValueError(f"Invalid custom_positional_encoding: {cpe}. None implemented.")
+        if cpe is not None:
+            # a callable reaches aat.py:612-616, where the position tensor is concatenated with the [None]
+            # of the scale token (TypeError in the reference): no MapAnything configuration runs with one
+            raise NotImplementedError("callable positional encodings do not run in the reference with the "
+                                      "scale token (aat.py:612-616); mab_rope2d is the RoPE2D kernel on its own")
         margs = (ic or {}).get("module_args", {})
         if margs.get("use_pe_for_non_reference_views", False):
             # aat.py:628-645 draws the non-reference view indices with torch.randint at every call

@@ -75,11 +75,13 @@ def test_constructor_rejects_unbuilt_trunk_configs_before_touching_the_gpu():
                 "module_args": dict(depth=24, indices=[11, 17], **margs)}
 
     for bad in (cfg(dim=512, num_heads=8), cfg(dim=1024, num_heads=12), cfg(use_pe_for_non_reference_views=True),
-                dict(cfg(), model_type="global_attention"), dict(cfg(), custom_positional_encoding="RoPE100")):
+                dict(cfg(), model_type="global_attention"), dict(cfg(), custom_positional_encoding=lambda x, p: x)):
         with pytest.raises(NotImplementedError):
             MapAnything(info_sharing_config=bad)
     with pytest.raises(NotImplementedError):
         MapAnything(pred_head_config={"type": "dpt"})
+    with pytest.raises(ValueError, match="None implemented"):  # model.py:259-267
+        MapAnything(info_sharing_config=dict(cfg(), custom_positional_encoding="RoPE100"))
     with pytest.raises(ValueError, match="2 or 3 indices"):   # model.py:328-331
         MapAnything(info_sharing_config=dict(cfg(), module_args=dict(depth=24, indices=[5, 11, 17, 23])))
     for ok in (cfg(), cfg(use_entropy_scaling=True), cfg(distinguish_ref_and_non_ref_views=False),
