@@ -48,6 +48,10 @@ typedef struct {
    * the dense head then takes [tap0, tap1, tap2, final] instead of [encoder, tap0, tap1, final]
    * (model.py:324-327,1724-1768).  <= 0: two intermediate features. */
   int aat_tap2;
+  /* 1: use_pe_for_non_reference_views (alternating_attention_transformer.py:30,628-645): every view adds
+   * a row of info_sharing.view_pos_table [max_num_views_for_pe, aat_dim] to its tokens; the rows come
+   * from mab_set_view_pe_rows before every forward (the reference draws them with torch.randint). */
+  int aat_nonref_view_pe;
 } mab_config;
 
 /* One scene, `views` views of H x W pixels held by this rank. */
@@ -108,6 +112,10 @@ int mab_destroy(mab_handle* h);
 /* Upload one tensor of the reference state dict (reference key names, fp32, host or device). */
 int mab_set_weight(mab_handle* h, const char* ref_key, const void* ptr, int dtype, int ndim,
                    const int64_t* shape);
+/* view_pos_table row of every view THIS RANK holds (host array of n ints, copied; row 0 for the scene's
+ * reference view, -1 = none), consumed by the next mab_forward / mab_stage_encode of a handle created
+ * with aat_nonref_view_pe.  n must equal that call's in->views. */
+int mab_set_view_pe_rows(mab_handle* h, const int* rows, int n);
 /* Pack bf16 GEMM/conv operands, merge aliases, drop the fp32 staging copies that are not needed. */
 int mab_finalize_weights(mab_handle* h, void* stream);
 

@@ -11,7 +11,7 @@ c_ubyte_p = C.POINTER(C.c_ubyte)
 class MabConfig(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("patch", "enc_dim", "enc_depth", "enc_heads", "enc_pos_grid",
                                        "aat_dim", "aat_depth", "aat_heads", "aat_tap0", "aat_tap1",
-                                       "head_chunk", "aat_ref_view_pe", "aat_entropy_scaling", "aat_tap2")]
+                                       "head_chunk", "aat_ref_view_pe", "aat_entropy_scaling", "aat_tap2", "aat_nonref_view_pe")]
 
 
 class MabInputs(C.Structure):
@@ -53,6 +53,7 @@ SYMBOLS = {
     "mab_destroy": (_i, [_vp]),
     "mab_set_weight": (_i, [_vp, C.c_char_p, _vp, _i, _i, C.POINTER(C.c_int64)]),
     "mab_finalize_weights": (_i, [_vp, _vp]),
+    "mab_set_view_pe_rows": (_i, [_vp, C.POINTER(C.c_int), _i]),
     "mab_workspace_bytes": (C.c_size_t, [_vp, _i, _i, _i, _i]),
     "mab_forward": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), _vp, C.c_size_t, _vp]),
     "mab_postprocess": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), C.POINTER(MabPostOutputs),

@@ -339,6 +339,18 @@ __global__ void add_row_vector_kernel(float* __restrict__ x, const float* __rest
     x[i] += pe[i % C];
 }
 
+// x[v * T + t, :] += table[rows[v], :]  (view positional encoding of every view of the shard,
+// use_pe_for_non_reference_views, aat.py:618-645; rows[v] < 0: none for that view)
+__global__ void add_view_rows_kernel(float* __restrict__ x, const float* __restrict__ table,
+                                     const int* __restrict__ rows, int views, int T, int C) {
+  const long long per_view = (long long)T * C, total = per_view * views;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int r = rows[i / per_view];
+    if (r >= 0) x[i] += table[(long long)r * C + i % C];
+  }
+}
+
 __global__ void f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                    long long n) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;

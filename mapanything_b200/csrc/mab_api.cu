@@ -569,7 +569,7 @@ struct Plan {  // every workspace pointer of one forward
   bf16* im2col; float* patch; float* pos; float* xs; bf16* ln; bf16* qkv; bf16* att; bf16* hid;
   float* enc_out; bf16* fused; float* geo_sum; float* geo_vec; float* geo_small;
   // info sharing
-  float* ys; bf16* tap[3]; bf16* fin; float* scale_tok; float* carry_o; float* carry_ml;
+  float* ys; int* view_rows; bf16* tap[3]; bf16* fin; float* scale_tok; float* carry_o; float* carry_ml;
   // heads (small)
   float* scale_tmp; float* pose_pool; float* pose_tmp; float* pose_raw; bf16* ph_in; bf16* ph_a; bf16* ph_b; bf16* ph_c; bf16* ph_d;
   // dense head chunk buffers
@@ -590,6 +590,7 @@ struct mab_handle {
   std::map<std::string, float*> packed32;     // fp32 (TF32) GEMM / conv operands, padded layouts
   std::map<std::string, float*> extra;        // derived fp32 tensors (tiled biases)
   std::vector<void*> owned;
+  std::vector<int> view_pe_rows;               // mab_set_view_pe_rows: one table row per view of the shard
   Plan plan;
 
   const float* F(const std::string& k) const {
@@ -633,6 +634,7 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
   p.geo_vec = b.take<float>((long long)V * D); // sum of the masked per-view (global) features
   p.geo_small = b.take<float>((long long)V * 4096 + 64);  // MLP scratch + masks + scalar inputs
   p.ys = b.take<float>((VT + 1) * A);
+  p.view_rows = b.take<int>(V);  // view_pos_table row of every view (use_pe_for_non_reference_views)
   p.tap[0] = b.take<bf16>(VT * A);
   p.tap[1] = b.take<bf16>(VT * A);
   p.tap[2] = c.aat_tap2 > 0 ? b.take<bf16>(VT * A) : nullptr;  // third intermediate feature (48-layer configs)
@@ -683,6 +685,8 @@ extern "C" int mab_create(const mab_config* cfg, int device, mab_handle** out) {
           "intermediate feature indices must satisfy 0 <= tap0 < tap1 < depth");
   MAB_ARG(cfg->aat_tap2 <= 0 || (cfg->aat_tap1 < cfg->aat_tap2 && cfg->aat_tap2 < cfg->aat_depth),
           "a third intermediate feature index must satisfy tap1 < tap2 < depth");
+  MAB_ARG(!cfg->aat_nonref_view_pe || cfg->aat_ref_view_pe,
+          "view PE of the non-reference views needs the reference-view PE (aat.py:64)");
   MAB_ARG(device >= 0, "bad device");
   MAB_CUDA(cudaSetDevice(device));
   mab_handle* h = new mab_handle();
@@ -697,6 +701,16 @@ extern "C" int mab_destroy(mab_handle* h) {
   for (auto& kv : h->raw) cudaFree(kv.second.p);
   for (void* p : h->owned) cudaFree(p);
   delete h;
+  return 0;
+}
+
+// view_pos_table row of every view this rank holds, for the next mab_stage_encode / mab_forward of a
+// handle with aat_nonref_view_pe (host array, copied; -1 = no encoding for that view)
+extern "C" int mab_set_view_pe_rows(mab_handle* h, const int* rows, int n) {
+  MAB_ARG(h && rows && n > 0, "bad arguments");
+  MAB_ARG(h->cfg.aat_nonref_view_pe, "the handle was created without aat_nonref_view_pe");
+  for (int i = 0; i < n; ++i) MAB_ARG(rows[i] >= -1, "rows must be >= -1");
+  h->view_pe_rows.assign(rows, rows + n);
   return 0;
 }
 
@@ -1231,7 +1245,20 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
                      h->F("info_sharing.proj_embed.bias"), ACT_NONE, nullptr, nullptr, p.ys, nullptr));
   }
   // reference-view PE on view 0's tokens (aat.py:618-626)
-  if (p.has_ref && cf.aat_ref_view_pe) {  // distinguish_ref_and_non_ref_views (aat.py:618-626)
+  if (cf.aat_ref_view_pe && cf.aat_nonref_view_pe) {
+    // use_pe_for_non_reference_views (aat.py:618-645): view 0 takes row 0 and every other view the row the
+    // caller drew for it (torch.randint in the reference, or 1..V-1); rows were checked against the table
+    MAB_ARG((int)h->view_pe_rows.size() == V, "mab_set_view_pe_rows must give one row per view of this shard");
+    const RawTensor& tab = h->raw.at("info_sharing.view_pos_table");
+    for (int r : h->view_pe_rows)
+      MAB_ARG(r < (int)tab.shape[0], "view_pos_table row out of range (max_num_views_for_pe)");
+    MAB_CUDA(cudaMemcpyAsync(p.view_rows, h->view_pe_rows.data(), (size_t)V * sizeof(int),
+                             cudaMemcpyHostToDevice, c.st));
+    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+               add_view_rows_kernel<<<ew_grid(VT * cf.aat_dim), 256, 0, c.st>>>(p.ys, tab.p, p.view_rows, V, T,
+                                                                              cf.aat_dim));
+    MAB_CUDA(cudaGetLastError());
+  } else if (p.has_ref && cf.aat_ref_view_pe) {  // distinguish_ref_and_non_ref_views (aat.py:618-626)
     MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
                add_row_vector_kernel<<<ew_grid((long long)T * cf.aat_dim), 256, 0, c.st>>>(
         p.ys, h->F("info_sharing.view_pos_table"), T, cf.aat_dim));

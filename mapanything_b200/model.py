@@ -62,7 +62,8 @@ def default_config():
     """Architecture of the production model (configs/model/mapanything.yaml)."""
     return dict(patch=14, enc_dim=1024, enc_depth=24, enc_heads=16, enc_pos_grid=37, aat_dim=768,
                 aat_depth=24, aat_heads=12, aat_tap0=11, aat_tap1=17, head_chunk=8,
-                aat_ref_view_pe=1, aat_entropy_scaling=0, aat_tap2=0)
+                aat_ref_view_pe=1, aat_entropy_scaling=0, aat_tap2=0,
+                aat_nonref_view_pe=0)
 
 
 def head_ranges(V, stream_chunk, default_chunk):
@@ -81,7 +82,7 @@ def head_ranges(V, stream_chunk, default_chunk):
     return out
 
 
-def check_state_dict(state_dict, aat_depth=24, ref_view_pe=True, aat_dim=768):
+def check_state_dict(state_dict, aat_depth=24, ref_view_pe=True, aat_dim=768, view_pe_rows=1):
     """torch.nn.Module.load_state_dict's key / shape bookkeeping for the reference key space
     (synthetic.manifest_for: the reference's own `state_dict()` of the default configuration, aliases
     of shared modules included, re-shaped for the trunk's width and depth).  Returns (missing,
@@ -90,7 +91,7 @@ def check_state_dict(state_dict, aat_depth=24, ref_view_pe=True, aat_dim=768):
     info_sharing.view_pos_table buffer (aat.py:160-172)."""
     from .synthetic import canonical_key, manifest_for
 
-    expected = {k: tuple(v) for k, v in manifest_for(aat_dim, aat_depth, ref_view_pe).items()}
+    expected = {k: tuple(v) for k, v in manifest_for(aat_dim, aat_depth, ref_view_pe, view_pe_rows).items()}
     unexpected = [k for k in state_dict if k not in expected]
     mismatch = [f"size mismatch for {k}: copying a param with shape {tuple(v.shape)} from checkpoint, "
                 f"the shape in current model is {expected[k]}."
@@ -136,6 +137,13 @@ class MapAnything(torch.nn.Module):
         # info_sharing variants: aat_ifr_24_layers_no_ref_view.yaml / aat_ifr_24_layers_escaling.yaml
         cfg["aat_ref_view_pe"] = int(bool(margs.get("distinguish_ref_and_non_ref_views", True)))
         cfg["aat_entropy_scaling"] = int(bool(margs.get("use_entropy_scaling", False)))
+        # use_pe_for_non_reference_views: "Only used if distinguish_ref_and_non_ref_views flag is True" (aat.py:64)
+        cfg["aat_nonref_view_pe"] = int(bool(margs.get("use_pe_for_non_reference_views", False)) and
+                                        bool(cfg["aat_ref_view_pe"]))
+        self._max_views_for_pe = int(margs.get("max_num_views_for_pe", 1000))
+        self._rand_view_pe = bool(margs.get("use_rand_idx_pe_for_non_reference_views", True))
+        self._check_view_count = bool(margs.get("use_pe_for_non_reference_views", False))
+        self._pinned_view_pe_rows = None
         cfg["head_chunk"] = int(head_chunk)
         self._cfg = _lib.MabConfig(**cfg)
         self._handle = C.c_void_p()
@@ -166,9 +174,6 @@ class MapAnything(torch.nn.Module):
             raise NotImplementedError("callable positional encodings do not run in the reference with the "
                                       "scale token (aat.py:612-616); mab_rope2d is the RoPE2D kernel on its own")
         margs = (ic or {}).get("module_args", {})
-        if margs.get("use_pe_for_non_reference_views", False):
-            # aat.py:628-645 draws the non-reference view indices with torch.randint at every call
-            raise NotImplementedError("view positional encodings of non-reference views are not built")
         dim = int(margs.get("dim", 768))
         if dim not in (768, 1024) or int(margs.get("num_heads", dim // 64)) * 64 != dim:
             raise NotImplementedError("the info-sharing transformer is built for widths 768 and 1024 with "
@@ -215,8 +220,9 @@ class MapAnything(torch.nn.Module):
         """Accepts the reference key space unchanged, aliases included."""
         if self._finalized:
             raise RuntimeError("weights are already finalized for this instance")
-        missing, unexpected, mismatch = check_state_dict(state_dict, self._cfg.aat_depth,
-                                                         bool(self._cfg.aat_ref_view_pe), self._cfg.aat_dim)
+        missing, unexpected, mismatch = check_state_dict(
+            state_dict, self._cfg.aat_depth, bool(self._cfg.aat_ref_view_pe), self._cfg.aat_dim,
+            self._max_views_for_pe if self._cfg.aat_nonref_view_pe else 1)
         errors = list(mismatch)  # a size mismatch is an error with strict=False as well (torch)
         if strict and unexpected:
             errors.insert(0, "Unexpected key(s) in state_dict: " + ", ".join(f'"{k}"' for k in unexpected) + ". ")
@@ -405,6 +411,7 @@ class MapAnything(torch.nn.Module):
             if nbytes == 0:
                 raise RuntimeError("mab_workspace_bytes rejected the problem shape")
             ws = self._get_workspace(nbytes)
+            self._set_view_pe_rows(view_lo, V, total)
             outs = self._alloc_outputs(V, H, W, want_logits)
             inp = self._input_struct(imgs, H, W, geo)
             ost = self._out_struct(outs)
@@ -426,6 +433,31 @@ class MapAnything(torch.nn.Module):
             else:
                 self._forward_sharded(inp, ost, outs, ws, V, H, W, view_lo, total)
         return outs
+
+    def _draw_view_pe_rows(self, total):
+        """view_pos_table row of every view of a scene (aat.py:618-645): 0 for the reference view, then
+        torch.randint(1, max_num_views_for_pe) from the global CPU generator like the reference (default)
+        or 1..V-1.  View-sharded runs take rank 0's draw."""
+        if self._rand_view_pe:
+            rows = torch.randint(low=1, high=self._max_views_for_pe, size=(total - 1,))
+        else:
+            rows = torch.arange(1, total)
+        rows = torch.cat([torch.zeros(1, dtype=torch.int64), rows.to(torch.int64)])
+        import torch.distributed as dist
+        if self._rand_view_pe and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dev_rows = rows.to(self._device)
+            dist.broadcast(dev_rows, src=0)
+            rows = dev_rows.cpu()
+        return rows
+
+    def _set_view_pe_rows(self, view_lo, V, total):
+        if self._check_view_count:  # aat.py:554-557
+            assert total <= self._max_views_for_pe, f"Expected less than {self._max_views_for_pe} views, got {total}"
+        if not self._cfg.aat_nonref_view_pe:
+            return
+        rows = self._pinned_view_pe_rows if self._pinned_view_pe_rows is not None else self._draw_view_pe_rows(total)
+        local = (C.c_int * V)(*[int(r) for r in rows[view_lo:view_lo + V]])
+        _lib.check(self._lib.mab_set_view_pe_rows(self._handle, local, V), "mab_set_view_pe_rows")
 
     def _head_ranges(self, V, stream_chunk):
         return head_ranges(V, stream_chunk, self._cfg.head_chunk)
@@ -651,11 +683,16 @@ class MapAnything(torch.nn.Module):
         B = int(views[0]["img"].shape[0])
         if B > 1:  # B independent scenes (see infer)
             per_scene = []
-            for b in range(B):
-                scene = [{k: (t[b:b + 1] if torch.is_tensor(t) and t.dim() > 0 and t.shape[0] == B else
-                              (tuple(c[b:b + 1] for c in t) if isinstance(t, tuple) else t))
-                          for k, t in v.items()} for v in views]
-                per_scene.append(self.forward(scene, memory_efficient_inference))
+            if self._cfg.aat_nonref_view_pe:  # the reference draws the view-PE rows once per call
+                self._pinned_view_pe_rows = self._draw_view_pe_rows(len(views))
+            try:
+                for b in range(B):
+                    scene = [{k: (t[b:b + 1] if torch.is_tensor(t) and t.dim() > 0 and t.shape[0] == B else
+                                  (tuple(c[b:b + 1] for c in t) if isinstance(t, tuple) else t))
+                              for k, t in v.items()} for v in views]
+                    per_scene.append(self.forward(scene, memory_efficient_inference))
+            finally:
+                self._pinned_view_pe_rows = None
             return [{k: torch.cat([per_scene[b][i][k] for b in range(B)], 0) for k in per_scene[0][i]}
                     for i in range(len(views))]
         imgs, H, W = self._pack_images(views)
@@ -710,13 +747,18 @@ class MapAnything(torch.nn.Module):
                       ignore_pose_scale_inputs=ignore_pose_scale_inputs, view_range=view_range,
                       total_views=total_views, host_outputs=host_outputs, stream_chunk=stream_chunk)
             per_scene = []
-            for b in range(B):
-                scene = [{k: (t[b:b + 1] if torch.is_tensor(t) and t.dim() > 0 and t.shape[0] == B else
-                              (tuple(c[b:b + 1] for c in t) if isinstance(t, tuple) else t))
-                          for k, t in v.items()} for v in views]
-                preds = self.infer(scene, **kw)
-                # host_outputs reuses one pinned pool per call: detach the scene's results from it
-                per_scene.append([{k: t.clone() for k, t in p.items()} for p in preds] if host_outputs else preds)
+            if self._cfg.aat_nonref_view_pe:  # the reference draws the view-PE rows once per call
+                self._pinned_view_pe_rows = self._draw_view_pe_rows(int(total_views or len(views)))
+            try:
+                for b in range(B):
+                    scene = [{k: (t[b:b + 1] if torch.is_tensor(t) and t.dim() > 0 and t.shape[0] == B else
+                                  (tuple(c[b:b + 1] for c in t) if isinstance(t, tuple) else t))
+                              for k, t in v.items()} for v in views]
+                    preds = self.infer(scene, **kw)
+                    # host_outputs reuses one pinned pool per call: detach the scene's results from it
+                    per_scene.append([{k: t.clone() for k, t in p.items()} for p in preds] if host_outputs else preds)
+            finally:
+                self._pinned_view_pe_rows = None
             for v in views:  # model.py:2316-2320: the caller's tensors end up on the model device
                 for name in list(v.keys()):
                     if name not in _PASS_THROUGH and torch.is_tensor(v[name]):

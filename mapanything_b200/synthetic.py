@@ -35,7 +35,7 @@ def load_manifest():
         return json.load(f)
 
 
-def manifest_for(aat_dim: int = 768, aat_depth: int = 24, ref_view_pe: bool = True):
+def manifest_for(aat_dim: int = 768, aat_depth: int = 24, ref_view_pe: bool = True, view_pe_rows: int = 1):
     """Key -> shape of the reference `state_dict()` for an info-sharing trunk of width `aat_dim` and
     `aat_depth` blocks (configs/model/info_sharing/aat_ifr_{24,48}_layers*.yaml), derived from the
     manifest of the default configuration: the blocks take the shapes of block 0 at the new width, the
@@ -70,8 +70,8 @@ def manifest_for(aat_dim: int = 768, aat_depth: int = 24, ref_view_pe: bool = Tr
         elif follows.match(key):
             if key.endswith("norm.weight") or key.endswith("norm.bias"):
                 shape = [aat_dim]
-            elif key.endswith("view_pos_table"):
-                shape = [shape[0], aat_dim]
+            elif key.endswith("view_pos_table"):  # max_num_views_for_pe rows with use_pe_for_non_reference_views
+                shape = [view_pe_rows, aat_dim]
             else:
                 shape = [shape[0], aat_dim] + list(shape[2:])
         out[key] = list(shape)
@@ -112,9 +112,11 @@ def _gen(key, shape, seed_salt=0):
     is_norm = bool(re.search(r"(norm\d?|norm_layer|fusion_norm_layer)\.(weight|bias)$", key))
     if key == "info_sharing.view_pos_table":
         # alternating_attention_transformer.py:190-200, position 0 -> [sin 0, cos 0, ...]
-        t = np.zeros(shape, np.float32)
-        t[:, 1::2] = 1.0
-        return t
+        pos = np.arange(shape[0], dtype=np.float64)[:, None]
+        ang = pos / np.power(10000.0, 2 * (np.arange(shape[1]) // 2) / shape[1])[None, :]
+        ang[:, 0::2] = np.sin(ang[:, 0::2])
+        ang[:, 1::2] = np.cos(ang[:, 1::2])
+        return ang.astype(np.float32)
     if is_norm:
         return 1.0 + normal(0.1) if leaf == "weight" else normal(0.05)
     if leaf == "gamma":  # LayerScale, dinov2 layers/layer_scale.py:14-26
@@ -156,9 +158,10 @@ def _gen(key, shape, seed_salt=0):
     return uniform(HEAD_GAIN.get(key, HEAD_GAIN_DEFAULT) * math.sqrt(3.0 / fi))
 
 
-def synthetic_state_dict(seed_salt: int = 0, keys=None, aat_dim: int = 768, aat_depth: int = 24):
+def synthetic_state_dict(seed_salt: int = 0, keys=None, aat_dim: int = 768, aat_depth: int = 24,
+                         view_pe_rows: int = 1):
     """Return {key: fp32 CPU tensor} for every key of the manifest (aliases share storage)."""
-    man = manifest_for(aat_dim, aat_depth)
+    man = manifest_for(aat_dim, aat_depth, True, view_pe_rows)
     cache = {}
     out = {}
     for k, shape in man.items():

@@ -55,12 +55,22 @@ CASES["small_noref_n3_70x98"] = (3, 70, 98, False, 1, {})
 CASE_MODULE_ARGS["small_48l_n2_56x84"] = dict(name="aat_48_layers_ifr", indices=[11, 23, 35], size="48_layers",
                                               depth=48, dim=1024, num_heads=16)
 CASES["small_48l_n2_56x84"] = (2, 56, 84, False, 1, {})
+# use_pe_for_non_reference_views (aat.py:30,628-645) with the rows drawn at random from a seeded global
+# generator (the default) and in sequence; a small table keeps the fixture's checkpoint cheap
+CASE_MODULE_ARGS["small_viewpe_rand_n3_70x98"] = dict(use_pe_for_non_reference_views=True, max_num_views_for_pe=64)
+CASE_MODULE_ARGS["small_viewpe_seq_n3_70x98"] = dict(use_pe_for_non_reference_views=True, max_num_views_for_pe=64,
+                                                     use_rand_idx_pe_for_non_reference_views=False)
+CASES["small_viewpe_rand_n3_70x98"] = (3, 70, 98, False, 1, {})
+CASES["small_viewpe_seq_n3_70x98"] = (3, 70, 98, False, 1, {})
+CASE_SEED = 1234  # torch.manual_seed before every run of a case: the random view-PE rows are part of the case
 
 
 def case_state_dict(name):
     """The synthetic checkpoint of a case: same generator, shapes of that case's trunk."""
     margs = CASE_MODULE_ARGS.get(name, {})
-    return weights.synthetic_state_dict(aat_dim=margs.get("dim", 768), aat_depth=margs.get("depth", 24))
+    rows = margs.get("max_num_views_for_pe", 1000) if margs.get("use_pe_for_non_reference_views") else 1
+    return weights.synthetic_state_dict(aat_dim=margs.get("dim", 768), aat_depth=margs.get("depth", 24),
+                                        view_pe_rows=rows)
 
 
 def case_views(name):
@@ -109,12 +119,35 @@ def main(only=None):
         model = models[mkey]
         views = case_views(name)
         t0 = time.time()
-        ref = model.infer([dict(v) for v in views], use_amp=False, amp_dtype="fp32", **kw)
+        # the view-PE rows the reference draws (torch.randint from the global CPU generator, after a
+        # device- and input-dependent number of other draws: model.py:999,1056,1223,1313-1362) are part
+        # of the fixture; the tests hand the same rows to the restatement and to the CUDA path
+        drawn, randint = [], torch.randint
+
+        def spy(*a, **k):
+            drawn.append(randint(*a, **k))
+            return drawn[-1]
+
+        torch.manual_seed(CASE_SEED)
+        torch.randint = spy
+        try:
+            ref = model.infer([dict(v) for v in views], use_amp=False, amp_dtype="fp32", **kw)
+        finally:
+            torch.randint = randint
         t_ref = time.time() - t0
         gold = pack_outputs(ref, stride)
+        if drawn:
+            assert len(drawn) == 1
+            gold["view_pe_rows"] = drawn[0].numpy().astype(np.int64)
         np.savez_compressed(os.path.join(GOLDEN_DIR, name + ".npz"), **gold)
         t0 = time.time()
-        mine = pack_outputs(orc.infer(sd, [dict(v) for v in views], aat_opts=margs, **kw), stride)
+        torch.randint = (lambda *a, **k: drawn[0].clone()) if drawn else randint
+        try:
+            mine = pack_outputs(orc.infer(sd, [dict(v) for v in views], aat_opts=margs, **kw), stride)
+        finally:
+            torch.randint = randint
+        if drawn:
+            mine["view_pe_rows"] = gold["view_pe_rows"]
         t_orc = time.time() - t0
         print(f"== {name}: reference {t_ref:.1f}s, restatement {t_orc:.1f}s")
         worst = 0.0

@@ -323,7 +323,12 @@ def _block(x, sd, p, heads, entropy_scaling=False):
 # info_sharing module_args that change the arithmetic (configs/model/info_sharing/*.yaml):
 #   use_entropy_scaling (aat_ifr_24_layers_escaling.yaml), distinguish_ref_and_non_ref_views
 #   (aat_ifr_24_layers_no_ref_view.yaml).  Set by infer(..., aat_opts=...).
-AAT_OPTS = {"use_entropy_scaling": False, "distinguish_ref_and_non_ref_views": True, "indices": (11, 17)}
+#   use_pe_for_non_reference_views (aat.py:30,628-645): every non-reference view adds a row of the
+#   view_pos_table; the rows are drawn with torch.randint(1, max_num_views_for_pe) from the global
+#   generator at every call (use_rand_idx_pe_for_non_reference_views, the default) or are 1..V-1.
+AAT_OPTS = {"use_entropy_scaling": False, "distinguish_ref_and_non_ref_views": True, "indices": (11, 17),
+            "use_pe_for_non_reference_views": False, "max_num_views_for_pe": 1000,
+            "use_rand_idx_pe_for_non_reference_views": True}
 
 
 def alternating_attention_transformer(feats, sd, indices=None, prefix="info_sharing", taps=None):
@@ -338,6 +343,14 @@ def alternating_attention_transformer(feats, sd, indices=None, prefix="info_shar
     heads = sd[prefix + ".norm.weight"].numel() // 64
     if AAT_OPTS["distinguish_ref_and_non_ref_views"]:  # aat.py:618-626
         x = torch.cat([x[:, :T] + sd[prefix + ".view_pos_table"][0].view(1, 1, -1), x[:, T:]], dim=1)
+        if AAT_OPTS["use_pe_for_non_reference_views"]:  # aat.py:554-557,628-645
+            assert V <= AAT_OPTS["max_num_views_for_pe"]
+            if AAT_OPTS["use_rand_idx_pe_for_non_reference_views"]:
+                rows = torch.randint(low=1, high=AAT_OPTS["max_num_views_for_pe"], size=(V - 1,))
+            else:
+                rows = torch.arange(1, V)
+            pe = sd[prefix + ".view_pos_table"][rows.to(x.device)].repeat_interleave(T, dim=0).unsqueeze(0)
+            x = torch.cat([x[:, :T], x[:, T:V * T] + pe, x[:, V * T:]], dim=1)
     es = AAT_OPTS["use_entropy_scaling"]
     if taps is not None:
         taps["aat_in"] = x[0]

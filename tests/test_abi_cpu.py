@@ -74,7 +74,7 @@ def test_constructor_rejects_unbuilt_trunk_configs_before_touching_the_gpu():
         return {"model_type": "alternating_attention", "custom_positional_encoding": None,
                 "module_args": dict(depth=24, indices=[11, 17], **margs)}
 
-    for bad in (cfg(dim=512, num_heads=8), cfg(dim=1024, num_heads=12), cfg(use_pe_for_non_reference_views=True),
+    for bad in (cfg(dim=512, num_heads=8), cfg(dim=1024, num_heads=12),
                 dict(cfg(), model_type="global_attention"), dict(cfg(), custom_positional_encoding=lambda x, p: x)):
         with pytest.raises(NotImplementedError):
             MapAnything(info_sharing_config=bad)
@@ -85,6 +85,7 @@ def test_constructor_rejects_unbuilt_trunk_configs_before_touching_the_gpu():
     with pytest.raises(ValueError, match="2 or 3 indices"):   # model.py:328-331
         MapAnything(info_sharing_config=dict(cfg(), module_args=dict(depth=24, indices=[5, 11, 17, 23])))
     for ok in (cfg(), cfg(use_entropy_scaling=True), cfg(distinguish_ref_and_non_ref_views=False),
+               cfg(use_pe_for_non_reference_views=True, max_num_views_for_pe=64),
                cfg(distinguish_ref_and_non_ref_views=True, max_num_views_for_pe=1000,
                    use_rand_idx_pe_for_non_reference_views=True),    # aat_ifr_24_layers_w_view_pe.yaml
                dict(cfg(), module_args=dict(depth=48, indices=[11, 23, 35], dim=1024, num_heads=16))):  # aat_ifr_48_layers.yaml
@@ -137,6 +138,7 @@ def test_create_refuses_inconsistent_configs():
     lib = _lib.load()
     for change in (dict(aat_tap1=24), dict(aat_tap0=17), dict(aat_dim=1024), dict(aat_dim=512, aat_heads=8),
                    dict(aat_tap2=17), dict(aat_tap2=24), dict(enc_heads=12),
+                   dict(aat_nonref_view_pe=1, aat_ref_view_pe=0),
                    dict(head_chunk=0), dict(patch=16), dict(enc_depth=0)):
         cfg = _lib.MabConfig(**dict(default_config(), **change))
         handle = C.c_void_p()
@@ -192,3 +194,23 @@ def test_state_dict_bookkeeping_follows_the_trunk_width_and_depth():
     assert check_state_dict(shapes, aat_depth=48, aat_dim=1024) == ([], [], [])
     missing, unexpected, mismatch = check_state_dict(shapes)      # into the production configuration
     assert "info_sharing.proj_embed.weight" in missing and unexpected and mismatch
+
+
+def test_view_pe_table_follows_max_num_views():
+    """use_pe_for_non_reference_views: the view_pos_table buffer has max_num_views_for_pe rows of the
+    sinusoid of aat.py:190-200 (row 0 = the reference-view row of every other configuration)."""
+    import numpy as np
+
+    from mapanything_b200 import synthetic
+    from mapanything_b200.model import check_state_dict
+
+    man = synthetic.manifest_for(view_pe_rows=64)
+    assert man["info_sharing.view_pos_table"] == [64, 768]
+    tab = synthetic._gen("info_sharing.view_pos_table", (64, 768))
+    pos, j = 37, 501
+    want = np.cos(pos / np.power(10000, 2 * (j // 2) / 768))
+    assert abs(tab[pos, j] - want) < 1e-6 and tab[0, 0] == 0 and tab[0, 1] == 1
+    assert (tab[:1] == synthetic._gen("info_sharing.view_pos_table", (1, 768))).all()
+    shapes = {k: torch.empty(v, device="meta") for k, v in man.items()}
+    assert check_state_dict(shapes, view_pe_rows=64) == ([], [], [])
+    assert len(check_state_dict(shapes)[2]) == 1   # into the production configuration: size mismatch
