@@ -52,6 +52,10 @@ typedef struct {
    * a row of info_sharing.view_pos_table [max_num_views_for_pe, aat_dim] to its tokens; the rows come
    * from mab_set_view_pe_rows before every forward (the reference draws them with torch.randint). */
   int aat_nonref_view_pe;
+  /* 1: model_type "global_attention" (gat_ifr_24_layers*.yaml, global_attention_transformer.py): every
+   * block attends over all tokens of the scene (the alternating trunk: even blocks only); that model
+   * always encodes every view (aat_ref_view_pe = aat_nonref_view_pe = 1, table of max_num_views rows). */
+  int aat_all_global;
 } mab_config;
 
 /* One scene, `views` views of H x W pixels held by this rank. */

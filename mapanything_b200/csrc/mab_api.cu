@@ -1267,13 +1267,17 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
   return 0;
 }
 
+// gat_ifr_24_layers*.yaml (model_type "global_attention"): every block attends over the whole scene;
+// the alternating trunk does so in its even blocks only (aat.py:657-705)
+static bool global_layer(const mab_config& cf, int layer) { return cf.aat_all_global || layer % 2 == 0; }
+
 extern "C" int mab_stage_aat_qkv(mab_handle* h, int layer, void** qkv_out, int* rows_out,
                                  void* stream) {
   MAB_ARG(h && h->plan.V > 0, "mab_stage_encode must run first");
   MAB_ARG(layer >= 0 && layer < h->cfg.aat_depth, "layer out of range");
   Ctx c{h, (cudaStream_t)stream};
   Plan& p = h->plan;
-  const long long rows = (layer % 2 == 0) ? p.L : (long long)p.V * p.T;  // odd: scale token skips
+  const long long rows = global_layer(h->cfg, layer) ? p.L : (long long)p.V * p.T;  // frame layers: scale token skips
   const std::string b = "info_sharing.self_attention_blocks." + std::to_string(layer);
   MAB_TRY(block_qkv(c, b, p.ys, rows, h->cfg.aat_dim, p.ln, p.qkv));
   if (qkv_out) *qkv_out = p.qkv;
@@ -1304,7 +1308,7 @@ extern "C" int mab_stage_aat_attend(mab_handle* h, int layer, const void* kv, in
   Plan& p = h->plan;
   const int T = p.T, V = p.V;
   const int first = flags & MAB_RING_FIRST, last = flags & MAB_RING_LAST;
-  if (layer % 2 == 0) {  // global attention over every token of the scene (aat.py:657-661)
+  if (global_layer(cf, layer)) {  // global attention over every token of the scene (aat.py:657-661)
     const long long rows = p.L;
     const void* kvp = kv ? kv : p.qkv;
     const int kvr = kv ? kv_rows : (int)rows;
@@ -1338,7 +1342,7 @@ extern "C" int mab_stage_aat_attend_kv(mab_handle* h, int layer, const void* kv,
                                        void* stream) {
   MAB_ARG(h && h->plan.V > 0 && kv && kv_rows > 0, "mab_stage_encode must run first");
   MAB_ARG(layer >= 0 && layer < h->cfg.aat_depth, "layer out of range");
-  MAB_ARG(layer % 2 == 0, "only the global (even) layers attend across ranks");
+  MAB_ARG(global_layer(h->cfg, layer), "only the global layers attend across ranks");
   const mab_config& cf = h->cfg;
   Plan& p = h->plan;
   const int first = flags & MAB_RING_FIRST, last = flags & MAB_RING_LAST;
@@ -1357,7 +1361,7 @@ extern "C" int mab_stage_aat_finish(mab_handle* h, int layer, void* stream) {
   Plan& p = h->plan;
   const int A = cf.aat_dim, T = p.T, V = p.V;
   const std::string b = "info_sharing.self_attention_blocks." + std::to_string(layer);
-  const long long rows = (layer % 2 == 0) ? p.L : (long long)V * T;
+  const long long rows = global_layer(cf, layer) ? p.L : (long long)V * T;
   MAB_TRY(block_tail(c, b, p.ys, rows, A, p.att, p.ln, p.hid, nullptr, nullptr));
   // intermediate taps + final norm (aat.py:706-716), token-major == NHWC for the dense head
   const long long VT = (long long)V * T;

@@ -63,7 +63,7 @@ def default_config():
     return dict(patch=14, enc_dim=1024, enc_depth=24, enc_heads=16, enc_pos_grid=37, aat_dim=768,
                 aat_depth=24, aat_heads=12, aat_tap0=11, aat_tap1=17, head_chunk=8,
                 aat_ref_view_pe=1, aat_entropy_scaling=0, aat_tap2=0,
-                aat_nonref_view_pe=0)
+                aat_nonref_view_pe=0, aat_all_global=0)
 
 
 def head_ranges(V, stream_chunk, default_chunk):
@@ -143,6 +143,13 @@ class MapAnything(torch.nn.Module):
         self._max_views_for_pe = int(margs.get("max_num_views_for_pe", 1000))
         self._rand_view_pe = bool(margs.get("use_rand_idx_pe_for_non_reference_views", True))
         self._check_view_count = bool(margs.get("use_pe_for_non_reference_views", False))
+        if self.info_sharing_config.get("model_type", "alternating_attention") == "global_attention":
+            # gat_ifr_24_layers*.yaml: every block is global and every view is always encoded with a row of
+            # the [max_num_views, dim] table (global_attention_transformer.py:543-560)
+            cfg["aat_all_global"] = cfg["aat_ref_view_pe"] = cfg["aat_nonref_view_pe"] = 1
+            self._max_views_for_pe = int(margs["max_num_views"])
+            self._rand_view_pe = bool(margs["use_rand_idx_pe_for_non_reference_views"])
+            self._check_view_count = True
         self._pinned_view_pe_rows = None
         cfg["head_chunk"] = int(head_chunk)
         self._cfg = _lib.MabConfig(**cfg)
@@ -163,8 +170,14 @@ class MapAnything(torch.nn.Module):
     # ------------------------------------------------------------------ construction helpers
     def _check_supported(self):
         ic = self.info_sharing_config
-        if ic and ic.get("model_type", "alternating_attention") != "alternating_attention":
-            raise NotImplementedError("only the alternating-attention info-sharing model is built")
+        if ic and ic.get("model_type", "alternating_attention") not in ("alternating_attention", "global_attention"):
+            raise NotImplementedError("the alternating- and global-attention info-sharing models are built; "
+                                      "cross_attention (cat_ifr_dust3r.yaml) is a two-view decoder of its own")
+        if ic and ic.get("model_type") == "global_attention":
+            for need in ("max_num_views", "use_rand_idx_pe_for_non_reference_views"):
+                if need not in ic.get("module_args", {}):  # positional in global_attention_transformer.py:350-356
+                    raise TypeError(f"MultiViewGlobalAttentionTransformerIFR.__init__() missing 1 required "
+                                    f"positional argument: '{need}'")
         cpe = (ic or {}).get("custom_positional_encoding")
         if isinstance(cpe, str):  # model.py:259-267: the reference implements none of the named encodings
             raise ValueError(f"Invalid custom_positional_encoding: {cpe}. None implemented.")
@@ -506,7 +519,7 @@ class MapAnything(torch.nn.Module):
         for layer in range(self._cfg.aat_depth):
             _lib.check(lib.mab_stage_aat_qkv(hd, layer, C.byref(qkv_ptr), C.byref(n_rows), self._stream_ptr()),
                        "mab_stage_aat_qkv")
-            if layer % 2 == 0:
+            if self._cfg.aat_all_global or layer % 2 == 0:
                 assert n_rows.value == rows[rank]
                 off = qkv_ptr.value - ws.data_ptr()
                 local = ws[off: off + n_rows.value * width * 2].view(torch.bfloat16).view(n_rows.value, width)

@@ -62,6 +62,13 @@ CASE_MODULE_ARGS["small_viewpe_seq_n3_70x98"] = dict(use_pe_for_non_reference_vi
                                                      use_rand_idx_pe_for_non_reference_views=False)
 CASES["small_viewpe_rand_n3_70x98"] = (3, 70, 98, False, 1, {})
 CASES["small_viewpe_seq_n3_70x98"] = (3, 70, 98, False, 1, {})
+# gat_ifr_24_layers.yaml: model_type "global_attention" (every block global, every view encoded)
+CASE_MODEL_TYPE = {"small_gat_n3_70x98": "global_attention"}
+CASE_MODULE_ARGS["small_gat_n3_70x98"] = dict(name="gat_24_layers_ifr", max_num_views=64,
+                                              use_rand_idx_pe_for_non_reference_views=True, indices=[11, 17],
+                                              norm_intermediate=True, size="24_layers", depth=24,
+                                              gradient_checkpointing=False)
+CASES["small_gat_n3_70x98"] = (3, 70, 98, False, 1, {})
 CASE_SEED = 1234  # torch.manual_seed before every run of a case: the random view-PE rows are part of the case
 
 
@@ -69,8 +76,14 @@ def case_state_dict(name):
     """The synthetic checkpoint of a case: same generator, shapes of that case's trunk."""
     margs = CASE_MODULE_ARGS.get(name, {})
     rows = margs.get("max_num_views_for_pe", 1000) if margs.get("use_pe_for_non_reference_views") else 1
+    rows = margs.get("max_num_views", rows)  # global_attention: always a [max_num_views, dim] table
     return weights.synthetic_state_dict(aat_dim=margs.get("dim", 768), aat_depth=margs.get("depth", 24),
                                         view_pe_rows=rows)
+
+def case_info_sharing_config(name):
+    """info_sharing_config overrides of a case, as MapAnything(info_sharing_config=...) takes them."""
+    return {"model_type": CASE_MODEL_TYPE.get(name, "alternating_attention"), "custom_positional_encoding": None,
+            "module_args": dict(CASE_MODULE_ARGS.get(name, {}))}
 
 
 def case_views(name):
@@ -107,9 +120,10 @@ def main(only=None):
             continue
         margs = CASE_MODULE_ARGS.get(name, {})
         sd = case_state_dict(name)
-        mkey = repr(sorted(margs.items()))
+        mkey = repr(sorted(margs.items())) + CASE_MODEL_TYPE.get(name, "")
+        oopts = orc.aat_opts_for(case_info_sharing_config(name))
         if mkey not in models:
-            models[mkey] = ref_shim.build_reference_model(sd, margs)
+            models[mkey] = ref_shim.build_reference_model(sd, margs, CASE_MODEL_TYPE.get(name))
             # the derived manifest is the live reference's key space and shapes for this variant
             live = {k: list(v.shape) for k, v in models[mkey].state_dict().items()}
             mine = {k: list(v.shape) for k, v in sd.items()}
@@ -143,7 +157,7 @@ def main(only=None):
         t0 = time.time()
         torch.randint = (lambda *a, **k: drawn[0].clone()) if drawn else randint
         try:
-            mine = pack_outputs(orc.infer(sd, [dict(v) for v in views], aat_opts=margs, **kw), stride)
+            mine = pack_outputs(orc.infer(sd, [dict(v) for v in views], aat_opts=oopts, **kw), stride)
         finally:
             torch.randint = randint
         if drawn:

@@ -328,7 +328,19 @@ def _block(x, sd, p, heads, entropy_scaling=False):
 #   generator at every call (use_rand_idx_pe_for_non_reference_views, the default) or are 1..V-1.
 AAT_OPTS = {"use_entropy_scaling": False, "distinguish_ref_and_non_ref_views": True, "indices": (11, 17),
             "use_pe_for_non_reference_views": False, "max_num_views_for_pe": 1000,
-            "use_rand_idx_pe_for_non_reference_views": True}
+            "use_rand_idx_pe_for_non_reference_views": True,
+            # model_type "global_attention" (global_attention_transformer.py:213-345,530-640): every block
+            # attends over the whole scene and every view takes a row of the [max_num_views, dim] table
+            "all_global": False}
+
+
+def aat_opts_for(info_sharing_config):
+    """AAT_OPTS overrides of an info_sharing config dict (model_type + module_args)."""
+    margs = dict(info_sharing_config.get("module_args", {}))
+    if info_sharing_config.get("model_type", "alternating_attention") == "global_attention":
+        margs.update(all_global=True, distinguish_ref_and_non_ref_views=True, use_pe_for_non_reference_views=True,
+                     max_num_views_for_pe=margs["max_num_views"])
+    return margs
 
 
 def alternating_attention_transformer(feats, sd, indices=None, prefix="info_sharing", taps=None):
@@ -358,7 +370,7 @@ def alternating_attention_transformer(feats, sd, indices=None, prefix="info_shar
     inter = []
     for i in range(depth):
         p = f"{prefix}.self_attention_blocks.{i}"
-        if i % 2 == 0:
+        if AAT_OPTS["all_global"] or i % 2 == 0:
             x = _block(x, sd, p, heads, es)
         else:
             extra = x[:, V * T:]

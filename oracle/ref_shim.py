@@ -149,7 +149,7 @@ def reference_config():
     return cfg
 
 
-def build_reference_model(state_dict=None, module_args=None):
+def build_reference_model(state_dict=None, module_args=None, model_type=None):
     """Construct the reference MapAnything (CPU, fp32, eval); optionally load a state dict.
     module_args: overrides of info_sharing_config.module_args (the configs/model/info_sharing/*.yaml
     variants, e.g. use_entropy_scaling=True, distinguish_ref_and_non_ref_views=False)."""
@@ -157,11 +157,16 @@ def build_reference_model(state_dict=None, module_args=None):
     from mapanything.models.mapanything.model import MapAnything
 
     cfg = copy.deepcopy(reference_config())
-    cfg["info_sharing_config"]["module_args"].update(module_args or {})
+    if model_type is not None and model_type != cfg["info_sharing_config"]["model_type"]:
+        # another transformer class (gat_ifr_24_layers.yaml): its module_args replace the AAT ones
+        cfg["info_sharing_config"]["model_type"] = model_type
+        cfg["info_sharing_config"]["module_args"] = dict(module_args or {})
+    else:
+        cfg["info_sharing_config"]["module_args"].update(module_args or {})
     model = MapAnything(**cfg).eval()
     if state_dict is not None:
         sd = dict(state_dict)
-        if not cfg["info_sharing_config"]["module_args"]["distinguish_ref_and_non_ref_views"]:
+        if not cfg["info_sharing_config"]["module_args"].get("distinguish_ref_and_non_ref_views", True):
             sd.pop("info_sharing.view_pos_table", None)  # the buffer only exists with the reference-view PE
         missing, unexpected = model.load_state_dict(sd, strict=True)
         assert not missing and not unexpected

@@ -75,17 +75,21 @@ def test_constructor_rejects_unbuilt_trunk_configs_before_touching_the_gpu():
                 "module_args": dict(depth=24, indices=[11, 17], **margs)}
 
     for bad in (cfg(dim=512, num_heads=8), cfg(dim=1024, num_heads=12),
-                dict(cfg(), model_type="global_attention"), dict(cfg(), custom_positional_encoding=lambda x, p: x)):
+                dict(cfg(), model_type="cross_attention"), dict(cfg(), custom_positional_encoding=lambda x, p: x)):
         with pytest.raises(NotImplementedError):
             MapAnything(info_sharing_config=bad)
     with pytest.raises(NotImplementedError):
         MapAnything(pred_head_config={"type": "dpt"})
+    with pytest.raises(TypeError, match="max_num_views"):      # gat_ifr_*.yaml: required by the GAT constructor
+        MapAnything(info_sharing_config=dict(cfg(), model_type="global_attention"))
     with pytest.raises(ValueError, match="None implemented"):  # model.py:259-267
         MapAnything(info_sharing_config=dict(cfg(), custom_positional_encoding="RoPE100"))
     with pytest.raises(ValueError, match="2 or 3 indices"):   # model.py:328-331
         MapAnything(info_sharing_config=dict(cfg(), module_args=dict(depth=24, indices=[5, 11, 17, 23])))
     for ok in (cfg(), cfg(use_entropy_scaling=True), cfg(distinguish_ref_and_non_ref_views=False),
                cfg(use_pe_for_non_reference_views=True, max_num_views_for_pe=64),
+               dict(cfg(max_num_views=1000, use_rand_idx_pe_for_non_reference_views=True),
+                    model_type="global_attention"),                  # gat_ifr_24_layers.yaml
                cfg(distinguish_ref_and_non_ref_views=True, max_num_views_for_pe=1000,
                    use_rand_idx_pe_for_non_reference_views=True),    # aat_ifr_24_layers_w_view_pe.yaml
                dict(cfg(), module_args=dict(depth=48, indices=[11, 23, 35], dim=1024, num_heads=16))):  # aat_ifr_48_layers.yaml

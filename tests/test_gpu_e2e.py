@@ -79,23 +79,24 @@ def test_infer_matches_reference_golden(name, model, sd_cuda):
 
 
 @pytest.mark.parametrize("name", ["small_escaling_n3_70x98", "small_noref_n3_70x98",
-                                  "small_viewpe_rand_n3_70x98", "small_viewpe_seq_n3_70x98"])
+                                  "small_viewpe_rand_n3_70x98", "small_viewpe_seq_n3_70x98", "small_gat_n3_70x98"])
 def test_info_sharing_variants_match_reference_golden(name, synthetic_sd, sd_cuda, monkeypatch):
-    """configs/model/info_sharing/aat_ifr_24_layers_escaling.yaml (entropy-scaled attention) and
-    aat_ifr_24_layers_no_ref_view.yaml (no reference-view PE) against goldens of the LIVE reference built
-    with those module_args; same tolerances and bf16 yardstick as the production config."""
+    """configs/model/info_sharing/aat_ifr_24_layers_escaling.yaml (entropy-scaled attention),
+    aat_ifr_24_layers_no_ref_view.yaml (no reference-view PE), use_pe_for_non_reference_views (random and
+    sequential rows) and gat_ifr_24_layers.yaml (model_type "global_attention") against goldens of the LIVE
+    reference built with those configs; same tolerances and bf16 yardstick as the production config."""
     from mapanything_b200 import MapAnything
     from oracle import make_golden
     from oracle import mapanything_oracle as orc
     from tests import helpers
 
     margs = make_golden.CASE_MODULE_ARGS[name]
-    m = MapAnything(device="cuda:0", head_chunk=2,
-                    info_sharing_config={"model_type": "alternating_attention", "module_args": dict(margs)})
+    m = MapAnything(device="cuda:0", head_chunk=2, info_sharing_config=make_golden.case_info_sharing_config(name))
+    oopts = orc.aat_opts_for(make_golden.case_info_sharing_config(name))
     sd = dict(synthetic_sd)
     if not margs.get("distinguish_ref_and_non_ref_views", True):
         sd.pop("info_sharing.view_pos_table")  # such a checkpoint has no view_pos_table buffer
-    if margs.get("use_pe_for_non_reference_views"):  # the table has max_num_views_for_pe rows (aat.py:160-166)
+    if margs.get("use_pe_for_non_reference_views") or "max_num_views" in margs:  # a table of max_num_views(_for_pe) rows
         sd = make_golden.case_state_dict(name)
         sd_cuda = {k: v.cuda() for k, v in sd.items()}
     m.load_state_dict(sd)
@@ -109,7 +110,7 @@ def test_info_sharing_variants_match_reference_golden(name, synthetic_sd, sd_cud
     preds = m.infer([dict(v) for v in views], **kw)
     torch.cuda.synchronize()
     rep = helpers.compare_with_golden(preds, g, stride, None, None)
-    yard = helpers.compare_with_golden(orc.infer(sd_cuda, _to_cuda(views), amp=True, aat_opts=margs, **kw), g,
+    yard = helpers.compare_with_golden(orc.infer(sd_cuda, _to_cuda(views), amp=True, aat_opts=oopts, **kw), g,
                                        stride, None, None)
     print("libmab200  :", {k: round(v, 5) for k, v in rep.items()})
     print("ref bf16   :", {k: round(v, 5) for k, v in yard.items()})

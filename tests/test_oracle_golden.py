@@ -10,7 +10,7 @@ from tests import helpers
 
 CASES = ["small_n3_70x98", "small_mm_n3_70x98", "small_conf_n2_56x84", "c1_loose_n2_392x518",
          "small_escaling_n3_70x98", "small_noref_n3_70x98", "small_48l_n2_56x84",
-         "small_viewpe_rand_n3_70x98", "small_viewpe_seq_n3_70x98"]
+         "small_viewpe_rand_n3_70x98", "small_viewpe_seq_n3_70x98", "small_gat_n3_70x98"]
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -19,12 +19,12 @@ def test_restatement_matches_reference_golden(name, synthetic_sd, monkeypatch):
     views = make_golden.case_views(name)
     margs = make_golden.CASE_MODULE_ARGS.get(name, {})
     # the 48-layer trunk and the view-PE table have their own shapes
-    own = "dim" in margs or margs.get("use_pe_for_non_reference_views")
+    own = "dim" in margs or margs.get("use_pe_for_non_reference_views") or "max_num_views" in margs
     sd = make_golden.case_state_dict(name) if own else synthetic_sd
     g = helpers.load_golden(name)
     if "view_pe_rows" in g:  # the rows the reference drew for this fixture (torch.randint, aat.py:631)
         monkeypatch.setattr(torch, "randint", lambda *a, **k: torch.from_numpy(g["view_pe_rows"]))
-    preds = orc.infer(sd, views, aat_opts=margs, **kw)
+    preds = orc.infer(sd, views, aat_opts=orc.aat_opts_for(make_golden.case_info_sharing_config(name)), **kw)
     monkeypatch.undo()
     rep = helpers.compare_with_golden(preds, g, stride, tol_dense=2e-5, tol_pose_deg=1e-3,
                                       min_mask_agree=0.9995)
