@@ -218,3 +218,42 @@ def test_view_pe_table_follows_max_num_views():
     shapes = {k: torch.empty(v, device="meta") for k, v in man.items()}
     assert check_state_dict(shapes, view_pe_rows=64) == ([], [], [])
     assert len(check_state_dict(shapes)[2]) == 1   # into the production configuration: size mismatch
+
+
+def test_view_pe_rows_are_drawn_like_the_reference(monkeypatch):
+    """aat.py:628-636 / global_attention_transformer.py:552-556: row 0 for the reference view, then
+    torch.randint(1, max_num_views_for_pe, (V-1,)) from the global CPU generator, or 1..V-1; the rows of
+    a rank's own views reach the library, one per view."""
+    from mapanything_b200 import _lib
+    from mapanything_b200.model import MapAnything
+
+    class FakeLib:
+        def mab_set_view_pe_rows(self, handle, rows, n):
+            self.rows = [rows[i] for i in range(n)]
+            return 0
+
+    m = MapAnything.__new__(MapAnything)   # host logic only: no device, no library
+    m._cfg = _lib.MabConfig(aat_nonref_view_pe=1)
+    m._lib, m._handle, m._pinned_view_pe_rows = FakeLib(), None, None
+    m._max_views_for_pe, m._rand_view_pe, m._check_view_count = 64, True, True
+
+    torch.manual_seed(7)
+    want = torch.randint(low=1, high=64, size=(4,))
+    torch.manual_seed(7)
+    rows = m._draw_view_pe_rows(5)
+    assert rows.tolist() == [0] + want.tolist()
+    torch.manual_seed(7)
+    m._set_view_pe_rows(2, 2, 5)            # a shard holding views 2 and 3 of 5
+    assert m._lib.rows == want.tolist()[1:3]
+    m._rand_view_pe = False
+    m._set_view_pe_rows(0, 5, 5)
+    assert m._lib.rows == [0, 1, 2, 3, 4]
+    m._pinned_view_pe_rows = torch.tensor([0, 9, 8, 7, 6])   # one draw for all scenes of a batched call
+    m._set_view_pe_rows(1, 3, 5)
+    assert m._lib.rows == [9, 8, 7]
+    with pytest.raises(AssertionError, match="Expected less than 64 views"):
+        m._set_view_pe_rows(0, 65, 65)
+    m._cfg = _lib.MabConfig(aat_nonref_view_pe=0)             # other configurations: nothing is set
+    m._lib.rows, m._check_view_count = None, False
+    m._set_view_pe_rows(0, 5, 5)
+    assert m._lib.rows is None
