@@ -197,6 +197,37 @@ class MapAnything(torch.nn.Module):
         pc = self.pred_head_config
         if pc and pc.get("type", "dpt+pose") != "dpt+pose":
             raise NotImplementedError("only the dpt+pose head is built")
+        # the fused regressor epilogue is the production adaptor (pred_head/adaptor_config/
+        # raydirs_depth_pose_confidence_mask_scale.yaml): anything else must be refused, not mis-computed
+        inf = float("inf")
+        want = {
+            None: dict(adaptor_type="raydirs+depth+pose+confidence+mask"),
+            "feature_head": dict(feature_dim=256, hooks=[0, 1, 2, 3]),
+            "regressor_head": dict(output_dim=6),
+            "pose_head": dict(num_resconv_block=2, rot_representation_dim=4),
+            "scale_head": dict(output_dim=1),
+            "dpt_adaptor": dict(ray_directions_mode="linear", ray_directions_normalize_to_unit_sphere=True,
+                                ray_directions_normalize_to_unit_image_plane=False, ray_directions_vmin=-inf,
+                                ray_directions_vmax=inf, ray_directions_clamp_min_of_z_dir=False, depth_mode="exp",
+                                depth_vmin=0, depth_vmax=inf, confidence_type="exp", confidence_vmin=1,
+                                confidence_vmax=inf),
+            "pose_adaptor": dict(cam_trans_mode="linear", cam_trans_vmin=-inf, cam_trans_vmax=inf,
+                                 quaternions_mode="linear", quaternions_normalize=True, quaternions_vmin=-inf,
+                                 quaternions_vmax=inf),
+            "scale_adaptor": dict(mode="exp", vmin=1e-8, vmax=inf),
+        }
+        for section, fields in want.items():
+            got = pc if section is None else pc.get(section) or {}
+            for k, v in fields.items():
+                if k in got and (list(got[k]) if isinstance(v, list) else got[k]) != v:
+                    where = f"pred_head_config[{section!r}]" if section else "pred_head_config"
+                    raise NotImplementedError(f"{where}[{k!r}] = {got[k]!r}: the built head is the production "
+                                              f"configuration ({k} = {v!r})")
+        ec = self.encoder_config
+        if ec.get("name", "dinov2_large") != "dinov2_large" or ec.get("with_registers", False):
+            raise NotImplementedError("only the dinov2_large encoder (ViT-L/14, no registers) is built")
+        if self.data_norm_type != "dinov2":
+            raise NotImplementedError("the encoder takes dinov2-normalised images")
 
     @classmethod
     def from_pretrained(cls, path: str, device="cuda", **kwargs):

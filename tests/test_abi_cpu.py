@@ -257,3 +257,45 @@ def test_view_pe_rows_are_drawn_like_the_reference(monkeypatch):
     m._lib.rows, m._check_view_count = None, False
     m._set_view_pe_rows(0, 5, 5)
     assert m._lib.rows is None
+
+
+def test_production_config_is_accepted_and_other_heads_are_refused():
+    """The constructor computes exactly one head / adaptor configuration (pred_head/dpt_pose_scale.yaml +
+    adaptor_config/raydirs_depth_pose_confidence_mask_scale.yaml): the production config, as config.json
+    carries it, passes the checks; a deviating one is refused by name instead of being mis-computed."""
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import copy
+    import json
+
+    from mapanything_b200 import MapAnything
+    from oracle import ref_shim
+
+    cfg = json.loads(json.dumps(ref_shim.reference_config()))  # +-inf survive as Infinity, like huggingface_hub's file
+    keys = ("name", "encoder_config", "info_sharing_config", "pred_head_config", "geometric_input_config")
+    prod = {k: cfg[k] for k in keys if k in cfg}
+    with pytest.raises(RuntimeError, match="CUDA device"):
+        MapAnything(**copy.deepcopy(prod))
+
+    def variant(path, value):
+        c = copy.deepcopy(prod)
+        d = c
+        for k in path[:-1]:
+            d = d[k]
+        d[path[-1]] = value
+        return c
+
+    for path, value in ((("pred_head_config", "adaptor_type"), "pointmap+confidence"),
+                        (("pred_head_config", "dpt_adaptor", "depth_mode"), "linear"),
+                        (("pred_head_config", "dpt_adaptor", "confidence_vmin"), 0),
+                        (("pred_head_config", "dpt_adaptor", "ray_directions_normalize_to_unit_sphere"), False),
+                        (("pred_head_config", "pose_adaptor", "quaternions_normalize"), False),
+                        (("pred_head_config", "scale_adaptor", "mode"), "linear"),
+                        (("pred_head_config", "feature_head", "feature_dim"), 128),
+                        (("pred_head_config", "feature_head", "hooks"), [0, 1, 2]),
+                        (("pred_head_config", "pose_head", "num_resconv_block"), 3),
+                        (("pred_head_config", "regressor_head", "output_dim"), 4),
+                        (("encoder_config", "name"), "dinov2_giant"),
+                        (("encoder_config", "data_norm_type"), "dust3r")):
+        with pytest.raises(NotImplementedError):
+            MapAnything(**variant(path, value))
