@@ -140,3 +140,53 @@ def test_gather_pass_gloo(world, n_views):
             assert p.exitcode == 0, f"rank exited with {p.exitcode}"
         assert len(result) == world
         assert max(result.values()) < 1e-5, dict(result)
+
+
+def _view_pe_worker(rank, world, port, total, result):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from mapanything_b200 import _lib
+        from mapanything_b200.model import MapAnything
+
+        class FakeLib:
+            def mab_set_view_pe_rows(self, handle, rows, n):
+                self.rows = [rows[i] for i in range(n)]
+                return 0
+
+        m = MapAnything.__new__(MapAnything)   # host logic only: no device, no library
+        m._cfg = _lib.MabConfig(aat_nonref_view_pe=1)
+        m._lib, m._handle, m._pinned_view_pe_rows = FakeLib(), None, None
+        m._max_views_for_pe, m._rand_view_pe, m._check_view_count = 1000, True, True
+        m._device = torch.device("cpu")
+        torch.manual_seed(100 + rank)          # the ranks' generators disagree: rank 0's draw must win
+        lo, hi = parallel.shard_views(total, world, rank)
+        m._set_view_pe_rows(lo, hi - lo, total)
+        result[rank] = (lo, m._lib.rows)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_view_pe_rows_agree_across_ranks_gloo():
+    """use_pe_for_non_reference_views on a view-sharded scene: every rank draws from its own generator,
+    rank 0's rows are broadcast, and each rank hands the library the rows of its own views."""
+    world, total = 2, 7
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as man:
+        result = man.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_view_pe_worker, args=(r, world, port, total, result)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(120)
+            assert p.exitcode == 0, f"rank exited with {p.exitcode}"
+        torch.manual_seed(100)
+        want = [0] + torch.randint(low=1, high=1000, size=(total - 1,)).tolist()
+        got = []
+        for r in range(world):
+            lo, rows = result[r]
+            assert lo == len(got)
+            got += rows
+        assert got == want
