@@ -69,6 +69,8 @@ CASE_MODULE_ARGS["small_gat_n3_70x98"] = dict(name="gat_24_layers_ifr", max_num_
                                               norm_intermediate=True, size="24_layers", depth=24,
                                               gradient_checkpointing=False)
 CASES["small_gat_n3_70x98"] = (3, 70, 98, False, 1, {})
+# a single view: global attention over one view's tokens + the scale token, identity pose
+CASES["small_n1_56x84"] = (1, 56, 84, False, 1, {})
 CASE_SEED = 1234  # torch.manual_seed before every run of a case: the random view-PE rows are part of the case
 
 

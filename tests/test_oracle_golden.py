@@ -8,7 +8,7 @@ import torch
 from oracle import make_golden, mapanything_oracle as orc
 from tests import helpers
 
-CASES = ["small_n3_70x98", "small_mm_n3_70x98", "small_conf_n2_56x84", "c1_loose_n2_392x518",
+CASES = ["small_n1_56x84", "small_n3_70x98", "small_mm_n3_70x98", "small_conf_n2_56x84", "c1_loose_n2_392x518",
          "small_escaling_n3_70x98", "small_noref_n3_70x98", "small_48l_n2_56x84",
          "small_viewpe_rand_n3_70x98", "small_viewpe_seq_n3_70x98", "small_gat_n3_70x98"]
 
