@@ -181,6 +181,9 @@ int mab_stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out,
  * per-launch CUDA-event profiler (events recorded on the launch stream around every kernel). */
 enum { MAB_CAT_GEMM = 0, MAB_CAT_CONV3 = 1, MAB_CAT_CONV3_REGRESS = 2, MAB_CAT_ATTENTION = 3,
        MAB_CAT_LAYERNORM = 4, MAB_CAT_ELEMENTWISE = 5, MAB_CAT_POSTPROCESS = 6, MAB_CAT_COUNT = 7 };
+/* K/V length up to which mab_attention uses the one-Q-tile kernel (two CTAs per SM) instead of the
+ * two-Q-tile kernel; < 0 restores the default (6000).  Test hook: both kernels at small sizes. */
+int mab_set_attention_short_max(int kv_len);
 long long mab_launch_count(void);
 int mab_prof_enable(int on); /* also clears the records */
 /* synchronises the device; sums device time, algorithmic FLOPs and bytes of one category */

@@ -70,6 +70,7 @@ SYMBOLS = {
     "mab_normalize_rays": (_i, [_vp, C.c_longlong, _vp, _vp]),
     "mab_depth_z_to_along_ray": (_i, [_vp, _vp, C.c_longlong, _vp, _vp]),
     "mab_stage_heads_range": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), _i, _i, _vp]),
+    "mab_set_attention_short_max": (_i, [_i]),
     "mab_launch_count": (C.c_longlong, []),
     "mab_prof_enable": (_i, [_i]),
     "mab_prof_query": (_i, [_i, C.POINTER(C.c_longlong), C.POINTER(C.c_double), C.POINTER(C.c_double),

@@ -51,17 +51,29 @@ constexpr int ATT_KV_STAGES = 4;
 #define ATT_POLY_MASK_SHORT 0x0101   // short sequences (one Q tile per CTA, two CTAs per SM)
 #endif
 #ifndef ATT_NO_TURNS
-#define ATT_NO_TURNS 0
+#define ATT_NO_TURNS 1   // measured with two threads per row (66 305 tokens): turns 686, no turns 816 TFLOP/s
 #endif
 // QT = 2: 4 control warps (one per scheduler partition) + 8 softmax warps, 4-stage K/V rings, 512 TMEM columns.
 // QT = 1: 2 control warps + 4 softmax warps, 2-stage rings, 256 TMEM columns -> two CTAs per SM whose
 //         prologues / epilogues / MMA latencies overlap each other (short sequences: 9 K/V tiles per CTA).
+// ATT_SPLIT threads share one query row (each owns 128 / ATT_SPLIT of the S columns of a K/V tile).  With
+// one thread per row a scheduler partition holds ONE softmax warp per Q tile, and a single in-order warp
+// has to cover its own MUFU / FMA latencies (~400 issued instructions per row and K/V tile at 0.46 IPC).
+// Two threads per row put two warps of the same tile on every partition: the halves of a row run
+// concurrently and only exchange the row max (through shared memory) and, once per CTA, the row sum.
+// Measured (profiles/r2_attn_variants.txt, 66 305 / 8289 tokens): 1 thread per row 716 / 599 TFLOP/s,
+// 2 threads with the exp-pass turns 686 / 576, 2 threads without turns 816 / 656.
+#ifndef ATT_SPLIT
+#define ATT_SPLIT 2
+#endif
 template <int QT> struct AttCfg {
   static constexpr int CTRL_WARPS = QT == 2 ? 4 : 2;
-  static constexpr int THREADS = 32 * CTRL_WARPS + QT * 128;
+  static constexpr int SOFTMAX_THREADS = QT * 128 * ATT_SPLIT;
+  static constexpr int THREADS = 32 * CTRL_WARPS + SOFTMAX_THREADS;
   static constexpr int STAGES = QT == 2 ? 4 : 2;
   static constexpr int TMEM_COLS = QT == 2 ? 512 : 256;
-  static constexpr int SMEM_BYTES = (QT + 2 * STAGES) * 128 * 64 * 2 + 512 + 1024;
+  static constexpr int XCH_BYTES = 2 * QT * 2 * 128 * 4;  // row-max / row-sum exchange, double-buffered
+  static constexpr int SMEM_BYTES = (QT + 2 * STAGES) * 128 * 64 * 2 + 512 + XCH_BYTES + 1024;
 };
 constexpr int ATT_THREADS = AttCfg<2>::THREADS;
 constexpr int ATT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: Q, K and V tiles alike
@@ -122,6 +134,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   constexpr int KS = AttCfg<QT>::STAGES;
   constexpr int POLY_MASK = QT == 2 ? ATT_POLY_MASK : ATT_POLY_MASK_SHORT;
   constexpr int CTRL = AttCfg<QT>::CTRL_WARPS;
+  constexpr int SPLIT = ATT_SPLIT;           // threads per query row
+  constexpr int NC = ATT_BKV / SPLIT;        // S columns of one K/V tile per thread
+  constexpr int OC = ATT_D / SPLIT;          // O columns per thread
+  constexpr int TILE_THREADS = ATT_BQ * SPLIT;
+  static_assert(SPLIT == 1 || SPLIT == 2, "one or two threads per query row");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
@@ -139,6 +156,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint64_t* p_full = s_free + QT;              // [QT]  P_t(j) is in TMEM (and O_t rescaled)
   uint64_t* pv_done = p_full + QT;             // [QT]  O_t += P_t(j) V_j has completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + QT);
+  float* xch = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);  // [2][QT][2][128]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q_tile = blockIdx.x, head = blockIdx.y, seq = blockIdx.z;
@@ -161,8 +179,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     }
     for (int t = 0; t < QT; ++t) {
       mbar_init(&s_full[t], 1);
-      mbar_init(&s_free[t], 4);  // one arrive per softmax warp of the tile
-      mbar_init(&p_full[t], 4);
+      mbar_init(&s_free[t], 4 * SPLIT);  // one arrive per softmax warp of the tile
+      mbar_init(&p_full[t], 4 * SPLIT);
       mbar_init(&pv_done[t], 1);
     }
     fence_barrier_init();
@@ -248,12 +266,18 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     }
   } else if (warp >= CTRL) {
     // ===================================== softmax ========================================
-    const int t = (warp - CTRL) >> 2;                      // Q tile of this warp
+    const int sw = warp - CTRL;                         // softmax warp index: (tile, column half, quarter)
+    const int t = sw / (4 * SPLIT);                     // Q tile of this warp
+    const int hf = SPLIT == 2 ? (sw >> 2) & 1 : 0;      // which half of the S / O columns this thread owns
     const int q = warp & 3;                             // TMEM lane quarter (warp id % 4)
     const int row = q * 32 + lane;                      // query row within the tile
     const uint32_t lane_addr = uint32_t(q * 32) << 16;
     const bool row_ok = q_tile * (QT * ATT_BQ) + t * ATT_BQ + row < p.q_len;
     const long long grow = (long long)q_row0 + t * ATT_BQ + row;
+    // row-max exchange slot of (buffer, tile, half, row); the two warps that share 32 rows meet on
+    // named barrier 3 + 4 t + q (64 threads)
+    auto xslot = [&](int buf, int h) { return xch + ((buf * QT + t) * 2 + h) * 128 + row; };
+    const int pair_bar = 3 + 4 * t + q;
     // A warp whose 32 rows all lie beyond the sequence (1037 = 8 * 128 + 13: three of the four warps
     // of every sequence's last tile) only keeps the barrier protocol going: no TMEM traffic, no
     // exponentials, so the MUFU of the SM goes to the co-resident CTA.  Short-sequence kernel only:
@@ -268,32 +292,30 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         if (lane == 0) mbar_arrive(&p_full[t]);
       }
     } else if (t < ntile) {
-      const uint32_t ts = TM_S(t) + lane_addr, to = TM_O(t) + lane_addr, tp = TM_P(t) + lane_addr;
+      const uint32_t ts = TM_S(t) + lane_addr + hf * NC, to = TM_O(t) + lane_addr + hf * OC,
+                     tp = TM_P(t) + lane_addr + hf * (NC / 2);
       const float sc = p.scale_log2e;
       const uint64_t sc2 = pack_f2(sc, sc);
       float m_ref = -INFINITY, l_run = 0.f;  // reference max of the exponentials, running sum
       if (p.carry_in) {  // resume from the carried state: O_t <- carry_o
-        uint32_t o[32];
+        uint32_t o[OC];
+        if (row_ok) {
+          const float4* src = reinterpret_cast<const float4*>(p.carry_o + grow * p.ldo + head * ATT_D + hf * OC);
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          if (row_ok) {
-            const float4* src = reinterpret_cast<const float4*>(p.carry_o + grow * p.ldo + head * ATT_D + h * 32);
-#pragma unroll
-            for (int d = 0; d < 8; ++d) {
-              const float4 v = src[d];
-              o[4 * d] = __float_as_uint(v.x); o[4 * d + 1] = __float_as_uint(v.y);
-              o[4 * d + 2] = __float_as_uint(v.z); o[4 * d + 3] = __float_as_uint(v.w);
-            }
-          } else {
-#pragma unroll
-            for (int d = 0; d < 32; ++d) o[d] = 0u;
+          for (int d = 0; d < OC / 4; ++d) {
+            const float4 v = src[d];
+            o[4 * d] = __float_as_uint(v.x); o[4 * d + 1] = __float_as_uint(v.y);
+            o[4 * d + 2] = __float_as_uint(v.z); o[4 * d + 3] = __float_as_uint(v.w);
           }
-          MAB_TMEM_ST_16(to + h * 32, o);
-          MAB_TMEM_ST_16(to + h * 32 + 16, (o + 16));
+        } else {
+#pragma unroll
+          for (int d = 0; d < OC; ++d) o[d] = 0u;
         }
+#pragma unroll
+        for (int c = 0; c < OC; c += 16) MAB_TMEM_ST_16(to + c, (o + c));
         if (row_ok) {
           const float2 ml = *reinterpret_cast<const float2*>(p.carry_ml + (grow * p.heads + head) * 2);
-          m_ref = ml.x; l_run = ml.y;
+          m_ref = ml.x; l_run = hf == 0 ? ml.y : 0.f;  // the halves' sums are added at the end
         }
         tmem_wait_st();
       }
@@ -302,42 +324,49 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       // barriers 1 = "A's turn", 2 = "B's turn") so that one tile's TMEM traffic, barrier waits and
       // MMA latency always sit under the other tile's exp pass.
       const bool take_turns = ntile == 2 && !ATT_NO_TURNS;
-      if (take_turns && t == 1) bar_arrive_named(1, 2 * ATT_BQ);  // tile A goes first
+      if (take_turns && t == 1) bar_arrive_named(1, 2 * TILE_THREADS);  // tile A goes first
       // One K/V tile of the softmax.  Full tiles and the partial last tile of a sequence are two
       // separate instantiations, so that the hot (full) body stays one straight-line block.
       auto kv_tile = [&](const int j, auto full_tag) {
         constexpr bool full = decltype(full_tag)::value;
-        const int valid = p.kv_len - j * ATT_BKV;  // columns >= valid are padding / next sequence
+        // columns >= valid (of this thread's NC) are padding / the next sequence
+        const int valid = p.kv_len - j * ATT_BKV - hf * NC;
         mbar_wait(&s_full[t], j & 1);
         tc_fence_after();
         // ---- the whole S row into registers, then hand S_t back to the tensor core ----
-        uint32_t v[128];
-        MAB_TMEM_LD_32(ts, v);
-        MAB_TMEM_LD_32(ts + 32, (v + 32));
-        MAB_TMEM_LD_32(ts + 64, (v + 64));
-        MAB_TMEM_LD_32(ts + 96, (v + 96));
+        uint32_t v[NC];
+#pragma unroll
+        for (int c = 0; c < NC; c += 32) MAB_TMEM_LD_32(ts + c, (v + c));
         tmem_wait_ld();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&s_free[t]);
 #if !ATT_TURN_LATE
-        if (take_turns) bar_sync_named(1 + t, 2 * ATT_BQ);
+        if (take_turns) bar_sync_named(1 + t, 2 * TILE_THREADS);
 #endif
-        if (!full || (QT == 2 && valid < ATT_BKV)) {  // partial last tile: columns >= valid become -inf (exp2 -> 0), common path unmasked
+        if (!full || (QT == 2 && valid < NC)) {  // partial last tile: columns >= valid become -inf (exp2 -> 0), common path unmasked
 #pragma unroll
-          for (int i = 0; i < 128; ++i)
+          for (int i = 0; i < NC; ++i)
             if (i >= valid) v[i] = 0xff800000u;
         }
         // ---- row max (four independent chains) ----
         float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < 128; i += 8) {
+        for (int i = 0; i < NC; i += 8) {
           mx0 = max3(mx0, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
           mx1 = max3(mx1, __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
           mx2 = max3(mx2, __uint_as_float(v[i + 4]), __uint_as_float(v[i + 5]));
           mx3 = max3(mx3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
         }
-        const float mx = fmaxf(max3(mx0, mx1, mx2), mx3);  // finite: every tile has >= 1 valid column
+        float mx = fmaxf(max3(mx0, mx1, mx2), mx3);
+        if (SPLIT == 2) {
+          // the other half of the row: through shared memory, double-buffered by the parity of j (the
+          // slot of tile j + 2 is only written after the partner has passed the barrier of tile j + 1)
+          *xslot(j & 1, hf) = mx;
+          bar_sync_named(pair_bar, 64);
+          mx = fmaxf(mx, *xslot(j & 1, hf ^ 1));
+        }
+        // mx is finite: every tile has >= 1 valid column (in one of the halves)
         // advance the reference max only when it is exceeded by more than 2^8 in the exp2 domain
         const bool grow_ref = (mx - m_ref) * sc > 8.0f;  // true on the first tile (m_ref = -inf)
         const float m_new = grow_ref ? mx : m_ref;
@@ -348,7 +377,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         // the turn covers the exp pass only: the row max above (ALU pipe) runs under the other tile's
         // exponentials, so the MUFU never waits for it.  nmb feeds every exponential: passing it
         // through the barrier keeps the exp pass behind it and the max in front of it.
-        if (take_turns) bar_sync_named_dep(1 + t, 2 * ATT_BQ, nmb);
+        if (take_turns) bar_sync_named_dep(1 + t, 2 * TILE_THREADS, nmb);
 #endif
         const uint64_t nmb2 = pack_f2(nmb, nmb);
         // ---- P = exp2(S*c - m*c) -> bf16 (registers), row sum ----
@@ -356,7 +385,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         // (round-to-nearest split x = n + f, |f| <= 0.5, degree-3 minimax 2^f, exponent add: relative
         // error 7.5e-5, far below the bf16 rounding of P) instead of the 16-lane MUFU, which is the
         // unit that bounds this loop.
-        uint32_t pk[64];
+        uint32_t pk[NC / 2];
         uint64_t sum_a = pack_f2(0.f, 0.f), sum_b = sum_a;
         const uint64_t magic2 = pack_f2(12582912.f, 12582912.f), nmagic2 = pack_f2(-12582912.f, -12582912.f);
         const uint64_t neg1_2 = pack_f2(-1.f, -1.f);
@@ -377,7 +406,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         };
         if constexpr (full) {
 #pragma unroll
-          for (int i = 0; i < 128; i += 2) {
+          for (int i = 0; i < NC; i += 2) {
             float x0, x1, e0, e1;
             unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])), sc2, nmb2), x0, x1);
             if ((POLY_MASK >> ((i >> 1) & 15)) & 1) {
@@ -393,7 +422,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           // partial last K/V tile (1037 = 8 * 128 + 13): only the 32-column chunks that hold a valid
           // column are evaluated (masked columns are -inf -> 0), the others are P = 0 outright
 #pragma unroll
-          for (int c = 0; c < 128; c += 32) {
+          for (int c = 0; c < NC; c += 32) {
             if (c < valid) {
 #pragma unroll
               for (int i = c; i < c + 32; i += 2) {
@@ -413,9 +442,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         unpack_f2(add_f2(sum_a, sum_b), s0, s1);
         const float row_sum = s0 + s1;  // depends on every exponential of the pass
 #if ATT_TURN_LATE
-        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named_dep(1 + (t ^ 1), 2 * ATT_BQ, row_sum);
+        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named_dep(1 + (t ^ 1), 2 * TILE_THREADS, row_sum);
 #else
-        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named(1 + (t ^ 1), 2 * ATT_BQ);
+        if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named(1 + (t ^ 1), 2 * TILE_THREADS);
 #endif
         // ---- P_t and O_t are free once P_t(j-1) V has completed ----
         if (j > 0) {
@@ -425,7 +454,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         if (rescale) {  // warp-uniform; rows that keep their reference multiply by 1
           const uint64_t a2 = pack_f2(alpha, alpha);
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
+          for (int h = 0; h < OC / 32; ++h) {
             uint32_t o[32];
             MAB_TMEM_LD_32(to + h * 32, o);
             tmem_wait_ld();
@@ -440,10 +469,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             MAB_TMEM_ST_16(to + h * 32 + 16, (o + 16));
           }
         }
-        MAB_TMEM_ST_16(tp, pk);
-        MAB_TMEM_ST_16(tp + 16, (pk + 16));
-        MAB_TMEM_ST_16(tp + 32, (pk + 32));
-        MAB_TMEM_ST_16(tp + 48, (pk + 48));
+#pragma unroll
+        for (int c = 0; c < NC / 2; c += 16) MAB_TMEM_ST_16(tp + c, (pk + c));
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
@@ -464,39 +491,36 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       }
 
       // ---- epilogue: O_t out of TMEM once the last P V has completed ----
+      if (SPLIT == 2) {  // the row sum of the two halves (m_ref is the same in both by construction)
+        *xslot(nkv & 1, hf) = l_run;
+        bar_sync_named(pair_bar, 64);
+        l_run += *xslot(nkv & 1, hf ^ 1);
+      }
       mbar_wait(&pv_done[t], (nkv - 1) & 1);
       tc_fence_after();
-      uint32_t o0[32], o1[32];
-      MAB_TMEM_LD_32(to, o0);
-      MAB_TMEM_LD_32(to + 32, o1);
+      uint32_t o[OC];
+#pragma unroll
+      for (int c = 0; c < OC; c += 32) MAB_TMEM_LD_32(to + c, (o + c));
       tmem_wait_ld();
       if (row_ok && p.carry_out) {
-        *reinterpret_cast<float2*>(p.carry_ml + (grow * p.heads + head) * 2) = make_float2(m_ref, l_run);
-        float4* dst = reinterpret_cast<float4*>(p.carry_o + grow * p.ldo + head * ATT_D);
+        if (hf == 0)
+          *reinterpret_cast<float2*>(p.carry_ml + (grow * p.heads + head) * 2) = make_float2(m_ref, l_run);
+        float4* dst = reinterpret_cast<float4*>(p.carry_o + grow * p.ldo + head * ATT_D + hf * OC);
 #pragma unroll
-        for (int d = 0; d < 8; ++d) {
-          dst[d] = make_float4(__uint_as_float(o0[4 * d]), __uint_as_float(o0[4 * d + 1]),
-                               __uint_as_float(o0[4 * d + 2]), __uint_as_float(o0[4 * d + 3]));
-          dst[d + 8] = make_float4(__uint_as_float(o1[4 * d]), __uint_as_float(o1[4 * d + 1]),
-                                   __uint_as_float(o1[4 * d + 2]), __uint_as_float(o1[4 * d + 3]));
-        }
+        for (int d = 0; d < OC / 4; ++d)
+          dst[d] = make_float4(__uint_as_float(o[4 * d]), __uint_as_float(o[4 * d + 1]),
+                               __uint_as_float(o[4 * d + 2]), __uint_as_float(o[4 * d + 3]));
       } else if (row_ok) {
         const float inv = 1.0f / l_run;
-        uint4* dst = reinterpret_cast<uint4*>(p.out + grow * p.ldo + head * ATT_D);
+        uint4* dst = reinterpret_cast<uint4*>(p.out + grow * p.ldo + head * ATT_D + hf * OC);
 #pragma unroll
-        for (int d = 0; d < 32; d += 8) {
+        for (int d = 0; d < OC; d += 8)
           dst[d >> 3] = make_uint4(
-              pack_bf16(__uint_as_float(o0[d]) * inv, __uint_as_float(o0[d + 1]) * inv),
-              pack_bf16(__uint_as_float(o0[d + 2]) * inv, __uint_as_float(o0[d + 3]) * inv),
-              pack_bf16(__uint_as_float(o0[d + 4]) * inv, __uint_as_float(o0[d + 5]) * inv),
-              pack_bf16(__uint_as_float(o0[d + 6]) * inv, __uint_as_float(o0[d + 7]) * inv));
-          dst[(d >> 3) + 4] = make_uint4(
-              pack_bf16(__uint_as_float(o1[d]) * inv, __uint_as_float(o1[d + 1]) * inv),
-              pack_bf16(__uint_as_float(o1[d + 2]) * inv, __uint_as_float(o1[d + 3]) * inv),
-              pack_bf16(__uint_as_float(o1[d + 4]) * inv, __uint_as_float(o1[d + 5]) * inv),
-              pack_bf16(__uint_as_float(o1[d + 6]) * inv, __uint_as_float(o1[d + 7]) * inv));
-        }
-        if (p.lse)
+              pack_bf16(__uint_as_float(o[d]) * inv, __uint_as_float(o[d + 1]) * inv),
+              pack_bf16(__uint_as_float(o[d + 2]) * inv, __uint_as_float(o[d + 3]) * inv),
+              pack_bf16(__uint_as_float(o[d + 4]) * inv, __uint_as_float(o[d + 5]) * inv),
+              pack_bf16(__uint_as_float(o[d + 6]) * inv, __uint_as_float(o[d + 7]) * inv));
+        if (p.lse && hf == 0)
           p.lse[grow * p.heads + head] = m_ref * p.scale_log2e * 0.6931471805599453f + logf(l_run);
       }
     }

@@ -331,6 +331,16 @@ inline int launch_conv3_regress(const void* x, int batch, int H, int W, const vo
 }
 
 // ---- attention launcher ------------------------------------------------------------------------
+// K/V length up to which the one-Q-tile kernel (two CTAs per SM) is used; MAB_ATT_SHORT_MAX in the
+// environment or mab_set_attention_short_max() (tests drive both kernels at small sizes with it)
+inline int& att_short_max() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("MAB_ATT_SHORT_MAX");
+    v = e ? atoi(e) : 6000;  // measured crossover between 4 and 8 views of global attention
+  }
+  return v;
+}
 // q_src / kv_src: packed [rows, 3*heads*64] bf16 buffers (q | k | v)
 inline int launch_attention(const void* q_src, long long q_rows_total, const void* kv_src,
                             long long kv_rows_total, int heads, int num_seqs, int q_len, int kv_len,
@@ -364,12 +374,7 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
   ProfScope ps(CAT_ATTENTION, 4.0 * q_len * (double)kv_len * 64.0 * heads * num_seqs, 0.0, st);
   // short sequences (frame / encoder attention: 9 K/V tiles): one Q tile per CTA, two CTAs per SM;
   // long ones (global attention): two Q tiles per CTA sharing every K/V tile in shared memory
-  static int short_max = -1;
-  if (short_max < 0) {
-    const char* e = getenv("MAB_ATT_SHORT_MAX");
-    short_max = e ? atoi(e) : 6000;  // measured crossover between 4 and 8 views of global attention
-  }
-  if (kv_len <= short_max) {
+  if (kv_len <= att_short_max()) {
     dim3 grid((q_len + ATT_BQ - 1) / ATT_BQ, heads, num_seqs);
     MAB_CUDA(launch_pdl(attention_kernel<1>, grid, dim3(AttCfg<1>::THREADS), AttCfg<1>::SMEM_BYTES, st, 1, tQ,
                         tKV, tKV, p));

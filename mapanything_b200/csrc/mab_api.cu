@@ -159,6 +159,12 @@ extern "C" int mab_gemm(const void* A, const void* B, int M, int N, int K, const
   return launch_gemm(A, K, B, K, M, N, K, ep, (cudaStream_t)stream);
 }
 
+// K/V length up to which attention uses the one-Q-tile kernel (< 0: back to the default)
+extern "C" int mab_set_attention_short_max(int kv_len) {
+  att_short_max() = kv_len < 0 ? 6000 : kv_len;
+  return 0;
+}
+
 extern "C" int mab_attention(const void* q_src, int q_rows_total, const void* kv_src,
                              int kv_rows_total, int heads, int num_seqs, int q_len, int kv_len,
                              int q_seq_stride, int kv_seq_stride, float scale, void* out, float* lse,

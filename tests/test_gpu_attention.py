@@ -5,6 +5,17 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=["short_kernel", "long_kernel"])
+def kernel(request):
+    """Both attention kernels at every test size: the one-Q-tile kernel (two CTAs per SM, production
+    choice up to 6000 keys) and the two-Q-tile kernel."""
+    from tests import gpu_helpers as g
+
+    g.check(g.lib().mab_set_attention_short_max(1 << 30 if request.param == "short_kernel" else 0))
+    yield request.param
+    g.check(g.lib().mab_set_attention_short_max(-1))
+
+
 def _ref(qkv, heads, num_seqs, q_len, kv_len, q_stride, kv_stride, kv=None):
     D = heads * 64
     kvt = qkv if kv is None else kv
@@ -31,7 +42,7 @@ def _ref(qkv, heads, num_seqs, q_len, kv_len, q_stride, kv_stride, kv=None):
     (12, 1, 2073, True),    # global attention, 2 views + scale token
     (3, 1, 5000, True),     # long sequence: many kv tiles, ring wrap-around of every barrier
 ])
-def test_attention_self(heads, num_seqs, length, peaky):
+def test_attention_self(heads, num_seqs, length, peaky, kernel):
     from tests import gpu_helpers as g
 
     torch.manual_seed(heads * 100 + length)
@@ -48,7 +59,7 @@ def test_attention_self(heads, num_seqs, length, peaky):
     assert (lse - ref_lse).abs().max() < 2e-2
 
 
-def test_attention_separate_kv():
+def test_attention_separate_kv(kernel):
     """global layer on a view shard: local queries against the gathered K/V of every rank"""
     from tests import gpu_helpers as g
 
@@ -61,7 +72,7 @@ def test_attention_separate_kv():
     assert g.rel(out.float(), ref) < 8e-3
 
 
-def test_attention_ring_carry():
+def test_attention_ring_carry(kernel):
     """ring global attention on one GPU: the K/V of the scene arrive as uneven blocks (as they do
     from the other ranks of a view-sharded run) and the online-softmax state is carried between the
     per-block launches; the result must equal attention over the concatenated K/V."""
