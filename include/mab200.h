@@ -278,6 +278,22 @@ int mab_export_points(const float* depth_z, const float* intrinsics, const float
                       const unsigned char* mask, const float* img_no_norm, int views, int H, int W,
                       float* world_points, float* out_xyz, unsigned char* out_rgb, long long capacity,
                       long long* counts, void* workspace, size_t workspace_bytes, void* stream);
+/* Allocation-free variant of mab_export_points.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments and results as mab_export_points without the
+ * workspace: the per-tile counts / offsets (12 bytes per tile of 1024 pixels) live in a file-scope
+ * `static __device__` array of MAB_EXPORT_STATIC_MAX_TILES tiles (768 KiB, held by every GPU that loads
+ * the library until exit).  views * ceil(H*W / 1024) above that limit is an argument error (-1, text in
+ * mab_last_error()); 65536 tiles = 329 views of 392 x 518.  The call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine; the launch profiler does not bracket it).  Every call on a
+ * device shares the ONE array, which keeps the previous call's contents (each call overwrites what it
+ * reads, nothing needs clearing): two calls that overlap on the GPU -- different streams, or graphs
+ * replayed concurrently -- race; calls ordered on one stream are safe. */
+#define MAB_EXPORT_STATIC_MAX_TILES 65536
+int mab_export_points_static(const float* depth_z, const float* intrinsics, const float* camera_poses,
+                             const unsigned char* mask, const float* img_no_norm, int views, int H, int W,
+                             float* world_points, float* out_xyz, unsigned char* out_rgb,
+                             long long capacity, long long* counts, void* stream);
 int mab_edge_mask(const float* pts3d, float* pts3d_cam, const unsigned char* fmask, int views, int H,
                   int W, float normal_tol_deg, float depth_rtol, void* workspace,
                   unsigned char* mask_out, void* stream);

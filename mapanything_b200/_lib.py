@@ -96,6 +96,7 @@ SYMBOLS = {
     "mab_export_workspace_bytes": (C.c_size_t, [_i, _i, _i]),
     "mab_export_points": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, C.c_longlong, _vp, _vp,
                                C.c_size_t, _vp]),
+    "mab_export_points_static": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, C.c_longlong, _vp, _vp]),
     "mab_edge_mask": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp, _vp]),
 }
 

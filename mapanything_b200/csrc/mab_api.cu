@@ -3,6 +3,7 @@
 #include "../../include/mab200.h"
 
 #include <map>
+#include <mutex>
 #include <vector>
 
 #include "host_util.cuh"
@@ -499,6 +500,67 @@ extern "C" int mab_export_points(const float* depth_z, const float* intrinsics, 
              export_scatter_kernel<<<(int)tiles, EXP_THREADS, 0, st>>>(
                  depth_z, intrinsics, camera_poses, mask, img_no_norm, W, npix, tpv, tile_offsets, capacity,
                  world_points, out_xyz, out_rgb));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---- allocation-free variant of mab_export_points (no counterpart in the reference) --------------
+// The tile counts / offsets live in a file-scope device array instead of a caller workspace, so the
+// call needs no cudaMalloc anywhere (graph capture, serving loops).  Every GPU that loads the library
+// holds the array until exit.  In HOST code `g_export_static_scratch` is only a stand-in for the
+// symbol: the device address comes from cudaGetSymbolAddress, once per device with that device
+// current, and is what the kernels get.
+static __device__ __align__(256) unsigned char
+    g_export_static_scratch[(size_t)MAB_EXPORT_STATIC_MAX_TILES * (sizeof(int) + sizeof(long long))];
+
+namespace {
+constexpr int kMaxDevices = 64;
+int export_static_scratch_address(void** out) {
+  static void* addr[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  MAB_CUDA(cudaGetDevice(&dev));
+  MAB_ARG(dev >= 0 && dev < kMaxDevices, "device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    MAB_CUDA(cudaGetSymbolAddress(&p, g_export_static_scratch));
+    MAB_ARG(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" int mab_export_points_static(const float* depth_z, const float* intrinsics,
+                                        const float* camera_poses, const unsigned char* mask,
+                                        const float* img_no_norm, int views, int H, int W,
+                                        float* world_points, float* out_xyz, unsigned char* out_rgb,
+                                        long long capacity, long long* counts, void* stream) {
+  MAB_ARG(depth_z && intrinsics && counts, "null argument");
+  MAB_ARG(views > 0 && H > 0 && W > 0 && capacity >= 0, "bad sizes");
+  MAB_ARG(!out_rgb || img_no_norm, "out_rgb needs img_no_norm");
+  MAB_ARG((long long)H * W < (1LL << 31), "view too large");
+  const int npix = H * W, tpv = (npix + EXP_TILE - 1) / EXP_TILE;
+  const long long tiles = (long long)views * tpv;
+  if (tiles > (long long)MAB_EXPORT_STATIC_MAX_TILES)
+    return fail(-1, "argument error: mab_export_points_static: %lld tiles of %d pixels exceed the static "
+                "scratch of MAB_EXPORT_STATIC_MAX_TILES = %d tiles; use mab_export_points with a workspace",
+                tiles, EXP_TILE, (int)MAB_EXPORT_STATIC_MAX_TILES);
+  void* scratch = nullptr;
+  MAB_TRY(export_static_scratch_address(&scratch));
+  cudaStream_t st = (cudaStream_t)stream;
+  // same carving as mab_export_points; every entry the scan and scatter passes read is written by
+  // the count / scan pass of THIS call first, so nothing has to start at zero
+  long long* tile_offsets = reinterpret_cast<long long*>(scratch);
+  int* tile_counts = reinterpret_cast<int*>(tile_offsets + tiles);
+  prof().launches += 3;  // counted, never event-bracketed: the profiler's event pool allocates
+  export_count_kernel<<<(int)tiles, EXP_THREADS, 0, st>>>(depth_z, mask, npix, tpv, tile_counts);
+  export_scan_kernel<<<1, 1024, 0, st>>>(tile_counts, (int)tiles, tpv, views, tile_offsets, counts);
+  export_scatter_kernel<<<(int)tiles, EXP_THREADS, 0, st>>>(depth_z, intrinsics, camera_poses, mask,
+                                                            img_no_norm, W, npix, tpv, tile_offsets,
+                                                            capacity, world_points, out_xyz, out_rgb);
   MAB_CUDA(cudaGetLastError());
   return 0;
 }
