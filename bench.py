@@ -7,7 +7,10 @@
 A step = one whole `infer()` of ONE scene (encoder -> 24 alternating-attention blocks -> DPT / pose /
 scale heads -> fused pointmap + post-processing) on synthetic views (518x392, DINOv2-normalised) with
 random-init weights of the production architecture.  N=1: BASELINE.json configs[1], 8 views on one
-B200.  N>1: one scene of 8*N views, view-sharded over N ranks with ring global attention over NCCL.
+B200.  N>1: one scene of 8*N views, view-sharded over N ranks (global attention: all-to-all K|V gather
+over NCCL by default, ring above MAB_GATHER_MAX_BYTES), after a sharded-vs-single parity check on the
+same GPUs (`sharded_parity`).  Every line also carries `fixed_scene` (the same 64-view scene at every N)
+and, at N = 8, `c4_512` (BASELINE.json configs[3]).
 
 JSON keys: see DESIGN.md "Measurement".  `value` times the C-ABI forward+postprocess with inputs
 resident in HBM (CUDA events, max over ranks); `e2e` times `MapAnything.infer` from pinned HOST images
@@ -89,58 +92,139 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def _reference_runner():
+    """(kind, build_s, fn) with fn(views, device, amp) -> predictions: the UNMODIFIED reference from
+    oracle/_ref (copied there from /root/reference by oracle/make_ref.py at build time; kind "reference"),
+    else the oracle port (kind "port").  Test/bench infrastructure: never on the product path."""
+    from mapanything_b200 import synthetic
+    from oracle import make_ref
+
+    sd = synthetic.synthetic_state_dict()
+    root = make_ref.ref_root()
+    t0 = time.perf_counter()
+    if root is not None:
+        os.environ["MAB_REFERENCE_ROOT"] = root
+        import importlib
+
+        from oracle import ref_shim
+        importlib.reload(ref_shim)
+        import contextlib
+        import io
+        with contextlib.redirect_stdout(io.StringIO()):  # the reference prints while it builds
+            model = ref_shim.build_reference_model(sd)
+        state = {"dev": "cpu"}
+
+        def run(views, device="cpu", amp=False):
+            if state["dev"] != device:
+                model.to(device)
+                state["dev"] = device
+            vs = [{k: (t.to(device) if torch.is_tensor(t) else t) for k, t in v.items()} for v in views]
+            with contextlib.redirect_stdout(io.StringIO()):
+                return model.infer(vs, use_amp=amp, amp_dtype="bf16")
+
+        return "reference", time.perf_counter() - t0, run
+    from oracle import mapanything_oracle as orc
+
+    def run_port(views, device="cpu", amp=False):
+        sdd = sd if device == "cpu" else {k: v.to(device) for k, v in sd.items()}
+        vs = [{k: (t.to(device) if torch.is_tensor(t) else t) for k, t in v.items()} for v in views]
+        return orc.infer(sdd, vs, amp=amp)
+
+    return "port", time.perf_counter() - t0, run_port
+
+
+def _kind_text(kind):
+    return ("the unmodified reference MapAnything.infer(use_amp=False) imported from oracle/_ref" if kind == "reference"
+            else "oracle/mapanything_oracle.py (restatement pinned to the live reference by tests/golden)")
+
+
 def reference_arm(args, rank, world):
-    """The reference's own CPU path for this hot path, timed on the box's host cores.  The reference
-    is pure Python and cannot travel to the GPU box, so this is the oracle port (oracle/, pinned to
-    the live reference by tests/golden); each step is a bounded sample (2 views) of the workload."""
+    """The reference's own CPU path for this hot path (fp32, all host cores), timed on the box's host
+    cores: the UNMODIFIED reference when oracle/_ref travelled with the snapshot, else the oracle port.
+    N=1: every step is the whole BASELINE configs[1] scene (8 views 518x392) -- the same config as the
+    GPU arm.  N>1 (a scene of 8*N views): each step is a bounded 8-view sample of that scene."""
     if rank != 0:
         return
     from mapanything_b200 import synthetic
-    from oracle import mapanything_oracle as orc
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    sample_views = 2
-    sd = synthetic.synthetic_state_dict()
+    n_views = args.views or VIEWS_PER_GPU * world
+    sample_views = min(n_views, VIEWS_PER_GPU)
+    kind, build_s, run = _reference_runner()
     views = synthetic.synthetic_views(sample_views, H_IMG, W_IMG, seed=1)
-    for _ in range(max(args.warmup, 1)):
-        orc.infer(sd, [dict(v) for v in views])
+    warm = max(args.warmup, 1)
+    # bounded sample: the first warm-up step is clocked; if K + W steps of the whole scene would not end
+    # within the budget (a few minutes), every step takes a sub-sample of 4 or 2 of its views instead
+    # (CPU views/s barely depends on the scene size at <= 8 views: the quadratic term is 2 % of the work)
+    budget = float(os.environ.get("MAB_REF_BUDGET_S", "420"))
+    t0 = time.perf_counter()
+    run(views)
+    first = time.perf_counter() - t0
+    while sample_views > 2 and first * (sample_views / len(views)) * (args.steps + warm - 1) > budget:
+        sample_views //= 2
+    views = views[:sample_views]
+    for _ in range(warm - 1):
+        run(views)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        orc.infer(sd, [dict(v) for v in views])
+        run(views)
     dt = (time.perf_counter() - t0) / args.steps
     v = sample_views / dt
-    n_views = args.views or VIEWS_PER_GPU * world
+    sample = (f"the whole scene: {sample_views} views 518x392 per step" if sample_views == n_views else
+              f"{sample_views} of the scene's {n_views} views 518x392 per step")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"MapAnything image-only infer, {n_views} views 518x392, random-init weights",
-                   "sample": f"{sample_views} of those views per step (fp32, CPU)"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{sample_views} views 518x392 per step, oracle/mapanything_oracle.py (fp32 torch CPU)"},
+        "config": {"workload": f"MapAnything image-only infer, {n_views} views 518x392 (WxH), one scene, random-init weights of the production architecture",
+                   "views": n_views, "sample": sample + " (fp32, CPU)", "same_config": sample_views == n_views},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": sample + ", " + _kind_text(kind) + f", fp32 torch CPU, {cores} threads"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
 
 
-def cpu_baseline_leg(budget_s=25.0):
+def cpu_and_gpu_baseline_legs(dev, budget_s=25.0):
+    """Rank 0, N=1: (cpu_baseline, reference_gpu).  cpu_baseline = the reference's CPU path on a bounded
+    sample (whole 8-view scenes for ~budget_s).  reference_gpu = the SAME reference code moved to this B200
+    and run the way its README does (infer(use_amp=True, amp_dtype="bf16"): eager PyTorch, library SDPA /
+    cuBLASLt / cuDNN), the bar SURVEY.md 8(d) names; forward() alone is timed too because the reference's
+    post-processing runs in numpy on the host."""
     from mapanything_b200 import synthetic
-    from oracle import mapanything_oracle as orc
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    sd = synthetic.synthetic_state_dict()
-    views = synthetic.synthetic_views(2, H_IMG, W_IMG, seed=1)
+    kind, build_s, run = _reference_runner()
+    views = synthetic.synthetic_views(VIEWS_PER_GPU, H_IMG, W_IMG, seed=1)
     t0 = time.perf_counter()
     reps = 0
     while True:
-        orc.infer(sd, [dict(v) for v in views])
+        run(views)
         reps += 1
         if time.perf_counter() - t0 > budget_s * 0.6 or reps >= 4:
             break
     dt = (time.perf_counter() - t0) / reps
-    return {"value": 2 / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{reps} x infer of 2 views 518x392 (fp32, oracle/mapanything_oracle.py, {cores} threads)"}
+    cpu = {"value": VIEWS_PER_GPU / dt, "unit": UNIT, "cores": cores, "kind": kind,
+           "sample": f"{reps} x infer of the whole 8-view scene 518x392 (fp32, {_kind_text(kind)}, {cores} threads)"}
+    gpu = None
+    try:
+        dname = str(dev)
+        for _ in range(2):
+            run(views, dname, True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        n = 3
+        for _ in range(n):
+            run(views, dname, True)
+        torch.cuda.synchronize()
+        dt_inf = (time.perf_counter() - t0) / n
+        gpu = {"value": VIEWS_PER_GPU / dt_inf, "unit": UNIT, "ms_per_step": dt_inf * 1e3, "kind": kind,
+               "what": "infer(use_amp=True, amp_dtype='bf16') of the 8-view scene on the same B200, inputs on the "
+                       "device, wall clock incl. the reference's host-side numpy post-processing"}
+    except Exception as e:  # the baseline leg must never take the bench line down
+        gpu = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+    return cpu, gpu
 
 
 def main():
@@ -153,6 +237,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-to-host leg (many-view sweeps)")
+    ap.add_argument("--no-fixed-scene", action="store_true", help="skip the fixed 64-view (and, at N=8, 512-view) legs")
     ap.add_argument("--multimodal", action="store_true",
                     help="BASELINE.json configs[2]: images + intrinsics + poses + sparse depth (use with --views 32)")
     args = ap.parse_args()
@@ -241,6 +326,29 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item()) / steps
 
+    # N > 1: before anything is timed, the view-sharded path must reproduce the single-GPU result on
+    # this box (both exchange schedules; an uneven multi-modal scene and a full-resolution one).  The
+    # result goes into the JSON line; a failure ends the run non-zero after the line is printed.
+    shard_par = None
+    if world > 1:
+        from mapanything_b200 import parallel
+        small = synthetic.add_multimodal_inputs(synthetic.synthetic_views(2 * world + 1, 70, 98, seed=3), seed=4)
+        rep_a = parallel.sharded_vs_single(model, small)
+        rep_b = parallel.sharded_vs_single(model, synthetic.synthetic_views(2 * world, H_IMG, W_IMG, seed=3))
+        # tolerances of tests/dist_sharded_check.py: bf16 tolerance of the path (the two runs differ in the
+        # K/V block order of the global layers); mask logits are a near-cancelling sum, the 70x98 intrinsics a
+        # least-squares fit through 7x10 ray samples
+        def _ok(rep, small_img):
+            tol = {"non_ambiguous_mask_logits": 3.5e-2, "intrinsics": 3e-2 if small_img else 1e-2}
+            return all(e < tol.get(k, 1e-2) for k, e in rep["per_key"].items()) and rep["mask_agree"] > 0.97
+        shard_par = {"worst_rel_l2": max(rep_a["worst_rel_l2"], rep_b["worst_rel_l2"]),
+                     "mask_agree": min(rep_a["mask_agree"], rep_b["mask_agree"]),
+                     "ok": bool(_ok(rep_a, True) and _ok(rep_b, False)),
+                     "what": "shard of the view-sharded result vs the same views of the single-GPU result, every rank, "
+                             "both exchange schedules (gather, ring), max over ranks",
+                     "cases": {f"{2 * world + 1} views 70x98 multi-modal (uneven shards)": rep_a,
+                               f"{2 * world} views 518x392 image-only": rep_b}}
+
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -317,9 +425,27 @@ def main():
             scene_par = {"value": VIEWS_PER_GPU * world / (ms_sp * 1e-3), "unit": UNIT, "ms_per_step": ms_sp,
                          "what": f"{world} independent {VIEWS_PER_GPU}-view scenes, one per GPU, no communication"}
 
-    cpu = None
+    # fixed-scene legs (strong scaling, driver-clocked): the SAME 64-view scene at every N, and at N = 8
+    # BASELINE.json configs[3] (512 views, one scene)
+    def fixed_leg(views_total, steps, warmup):
+        flo, fhi = shard_views(views_total, world, rank)
+        base = synthetic.synthetic_views(64, H_IMG, W_IMG, seed=1)
+        imgs = torch.cat([base[i % 64]["img"] for i in range(flo, fhi)], 0).to(dev)
+        ms = timed(lambda: model.run_resident(imgs, H_IMG, W_IMG, view_range=(flo, fhi), total_views=views_total),
+                   steps, warmup)
+        del imgs
+        return {"views": views_total, "ms_per_step": ms, "views_per_s": views_total / (ms * 1e-3), "steps": steps,
+                "warmup": warmup, "tflops_per_gpu": flops_per_scene(views_total) / (ms * 1e-3) / 1e12 / world}
+
+    fixed = c4 = None
+    if not args.views and not args.multimodal and not args.no_fixed_scene:
+        fixed = fixed_leg(64, 3, 1)
+        if world == 8:
+            c4 = fixed_leg(512, 2, 1)
+
+    cpu = ref_gpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline_leg()
+        cpu, ref_gpu = cpu_and_gpu_baseline_legs(dev)
 
     if rank == 0:
         value = n_views / (ms_step * 1e-3)
@@ -342,6 +468,14 @@ def main():
         }
         if scene_par is not None:
             line["scene_parallel"] = scene_par
+        if shard_par is not None:
+            line["sharded_parity"] = shard_par
+        if fixed is not None:
+            line["fixed_scene"] = fixed
+        if c4 is not None:
+            line["c4_512"] = c4
+        if ref_gpu is not None:
+            line["reference_gpu"] = ref_gpu
         if roof is not None:
             line["roofline"] = roof
         if cpu is not None:
@@ -349,6 +483,8 @@ def main():
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if shard_par is not None and not shard_par["ok"]:
+        sys.exit("sharded_parity failed: " + json.dumps(shard_par["cases"]))
 
 
 if __name__ == "__main__":

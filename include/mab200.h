@@ -56,6 +56,12 @@ typedef struct {
    * block attends over all tokens of the scene (the alternating trunk: even blocks only); that model
    * always encodes every view (aat_ref_view_pe = aat_nonref_view_pe = 1, table of max_num_views rows). */
   int aat_all_global;
+  /* Dense head (DPT feature + regressor) arithmetic.  1: fp32 activations and TF32 tensor-core
+   * contractions -- the reference's own precision for this region (autocast off at model.py:1774, TF32
+   * allowed at model.py:89-93; uniception/models/prediction_heads/dpt.py:180-232,285-311) -- the Python
+   * mirror's default.  0: bf16 operands (about 2 ms faster per 8 views; the mask-logit channel is then
+   * 1.6e-2 from fp32 on identical inputs instead of < 5e-3). */
+  int head_tf32;
 } mab_config;
 
 /* One scene, `views` views of H x W pixels held by this rank. */

@@ -83,6 +83,18 @@ __device__ __forceinline__ float fast_rcp(float x) {  // MUFU.RCP, 1 ulp, branch
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// fp32 -> the nearest TF32 value (10 mantissa bits), returned as fp32.  tcgen05.mma kind::tf32 IGNORES the
+// low 13 mantissa bits of an fp32 operand (truncation: every product shrinks by ~1e-3 on average, a bias that
+// compounds through the ~20 convolutions of the dense head); operands rounded to nearest where they are
+// PRODUCED make that truncation exact, which is what cuDNN / cuBLAS TF32 kernels do with cvt.rna.
+__device__ __forceinline__ float tf32_rn(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+__device__ __forceinline__ float4 tf32_rn(float4 v) {
+  return make_float4(tf32_rn(v.x), tf32_rn(v.y), tf32_rn(v.z), tf32_rn(v.w));
+}
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 

@@ -26,7 +26,7 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows_out, int 
                                  const float* __restrict__ b2, float eps,
                                  __nv_bfloat16* __restrict__ out_bf16, float* __restrict__ out_f32,
                                  float* __restrict__ out_mid_f32,
-                                 __nv_bfloat16* __restrict__ out_split) {
+                                 __nv_bfloat16* __restrict__ out_split, int round_f32) {
   constexpr int C = 128 * VPL;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   pdl_wait();
@@ -72,7 +72,8 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows_out, int 
   if (w2) normalise(w2, b2);
 #pragma unroll
   for (int i = 0; i < VPL; ++i) {
-    if (out_f32) reinterpret_cast<float4*>(out_f32 + (long long)warp * C)[lane + 32 * i] = v[i];
+    // round_f32: the fp32 row is an operand of a kind::tf32 contraction (dense-head input), see tf32_rn
+    if (out_f32) reinterpret_cast<float4*>(out_f32 + (long long)warp * C)[lane + 32 * i] = round_f32 ? tf32_rn(v[i]) : v[i];
     if (out_bf16)
       reinterpret_cast<uint2*>(out_bf16 + (long long)warp * C)[lane + 32 * i] =
           make_uint2(pack_bf16(v[i].x, v[i].y), pack_bf16(v[i].z, v[i].w));
@@ -116,7 +117,7 @@ __global__ void patch_im2col_kernel(const float* __restrict__ img, int views, in
       if (log_mode) val = copysignf(log1pf(fabsf(val)), val);
     }
     if (out) out[i] = __float2bfloat16(val);
-    if (out_f32) out_f32[i] = val;  // fp32 operand of the TF32 geometric-input encoders
+    if (out_f32) out_f32[i] = tf32_rn(val);  // fp32 operand of the TF32 geometric-input encoders
   }
 }
 
@@ -231,7 +232,7 @@ template <int VPL>
 __global__ void fuse_norm_kernel(const float* __restrict__ enc, const float* __restrict__ dense,
                                  const float* __restrict__ vec, int rows, int T,
                                  const float* __restrict__ w, const float* __restrict__ b, float eps,
-                                 __nv_bfloat16* __restrict__ out, float* __restrict__ out_f32) {
+                                 __nv_bfloat16* __restrict__ out, float* __restrict__ out_f32, int round_f32) {
   constexpr int C = 128 * VPL;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= rows) return;
@@ -263,7 +264,7 @@ __global__ void fuse_norm_kernel(const float* __restrict__ enc, const float* __r
                                  (v[i].z - mean) * rstd * g.z + h.z, (v[i].w - mean) * rstd * g.w + h.w);
     reinterpret_cast<uint2*>(out + (long long)warp * C)[lane + 32 * i] =
         make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
-    if (out_f32) reinterpret_cast<float4*>(out_f32 + (long long)warp * C)[lane + 32 * i] = y;
+    if (out_f32) reinterpret_cast<float4*>(out_f32 + (long long)warp * C)[lane + 32 * i] = round_f32 ? tf32_rn(y) : y;
   }
 }
 
@@ -400,6 +401,36 @@ __global__ void resize_bilinear_ac_kernel(const __nv_bfloat16* __restrict__ in, 
   const long long i = (((long long)v * Ho + oy) * Wo + ox) * c8n + c8;
   if (out) reinterpret_cast<uint4*>(out)[i] = make_uint4(o[0], o[1], o[2], o[3]);
   if (out_relu) reinterpret_cast<uint4*>(out_relu)[i] = make_uint4(orl[0], orl[1], orl[2], orl[3]);
+}
+
+// the same on fp32 NHWC activations, 4 channels per thread (fp32 / TF32 dense head)
+__global__ void resize_bilinear_ac_f32_kernel(const float* __restrict__ in, int views, int Hi, int Wi, int C,
+                                              int Hv, int Wv, int Ho, int Wo, float* __restrict__ out,
+                                              float* __restrict__ out_relu) {
+  const int c4n = C / 4;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= Wo * c4n) return;
+  const int ox = idx / c4n, c4 = idx - ox * c4n;
+  const int oy = blockIdx.y, v = blockIdx.z;
+  const float ry = Hv > 1 ? float(Hi - 1) / float(Hv - 1) : 0.f;
+  const float rx = Wv > 1 ? float(Wi - 1) / float(Wv - 1) : 0.f;
+  const float sy = ry * oy, sx = rx * ox;
+  const int y0 = min((int)sy, Hi - 1), x0 = min((int)sx, Wi - 1);
+  const int y1 = min(y0 + 1, Hi - 1), x1 = min(x0 + 1, Wi - 1);
+  const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
+  const float4* base = reinterpret_cast<const float4*>(in) + (long long)v * Hi * Wi * c4n + c4;
+  const float4 a = base[((long long)y0 * Wi + x0) * c4n], b = base[((long long)y0 * Wi + x1) * c4n];
+  const float4 c = base[((long long)y1 * Wi + x0) * c4n], d = base[((long long)y1 * Wi + x1) * c4n];
+  float4 o;  // ATen: hy*(hx*a + lx*b) + ly*(hx*c + lx*d)
+  o.x = hy * (hx * a.x + lx * b.x) + ly * (hx * c.x + lx * d.x);
+  o.y = hy * (hx * a.y + lx * b.y) + ly * (hx * c.y + lx * d.y);
+  o.z = hy * (hx * a.z + lx * b.z) + ly * (hx * c.z + lx * d.z);
+  o.w = hy * (hx * a.w + lx * b.w) + ly * (hx * c.w + lx * d.w);
+  const long long i = (((long long)v * Ho + oy) * Wo + ox) * c4n + c4;
+  o = tf32_rn(o);  // operand of the next kind::tf32 contraction
+  if (out) reinterpret_cast<float4*>(out)[i] = o;
+  if (out_relu)
+    reinterpret_cast<float4*>(out_relu)[i] = make_float4(fmaxf(o.x, 0.f), fmaxf(o.y, 0.f), fmaxf(o.z, 0.f), fmaxf(o.w, 0.f));
 }
 
 // ConvTranspose2d with kernel == stride (dpt.py:117-127,139-149) = GEMM + pixel shuffle.

@@ -45,6 +45,10 @@ struct GemmEpilogue {
                                  // GEMM: x ~ hi + lo, |x - hi - lo| <= 2^-17 |x|)
   int act_post;                  // 1: the activation is applied AFTER the residual adds
                                  // (ResidualBlock: act(conv2(.) + shortcut), dense_rep_encoder.py:31-52)
+  const float* res2_f32;         // second fp32 residual and fp32 relu(value) copy: the fp32 / TF32 dense
+  float* out_relu_f32;           // head (the reference's autocast-off region, model.py:1774)
+  int round_tf32;                // 1: out_f32 / out_relu_f32 are stored rounded to the nearest TF32 value
+                                 // (they are the A operands of the next kind::tf32 contraction, tf32_rn)
 };
 
 // Fused tail of the dense head: ReLU -> 1x1 conv 128->6 -> adaptor -> pointmap (EPI_REGRESS)
@@ -111,13 +115,15 @@ struct GemmSmem {
 // ---- store half of the generic epilogue, specialised on the operands that exist -----------------
 enum {
   EF_OUTBF16 = 1, EF_OUTF32 = 2, EF_OUTRELU = 4, EF_RESF32 = 8, EF_RES1 = 16, EF_RES2 = 32,
-  EF_GAMMA = 64, EF_GELU = 128, EF_RELU = 256, EF_GENERIC = 1 << 20  // generic: test pointers at run time
+  EF_GAMMA = 64, EF_GELU = 128, EF_RELU = 256, EF_RES2F = 512, EF_OUTRELUF = 1024,
+  EF_GENERIC = 1 << 20  // generic: test pointers at run time
 };
 __device__ __forceinline__ int epilogue_flags(const GemmEpilogue& ep) {
   if (ep.split_n || ep.act_post) return EF_GENERIC;
   return (ep.out_bf16 ? EF_OUTBF16 : 0) | (ep.out_f32 ? EF_OUTF32 : 0) | (ep.out_relu ? EF_OUTRELU : 0) |
          (ep.res_f32 ? EF_RESF32 : 0) | (ep.res1 ? EF_RES1 : 0) | (ep.res2 ? EF_RES2 : 0) |
-         (ep.gamma ? EF_GAMMA : 0) | (ep.act == ACT_GELU ? EF_GELU : 0) | (ep.act == ACT_RELU ? EF_RELU : 0);
+         (ep.gamma ? EF_GAMMA : 0) | (ep.act == ACT_GELU ? EF_GELU : 0) | (ep.act == ACT_RELU ? EF_RELU : 0) |
+         (ep.res2_f32 ? EF_RES2F : 0) | (ep.out_relu_f32 ? EF_OUTRELUF : 0);
 }
 
 template <int F>
@@ -132,6 +138,8 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
   const bool has_r1 = G ? ep.res1 != nullptr : (F & EF_RES1) != 0;
   const bool has_r2 = G ? ep.res2 != nullptr : (F & EF_RES2) != 0;
   const bool has_g = G ? ep.gamma != nullptr : (F & EF_GAMMA) != 0;
+  const bool has_r2f = G ? ep.res2_f32 != nullptr : (F & EF_RES2F) != 0;
+  const bool has_orf = G ? ep.out_relu_f32 != nullptr : (F & EF_OUTRELUF) != 0;
   const bool gelu = G ? ep.act == ACT_GELU : (F & EF_GELU) != 0;
   const bool relu = G ? ep.act == ACT_RELU : (F & EF_RELU) != 0;
   const uint64_t keep = l2_policy_evict_last();
@@ -187,12 +195,17 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
       if (has_r2) {
         x.x += bf16_lo(r2[i].x); x.y += bf16_hi(r2[i].x); x.z += bf16_lo(r2[i].y); x.w += bf16_hi(r2[i].y);
       }
+      if (has_r2f) {  // loaded here, not with the prefetched operands: 32 more live registers otherwise
+        const float4 e = *reinterpret_cast<const float4*>(ep.res2_f32 + ro[i] + col);
+        x.x += e.x; x.y += e.y; x.z += e.z; x.w += e.w;
+      }
       if (post && gelu) {
         x.x = gelu_erf(x.x); x.y = gelu_erf(x.y); x.z = gelu_erf(x.z); x.w = gelu_erf(x.w);
       } else if (post && relu) {
         x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
       }
       const long long off = ro[i] + col;
+      if (ep.round_tf32) x = tf32_rn(x);
       if (has_of) {
         if (has_rf) st_f4_l2hint(ep.out_f32 + off, x, keep);  // the residual stream stays in L2
         else *reinterpret_cast<float4*>(ep.out_f32 + off) = x;
@@ -211,6 +224,9 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
         *reinterpret_cast<uint2*>(ep.out_relu + off) =
             make_uint2(pack_bf16(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)),
                        pack_bf16(fmaxf(x.z, 0.f), fmaxf(x.w, 0.f)));
+      if (has_orf)
+        *reinterpret_cast<float4*>(ep.out_relu_f32 + off) =
+            make_float4(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f), fmaxf(x.z, 0.f), fmaxf(x.w, 0.f));
     }
   }
 }
@@ -474,23 +490,36 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       const int c_begin = chalf * (BN / 2), c_end = (chalf + 1) * (BN / 2);
       const int n0 = n_blk * BN;
-      switch (epi_flags) {
 #define MAB_EPI_CASE(F) \
   case F: epilogue_chunks<F>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro, row_mask, c_begin, c_end, n0); break;
-        MAB_EPI_CASE(EF_OUTBF16)
-        MAB_EPI_CASE(EF_OUTBF16 | EF_GELU)
-        MAB_EPI_CASE(EF_OUTBF16 | EF_RELU)
-        MAB_EPI_CASE(EF_OUTF32)
-        MAB_EPI_CASE(EF_OUTF32 | EF_RESF32)
-        MAB_EPI_CASE(EF_OUTF32 | EF_RESF32 | EF_GAMMA)
-        MAB_EPI_CASE(EF_OUTBF16 | EF_OUTRELU)
-        MAB_EPI_CASE(EF_OUTBF16 | EF_RES1)
-        MAB_EPI_CASE(EF_OUTBF16 | EF_RES1 | EF_OUTRELU)
-        MAB_EPI_CASE(EF_OUTBF16 | EF_RES1 | EF_RES2 | EF_OUTRELU)
-        default:
-          epilogue_chunks<EF_GENERIC>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro, row_mask, c_begin, c_end, n0);
-#undef MAB_EPI_CASE
+      if constexpr (TF) {  // fp32 operands: geometric-input encoders and the fp32 / TF32 dense head
+        switch (epi_flags) {
+          MAB_EPI_CASE(EF_OUTF32)
+          MAB_EPI_CASE(EF_OUTF32 | EF_RELU)
+          MAB_EPI_CASE(EF_OUTF32 | EF_GELU)
+          MAB_EPI_CASE(EF_OUTF32 | EF_OUTRELUF)
+          MAB_EPI_CASE(EF_OUTF32 | EF_RESF32)
+          MAB_EPI_CASE(EF_OUTF32 | EF_RESF32 | EF_RES2F | EF_OUTRELUF)
+          default:
+            epilogue_chunks<EF_GENERIC>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro, row_mask, c_begin, c_end, n0);
+        }
+      } else {
+        switch (epi_flags) {
+          MAB_EPI_CASE(EF_OUTBF16)
+          MAB_EPI_CASE(EF_OUTBF16 | EF_GELU)
+          MAB_EPI_CASE(EF_OUTBF16 | EF_RELU)
+          MAB_EPI_CASE(EF_OUTF32)
+          MAB_EPI_CASE(EF_OUTF32 | EF_RESF32)
+          MAB_EPI_CASE(EF_OUTF32 | EF_RESF32 | EF_GAMMA)
+          MAB_EPI_CASE(EF_OUTBF16 | EF_OUTRELU)
+          MAB_EPI_CASE(EF_OUTBF16 | EF_RES1)
+          MAB_EPI_CASE(EF_OUTBF16 | EF_RES1 | EF_OUTRELU)
+          MAB_EPI_CASE(EF_OUTBF16 | EF_RES1 | EF_RES2 | EF_OUTRELU)
+          default:
+            epilogue_chunks<EF_GENERIC>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro, row_mask, c_begin, c_end, n0);
+        }
       }
+#undef MAB_EPI_CASE
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[acc]), 0));

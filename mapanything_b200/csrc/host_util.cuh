@@ -304,6 +304,10 @@ inline int launch_gemm_tf32(const float* A, long long lda, const float* B, long 
   GemmShape shp{M, N, K, 0, 0, 0, 0, 0};
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM, true));
+  if (N <= 128) {
+    MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 128 / GEMM_CL, true));
+    return launch_gemm_t<128, 8, MODE_GEMM, EPI_GENERIC, GEMM_CL, 1>(tA, tB, shp, ep, rg, st);
+  }
   MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 256 / GEMM_CL, true));
   return launch_gemm_t<256, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL, 1>(tA, tB, shp, ep, rg, st);
 }
@@ -315,6 +319,10 @@ inline int launch_conv3_tf32(const float* x, int batch, int H, int W, int C, int
   GemmShape shp{0, Cout, 9 * cblocks * 32, batch, H, W, cblocks, Creal};
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, C, true));
+  if (Cout <= 128) {
+    MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 32, 9LL * cblocks * 32, 128 / GEMM_CL, true));
+    return launch_gemm_t<128, 8, MODE_CONV3, EPI_GENERIC, GEMM_CL, 1>(tA, tB, shp, ep, rg, st);
+  }
   MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 32, 9LL * cblocks * 32, 256 / GEMM_CL, true));
   return launch_gemm_t<256, 6, MODE_CONV3, EPI_GENERIC, GEMM_CL, 1>(tA, tB, shp, ep, rg, st);
 }
@@ -328,6 +336,17 @@ inline int launch_conv3_regress(const void* x, int batch, int H, int W, const vo
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, 128));
   MAB_TRY(make_tmap_2d(&tB, w, 128, 9LL * 128, 9LL * 128, 128 / GEMM_CL));
   return launch_gemm_t<128, 8, MODE_CONV3, EPI_REGRESS, GEMM_CL>(tA, tB, shp, ep, rg, st);
+}
+
+// the same with fp32 activations / weights (kind::tf32): the reference's precision for this conv
+inline int launch_conv3_regress_tf32(const float* x, int batch, int H, int W, const float* w,
+                                     const RegressEpilogue& rg, cudaStream_t st) {
+  CUtensorMap tA, tB;
+  GemmShape shp{0, 128, 9 * 4 * 32, batch, H, W, 4, 128};
+  GemmEpilogue ep{};
+  MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, 128, true));
+  MAB_TRY(make_tmap_2d(&tB, w, 128, 9LL * 128, 9LL * 128, 128 / GEMM_CL, true));
+  return launch_gemm_t<128, 8, MODE_CONV3, EPI_REGRESS, GEMM_CL, 1>(tA, tB, shp, ep, rg, st);
 }
 
 // ---- attention launcher ------------------------------------------------------------------------
@@ -390,7 +409,7 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
 inline int launch_layernorm(const float* x, int rows_out, int C, int group_out, int group_in,
                             int skip, const float* w, const float* b, const float* w2,
                             const float* b2, float eps, void* out_bf16, float* out_f32,
-                            float* out_mid, cudaStream_t st, void* out_split = nullptr) {
+                            float* out_mid, cudaStream_t st, void* out_split = nullptr, int round_f32 = 0) {
   if (rows_out <= 0) return 0;
   auto os = reinterpret_cast<__nv_bfloat16*>(out_split);
   const int block = 256, rows_per_block = block / 32;
@@ -402,13 +421,13 @@ inline int launch_layernorm(const float* x, int rows_out, int C, int group_out, 
   ProfScope ps(CAT_LAYERNORM, 0.0, bytes, st);
   if (C == 768)
     MAB_CUDA(launch_pdl(layernorm_kernel<6>, dim3(grid), dim3(block), 0, st, 1, x, rows_out, group_out,
-                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os));
+                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os, round_f32));
   else if (C == 1024)
     MAB_CUDA(launch_pdl(layernorm_kernel<8>, dim3(grid), dim3(block), 0, st, 1, x, rows_out, group_out,
-                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os));
+                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os, round_f32));
   else if (C == 128)
     MAB_CUDA(launch_pdl(layernorm_kernel<1>, dim3(grid), dim3(block), 0, st, 1, x, rows_out, group_out,
-                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os));
+                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os, round_f32));
   else
     return fail(-1, "layernorm: unsupported width %d (supported 128, 768, 1024)", C);
   MAB_CUDA(cudaGetLastError());

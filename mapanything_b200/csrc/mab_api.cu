@@ -18,7 +18,7 @@ namespace {
 
 // fp32 [rows, cols] -> bf16 [rows, ldo] zero padded
 __device__ __forceinline__ void store_as(bf16* p, float v) { *p = __float2bfloat16(v); }
-__device__ __forceinline__ void store_as(float* p, float v) { *p = v; }
+__device__ __forceinline__ void store_as(float* p, float v) { *p = tf32_rn(v); }  // kind::tf32 operand
 
 template <typename T>
 __global__ void pack_matrix_kernel(const float* __restrict__ w, int rows, int cols, int ldo,
@@ -64,15 +64,16 @@ __global__ void pack_conv3_kernel(const float* __restrict__ w, int Cout, int Cin
 }
 
 // ConvTranspose2d weight [Cin, Cout, k, k] -> GEMM B [k*k*Cout, Cin] with row (i*k+j)*Cout + co
+template <typename T>
 __global__ void pack_convT_kernel(const float* __restrict__ w, int Cin, int Cout, int k,
-                                  bf16* __restrict__ out) {
+                                  T* __restrict__ out) {
   const long long total = (long long)k * k * Cout * Cin;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
     const int ci = idx % Cin;
     const int row = idx / Cin;
     const int co = row % Cout, ij = row / Cout;
-    out[idx] = __float2bfloat16(w[((long long)ci * Cout + co) * k * k + ij]);
+    store_as(out + idx, w[((long long)ci * Cout + co) * k * k + ij]);
   }
 }
 
@@ -640,10 +641,12 @@ struct Plan {  // every workspace pointer of one forward
   float* ys; int* view_rows; bf16* tap[3]; bf16* fin; float* scale_tok; float* carry_o; float* carry_ml;
   // heads (small)
   float* scale_tmp; float* pose_pool; float* pose_tmp; float* pose_raw; bf16* ph_in; bf16* ph_a; bf16* ph_b; bf16* ph_c; bf16* ph_d;
-  // dense head chunk buffers
+  // dense head chunk buffers: bf16, or fp32 when cfg.head_tf32 (typed by stage_heads_range<T>)
   int vc = 0;
-  bf16* d_a; bf16* d_s; bf16* d_u; bf16* lvl[4]; bf16* lvl_relu[4]; bf16* t0; bf16* t1; bf16* t2; bf16* t3;
-  bf16* path; bf16* feat8; bf16* r1; bf16* r2;
+  void* d_a; void* d_s; void* d_u; void* lvl[4]; void* lvl_relu[4]; void* t0; void* t1; void* t2; void* t3;
+  void* path; void* feat8; void* r1; void* r2;
+  // fp32 copies of the dense head's inputs (cfg.head_tf32): the reference hands the head fp32 features
+  float* fused32 = nullptr; float* tap32[3] = {nullptr, nullptr, nullptr}; float* fin32 = nullptr;
   size_t total = 0;
 };
 
@@ -703,10 +706,21 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
   p.geo_small = b.take<float>((long long)V * 4096 + 64);  // MLP scratch + masks + scalar inputs
   p.ys = b.take<float>((VT + 1) * A);
   p.view_rows = b.take<int>(V);  // view_pos_table row of every view (use_pe_for_non_reference_views)
-  p.tap[0] = b.take<bf16>(VT * A);
-  p.tap[1] = b.take<bf16>(VT * A);
-  p.tap[2] = c.aat_tap2 > 0 ? b.take<bf16>(VT * A) : nullptr;  // third intermediate feature (48-layer configs)
-  p.fin = b.take<bf16>(VT * A);
+  const bool tf = c.head_tf32 != 0;
+  p.tap[0] = p.tap[1] = p.tap[2] = p.fin = nullptr;
+  p.fused32 = p.tap32[0] = p.tap32[1] = p.tap32[2] = p.fin32 = nullptr;
+  if (tf) {
+    p.fused32 = c.aat_tap2 > 0 ? nullptr : b.take<float>(VT * D);  // three taps: the head takes no encoder features
+    p.tap32[0] = b.take<float>(VT * A);
+    p.tap32[1] = b.take<float>(VT * A);
+    p.tap32[2] = c.aat_tap2 > 0 ? b.take<float>(VT * A) : nullptr;
+    p.fin32 = b.take<float>(VT * A);
+  } else {
+    p.tap[0] = b.take<bf16>(VT * A);
+    p.tap[1] = b.take<bf16>(VT * A);
+    p.tap[2] = c.aat_tap2 > 0 ? b.take<bf16>(VT * A) : nullptr;  // third intermediate feature (48-layer configs)
+    p.fin = b.take<bf16>(VT * A);
+  }
   p.scale_tok = b.take<float>(A);
   p.carry_o = Vtot > V ? b.take<float>((VT + 1) * A) : nullptr;   // ring attention state
   p.carry_ml = Vtot > V ? b.take<float>((VT + 1) * (A / 64) * 2) : nullptr;
@@ -723,20 +737,22 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
   p.ph_c = b.take<bf16>(vc * T * 3 * 784);
   p.ph_d = b.take<bf16>(vc * T * 3 * 784);
   const int h = p.h, w = p.w;
-  p.d_a = b.take<bf16>(vc * T * 768);
-  p.d_s = b.take<bf16>(vc * T * 6912 / 1);  // >= T*1536 (convT) and >= Ho*Wo*9*768 (im2col s2)
-  p.d_u = b.take<bf16>(vc * 16 * T * 96);   // 4h x 4w x 96 == 2h x 2w x 192 * 2
+  const long long es = tf ? 4 : 2;  // bytes per activation element of the dense head
+  auto act = [&](long long elems) { return (void*)b.take<uint8_t>(elems * es); };
+  p.d_a = act(vc * T * 768);
+  p.d_s = act(vc * T * 6912 / 1);  // >= T*1536 (convT) and >= Ho*Wo*9*768 (im2col s2)
+  p.d_u = act(vc * 16 * T * 96);   // 4h x 4w x 96 == 2h x 2w x 192 * 2
   const long long lvl_pix[4] = {16LL * T, 4LL * T, T, (long long)((h + 1) / 2) * ((w + 1) / 2)};
   for (int i = 0; i < 4; ++i) {
-    p.lvl[i] = b.take<bf16>(vc * lvl_pix[i] * 256);
-    p.lvl_relu[i] = b.take<bf16>(vc * lvl_pix[i] * 256);
+    p.lvl[i] = act(vc * lvl_pix[i] * 256);
+    p.lvl_relu[i] = act(vc * lvl_pix[i] * 256);
   }
   const long long big = vc * 16 * T * 256;  // 4h x 4w x 256
-  p.t0 = b.take<bf16>(big); p.t1 = b.take<bf16>(big); p.t2 = b.take<bf16>(big); p.t3 = b.take<bf16>(big);
-  p.path = b.take<bf16>(big);
-  p.feat8 = b.take<bf16>(vc * 64 * T * 256);
-  p.r1 = b.take<bf16>(vc * 64 * T * 128);
-  p.r2 = b.take<bf16>(vc * (long long)H * W * 128);
+  p.t0 = act(big); p.t1 = act(big); p.t2 = act(big); p.t3 = act(big);
+  p.path = act(big);
+  p.feat8 = act(vc * 64 * T * 256);
+  p.r1 = act(vc * 64 * T * 128);
+  p.r2 = act(vc * (long long)H * W * 128);
   p.total = b.off + 256;
 }
 
@@ -885,22 +901,26 @@ int pack_conv3_f32(mab_handle* h, const std::string& key, int cpad, cudaStream_t
   return 0;
 }
 
-int pack_convT(mab_handle* h, const std::string& wkey, const std::string& bkey, cudaStream_t st) {
+int pack_convT(mab_handle* h, const std::string& wkey, const std::string& bkey, cudaStream_t st, bool f32 = false) {
   auto it = h->raw.find(wkey);
   auto ib = h->raw.find(bkey);
   if (it == h->raw.end() || ib == h->raw.end()) return fail(-4, "missing weight %s", wkey.c_str());
   const RawTensor& t = it->second;
   const int Cin = (int)t.shape[0], Cout = (int)t.shape[1], k = (int)t.shape[2];
-  bf16* out;
-  MAB_CUDA(cudaMalloc(&out, (size_t)k * k * Cout * Cin * sizeof(bf16)));
+  void* out;
+  MAB_CUDA(cudaMalloc(&out, (size_t)k * k * Cout * Cin * (f32 ? sizeof(float) : sizeof(bf16))));
   h->owned.push_back(out);
-  pack_convT_kernel<<<ew_grid((long long)k * k * Cout * Cin), 256, 0, st>>>(t.p, Cin, Cout, k, out);
+  if (f32)
+    pack_convT_kernel<float><<<ew_grid((long long)k * k * Cout * Cin), 256, 0, st>>>(t.p, Cin, Cout, k, (float*)out);
+  else
+    pack_convT_kernel<bf16><<<ew_grid((long long)k * k * Cout * Cin), 256, 0, st>>>(t.p, Cin, Cout, k, (bf16*)out);
   float* bt;
   MAB_CUDA(cudaMalloc(&bt, (size_t)k * k * Cout * sizeof(float)));
   h->owned.push_back(bt);
   tile_bias_kernel<<<(k * k * Cout + 255) / 256, 256, 0, st>>>(ib->second.p, Cout, k * k, bt);
   MAB_CUDA(cudaGetLastError());
-  h->packed[wkey] = out;
+  if (f32) h->packed32[wkey] = (float*)out;
+  else h->packed[wkey] = (bf16*)out;
   h->extra[bkey + ".tiled"] = bt;
   return 0;
 }
@@ -927,23 +947,51 @@ extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
       MAB_TRY(pack_linear(h, p + s, 0, st));
   }
   const std::string ip = "dpt_feature_head.input_process.";
-  for (int i = 0; i < 4; ++i) MAB_TRY(pack_linear(h, ip + std::to_string(i) + ".0.0.weight", 0, st));
-  MAB_TRY(pack_convT(h, ip + "0.0.1.weight", ip + "0.0.1.bias", st));
-  MAB_TRY(pack_convT(h, ip + "1.0.1.weight", ip + "1.0.1.bias", st));
-  MAB_TRY(pack_conv3(h, ip + "3.0.1.weight", st));
   const std::string sc = "dpt_feature_head.scratch.";
-  for (int i = 1; i <= 4; ++i) {
-    MAB_TRY(pack_conv3(h, sc + "layer" + std::to_string(i) + "_rn.weight", st));
-    const std::string r = sc + "refinenet" + std::to_string(i);
-    for (const char* u : {".resConfUnit1", ".resConfUnit2"}) {
-      if (i == 4 && std::string(u) == ".resConfUnit1") continue;  // dpt.py:82-83
-      MAB_TRY(pack_conv3(h, r + u + ".conv1.weight", st));
-      MAB_TRY(pack_conv3(h, r + u + ".conv2.weight", st));
+  if (c.head_tf32) {
+    // dense head with fp32 activations and TF32 contractions, the reference's own precision for this
+    // region (autocast off, model.py:1774; dpt.py:180-232,285-311): fp32 operands, channels already
+    // multiples of 32 (96, 192, 384, 768, 256, 128)
+    auto cin_of = [&](const std::string& k) { auto it = h->raw.find(k); return it == h->raw.end() ? 0 : (int)it->second.shape[1]; };
+    auto conv32 = [&](const std::string& k) {
+      const int cin = cin_of(k);
+      if (cin <= 0 || cin % 32) return fail(-4, "missing weight %s (or input channels not a multiple of 32)", k.c_str());
+      return pack_conv3_f32(h, k, cin, st);
+    };
+    for (int i = 0; i < 4; ++i) MAB_TRY(pack_linear_f32(h, ip + std::to_string(i) + ".0.0.weight", 0, st));
+    MAB_TRY(pack_convT(h, ip + "0.0.1.weight", ip + "0.0.1.bias", st, true));
+    MAB_TRY(pack_convT(h, ip + "1.0.1.weight", ip + "1.0.1.bias", st, true));
+    MAB_TRY(conv32(ip + "3.0.1.weight"));
+    for (int i = 1; i <= 4; ++i) {
+      MAB_TRY(conv32(sc + "layer" + std::to_string(i) + "_rn.weight"));
+      const std::string r = sc + "refinenet" + std::to_string(i);
+      for (const char* u : {".resConfUnit1", ".resConfUnit2"}) {
+        if (i == 4 && std::string(u) == ".resConfUnit1") continue;  // dpt.py:82-83
+        MAB_TRY(conv32(r + u + ".conv1.weight"));
+        MAB_TRY(conv32(r + u + ".conv2.weight"));
+      }
+      MAB_TRY(pack_linear_f32(h, r + ".out_conv.weight", 0, st));
     }
-    MAB_TRY(pack_linear(h, r + ".out_conv.weight", 0, st));
+    MAB_TRY(conv32("dpt_regressor_head.conv1.weight"));
+    MAB_TRY(conv32("dpt_regressor_head.conv2.0.weight"));
+  } else {
+    for (int i = 0; i < 4; ++i) MAB_TRY(pack_linear(h, ip + std::to_string(i) + ".0.0.weight", 0, st));
+    MAB_TRY(pack_convT(h, ip + "0.0.1.weight", ip + "0.0.1.bias", st));
+    MAB_TRY(pack_convT(h, ip + "1.0.1.weight", ip + "1.0.1.bias", st));
+    MAB_TRY(pack_conv3(h, ip + "3.0.1.weight", st));
+    for (int i = 1; i <= 4; ++i) {
+      MAB_TRY(pack_conv3(h, sc + "layer" + std::to_string(i) + "_rn.weight", st));
+      const std::string r = sc + "refinenet" + std::to_string(i);
+      for (const char* u : {".resConfUnit1", ".resConfUnit2"}) {
+        if (i == 4 && std::string(u) == ".resConfUnit1") continue;  // dpt.py:82-83
+        MAB_TRY(pack_conv3(h, r + u + ".conv1.weight", st));
+        MAB_TRY(pack_conv3(h, r + u + ".conv2.weight", st));
+      }
+      MAB_TRY(pack_linear(h, r + ".out_conv.weight", 0, st));
+    }
+    MAB_TRY(pack_conv3(h, "dpt_regressor_head.conv1.weight", st));
+    MAB_TRY(pack_conv3(h, "dpt_regressor_head.conv2.0.weight", st));
   }
-  MAB_TRY(pack_conv3(h, "dpt_regressor_head.conv1.weight", st));
-  MAB_TRY(pack_conv3(h, "dpt_regressor_head.conv2.0.weight", st));
   // pose head: bf16x3 operands (the reference runs it in fp32/TF32, model.py:1774; its output is
   // normalised to a unit quaternion, which plain bf16 operands do not resolve to 0.1 deg)
   MAB_TRY(pack_linear_split(h, "pose_head.proj.weight", st));
@@ -1000,16 +1048,21 @@ extern "C" int mab_debug_buffer(mab_handle* h, const char* name, void** ptr, lon
   const int D = h->cfg.enc_dim, A = h->cfg.aat_dim;
   const std::string n = name;
   if (n == "enc_tokens") { *ptr = p.xs; *numel = p.Lenc * D; *dtype = MAB_F32; }
+  else if (n == "fused" && p.fused32) { *ptr = p.fused32; *numel = VT * D; *dtype = MAB_F32; }
   else if (n == "fused") { *ptr = p.fused; *numel = VT * D; *dtype = MAB_BF16; }
   else if (n == "aat_stream") { *ptr = p.ys; *numel = p.L * A; *dtype = MAB_F32; }
-  else if (n == "tap0") { *ptr = p.tap[0]; *numel = VT * A; *dtype = MAB_BF16; }
-  else if (n == "tap1") { *ptr = p.tap[1]; *numel = VT * A; *dtype = MAB_BF16; }
+  else if (n == "tap0" && p.tap32[0]) { *ptr = p.tap32[0]; *numel = VT * A; *dtype = MAB_F32; }
+  else if (n == "tap1" && p.tap32[1]) { *ptr = p.tap32[1]; *numel = VT * A; *dtype = MAB_F32; }
+  else if (n == "tap2" && p.tap32[2]) { *ptr = p.tap32[2]; *numel = VT * A; *dtype = MAB_F32; }
+  else if (n == "final" && p.fin32) { *ptr = p.fin32; *numel = VT * A; *dtype = MAB_F32; }
+  else if (n == "tap0" && p.tap[0]) { *ptr = p.tap[0]; *numel = VT * A; *dtype = MAB_BF16; }
+  else if (n == "tap1" && p.tap[1]) { *ptr = p.tap[1]; *numel = VT * A; *dtype = MAB_BF16; }
   else if (n == "tap2" && p.tap[2]) { *ptr = p.tap[2]; *numel = VT * A; *dtype = MAB_BF16; }
-  else if (n == "final") { *ptr = p.fin; *numel = VT * A; *dtype = MAB_BF16; }
+  else if (n == "final" && p.fin) { *ptr = p.fin; *numel = VT * A; *dtype = MAB_BF16; }
   else if (n == "scale_token") { *ptr = p.scale_tok; *numel = A; *dtype = MAB_F32; }
   else if (n == "pose_raw") { *ptr = p.pose_raw; *numel = (long long)p.V * 7; *dtype = MAB_F32; }
   else if (n == "pose_pool") { *ptr = p.pose_pool; *numel = (long long)p.V * 784; *dtype = MAB_F32; }
-  else if (n == "feat8") { *ptr = p.feat8; *numel = (long long)p.vc * 64 * p.T * 256; *dtype = MAB_BF16; }
+  else if (n == "feat8") { *ptr = p.feat8; *numel = (long long)p.vc * 64 * p.T * 256; *dtype = h->cfg.head_tf32 ? MAB_F32 : MAB_BF16; }
   else return fail(-1, "unknown debug buffer %s", name);
   return 0;
 }
@@ -1061,6 +1114,70 @@ struct Ctx {
     return launch_conv3(x, batch, H, W, C, Wp, Cout, ep, st);
   }
 };
+
+// ---- dense-head operators, typed by the activation element: bf16 (bf16 operands) or float (fp32
+// activations, TF32 contractions -- the reference's precision for this region, model.py:1774) ----------
+int head_linear(Ctx& c, const bf16* A, int M, int K, const std::string& wkey, int N, const float* bias, bf16* out) {
+  return c.linear(A, M, K, K, wkey, N, bias, ACT_NONE, nullptr, nullptr, nullptr, out);
+}
+int head_linear(Ctx& c, const float* A, int M, int K, const std::string& wkey, int N, const float* bias, float* out) {
+  const float* W = c.h->P32(wkey);
+  if (!W) return fail(-4, "weight %s was not packed (fp32)", wkey.c_str());
+  GemmEpilogue ep{};
+  ep.bias = bias; ep.out_f32 = out; ep.ldo = N; ep.round_tf32 = 1;
+  return launch_gemm_tf32(A, K, W, K, M, N, K, ep, c.st);
+}
+int head_conv3(Ctx& c, const bf16* x, int batch, int H, int W, int C, const std::string& wkey, int Cout,
+               const float* bias, int act, const bf16* res1, const bf16* res2, bf16* out, bf16* out_relu) {
+  return c.conv3(x, batch, H, W, C, wkey, Cout, bias, act, res1, res2, out, out_relu);
+}
+int head_conv3(Ctx& c, const float* x, int batch, int H, int W, int C, const std::string& wkey, int Cout,
+               const float* bias, int act, const float* res1, const float* res2, float* out, float* out_relu) {
+  const float* Wp = c.h->P32(wkey);
+  if (!Wp) return fail(-4, "weight %s was not packed (fp32)", wkey.c_str());
+  GemmEpilogue ep{};
+  ep.bias = bias; ep.res_f32 = res1; ep.res2_f32 = res2; ep.out_f32 = out; ep.out_relu_f32 = out_relu;
+  ep.ldo = Cout; ep.act = act; ep.round_tf32 = 1;
+  return launch_conv3_tf32(x, batch, H, W, C, C, Wp, Cout, ep, c.st);
+}
+// the two layout kernels move 16-byte units: an fp32 tensor is a bf16 tensor of twice the channels
+int head_pixel_shuffle(Ctx& c, const void* in, int es, int views, int h, int w, int k, int C, void* out) {
+  const int cb = C * es / 2;  // channels in bf16 units
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+             pixel_shuffle_kernel<<<ew_grid((long long)views * h * w * k * k * (cb / 8)), 256, 0, c.st>>>(
+                 reinterpret_cast<const bf16*>(in), views, h, w, k, cb, reinterpret_cast<bf16*>(out)));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+int head_im2col_s2(Ctx& c, const void* in, int es, int views, int H, int W, int C, int Ho, int Wo, void* out) {
+  const int cb = C * es / 2;
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+             im2col3x3_s2_kernel<<<ew_grid((long long)views * Ho * Wo * 9 * (cb / 8)), 256, 0, c.st>>>(
+                 reinterpret_cast<const bf16*>(in), views, H, W, cb, Ho, Wo, reinterpret_cast<bf16*>(out)));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+int head_resize(Ctx& c, const bf16* x, int batch, int Hi, int Wi, int C, int Hv, int Wv, int Ho, int Wo, bf16* out) {
+  return mab_resize_bilinear(x, batch, Hi, Wi, C, Hv, Wv, Ho, Wo, out, nullptr, c.st);
+}
+int head_resize(Ctx& c, const float* x, int batch, int Hi, int Wi, int C, int Hv, int Wv, int Ho, int Wo, float* out) {
+  MAB_ARG(batch > 0 && batch <= 65535 && Ho > 0 && Ho <= 65535 && Wo > 0 && C % 4 == 0, "resize: bad sizes");
+  const dim3 grid((Wo * (C / 4) + 255) / 256, Ho, batch);
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+             resize_bilinear_ac_f32_kernel<<<grid, 256, 0, c.st>>>(x, batch, Hi, Wi, C, Hv, Wv, Ho, Wo, out, nullptr));
+  MAB_CUDA(cudaGetLastError());
+  return 0;
+}
+int head_regress(Ctx& c, const bf16* x, int batch, int H, int W, const RegressEpilogue& rg) {
+  const bf16* w2 = c.h->P("dpt_regressor_head.conv2.0.weight");
+  if (!w2) return fail(-4, "dpt_regressor_head.conv2.0.weight was not packed");
+  return launch_conv3_regress(x, batch, H, W, w2, rg, c.st);
+}
+int head_regress(Ctx& c, const float* x, int batch, int H, int W, const RegressEpilogue& rg) {
+  const float* w2 = c.h->P32("dpt_regressor_head.conv2.0.weight");
+  if (!w2) return fail(-4, "dpt_regressor_head.conv2.0.weight was not packed (fp32)");
+  return launch_conv3_regress_tf32(x, batch, H, W, w2, rg, c.st);
+}
 
 // one pre-LN transformer block over `rows` tokens of width D (block.py:93-118,
 // transformer_blocks.py:467-468): x += g1*proj(attn(LN1 x)); x += g2*fc2(gelu(fc1(LN2 x)))
@@ -1114,13 +1231,14 @@ int dense_rep_encode(Ctx& c, const std::string& e, float* scratch, int cin_pad, 
     if (!W) return fail(-4, "weight %s was not packed", key.c_str());
     GemmEpilogue ep{};
     ep.bias = bias; ep.out_f32 = out; ep.ldo = ldo; ep.act = act; ep.res_f32 = res; ep.act_post = act_post;
+    ep.round_tf32 = 1;
     return launch_conv3_tf32(x, V, hh, ww, C, Creal, W, Cout, ep, c.st);
   };
   auto lin = [&](const float* x, int K, int lda, const std::string& key, int N, const float* bias, float* out) {
     const float* W = h->P32(key);
     if (!W) return fail(-4, "weight %s was not packed", key.c_str());
     GemmEpilogue ep{};
-    ep.bias = bias; ep.out_f32 = out; ep.ldo = N;
+    ep.bias = bias; ep.out_f32 = out; ep.ldo = N; ep.round_tf32 = 1;
     return launch_gemm_tf32(x, lda, W, K, (int)VT, N, K, ep, c.st);
   };
   MAB_TRY(conv(unsh, cin_pad, cin_real, e + ".conv_in.weight", 588, h->F(e + ".conv_in.bias"), ACT_NONE,
@@ -1236,7 +1354,7 @@ int encode_geometric_inputs(Ctx& c, const mab_inputs* in) {
              fuse_norm_kernel<8><<<(int)((VT + 7) / 8), 256, 0, c.st>>>(
                  p.enc_out, first_dense ? nullptr : p.geo_sum, first_vec ? nullptr : p.geo_vec, (int)VT, T,
                  h->F("fusion_norm_layer.weight"), h->F("fusion_norm_layer.bias"), 1e-6f, p.fused,
-                 c.h->cfg.aat_dim == D ? p.ys : nullptr));
+                 c.h->cfg.aat_dim == D ? p.ys : p.fused32, c.h->cfg.aat_dim == D ? 0 : 1));
   MAB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -1289,8 +1407,8 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
     // (image-only: the geometric features are exactly zero, model.py:931-968 / SURVEY 8a a6)
     MAB_TRY(launch_layernorm(p.xs, (int)VT, D, T, T + 1, 1, h->F("encoder.model.norm.weight"),
                              h->F("encoder.model.norm.bias"), h->F("fusion_norm_layer.weight"),
-                             h->F("fusion_norm_layer.bias"), 1e-6f, p.fused, identity_embed ? p.ys : nullptr,
-                             nullptr, c.st));
+                             h->F("fusion_norm_layer.bias"), 1e-6f, p.fused, identity_embed ? p.ys : p.fused32,
+                             nullptr, c.st, nullptr, identity_embed ? 0 : 1));
   } else {
     MAB_TRY(launch_layernorm(p.xs, (int)VT, D, T, T + 1, 1, h->F("encoder.model.norm.weight"),
                              h->F("encoder.model.norm.bias"), nullptr, nullptr, 1e-6f, nullptr, p.enc_out,
@@ -1435,16 +1553,17 @@ extern "C" int mab_stage_aat_finish(mab_handle* h, int layer, void* stream) {
   const long long VT = (long long)V * T;
   const float* nw = h->F("info_sharing.norm.weight");
   const float* nb = h->F("info_sharing.norm.bias");
-  bf16* dst = nullptr;
-  if (layer == cf.aat_tap0) dst = p.tap[0];
-  else if (layer == cf.aat_tap1) dst = p.tap[1];
-  else if (cf.aat_tap2 > 0 && layer == cf.aat_tap2) dst = p.tap[2];
-  if (dst)
+  int tap = -1;
+  if (layer == cf.aat_tap0) tap = 0;
+  else if (layer == cf.aat_tap1) tap = 1;
+  else if (cf.aat_tap2 > 0 && layer == cf.aat_tap2) tap = 2;
+  // bf16 for the bf16 head; fp32 for the fp32 / TF32 head (exactly one of the two buffers exists)
+  if (tap >= 0)
     MAB_TRY(launch_layernorm(p.ys, (int)VT, A, (int)VT, (int)VT, 0, nw, nb, nullptr, nullptr, 1e-6f,
-                             dst, nullptr, nullptr, c.st));
+                             p.tap[tap], p.tap32[tap], nullptr, c.st, nullptr, 1));
   if (layer == cf.aat_depth - 1) {
     MAB_TRY(launch_layernorm(p.ys, (int)VT, A, (int)VT, (int)VT, 0, nw, nb, nullptr, nullptr, 1e-6f,
-                             p.fin, nullptr, nullptr, c.st));
+                             p.fin, p.fin32, nullptr, c.st, nullptr, 1));
     if (p.has_scale)
       MAB_TRY(launch_layernorm(p.ys + VT * A, 1, A, 1, 1, 0, nw, nb, nullptr, nullptr, 1e-6f, nullptr,
                                p.scale_tok, nullptr, c.st));
@@ -1468,13 +1587,14 @@ int small_linear(cudaStream_t st, const float* x, const float* w, const float* b
 
 // ResidualConvUnit_custom (dpt_block.py:156-177) on `x` (with relu(x) precomputed in x_relu):
 //   out = conv2(relu(conv1(relu(x)) + b1)) + b2 + x (+ extra)
-int rcu(Ctx& c, const std::string& p, const bf16* x, const bf16* x_relu, const bf16* extra, int batch,
-        int H, int W, bf16* tmp_relu, bf16* out, bf16* out_relu) {
+template <typename T>
+int rcu(Ctx& c, const std::string& p, const T* x, const T* x_relu, const T* extra, int batch,
+        int H, int W, T* tmp_relu, T* out, T* out_relu) {
   mab_handle* h = c.h;
-  MAB_TRY(c.conv3(x_relu, batch, H, W, 256, p + ".conv1.weight", 256, h->F(p + ".conv1.bias"), ACT_RELU,
-                  nullptr, nullptr, tmp_relu, nullptr));
-  return c.conv3(tmp_relu, batch, H, W, 256, p + ".conv2.weight", 256, h->F(p + ".conv2.bias"), ACT_NONE,
-                 x, extra, out, out_relu);
+  MAB_TRY(head_conv3(c, x_relu, batch, H, W, 256, p + ".conv1.weight", 256, h->F(p + ".conv1.bias"), ACT_RELU,
+                     (const T*)nullptr, (const T*)nullptr, tmp_relu, (T*)nullptr));
+  return head_conv3(c, tmp_relu, batch, H, W, 256, p + ".conv2.weight", 256, h->F(p + ".conv2.bias"), ACT_NONE,
+                    x, extra, out, out_relu);
 }
 
 }  // namespace
@@ -1496,6 +1616,9 @@ extern "C" int mab_stage_scale_head(mab_handle* h, float* metric_scale_out, void
 }
 
 namespace {
+template <typename T>
+int stage_heads_range_t(mab_handle* h, const mab_inputs* in, mab_outputs* out, const float* metric_scale_in,
+                        int view_lo, int view_hi, bool with_scale, void* stream);
 int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, const float* metric_scale_in,
                       int view_lo, int view_hi, bool with_scale, void* stream);
 // every array of mab_outputs except logits6 is written by the heads
@@ -1526,11 +1649,20 @@ extern "C" int mab_stage_heads_range(mab_handle* h, const mab_inputs* in, mab_ou
 namespace {
 int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, const float* metric_scale_in,
                       int view_lo, int view_hi, bool with_scale, void* stream) {
+  if (h->cfg.head_tf32)
+    return stage_heads_range_t<float>(h, in, out, metric_scale_in, view_lo, view_hi, with_scale, stream);
+  return stage_heads_range_t<bf16>(h, in, out, metric_scale_in, view_lo, view_hi, with_scale, stream);
+}
+
+template <typename T>
+int stage_heads_range_t(mab_handle* h, const mab_inputs* in, mab_outputs* out, const float* metric_scale_in,
+                        int view_lo, int view_hi, bool with_scale, void* stream) {
+  constexpr bool TF = sizeof(T) == 4;
+  constexpr int ES = (int)sizeof(T);
   const mab_config& cf = h->cfg;
   Ctx c{h, (cudaStream_t)stream};
   Plan& p = h->plan;
-  const int V = p.V, T = p.T, A = cf.aat_dim, hh = p.h, ww = p.w, H = p.H, W = p.W;
-  const long long VT = (long long)V * T;
+  const int V = p.V, T_ = p.T, A = cf.aat_dim, hh = p.h, ww = p.w, H = p.H, W = p.W;
 
   // ---- scale head: computed here by the rank that owns the scale token, unless the caller
   // already ran mab_stage_scale_head and broadcast its result (view-sharded run) ------------------
@@ -1550,20 +1682,30 @@ int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, con
   const int h3 = (hh + 1) / 2, w3 = (ww + 1) / 2;
   for (int v0 = view_lo; v0 < view_hi; v0 += p.vc) {
     const int vc = (view_hi - v0 < p.vc) ? view_hi - v0 : p.vc;
-    const int M = vc * T;
+    const int M = vc * T_;
     // model.py:1724-1768: [encoder features, 2 intermediate, final] or, with three intermediate
     // features (48-layer configs), [3 intermediate, final] and no encoder features
     const bool three = cf.aat_tap2 > 0;
     const int K0 = three ? A : cf.enc_dim;
-    const bf16* f0 = three ? p.tap[0] + (long long)v0 * T * A : p.fused + (long long)v0 * T * cf.enc_dim;
-    const bf16* f1 = p.tap[three ? 1 : 0] + (long long)v0 * T * A;
-    const bf16* f2 = p.tap[three ? 2 : 1] + (long long)v0 * T * A;
-    const bf16* f3 = p.fin + (long long)v0 * T * A;
+    // head inputs: bf16 token-major buffers, or their fp32 twins for the fp32 / TF32 head
+    auto head_in = [&](const bf16* b16, const float* f32, int dim) -> const T* {
+      if (TF) return reinterpret_cast<const T*>(f32 + (long long)v0 * T_ * dim);
+      return reinterpret_cast<const T*>(b16 + (long long)v0 * T_ * dim);
+    };
+    const T* f0 = three ? head_in(p.tap[0], p.tap32[0], A) : head_in(p.fused, p.fused32, cf.enc_dim);
+    const T* f1 = head_in(p.tap[three ? 1 : 0], p.tap32[three ? 1 : 0], A);
+    const T* f2 = head_in(p.tap[three ? 2 : 1], p.tap32[three ? 2 : 1], A);
+    const T* f3 = head_in(p.fin, p.fin32, A);
+    T* d_a = (T*)p.d_a; T* d_s = (T*)p.d_s; T* d_u = (T*)p.d_u; T* t0 = (T*)p.t0; T* t1 = (T*)p.t1;
+    T* t2 = (T*)p.t2; T* t3 = (T*)p.t3; T* path = (T*)p.path; T* feat8 = (T*)p.feat8; T* r1 = (T*)p.r1; T* r2 = (T*)p.r2;
+    T* lvl[4]; T* lvl_relu[4];
+    for (int i = 0; i < 4; ++i) { lvl[i] = (T*)p.lvl[i]; lvl_relu[i] = (T*)p.lvl_relu[i]; }
+    const T* nil = nullptr;
     // ---- pose head (pose_head.py:115-159, adaptors.py:714-732) in bf16x3 (~fp32) arithmetic:
     // final norm of this chunk's tokens as a split value, 7 token-wise GEMMs, mean over tokens
     {
       const std::string ph = "pose_head.";
-      MAB_TRY(launch_layernorm(p.ys + (long long)v0 * T * A, M, A, M, M, 0, h->F("info_sharing.norm.weight"),
+      MAB_TRY(launch_layernorm(p.ys + (long long)v0 * T_ * A, M, A, M, M, 0, h->F("info_sharing.norm.weight"),
                                h->F("info_sharing.norm.bias"), nullptr, nullptr, 1e-6f, nullptr, nullptr,
                                nullptr, c.st, p.ph_in));
       MAB_TRY(c.linear_x3(p.ph_in, M, A, ph + "proj.weight", 784, h->F(ph + "proj.bias"), ACT_NONE, nullptr, p.ph_a));
@@ -1577,7 +1719,7 @@ int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, con
       }
       dim3 blk(128, 8), grd((784 + 127) / 128, vc);
       MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
-                 token_mean_kernel<<<grd, blk, 0, c.st>>>(feat, T, 784, 3 * 784, 784, p.pose_pool + (long long)v0 * 784));
+                 token_mean_kernel<<<grd, blk, 0, c.st>>>(feat, T_, 784, 3 * 784, 784, p.pose_pool + (long long)v0 * 784));
       MAB_CUDA(cudaGetLastError());
       float* pool = p.pose_pool + (long long)v0 * 784;
       float* m0 = p.pose_tmp; float* m1 = p.pose_tmp + (long long)V * 784;
@@ -1593,47 +1735,44 @@ int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, con
       MAB_CUDA(cudaGetLastError());
     }
     // layer 0: 1x1 (1024->96) -> convT 4x4/s4 -> 3x3 (96->256, no bias)           dpt.py:107-128
-    MAB_TRY(c.linear(f0, M, K0, K0, ip + "0.0.0.weight", 96, h->F(ip + "0.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
-    MAB_TRY(c.linear(p.d_a, M, 96, 96, ip + "0.0.1.weight", 16 * 96, h->extra[ip + "0.0.1.bias.tiled"], ACT_NONE, nullptr, nullptr, nullptr, p.d_s));
-    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
-               pixel_shuffle_kernel<<<ew_grid((long long)M * 16 * 12), 256, 0, c.st>>>(p.d_s, vc, hh, ww, 4, 96, p.d_u));
-    MAB_TRY(c.conv3(p.d_u, vc, 4 * hh, 4 * ww, 96, sc + "layer1_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[0], p.lvl_relu[0]));
+    MAB_TRY(head_linear(c, f0, M, K0, ip + "0.0.0.weight", 96, h->F(ip + "0.0.0.bias"), d_a));
+    MAB_TRY(head_linear(c, d_a, M, 96, ip + "0.0.1.weight", 16 * 96, h->extra[ip + "0.0.1.bias.tiled"], d_s));
+    MAB_TRY(head_pixel_shuffle(c, d_s, ES, vc, hh, ww, 4, 96, d_u));
+    MAB_TRY(head_conv3(c, d_u, vc, 4 * hh, 4 * ww, 96, sc + "layer1_rn.weight", 256, nullptr, ACT_NONE, nil, nil, lvl[0], lvl_relu[0]));
     // layer 1: 1x1 (768->192) -> convT 2x2/s2 -> 3x3 (192->256)
-    MAB_TRY(c.linear(f1, M, A, A, ip + "1.0.0.weight", 192, h->F(ip + "1.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
-    MAB_TRY(c.linear(p.d_a, M, 192, 192, ip + "1.0.1.weight", 4 * 192, h->extra[ip + "1.0.1.bias.tiled"], ACT_NONE, nullptr, nullptr, nullptr, p.d_s));
-    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
-               pixel_shuffle_kernel<<<ew_grid((long long)M * 4 * 24), 256, 0, c.st>>>(p.d_s, vc, hh, ww, 2, 192, p.d_u));
-    MAB_TRY(c.conv3(p.d_u, vc, 2 * hh, 2 * ww, 192, sc + "layer2_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[1], p.lvl_relu[1]));
+    MAB_TRY(head_linear(c, f1, M, A, ip + "1.0.0.weight", 192, h->F(ip + "1.0.0.bias"), d_a));
+    MAB_TRY(head_linear(c, d_a, M, 192, ip + "1.0.1.weight", 4 * 192, h->extra[ip + "1.0.1.bias.tiled"], d_s));
+    MAB_TRY(head_pixel_shuffle(c, d_s, ES, vc, hh, ww, 2, 192, d_u));
+    MAB_TRY(head_conv3(c, d_u, vc, 2 * hh, 2 * ww, 192, sc + "layer2_rn.weight", 256, nullptr, ACT_NONE, nil, nil, lvl[1], lvl_relu[1]));
     // layer 2: 1x1 (768->384) -> 3x3 (384->256)
-    MAB_TRY(c.linear(f2, M, A, A, ip + "2.0.0.weight", 384, h->F(ip + "2.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
-    MAB_TRY(c.conv3(p.d_a, vc, hh, ww, 384, sc + "layer3_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[2], p.lvl_relu[2]));
+    MAB_TRY(head_linear(c, f2, M, A, ip + "2.0.0.weight", 384, h->F(ip + "2.0.0.bias"), d_a));
+    MAB_TRY(head_conv3(c, d_a, vc, hh, ww, 384, sc + "layer3_rn.weight", 256, nullptr, ACT_NONE, nil, nil, lvl[2], lvl_relu[2]));
     // layer 3: 1x1 (768->768) -> 3x3/s2 (im2col + GEMM) -> 3x3 (768->256)
-    MAB_TRY(c.linear(f3, M, A, A, ip + "3.0.0.weight", 768, h->F(ip + "3.0.0.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_a));
-    MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
-               im2col3x3_s2_kernel<<<ew_grid((long long)vc * h3 * w3 * 9 * 96), 256, 0, c.st>>>(p.d_a, vc, hh, ww, 768, h3, w3, p.d_s));
-    MAB_TRY(c.linear(p.d_s, vc * h3 * w3, 9 * 768, 9 * 768, ip + "3.0.1.weight", 768, h->F(ip + "3.0.1.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.d_u));
-    MAB_TRY(c.conv3(p.d_u, vc, h3, w3, 768, sc + "layer4_rn.weight", 256, nullptr, ACT_NONE, nullptr, nullptr, p.lvl[3], p.lvl_relu[3]));
+    MAB_TRY(head_linear(c, f3, M, A, ip + "3.0.0.weight", 768, h->F(ip + "3.0.0.bias"), d_a));
+    MAB_TRY(head_im2col_s2(c, d_a, ES, vc, hh, ww, 768, h3, w3, d_s));
+    MAB_TRY(head_linear(c, d_s, vc * h3 * w3, 9 * 768, ip + "3.0.1.weight", 768, h->F(ip + "3.0.1.bias"), d_u));
+    MAB_TRY(head_conv3(c, d_u, vc, h3, w3, 768, sc + "layer4_rn.weight", 256, nullptr, ACT_NONE, nil, nil, lvl[3], lvl_relu[3]));
     MAB_CUDA(cudaGetLastError());
 
     // refinenet4: RCU2 -> out_conv (1x1, commutes with the bilinear x2) -> x2 -> crop   dpt.py:213
-    MAB_TRY(rcu(c, sc + "refinenet4.resConfUnit2", p.lvl[3], p.lvl_relu[3], nullptr, vc, h3, w3, p.t0, p.t1, nullptr));
-    MAB_TRY(c.linear(p.t1, vc * h3 * w3, 256, 256, sc + "refinenet4.out_conv.weight", 256, h->F(sc + "refinenet4.out_conv.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.t2));
-    MAB_TRY(mab_resize_bilinear(p.t2, vc, h3, w3, 256, 2 * h3, 2 * w3, hh, ww, p.path, nullptr, c.st));
+    MAB_TRY(rcu<T>(c, sc + "refinenet4.resConfUnit2", lvl[3], lvl_relu[3], nil, vc, h3, w3, t0, t1, (T*)nullptr));
+    MAB_TRY(head_linear(c, t1, vc * h3 * w3, 256, sc + "refinenet4.out_conv.weight", 256, h->F(sc + "refinenet4.out_conv.bias"), t2));
+    MAB_TRY(head_resize(c, t2, vc, h3, w3, 256, 2 * h3, 2 * w3, hh, ww, path));
     // refinenet3/2/1: x = path + RCU1(skip); x = RCU2(x); out_conv; x2                dpt_block.py:225-255
     int lh = hh, lw = ww;
-    for (int lvl = 2; lvl >= 0; --lvl) {
-      const std::string r = sc + "refinenet" + std::to_string(lvl + 1);
-      MAB_TRY(rcu(c, r + ".resConfUnit1", p.lvl[lvl], p.lvl_relu[lvl], p.path, vc, lh, lw, p.t0, p.t1, p.t2));
-      MAB_TRY(rcu(c, r + ".resConfUnit2", p.t1, p.t2, nullptr, vc, lh, lw, p.t0, p.t3, nullptr));
-      MAB_TRY(c.linear(p.t3, vc * lh * lw, 256, 256, r + ".out_conv.weight", 256, h->F(r + ".out_conv.bias"), ACT_NONE, nullptr, nullptr, nullptr, p.t0));
-      bf16* dst = (lvl == 0) ? p.feat8 : p.path;
-      MAB_TRY(mab_resize_bilinear(p.t0, vc, lh, lw, 256, 2 * lh, 2 * lw, 2 * lh, 2 * lw, dst, nullptr, c.st));
+    for (int l = 2; l >= 0; --l) {
+      const std::string r = sc + "refinenet" + std::to_string(l + 1);
+      MAB_TRY(rcu<T>(c, r + ".resConfUnit1", lvl[l], lvl_relu[l], path, vc, lh, lw, t0, t1, t2));
+      MAB_TRY(rcu<T>(c, r + ".resConfUnit2", t1, t2, nil, vc, lh, lw, t0, t3, (T*)nullptr));
+      MAB_TRY(head_linear(c, t3, vc * lh * lw, 256, r + ".out_conv.weight", 256, h->F(r + ".out_conv.bias"), t0));
+      T* dst = (l == 0) ? feat8 : path;
+      MAB_TRY(head_resize(c, t0, vc, lh, lw, 256, 2 * lh, 2 * lw, 2 * lh, 2 * lw, dst));
       lh *= 2; lw *= 2;
     }
     // regressor: 3x3 (256->128) -> bilinear to HxW -> [3x3 (128->128) + ReLU + 1x1 (128->6) +
     // adaptor + pointmap] in one kernel                                               dpt.py:285-311
-    MAB_TRY(c.conv3(p.feat8, vc, lh, lw, 256, "dpt_regressor_head.conv1.weight", 128, h->F("dpt_regressor_head.conv1.bias"), ACT_NONE, nullptr, nullptr, p.r1, nullptr));
-    MAB_TRY(mab_resize_bilinear(p.r1, vc, lh, lw, 128, H, W, H, W, p.r2, nullptr, c.st));
+    MAB_TRY(head_conv3(c, feat8, vc, lh, lw, 256, "dpt_regressor_head.conv1.weight", 128, h->F("dpt_regressor_head.conv1.bias"), ACT_NONE, nil, nil, r1, (T*)nullptr));
+    MAB_TRY(head_resize(c, r1, vc, lh, lw, 128, H, W, H, W, r2));
     RegressEpilogue rg{};
     const long long px0 = (long long)v0 * H * W;
     rg.bias2 = h->F("dpt_regressor_head.conv2.0.bias");
@@ -1646,8 +1785,7 @@ int stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, con
     rg.conf = out->conf + px0; rg.mask_logits = out->mask_logits + px0;
     rg.mask = out->non_ambiguous_mask + px0;
     rg.logits6 = out->logits6 ? out->logits6 + px0 * 6 : nullptr;
-    const bf16* w2 = h->P("dpt_regressor_head.conv2.0.weight");
-    MAB_TRY(launch_conv3_regress(p.r2, vc, H, W, w2, rg, c.st));
+    MAB_TRY(head_regress(c, r2, vc, H, W, rg));
   }
   return 0;
 }

@@ -63,7 +63,7 @@ def default_config():
     return dict(patch=14, enc_dim=1024, enc_depth=24, enc_heads=16, enc_pos_grid=37, aat_dim=768,
                 aat_depth=24, aat_heads=12, aat_tap0=11, aat_tap1=17, head_chunk=8,
                 aat_ref_view_pe=1, aat_entropy_scaling=0, aat_tap2=0,
-                aat_nonref_view_pe=0, aat_all_global=0)
+                aat_nonref_view_pe=0, aat_all_global=0, head_tf32=1)
 
 
 def head_ranges(V, stream_chunk, default_chunk):
@@ -111,8 +111,16 @@ class MapAnything(torch.nn.Module):
                  pretrained_checkpoint_path: Optional[str] = None,
                  load_specific_pretrained_submodules: bool = False,
                  specific_pretrained_submodules: Optional[list] = None,
-                 torch_hub_force_reload: bool = False, device="cuda", head_chunk: int = 8):
+                 torch_hub_force_reload: bool = False, device="cuda", head_chunk: int = 8,
+                 head_precision: str = "tf32"):
+        """Reference constructor arguments (model.py:99-113) plus three of this implementation: `device`,
+        `head_chunk` (views per dense-head pass; a workspace knob, results do not depend on it) and
+        `head_precision`: "tf32" (default) runs the DPT feature head and the regressor with fp32
+        activations and TF32 contractions, the reference's own arithmetic for that region (autocast off,
+        model.py:1774); "bf16" is the faster opt-in with bf16 operands."""
         super().__init__()
+        if head_precision not in ("tf32", "bf16"):
+            raise ValueError(f"head_precision must be 'tf32' or 'bf16', got {head_precision!r}")
         self.name = name
         self.encoder_config = encoder_config or {"data_norm_type": "dinov2", "name": "dinov2_large"}
         self.info_sharing_config = info_sharing_config or {}
@@ -152,6 +160,8 @@ class MapAnything(torch.nn.Module):
             self._check_view_count = True
         self._pinned_view_pe_rows = None
         cfg["head_chunk"] = int(head_chunk)
+        cfg["head_tf32"] = int(head_precision == "tf32")
+        self.head_precision = head_precision
         self._cfg = _lib.MabConfig(**cfg)
         self._handle = C.c_void_p()
         _lib.check(self._lib.mab_create(C.byref(self._cfg), self._device.index or 0, C.byref(self._handle)),
@@ -478,17 +488,20 @@ class MapAnything(torch.nn.Module):
                 self._forward_sharded(inp, ost, outs, ws, V, H, W, view_lo, total)
         return outs
 
-    def _draw_view_pe_rows(self, total):
+    def _draw_view_pe_rows(self, total, sharded=False):
         """view_pos_table row of every view of a scene (aat.py:618-645): 0 for the reference view, then
         torch.randint(1, max_num_views_for_pe) from the global CPU generator like the reference (default)
-        or 1..V-1.  View-sharded runs take rank 0's draw."""
+        or 1..V-1.  A view-SHARDED call (this rank holds fewer views than the scene has) takes rank 0's
+        draw; ranks that run independent scenes under an initialised process group draw locally -- no
+        hidden collective outside the sharded path."""
         if self._rand_view_pe:
             rows = torch.randint(low=1, high=self._max_views_for_pe, size=(total - 1,))
         else:
             rows = torch.arange(1, total)
         rows = torch.cat([torch.zeros(1, dtype=torch.int64), rows.to(torch.int64)])
         import torch.distributed as dist
-        if self._rand_view_pe and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        if (sharded and self._rand_view_pe and dist.is_available() and dist.is_initialized()
+                and dist.get_world_size() > 1):
             dev_rows = rows.to(self._device)
             dist.broadcast(dev_rows, src=0)
             rows = dev_rows.cpu()
@@ -499,7 +512,8 @@ class MapAnything(torch.nn.Module):
             assert total <= self._max_views_for_pe, f"Expected less than {self._max_views_for_pe} views, got {total}"
         if not self._cfg.aat_nonref_view_pe:
             return
-        rows = self._pinned_view_pe_rows if self._pinned_view_pe_rows is not None else self._draw_view_pe_rows(total)
+        rows = (self._pinned_view_pe_rows if self._pinned_view_pe_rows is not None
+                else self._draw_view_pe_rows(total, sharded=total > V))
         local = (C.c_int * V)(*[int(r) for r in rows[view_lo:view_lo + V]])
         _lib.check(self._lib.mab_set_view_pe_rows(self._handle, local, V), "mab_set_view_pe_rows")
 
@@ -667,22 +681,35 @@ class MapAnything(torch.nn.Module):
                   ("depth_z", "post", "depth_z"), ("intrinsics", "post", "intrinsics"),
                   ("camera_poses", "post", "camera_poses"), ("mask", "post", "mask"))
 
-    def _infer_to_host(self, imgs, H, W, view_lo, total_views, geo, post_args, stream_chunk):
+    # per-view shape of every prediction (-1 = H, -2 = W) and its dtype
+    _PRED_SHAPES = {"pts3d": ((-1, -2, 3), torch.float32), "pts3d_cam": ((-1, -2, 3), torch.float32),
+                    "ray_directions": ((-1, -2, 3), torch.float32), "depth_along_ray": ((-1, -2, 1), torch.float32),
+                    "cam_trans": ((3,), torch.float32), "cam_quats": ((4,), torch.float32),
+                    "conf": ((-1, -2), torch.float32), "non_ambiguous_mask": ((-1, -2), torch.bool),
+                    "non_ambiguous_mask_logits": ((-1, -2), torch.float32), "img_no_norm": ((-1, -2, 3), torch.float32),
+                    "depth_z": ((-1, -2, 1), torch.float32), "intrinsics": ((3, 3), torch.float32),
+                    "camera_poses": ((4, 4), torch.float32), "mask": ((-1, -2, 1), torch.bool)}
+
+    def _infer_to_host(self, imgs, H, W, view_lo, total_views, geo, post_args, stream_chunk,
+                       reuse_host_buffers=False):
         """infer(host_outputs=True): heads in ranges of `stream_chunk` views; post-processing of a
         finished range on the compute stream, its device-to-host copies on a second stream."""
         V, dev = imgs.shape[0], self._device
         apply_mask = post_args[0]
         post = self._alloc_post(V, H, W)
         key = (V, H, W)
-        if self._host_pool is None or self._host_pool[0] != key:
-            raw_shapes = self._alloc_outputs(1, H, W)  # one view: shapes / dtypes only
+        if not reuse_host_buffers or self._host_pool is None or self._host_pool[0] != key:
+            # fresh, caller-owned pinned tensors (the reference returns fresh tensors, SURVEY 8b); torch's
+            # pinned-memory caching allocator recycles the blocks of results the caller has dropped
             bufs = {}
             for name, src, k in self._PRED_KEYS:
-                t = raw_shapes[k] if src == "raw" else self._alloc_post(1, H, W)[k]
-                bufs[name] = torch.empty((V,) + tuple(t.shape[1:]), dtype=t.dtype, pin_memory=True)
+                shape, dtype = self._PRED_SHAPES[name]
+                bufs[name] = torch.empty((V,) + tuple(x if x >= 0 else (H, W)[-x - 1] for x in shape), dtype=dtype,
+                                         pin_memory=True)
             bufs["metric_scaling_factor"] = torch.empty((1, 1), dtype=torch.float32, pin_memory=True)
-            self._host_pool = (key, bufs)
-        host = self._host_pool[1]
+            if reuse_host_buffers:
+                self._host_pool = (key, bufs)
+        host = self._host_pool[1] if reuse_host_buffers else bufs
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(device=dev)
         side = self._copy_stream
@@ -702,7 +729,7 @@ class MapAnything(torch.nn.Module):
                     host["metric_scaling_factor"].copy_(outs["metric_scale"], non_blocking=True)
 
         with torch.cuda.device(dev):
-            side.wait_stream(main)  # the pool may still be read by copies of the previous call
+            side.wait_stream(main)  # a reused pool may still be read by copies of the previous call
             outs = self._run_forward(imgs, H, W, view_lo=view_lo, total_views=total_views, geo=geo,
                                      on_views=on_views, stream_chunk=stream_chunk)
             side.synchronize()
@@ -753,10 +780,12 @@ class MapAnything(torch.nn.Module):
               ignore_depth_inputs: bool = False, ignore_pose_inputs: bool = False,
               ignore_depth_scale_inputs: bool = False, ignore_pose_scale_inputs: bool = False,
               view_range=None, total_views: Optional[int] = None, host_outputs: bool = False,
-              stream_chunk: int = 4) -> List[Dict[str, torch.Tensor]]:
-        """model.py:2206-2355.  The kernels always compute in bf16 with fp32 accumulation / fp32
-        residual streams (the reference's bf16-autocast semantics); `use_amp`/`amp_dtype` are
-        accepted for signature compatibility.
+              stream_chunk: int = 4, reuse_host_buffers: bool = False) -> List[Dict[str, torch.Tensor]]:
+        """model.py:2206-2355.  The kernels compute with the precision regions of the reference's
+        DEFAULT call -- `use_amp=True, amp_dtype="bf16"` (model.py:2287-2302): bf16 operands with fp32
+        accumulation and fp32 residual streams in the encoder and the info-sharing transformer, fp32/TF32
+        elsewhere.  There is no fp32 trunk and no fp16 path here, so `use_amp=False` and any other
+        `amp_dtype` raise NotImplementedError instead of silently returning bf16 results.
 
         Extension for view-sharded scenes (one process per GPU, torch.distributed initialised):
         `views` are THIS rank's views [view_range[0], view_range[1]) of a scene of `total_views`
@@ -769,10 +798,16 @@ class MapAnything(torch.nn.Module):
         it.  `stream_chunk` may also be a sequence of range sizes (last one repeating); measured at
         8 views (profiles/e2e_variants.py): 4|4 20.28 ms, 4|3|1 20.40, 4|2|2 20.70, 8 20.87, 2|2|2|2
         21.44 -- shrinking the last range shortens the copy-out tail by less than small ranges cost
-        the dense head.  The returned tensors are views into a buffer the model reuses: valid until
-        the next `infer(host_outputs=True)` call on this model."""
+        the dense head.  The returned tensors are fresh and caller-owned, like the reference's;
+        `reuse_host_buffers=True` returns views into ONE pool the model keeps instead (valid until the
+        next such call on this model), which saves the pinned allocation of a first call."""
         if not self._finalized:
             raise RuntimeError("load_state_dict() / from_pretrained() must be called before inference")
+        if not use_amp or amp_dtype != "bf16":
+            raise NotImplementedError(
+                f"infer(use_amp={use_amp!r}, amp_dtype={amp_dtype!r}): mapanything_b200 implements the reference's "
+                "default mixed-precision path only (use_amp=True, amp_dtype='bf16', model.py:2287-2302); an fp32 or "
+                "fp16 run has to use the reference")
         views = validate_input_views_for_inference(views)
         for v in views:
             if v["data_norm_type"][0] != self.data_norm_type:  # encoders/base.py:83-96
@@ -789,18 +824,21 @@ class MapAnything(torch.nn.Module):
                       ignore_depth_inputs=ignore_depth_inputs, ignore_pose_inputs=ignore_pose_inputs,
                       ignore_depth_scale_inputs=ignore_depth_scale_inputs,
                       ignore_pose_scale_inputs=ignore_pose_scale_inputs, view_range=view_range,
-                      total_views=total_views, host_outputs=host_outputs, stream_chunk=stream_chunk)
+                      total_views=total_views, host_outputs=host_outputs, stream_chunk=stream_chunk,
+                      reuse_host_buffers=reuse_host_buffers)
             per_scene = []
             if self._cfg.aat_nonref_view_pe:  # the reference draws the view-PE rows once per call
-                self._pinned_view_pe_rows = self._draw_view_pe_rows(int(total_views or len(views)))
+                total = int(total_views or len(views))
+                self._pinned_view_pe_rows = self._draw_view_pe_rows(total, sharded=total > len(views))
             try:
                 for b in range(B):
                     scene = [{k: (t[b:b + 1] if torch.is_tensor(t) and t.dim() > 0 and t.shape[0] == B else
                                   (tuple(c[b:b + 1] for c in t) if isinstance(t, tuple) else t))
                               for k, t in v.items()} for v in views]
                     preds = self.infer(scene, **kw)
-                    # host_outputs reuses one pinned pool per call: detach the scene's results from it
-                    per_scene.append([{k: t.clone() for k, t in p.items()} for p in preds] if host_outputs else preds)
+                    # a reused pinned pool is overwritten by the next scene: detach this scene's results
+                    per_scene.append([{k: t.clone() for k, t in p.items()} for p in preds]
+                                     if host_outputs and reuse_host_buffers else preds)
             finally:
                 self._pinned_view_pe_rows = None
             for v in views:  # model.py:2316-2320: the caller's tensors end up on the model device
@@ -827,7 +865,8 @@ class MapAnything(torch.nn.Module):
         post_args = (apply_mask, mask_edges, edge_normal_threshold, edge_depth_threshold, apply_confidence_mask,
                      confidence_percentile)
         if host_outputs:
-            return self._infer_to_host(imgs, H, W, lo, total_views, geo, post_args, stream_chunk)
+            return self._infer_to_host(imgs, H, W, lo, total_views, geo, post_args, stream_chunk,
+                                       reuse_host_buffers)
         outs = self._run_forward(imgs, H, W, view_lo=lo, total_views=total_views, geo=geo)
         post = self._run_postprocess(imgs, outs, H, W, *post_args)
         preds = []

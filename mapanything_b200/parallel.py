@@ -112,3 +112,55 @@ def gather_pass(rows: Sequence[int], kv_all: torch.Tensor, export_local: Callabl
         r.wait()
     for i, (a, b) in enumerate(spans):
         attend_kv(kv_all[a:b], b - a, False, i == len(spans) - 1)
+
+
+SELF_CHECK_KEYS = ("pts3d", "pts3d_cam", "ray_directions", "depth_along_ray", "conf", "non_ambiguous_mask_logits",
+                   "cam_trans", "cam_quats", "metric_scaling_factor", "intrinsics")
+
+
+def sharded_vs_single(model, views, exchange=("gather", "ring"), infer_kwargs=None, group=None):
+    """Self-check of the view-sharded path on the GPUs of this job: every rank runs `views` (the WHOLE
+    scene, a list of view dicts, identical on every rank) once on its own GPU and once view-sharded over
+    the process group, per exchange schedule, and compares its shard of the sharded result with the
+    same views of the single-GPU result.  Returns {"worst_rel_l2", "per_key", "mask_agree", "schedules"}
+    reduced over ranks (max of the errors, min of the agreement).  Used by bench.py --gpus N (N > 1)
+    before its timed region and by tests/dist_sharded_check.py.
+
+    The two runs execute the same kernels on the same data except for the order in which the K/V blocks
+    of the global layers are presented, which re-draws the bf16 rounding noise downstream: agreement is
+    to the bf16 tolerance of the path (1e-2), not to fp32 round-off."""
+    import os
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    kw = dict(infer_kwargs or {})
+    n = len(views)
+    lo, hi = shard_views(n, world, rank)
+    full = model.infer([dict(v) for v in views], **kw)
+    per_key, agree = {}, 1.0
+    saved = os.environ.get("MAB_EXCHANGE")
+    try:
+        for mode in exchange:
+            os.environ["MAB_EXCHANGE"] = mode
+            mine = model.infer([dict(v) for v in views[lo:hi]], view_range=(lo, hi), total_views=n, **kw)
+            for p, r in zip(mine, full[lo:hi]):
+                both = (p["mask"] & r["mask"]).double() if "mask" in p else None
+                for k in SELF_CHECK_KEYS:
+                    a, b = p[k].double(), r[k].double()
+                    if both is not None and k in ("pts3d", "pts3d_cam", "depth_along_ray"):
+                        a, b = a * both, b * both  # infer() zeroes masked pixels
+                    e = float((a - b).norm() / (b.norm() + 1e-30))
+                    per_key[k] = max(per_key.get(k, 0.0), e)
+                if "mask" in p:
+                    agree = min(agree, float((p["mask"] == r["mask"]).float().mean()))
+    finally:
+        if saved is None:
+            os.environ.pop("MAB_EXCHANGE", None)
+        else:
+            os.environ["MAB_EXCHANGE"] = saved
+    dev = full[0]["pts3d"].device
+    t = torch.tensor([per_key[k] for k in SELF_CHECK_KEYS] + [-agree], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    vals = t.tolist()
+    per_key = {k: vals[i] for i, k in enumerate(SELF_CHECK_KEYS)}
+    return {"worst_rel_l2": max(per_key.values()), "per_key": per_key, "mask_agree": -vals[-1],
+            "schedules": list(exchange), "views": n, "world": world}

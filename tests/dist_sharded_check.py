@@ -1,5 +1,8 @@
-"""TEST INFRASTRUCTURE -- run under torch.distributed.run on >= 2 GPUs (tests/test_gpu_sharded.py):
-view-sharded infer with ring global attention over NCCL must reproduce the single-GPU result."""
+"""TEST INFRASTRUCTURE -- run under torch.distributed.run on >= 2 GPUs (tests/test_gpu_sharded.py, and by
+hand `gpurun --gpus 2`): view-sharded infer over NCCL, with BOTH exchange schedules of the global layers
+(all-to-all K|V gather, ring), must reproduce the single-GPU result.  bench.py --gpus N runs the same
+comparison (parallel.sharded_vs_single) before its timed region, which is where the driver sees it."""
+import json
 import os
 import sys
 
@@ -9,51 +12,51 @@ import torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
+# the two runs differ only in the order the K/V blocks of the global layers are presented in, which
+# re-draws the bf16 rounding noise downstream (each path is ~4e-3 from fp32): bf16 tolerance, not round-off
+TOL = 1e-2
+# least-squares fit through <= 7x10 ray samples of a 70x98 image: amplifies the 2-3e-3 ray noise about 6x
+# (tests/helpers.py POSE_DEPENDENT_KEYS); only applied below 392x518
+TOL_INTRINSICS_SMALL = 3e-2
+# a near-cancelling sum (zero-mean channel of the last 1x1 conv): the trunk noise of two runs shows up
+# 3-4x larger relative to its small norm; the boolean mask it thresholds is checked by agreement
+TOL_MASK_LOGITS = 3.5e-2
+
 
 def main():
     n_views, H, W = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
-    multimodal = len(sys.argv) > 4 and sys.argv[4] == "mm"
+    mode = sys.argv[4] if len(sys.argv) > 4 else "img"
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
     dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
     dist.init_process_group("nccl", device_id=dev)
     from mapanything_b200 import MapAnything, parallel, synthetic
 
-    model = MapAnything(device=dev, head_chunk=3)
-    model.load_state_dict(synthetic.synthetic_state_dict())
+    kwargs = {}
+    sd = synthetic.synthetic_state_dict()
+    if mode == "viewpe":  # use_pe_for_non_reference_views: rank 0's draw of the rows is broadcast
+        margs = {"use_pe_for_non_reference_views": True, "max_num_views_for_pe": 16,
+                 "use_rand_idx_pe_for_non_reference_views": True}
+        kwargs["info_sharing_config"] = {"model_type": "alternating_attention", "module_args": margs}
+        sd = synthetic.synthetic_state_dict(view_pe_rows=16)
+    model = MapAnything(device=dev, head_chunk=3, **kwargs)
+    model.load_state_dict(sd)
     views = synthetic.synthetic_views(n_views, H, W, seed=3)
-    if multimodal:  # rays + sparse depth + poses: pose algebra needs view 0 and a scene-wide norm
+    if mode == "mm":  # rays + sparse depth + poses: pose algebra needs view 0 and a scene-wide norm
         views = synthetic.add_multimodal_inputs(views, seed=4)
-    lo, hi = parallel.shard_views(n_views, world, rank)
-    mine = model.infer([dict(v) for v in views[lo:hi]], view_range=(lo, hi), total_views=n_views)
-    full = model.infer([dict(v) for v in views])  # every rank also runs the whole scene on its own GPU
-    torch.cuda.synchronize()
-    worst, per_key = 0.0, {}
-    for p, r in zip(mine, full[lo:hi]):
-        for k in ("pts3d_cam", "ray_directions", "conf", "non_ambiguous_mask_logits", "cam_trans", "cam_quats",
-                  "metric_scaling_factor", "intrinsics"):
-            a, b = p[k].double(), r[k].double()
-            if k == "pts3d_cam":  # infer() zeroes masked pixels: compare where both runs keep the pixel
-                both = (p["mask"] & r["mask"]).double()
-                a, b = a * both, b * both
-            e = float((a - b).norm() / (b.norm() + 1e-30))
-            # mask logits are a near-cancelling sum: 3.5e-2 like tests/test_gpu_e2e.py TOL_MASK_LOGITS
-            # intrinsics: least-squares fit through <= 7x10 ray samples on a 70x98 image, amplifies the
-            # ray noise (2-3e-3) about 6x (tests/helpers.py POSE_DEPENDENT_KEYS)
-            scale = {"non_ambiguous_mask_logits": 3.5, "intrinsics": 3.0}.get(k, 1.0)
-            per_key[k] = max(per_key.get(k, 0.0), e)
-            worst = max(worst, e / scale)
-        agree = float((p["mask"] == r["mask"]).float().mean())
-        assert agree > 0.95, agree
-    t = torch.tensor([worst], device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    print(f"rank {rank}: " + " ".join(f"{k}={v:.2e}" for k, v in per_key.items()), flush=True)
+    if mode == "viewpe":
+        # the single-GPU run and the sharded runs must use the SAME rows: pin one draw for all of them
+        rows = torch.cat([torch.zeros(1, dtype=torch.int64), torch.randperm(15)[: n_views - 1] + 1]).to(dev)
+        dist.broadcast(rows, src=0)
+        model._pinned_view_pe_rows = rows.cpu()
+    rep = parallel.sharded_vs_single(model, views)
     if rank == 0:
-        print(f"sharded-vs-single worst (tolerance-scaled) rel-L2 = {t.item():.3e}")
-    # identical kernels on identical data except for the K/V block order of the global layers; that
-    # alone re-draws the bf16 rounding noise of everything downstream (each path is ~4e-3 from fp32,
-    # tests/diag_stages.py), so the two runs agree to the bf16 tolerance, not to fp32 round-off
-    assert t.item() < 1e-2, t.item()
+        print("sharded-vs-single " + json.dumps(rep), flush=True)
+    for k, e in rep["per_key"].items():
+        tol = TOL_INTRINSICS_SMALL if (k == "intrinsics" and H < 392) else TOL
+        tol = TOL_MASK_LOGITS if k == "non_ambiguous_mask_logits" else tol
+        assert e < tol, (k, e, rep)
+    assert rep["mask_agree"] > 0.97, rep
     dist.destroy_process_group()
 
 

@@ -14,8 +14,9 @@ TOL_POSE_DEG = 0.1
 # reference runs that head in TF32); measured per channel in test_heads_on_identical_inputs and in
 # DESIGN.md "Parity".  They are not one of BASELINE.json's toleranced quantities; the boolean mask
 # they produce is checked by agreement rate.
-TOL_MASK_LOGITS = 3.5e-2
-TOL_LOGIT_CHANNEL = 2.5e-2
+TOL_MASK_LOGITS = 3.5e-2         # bf16 head (opt-in) end to end; the default head follows the general rule
+TOL_LOGIT_CHANNEL = 2.5e-2       # bf16 head (opt-in), mask-logit channel on identical inputs
+TOL_LOGIT_CHANNEL_TF32 = 5e-3    # default head (fp32 activations / TF32 contractions), every channel
 
 
 @pytest.fixture(scope="module")
@@ -57,16 +58,16 @@ def test_infer_matches_reference_golden(name, model, sd_cuda):
     yard = helpers.compare_with_golden(ref_amp, g, stride, None, None)
     print("libmab200  :", {k: round(v, 5) for k, v in rep.items()})
     print("ref bf16   :", {k: round(v, 5) for k, v in yard.items()})
+    helpers.record_parity("golden:" + name, rep, yard)
     # (1) absolute tolerances on everything that does not contain the predicted pose
     cam_frame = {k: v for k, v in rep.items() if k.split(".", 1)[1] not in helpers.POSE_DEPENDENT_KEYS
                  and k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
-    bad = helpers.out_of_tolerance(cam_frame, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97)
+    bad = helpers.out_of_tolerance(cam_frame, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=helpers.MIN_MASK_AGREE)
     assert not bad, f"camera-frame keys out of absolute tolerance: {bad}"
-    # (2) every key: no further from fp32 than 3x the reference's own bf16 path
-    rest = {k: v for k, v in rep.items() if k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
-    bad = helpers.out_of_tolerance(rest, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97,
-                                   yardstick=yard, slack=3.0)
-    bad += [(k, v) for k, v in rep.items() if k.endswith("non_ambiguous_mask_logits") and v > TOL_MASK_LOGITS]
+    # (2) every key: inside its absolute tolerance, or no further from fp32 than helpers.YARDSTICK_SLACK x the
+    # reference's own bf16 path (worst view of the scene)
+    bad = helpers.out_of_tolerance(rep, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=helpers.MIN_MASK_AGREE,
+                                   yardstick=yard, tol_intrinsics=helpers.tol_intrinsics_for(H))
     assert not bad, f"further from the fp32 reference than the reference's bf16 path: {bad}\nyardstick {yard}"
     p = preds[0]
     assert p["pts3d"].shape == (1, H, W, 3) and p["pts3d"].dtype == torch.float32
@@ -114,13 +115,13 @@ def test_info_sharing_variants_match_reference_golden(name, synthetic_sd, sd_cud
                                        stride, None, None)
     print("libmab200  :", {k: round(v, 5) for k, v in rep.items()})
     print("ref bf16   :", {k: round(v, 5) for k, v in yard.items()})
+    helpers.record_parity("golden:" + name, rep, yard)
     cam_frame = {k: v for k, v in rep.items() if k.split(".", 1)[1] not in helpers.POSE_DEPENDENT_KEYS
                  and k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
-    bad = helpers.out_of_tolerance(cam_frame, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97)
+    bad = helpers.out_of_tolerance(cam_frame, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=helpers.MIN_MASK_AGREE)
     assert not bad, f"camera-frame keys out of absolute tolerance: {bad}"
-    rest = {k: v for k, v in rep.items() if k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
-    bad = helpers.out_of_tolerance(rest, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97,
-                                   yardstick=yard, slack=3.0)
+    bad = helpers.out_of_tolerance(rep, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=helpers.MIN_MASK_AGREE,
+                                   yardstick=yard, tol_intrinsics=helpers.tol_intrinsics_for(H))
     assert not bad, f"further from the fp32 reference than the reference's bf16 path: {bad}\nyardstick {yard}"
     monkeypatch.undo()
     # and the variant really is a different function: the production config misses this golden
@@ -166,13 +167,13 @@ def test_48_layer_trunk_matches_reference_golden():
                                        stride, None, None)
     print("libmab200  :", {k: round(v, 5) for k, v in rep.items()})
     print("ref bf16   :", {k: round(v, 5) for k, v in yard.items()})
+    helpers.record_parity("golden:" + name, rep, yard)
     cam_frame = {k: v for k, v in rep.items() if k.split(".", 1)[1] not in helpers.POSE_DEPENDENT_KEYS
                  and k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
-    bad = helpers.out_of_tolerance(cam_frame, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97)
+    bad = helpers.out_of_tolerance(cam_frame, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=helpers.MIN_MASK_AGREE)
     assert not bad, f"camera-frame keys out of absolute tolerance: {bad}"
-    rest = {k: v for k, v in rep.items() if k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
-    bad = helpers.out_of_tolerance(rest, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=0.97,
-                                   yardstick=yard, slack=3.0)
+    bad = helpers.out_of_tolerance(rep, TOL_DENSE, TOL_POSE_DEG, TOL_DENSE, min_mask_agree=helpers.MIN_MASK_AGREE,
+                                   yardstick=yard, tol_intrinsics=helpers.tol_intrinsics_for(H))
     assert not bad, f"further from the fp32 reference than the reference's bf16 path: {bad}\nyardstick {yard}"
 
 
@@ -277,23 +278,60 @@ def test_forward_raw_matches_oracle(model, synthetic_sd, sd_cuda):
             assert p[k].shape == r[k].shape, k
             e = helpers.rel_l2(p[k].float().cpu().numpy(), r[k].numpy())
             y = max(helpers.rel_l2(a2[k].numpy(), r2[k].numpy()) for a2, r2 in zip(amp, ref))
-            tol = TOL_MASK_LOGITS if k == "non_ambiguous_mask_logits" else max(TOL_DENSE, 3.0 * y)
+            tol = max(TOL_DENSE, helpers.YARDSTICK_SLACK * y)
             assert e < tol, (k, e, y)
         e = helpers.quat_angle_deg(p["cam_quats"].cpu().numpy(), r["cam_quats"].numpy())
         y = max(helpers.quat_angle_deg(a2["cam_quats"].numpy(), r2["cam_quats"].numpy()) for a2, r2 in zip(amp, ref))
-        assert e < max(TOL_POSE_DEG, 3.0 * y), (e, y)
+        assert e < max(TOL_POSE_DEG, helpers.YARDSTICK_SLACK * y), (e, y)
         agree = float((p["non_ambiguous_mask"].cpu() == r["non_ambiguous_mask"]).float().mean())
         assert agree > 0.98
 
 
-def test_heads_on_identical_inputs(model, sd_cuda):
+@pytest.fixture(scope="module")
+def model_bf16_head(synthetic_sd):
+    from mapanything_b200 import MapAnything
+
+    m = MapAnything(device="cuda:0", head_chunk=2, head_precision="bf16")
+    m.load_state_dict(synthetic_sd)
+    return m
+
+
+def test_bf16_head_opt_in_matches_reference_golden(model_bf16_head, sd_cuda):
+    """head_precision="bf16" (the faster opt-in: bf16 operands where the reference runs fp32 / TF32) on the
+    full-resolution golden: camera-frame geometry still inside BASELINE.json's tolerance; the mask-logit
+    channel, a near-cancelling sum, at its measured bf16 bound (TOL_MASK_LOGITS) and the boolean masks at
+    >= 97 % agreement -- the figures the default head improves on."""
+    from oracle import make_golden
+    from tests import helpers
+
+    name = "c1_n2_392x518"
+    n, H, W, mm, stride, kw = make_golden.CASES[name]
+    preds = model_bf16_head.infer([dict(v) for v in make_golden.case_views(name)], **kw)
+    torch.cuda.synchronize()
+    rep = helpers.compare_with_golden(preds, helpers.load_golden(name), stride, None, None)
+    helpers.record_parity("golden:" + name + ":bf16_head", rep)
+    for k, v in rep.items():
+        key = k.split(".", 1)[1]
+        if key in ("pts3d_cam", "ray_directions", "depth_along_ray", "depth_z", "conf"):
+            assert v < TOL_DENSE, (k, v)
+        elif key == "non_ambiguous_mask_logits":
+            assert v < TOL_MASK_LOGITS, (k, v)
+        elif key.endswith("_agree"):
+            assert v > 0.97, (k, v)
+
+
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
+def test_heads_on_identical_inputs(precision, model, model_bf16_head, sd_cuda):
     """Isolates the head kernels from bf16 trunk noise: the oracle's fp32 heads are fed the CUDA
     path's own trunk outputs, so the absolute BASELINE tolerances (dense <= 1e-2, pose <= 0.1 deg)
-    apply to the head arithmetic itself."""
+    apply to the head arithmetic itself.  Default head (fp32 activations, TF32 contractions = the
+    reference's precision, model.py:1774): every logit channel, the near-cancelling mask-logit channel
+    included, within TOL_LOGIT_CHANNEL_TF32; the bf16 opt-in keeps its measured bounds."""
     from oracle import mapanything_oracle as orc, weights
     from tests import helpers
     from tests.diag_stages import debug_buffer
 
+    model = model if precision == "tf32" else model_bf16_head
     V, H, W = 2, 70, 98
     h, w = H // 14, W // 14
     views = weights.synthetic_views(V, H, W, seed=11)
@@ -313,9 +351,13 @@ def test_heads_on_identical_inputs(model, sd_cuda):
         scale = orc.scale_head(feats["scale_token"], sd_cuda)
     e = helpers.rel_l2(outs["logits6"].cpu().numpy(), logits.cpu().numpy())
     per = [helpers.rel_l2(outs["logits6"][..., c].cpu().numpy(), logits[..., c].cpu().numpy()) for c in range(6)]
-    print("head-only logits rel-L2 per channel:", [round(x, 5) for x in per])
+    print(f"head-only logits rel-L2 per channel ({precision}):", [round(x, 5) for x in per])
+    helpers.record_parity(f"heads_on_identical_inputs:{precision}", {f"logit_channel_{c}": per[c] for c in range(6)})
     assert e < TOL_DENSE, ("logits", e)
-    assert max(per[:5]) < 1.2e-2 and per[5] < TOL_LOGIT_CHANNEL, ("logits per channel", per)
+    if precision == "tf32":
+        assert max(per) < TOL_LOGIT_CHANNEL_TF32, ("logits per channel", per)
+    else:
+        assert max(per[:5]) < 1.2e-2 and per[5] < TOL_LOGIT_CHANNEL, ("logits per channel", per)
     assert helpers.rel_l2(outs["pose"][:, :3].cpu().numpy(), t.cpu().numpy()) < TOL_DENSE
     ang = helpers.quat_angle_deg(outs["pose"][:, 3:7].cpu().numpy(), q.cpu().numpy())
     print("head-only pose angle (deg):", ang)
@@ -335,6 +377,11 @@ def test_validation_errors_match_reference(model):
         model.infer([v, dict(v, camera_poses=torch.eye(4)[None])])
     with pytest.raises(AssertionError):
         model.infer([dict(v, img=torch.zeros(1, 3, 30, 28))])
+    # model.py:2287-2302: only the default mixed-precision path is built -- refused, not silently bf16
+    with pytest.raises(NotImplementedError):
+        model.infer([dict(v)], use_amp=False)
+    with pytest.raises(NotImplementedError):
+        model.infer([dict(v)], amp_dtype="fp16")
 
 
 def test_geometric_input_preprocessing_matches_oracle(model):
@@ -392,7 +439,7 @@ def test_multimodal_ignore_flags_match_oracle(ignore, model, sd_cuda):
                 m = 1.0
             e = helpers.rel_l2((p[k].float().cpu() * m).numpy(), (r[k] * m).numpy())
             y = helpers.rel_l2((a[k] * m).numpy(), (r[k] * m).numpy())
-            assert e < max(TOL_DENSE, 3.0 * y), (k, e, y)
+            assert e < max(TOL_DENSE, helpers.YARDSTICK_SLACK * y), (k, e, y)
 
 
 def test_infer_host_outputs_equals_device_outputs(model):
@@ -413,3 +460,16 @@ def test_infer_host_outputs_equals_device_outputs(model):
                 assert h[k].device.type == "cpu" and h[k].is_pinned(), k
                 assert h[k].shape == d[k].shape and h[k].dtype == d[k].dtype, k
                 assert torch.equal(h[k], d[k].cpu()), (k, chunk)
+    # results are caller-owned: a second call must not overwrite the first call's tensors ...
+    first = model.infer([dict(v) for v in views], host_outputs=True, **kw)
+    keep = {k: t.clone() for k, t in first[0].items()}
+    other = weights.add_multimodal_inputs(weights.synthetic_views(5, 56, 84, seed=31), seed=32)
+    second = model.infer([dict(v) for v in other], host_outputs=True, **kw)
+    assert all(torch.equal(first[0][k], keep[k]) for k in keep)
+    assert not torch.equal(second[0]["pts3d_cam"], first[0]["pts3d_cam"])
+    # ... unless the caller opts into the model's reused pool
+    a = model.infer([dict(v) for v in views], host_outputs=True, reuse_host_buffers=True, **kw)
+    ptr_a = a[0]["pts3d"].data_ptr()
+    assert all(torch.equal(a[0][k], keep[k]) for k in keep)
+    b = model.infer([dict(v) for v in other], host_outputs=True, reuse_host_buffers=True, **kw)
+    assert b[0]["pts3d"].data_ptr() == ptr_a and torch.equal(b[0]["pts3d_cam"], second[0]["pts3d_cam"])

@@ -1,4 +1,4 @@
-"""View-sharded infer (ring global attention over NCCL) == single-GPU infer.  Needs >= 2 GPUs
+"""View-sharded infer (global attention by K|V gather AND by ring, over NCCL) == single-GPU infer.  Needs >= 2 GPUs
 (`gpurun --gpus 2`); skipped on a 1-GPU box, where tests/test_gpu_attention.py::test_attention_ring_carry
 and the gloo tests of tests/test_parallel_cpu.py cover the same pieces separately."""
 import os
@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("n_views,H,W,mode", [(5, 70, 98, "img"), (4, 392, 518, "img"), (5, 70, 98, "mm")])
+@pytest.mark.parametrize("n_views,H,W,mode", [(5, 70, 98, "img"), (4, 392, 518, "img"), (5, 70, 98, "mm"), (5, 70, 98, "viewpe")])
 def test_sharded_equals_single(n_views, H, W, mode):
     ngpu = torch.cuda.device_count()
     if ngpu < 2:

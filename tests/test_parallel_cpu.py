@@ -163,7 +163,12 @@ def _view_pe_worker(rank, world, port, total, result):
         torch.manual_seed(100 + rank)          # the ranks' generators disagree: rank 0's draw must win
         lo, hi = parallel.shard_views(total, world, rank)
         m._set_view_pe_rows(lo, hi - lo, total)
-        result[rank] = (lo, m._lib.rows)
+        sharded_rows = m._lib.rows
+        # the same ranks running INDEPENDENT scenes (each holds its whole scene): no collective, own draw
+        torch.manual_seed(200 + rank)
+        if rank == 1:
+            m._set_view_pe_rows(0, 4, 4)       # rank 1 alone: would hang if a broadcast were issued
+        result[rank] = (lo, sharded_rows, m._lib.rows)
     finally:
         dist.destroy_process_group()
 
@@ -186,7 +191,9 @@ def test_view_pe_rows_agree_across_ranks_gloo():
         want = [0] + torch.randint(low=1, high=1000, size=(total - 1,)).tolist()
         got = []
         for r in range(world):
-            lo, rows = result[r]
+            lo, rows, _ = result[r]
             assert lo == len(got)
             got += rows
         assert got == want
+        torch.manual_seed(201)
+        assert result[1][2] == [0] + torch.randint(low=1, high=1000, size=(3,)).tolist()

@@ -29,9 +29,9 @@ def test_single_view_matches_reference_golden(synthetic_sd):
     print("ref bf16   :", {k: round(v, 5) for k, v in yard.items()})
     cam_frame = {k: v for k, v in rep.items() if k.split(".", 1)[1] not in helpers.POSE_DEPENDENT_KEYS
                  and k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
-    bad = helpers.out_of_tolerance(cam_frame, 1e-2, 0.1, 1e-2, min_mask_agree=0.97)
+    bad = helpers.out_of_tolerance(cam_frame, 1e-2, 0.1, 1e-2, min_mask_agree=helpers.MIN_MASK_AGREE)
     assert not bad, f"camera-frame keys out of absolute tolerance: {bad}"
-    rest = {k: v for k, v in rep.items() if k.split(".", 1)[1] != "non_ambiguous_mask_logits"}
-    bad = helpers.out_of_tolerance(rest, 1e-2, 0.1, 1e-2, min_mask_agree=0.97, yardstick=yard, slack=3.0)
+    helpers.record_parity("golden:" + name, rep, yard)
+    bad = helpers.out_of_tolerance(rep, 1e-2, 0.1, 1e-2, min_mask_agree=helpers.MIN_MASK_AGREE, yardstick=yard, tol_intrinsics=helpers.tol_intrinsics_for(H))
     assert not bad, f"further from the fp32 reference than the reference's bf16 path: {bad}\nyardstick {yard}"
     assert len(preds) == 1 and preds[0]["pts3d"].shape == (1, H, W, 3)
