@@ -335,12 +335,10 @@ def main():
         small = synthetic.add_multimodal_inputs(synthetic.synthetic_views(2 * world + 1, 70, 98, seed=3), seed=4)
         rep_a = parallel.sharded_vs_single(model, small)
         rep_b = parallel.sharded_vs_single(model, synthetic.synthetic_views(2 * world, H_IMG, W_IMG, seed=3))
-        # tolerances of tests/dist_sharded_check.py: bf16 tolerance of the path (the two runs differ in the
-        # K/V block order of the global layers); mask logits are a near-cancelling sum, the 70x98 intrinsics a
-        # least-squares fit through 7x10 ray samples
+        # tolerance of tests/dist_sharded_check.py: the two runs differ in the K/V block order of the global
+        # layers only, which re-draws the bf16 rounding noise downstream -> bf16 tolerance of the path, every key
         def _ok(rep, small_img):
-            tol = {"non_ambiguous_mask_logits": 3.5e-2, "intrinsics": 3e-2 if small_img else 1e-2}
-            return all(e < tol.get(k, 1e-2) for k, e in rep["per_key"].items()) and rep["mask_agree"] > 0.97
+            return all(e < 1e-2 for e in rep["per_key"].values()) and rep["mask_agree"] > 0.985
         shard_par = {"worst_rel_l2": max(rep_a["worst_rel_l2"], rep_b["worst_rel_l2"]),
                      "mask_agree": min(rep_a["mask_agree"], rep_b["mask_agree"]),
                      "ok": bool(_ok(rep_a, True) and _ok(rep_b, False)),
