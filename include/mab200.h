@@ -62,6 +62,13 @@ typedef struct {
    * mirror's default.  0: bf16 operands (about 2 ms faster per 8 views; the mask-logit channel is then
    * 1.6e-2 from fp32 on identical inputs instead of < 5e-3). */
   int head_tf32;
+  /* Views per encoder pass (SURVEY.md 8(f) many-view streaming; the reference chunks only its heads,
+   * model.py:1440-1477,1533-1618).  The DINOv2 encoder and the geometric-input encoders are per-view
+   * independent, so they run enc_chunk views at a time through ONE pass-sized set of activations
+   * (38 KB per token); only the fused tokens, the info-sharing stream / activations and its taps stay
+   * resident per view (about 35 MB per view at 518x392 instead of 60 MB).  Outputs do not depend on it.
+   * <= 0 or >= the views held: one pass. */
+  int enc_chunk;
 } mab_config;
 
 /* One scene, `views` views of H x W pixels held by this rank. */
@@ -194,6 +201,9 @@ long long mab_launch_count(void);
 int mab_prof_enable(int on); /* also clears the records */
 /* synchronises the device; sums device time, algorithmic FLOPs and bytes of one category */
 int mab_prof_query(int cat, long long* launches, double* ms, double* flops, double* bytes);
+/* the same records one by one, in launch order (arrays of `max` entries, any may be NULL); returns the number
+ * of records held, -1 on a CUDA error.  profiles/step_breakdown.py groups them by operator shape. */
+long long mab_prof_records(int* cat, double* ms, double* flops, double* bytes, long long max);
 
 /* Diagnostic hook for the parity tests: device pointer, element count and dtype (MAB_F32 /
  * MAB_BF16) of a named intermediate of the last forward ("enc_tokens", "fused", "aat_stream",

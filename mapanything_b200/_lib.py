@@ -12,7 +12,7 @@ class MabConfig(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("patch", "enc_dim", "enc_depth", "enc_heads", "enc_pos_grid",
                                        "aat_dim", "aat_depth", "aat_heads", "aat_tap0", "aat_tap1",
                                        "head_chunk", "aat_ref_view_pe", "aat_entropy_scaling", "aat_tap2", "aat_nonref_view_pe", "aat_all_global",
-                                       "head_tf32")]
+                                       "head_tf32", "enc_chunk")]
 
 
 class MabInputs(C.Structure):
@@ -76,6 +76,8 @@ SYMBOLS = {
     "mab_prof_enable": (_i, [_i]),
     "mab_prof_query": (_i, [_i, C.POINTER(C.c_longlong), C.POINTER(C.c_double), C.POINTER(C.c_double),
                             C.POINTER(C.c_double)]),
+    "mab_prof_records": (C.c_longlong, [C.POINTER(_i), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                        C.POINTER(C.c_double), C.c_longlong]),
     "mab_debug_buffer": (_i, [_vp, C.c_char_p, C.POINTER(_vp), C.POINTER(C.c_longlong), C.POINTER(_i)]),
     "mab_layernorm": (_i, [_vp, _i, _i, _vp, _vp, _f, _vp, _vp, _vp]),
     "mab_gemm": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
@@ -119,7 +121,12 @@ def load(allow_build=True):
         _build.build()
     lib = C.CDLL(path)
     for name, (res, args) in SYMBOLS.items():
-        fn = getattr(lib, name)  # AttributeError if the ABI and the header ever diverge
+        try:
+            fn = getattr(lib, name)  # AttributeError if the ABI and the header ever diverge
+        except AttributeError:
+            if os.environ.get("MAB_LIB"):  # an experiment build of an older tree (profiles/): bind what it has
+                continue
+            raise
         fn.restype = res
         fn.argtypes = args
     _lib = lib

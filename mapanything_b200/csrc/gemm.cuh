@@ -91,6 +91,23 @@ __device__ __forceinline__ float gelu_erf(float x) {
   const float e_ = 1.0f - p * t * __expf(-z * z);
   return 0.5f * x * (1.0f + copysignf(e_, x));
 #endif
+#ifdef MAB_GELU_TANH
+  {
+    // Experiment, NOT the default: the fit below through ONE MUFU op instead of two, x * sigmoid(2u) =
+    // 0.5 x (1 + tanh(u)).  3 us faster per fc1 GEMM (profiles/r2_gemm_variants.txt: 62.9 -> 59.8 us,
+    // 44.7 -> 41.5 us) but tanh.approx.f32 is only 2^-11 RELATIVE to tanh, and 1 + tanh(u) cancels in the
+    // negative tail: up to 7e-4 absolute on activations that should be ~1e-3 -- as much noise as the bf16
+    // rounding of the whole hidden activation, for 0.7 % of the step.  Parity first.
+    const float xt = fminf(fmaxf(x, -5.0f), 5.0f);
+    const float xx = xt * xt;
+    float pl = fmaf(xx, -3.51902e-04f, 3.70080e-02f);
+    pl = fmaf(pl, xx, 7.97505e-01f);
+    float th;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(xt * pl));
+    const float hx = 0.5f * x;
+    return fmaf(hx, th, hx);
+  }
+#endif
   const float xc = fminf(fmaxf(x, -5.0f), 5.0f);
   const float x2 = xc * xc;
   // -2 * log2(e) * (a0 + a1 x^2 + a2 x^4)
@@ -143,10 +160,40 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
   const bool gelu = G ? ep.act == ACT_GELU : (F & EF_GELU) != 0;
   const bool relu = G ? ep.act == ACT_RELU : (F & EF_RELU) != 0;
   const uint64_t keep = l2_policy_evict_last();
+  // In-place fp32 residual (x += gamma * (A B^T + bias): out_f32 == res_f32 and nothing else written -- the
+  // proj and fc2 GEMMs of every transformer block): the add is performed by the L2 with a fire-and-forget
+  // vector reduction (red.global.add.v4.f32), so the epilogue never waits for a residual load.  One fp32 add
+  // per element either way: bit-identical.  Only these two instantiations carry the extra path (in the
+  // others the run-time test cost registers: fc1 62.9 -> 75.9 us).  profiles/r2_gemm_variants.txt:
+  // proj 23.5 -> 20.0 us, fc2 60.0 -> 56.9 us (encoder), 17.7 -> 15.2 / 35.3 -> 33.0 us (info sharing).
+#ifndef MAB_NO_EPI_RED
+  constexpr bool RED_CASE = F == (EF_OUTF32 | EF_RESF32 | EF_GAMMA) || F == (EF_OUTF32 | EF_RESF32);
+#else
+  constexpr bool RED_CASE = false;
+#endif
+  const bool red_inplace = RED_CASE && ep.out_f32 == ep.res_f32 && !ep.round_tf32;
 #pragma unroll 1
   for (int c0 = c_begin; c0 < c_end; c0 += 32) {
     const int ncol0 = n0 + c0;
     if (ncol0 >= N) break;
+    const int col = ncol0 + sub_c4 * 4;
+    const uint32_t mask = col < N ? row_mask : 0u;  // N is a multiple of 4 for every layer of the path
+    // every global load of the chunk is issued first: they do not depend on the accumulator, so the TMEM
+    // load and the shared-memory transpose below run under their latency (one or two warps per scheduler
+    // have to cover their own latencies)
+    float4 b4 = make_float4(0, 0, 0, 0), g4 = make_float4(1, 1, 1, 1);
+    if (mask && ep.bias) b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
+    if (mask && has_g) g4 = __ldg(reinterpret_cast<const float4*>(ep.gamma + col));
+    float4 a[8], rf[8];
+    uint2 r1[8], r2[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const bool ok = (mask >> i) & 1;
+      const long long off = ro[i] + col;
+      if (has_rf && !red_inplace) rf[i] = ok ? ld_f4_l2hint(ep.res_f32 + off, keep) : make_float4(0, 0, 0, 0);
+      if (has_r1) r1[i] = ok ? *reinterpret_cast<const uint2*>(ep.res1 + off) : make_uint2(0, 0);
+      if (has_r2) r2[i] = ok ? *reinterpret_cast<const uint2*>(ep.res2 + off) : make_uint2(0, 0);
+    }
     uint32_t v[32];
     MAB_TMEM_LD_32(t_row + c0, v);
     tmem_wait_ld();
@@ -157,24 +204,10 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
           make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
                       __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
     __syncwarp();
-    const int col = ncol0 + sub_c4 * 4;
-    const uint32_t mask = col < N ? row_mask : 0u;  // N is a multiple of 4 for every layer of the path
-    float4 b4 = make_float4(0, 0, 0, 0), g4 = make_float4(1, 1, 1, 1);
-    if (mask && ep.bias) b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
-    if (mask && has_g) g4 = __ldg(reinterpret_cast<const float4*>(ep.gamma + col));
-    // every load of the chunk is issued before any arithmetic (one or two warps per scheduler have
-    // to cover their own latencies)
-    float4 a[8], rf[8];
-    uint2 r1[8], r2[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = 4 * i + sub_r;
       a[i] = *reinterpret_cast<const float4*>(stg + r * 32 + ((sub_c4 ^ (r & 7)) << 2));
-      const bool ok = (mask >> i) & 1;
-      const long long off = ro[i] + col;
-      if (has_rf) rf[i] = ok ? ld_f4_l2hint(ep.res_f32 + off, keep) : make_float4(0, 0, 0, 0);
-      if (has_r1) r1[i] = ok ? *reinterpret_cast<const uint2*>(ep.res1 + off) : make_uint2(0, 0);
-      if (has_r2) r2[i] = ok ? *reinterpret_cast<const uint2*>(ep.res2 + off) : make_uint2(0, 0);
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -188,6 +221,10 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
         x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
       }
       if (has_g) { x.x *= g4.x; x.y *= g4.y; x.z *= g4.z; x.w *= g4.w; }
+      if (red_inplace) {
+        red_add_f4(ep.out_f32 + ro[i] + col, x);
+        continue;
+      }
       if (has_rf) { x.x += rf[i].x; x.y += rf[i].y; x.z += rf[i].z; x.w += rf[i].w; }
       if (has_r1) {
         x.x += bf16_lo(r1[i].x); x.y += bf16_hi(r1[i].x); x.z += bf16_lo(r1[i].y); x.w += bf16_hi(r1[i].y);

@@ -113,6 +113,25 @@ extern "C" int mab_prof_query(int cat, long long* launches, double* ms, double* 
   return 0;
 }
 
+// Per-launch records of the profiler, in launch order: category, device milliseconds, algorithmic FLOPs and
+// bytes of up to `max` launches; returns the number of records held (synchronises the device).
+extern "C" long long mab_prof_records(int* cat, double* ms, double* flops, double* bytes, long long max) {
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  long long n = 0;
+  for (const ProfRec& r : prof().recs) {
+    if (n < max) {
+      float t = 0.f;
+      if (cudaEventElapsedTime(&t, r.e0, r.e1) != cudaSuccess) return -1;
+      if (cat) cat[n] = r.cat;
+      if (ms) ms[n] = t;
+      if (flops) flops[n] = r.flops;
+      if (bytes) bytes[n] = r.bytes;
+    }
+    ++n;
+  }
+  return n;
+}
+
 // ---- a1 pre-processing entry points (inference.py:222-311) ---------------------------------------
 extern "C" int mab_rays_from_intrinsics(const void* K, int views, int H, int W, void* rays, void* stream) {
   MAB_ARG(K && rays && views > 0 && H > 0 && W > 0, "bad arguments");
@@ -632,6 +651,7 @@ struct Bump {  // bump allocator over the caller's workspace (256-byte aligned)
 
 struct Plan {  // every workspace pointer of one forward
   int V = 0, Vtot = 0, H = 0, W = 0, h = 0, w = 0, T = 0;
+  int Ve = 0;  // views per encoder pass (cfg.enc_chunk): the encoder's activations are sized for Ve views
   int has_scale = 0, has_ref = 0;
   long long Lenc = 0, L = 0;  // encoder rows V*(T+1); info-sharing rows V*T (+1)
   // encoder
@@ -691,19 +711,26 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
   const long long VT = (long long)V * p.T;
   const int D = c.enc_dim, A = c.aat_dim;
   Bump b; b.base = reinterpret_cast<uint8_t*>(ws);
-  p.im2col = b.take<bf16>(VT * 640);
-  p.patch = b.take<float>(VT * D);
+  // The encoder (a3-a6) is per-view independent and runs Ve views at a time (mab_stage_encode), so its
+  // activations cost Ve, not V, views of memory; what stays resident per view is the fused token (bf16 +
+  // fp32 for the fp32 head), the info-sharing stream, its taps and the info-sharing activations, which
+  // share the ln | qkv | att | hid buffers with the encoder (each sized for the larger of the two uses).
+  p.Ve = (c.enc_chunk > 0 && c.enc_chunk < V) ? c.enc_chunk : V;
+  const long long VTe = (long long)p.Ve * p.T, Le = (long long)p.Ve * (p.T + 1);
+  auto mx = [](long long a, long long b2) { return a > b2 ? a : b2; };
+  p.im2col = b.take<bf16>(VTe * 640);
+  p.patch = b.take<float>(VTe * D);
   p.pos = b.take<float>((long long)(p.T + 1) * D);
-  p.xs = b.take<float>(p.Lenc * D);
-  p.ln = b.take<bf16>(p.Lenc * D);
-  p.qkv = b.take<bf16>(p.Lenc * 3 * D);
-  p.att = b.take<bf16>(p.Lenc * D);
-  p.hid = b.take<bf16>(p.Lenc * 4 * D);
-  p.enc_out = b.take<float>(VT * D);
+  p.xs = b.take<float>(Le * D);
+  p.ln = b.take<bf16>(mx(Le * D, (VT + 1) * A));
+  p.qkv = b.take<bf16>(mx(Le * 3 * D, (VT + 1) * 3 * A));
+  p.att = b.take<bf16>(mx(Le * D, (VT + 1) * A));
+  p.hid = b.take<bf16>(mx(Le * 4 * D, (VT + 1) * 4 * A));
+  p.enc_out = b.take<float>(VTe * D);
   p.fused = b.take<bf16>((VT + 1) * D);
-  p.geo_sum = b.take<float>(VT * D);          // sum of the masked dense geometric features
-  p.geo_vec = b.take<float>((long long)V * D); // sum of the masked per-view (global) features
-  p.geo_small = b.take<float>((long long)V * 4096 + 64);  // MLP scratch + masks + scalar inputs
+  p.geo_sum = b.take<float>(VTe * D);          // sum of the masked dense geometric features
+  p.geo_vec = b.take<float>((long long)p.Ve * D); // sum of the masked per-view (global) features
+  p.geo_small = b.take<float>((long long)p.Ve * 4096 + 64);  // MLP scratch + masks + scalar inputs
   p.ys = b.take<float>((VT + 1) * A);
   p.view_rows = b.take<int>(V);  // view_pos_table row of every view (use_pe_for_non_reference_views)
   const bool tf = c.head_tf32 != 0;
@@ -1047,7 +1074,7 @@ extern "C" int mab_debug_buffer(mab_handle* h, const char* name, void** ptr, lon
   const long long VT = (long long)p.V * p.T;
   const int D = h->cfg.enc_dim, A = h->cfg.aat_dim;
   const std::string n = name;
-  if (n == "enc_tokens") { *ptr = p.xs; *numel = p.Lenc * D; *dtype = MAB_F32; }
+  if (n == "enc_tokens") { *ptr = p.xs; *numel = (long long)p.Ve * (p.T + 1) * D; *dtype = MAB_F32; }  // last encoder pass
   else if (n == "fused" && p.fused32) { *ptr = p.fused32; *numel = VT * D; *dtype = MAB_F32; }
   else if (n == "fused") { *ptr = p.fused; *numel = VT * D; *dtype = MAB_BF16; }
   else if (n == "aat_stream") { *ptr = p.ys; *numel = p.L * A; *dtype = MAB_F32; }
@@ -1323,7 +1350,9 @@ int encode_geometric_inputs(Ctx& c, const mab_inputs* in) {
   // the encoder's activation buffers (ln | qkv | att | hid, contiguous in the plan) are free here
   bool first_dense = true, first_vec = true;
   float* scratch = reinterpret_cast<float*>(p.ln);
-  if ((size_t)VT * 3840 * sizeof(float) > (size_t)((uint8_t*)(p.hid + p.Lenc * 4 * D) - (uint8_t*)p.ln))
+  // ln | qkv | att | hid are contiguous in the plan and hold at least (T+1) * 9 * D bf16 per view of this
+  // pass = 18 KB per token, against 15 KB per token of scratch
+  if ((size_t)VT * 3840 * sizeof(float) > (size_t)p.Lenc * 9 * D * sizeof(bf16))
     return fail(-5, "geometric encoder scratch overflows the encoder activation buffers");
   for (int which = 0; which < 2; ++which) {
     if ((which == 0 && !has_rays) || (which == 1 && !has_depth)) continue;
@@ -1361,35 +1390,20 @@ int encode_geometric_inputs(Ctx& c, const mab_inputs* in) {
 
 }  // namespace
 
-// a2-a7: patch embed, 24 DINOv2 blocks, encoder norm (+ fusion norm), proj_embed, ref-view PE
-extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_total, void* workspace,
-                                size_t workspace_bytes, int has_scale_token, void* stream) {
-  MAB_ARG(h && in && workspace && h->finalized, "handle not ready");
-  MAB_ARG(in->views > 0 && in->H > 0 && in->W > 0 && in->H % 14 == 0 && in->W % 14 == 0 && in->images,
-          "bad inputs");
-  MAB_CUDA(cudaSetDevice(h->device));
+// a2-a6 for the views of one encoder pass (h->plan describes the pass: V views, outputs at p.fused /
+// p.fused32 / p.ys): patch embed, the DINOv2 blocks, encoder norm, geometric encoders and fusion norm
+static int encode_views(Ctx& c, const mab_inputs* in, bool multimodal, bool identity_embed) {
+  mab_handle* h = c.h;
   const mab_config& cf = h->cfg;
-  Ctx c{h, (cudaStream_t)stream};
-  // has_scale_token bit0: this rank owns the scale token; bit1: this rank owns view 0
-  make_plan(h, in->views, views_total > in->views ? views_total : in->views, in->H, in->W,
-            has_scale_token & 1, (has_scale_token >> 1) & 1, workspace, &h->plan);
   Plan& p = h->plan;
-  if (p.total > workspace_bytes)
-    return fail(-5, "workspace too small: need %zu bytes, got %zu", p.total, workspace_bytes);
   const int V = p.V, T = p.T, D = cf.enc_dim;
   const long long VT = (long long)V * T;
-  const bool multimodal = in->ray_dirs || in->depth_along_ray || in->cam_quats;
-  const bool identity_embed = cf.aat_dim == D;  // no proj_embed: the fused tokens ARE the residual stream
-  if (multimodal && !h->P32("ray_dirs_encoder.conv_in.weight"))
-    return fail(-4, "geometric inputs given but the checkpoint has no geometric encoders");
-
   MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
              patch_im2col_kernel<<<ew_grid(VT * 640), 256, 0, c.st>>>(in->images, V, p.H, p.W, 3, 0, 640,
                                                                       nullptr, 0, p.im2col, nullptr));
   MAB_TRY(c.linear(p.im2col, (int)VT, 640, 640, "encoder.model.patch_embed.proj.weight", D,
                    h->F("encoder.model.patch_embed.proj.bias"), ACT_NONE, nullptr, nullptr, p.patch,
                    nullptr, nullptr, 640));
-  MAB_TRY(mab_posembed_resize(h->F("encoder.model.pos_embed"), cf.enc_pos_grid, D, p.h, p.w, p.pos, c.st));
   MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
              assemble_tokens_kernel<<<ew_grid(p.Lenc * D / 4), 256, 0, c.st>>>(
       p.patch, h->F("encoder.model.cls_token"), p.pos, V, T, D, p.xs));
@@ -1415,6 +1429,63 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
                              nullptr, c.st));
     MAB_TRY(encode_geometric_inputs(c, in));
   }
+  return 0;
+}
+
+// a2-a7: patch embed, 24 DINOv2 blocks, encoder norm (+ fusion norm), proj_embed, ref-view PE
+extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_total, void* workspace,
+                                size_t workspace_bytes, int has_scale_token, void* stream) {
+  MAB_ARG(h && in && workspace && h->finalized, "handle not ready");
+  MAB_ARG(in->views > 0 && in->H > 0 && in->W > 0 && in->H % 14 == 0 && in->W % 14 == 0 && in->images,
+          "bad inputs");
+  MAB_CUDA(cudaSetDevice(h->device));
+  const mab_config& cf = h->cfg;
+  Ctx c{h, (cudaStream_t)stream};
+  // has_scale_token bit0: this rank owns the scale token; bit1: this rank owns view 0
+  make_plan(h, in->views, views_total > in->views ? views_total : in->views, in->H, in->W,
+            has_scale_token & 1, (has_scale_token >> 1) & 1, workspace, &h->plan);
+  Plan& p = h->plan;
+  if (p.total > workspace_bytes)
+    return fail(-5, "workspace too small: need %zu bytes, got %zu", p.total, workspace_bytes);
+  const int V = p.V, T = p.T, D = cf.enc_dim;
+  const long long VT = (long long)V * T;
+  const bool multimodal = in->ray_dirs || in->depth_along_ray || in->cam_quats;
+  const bool identity_embed = cf.aat_dim == D;  // no proj_embed: the fused tokens ARE the residual stream
+  if (multimodal && !h->P32("ray_dirs_encoder.conv_in.weight"))
+    return fail(-4, "geometric inputs given but the checkpoint has no geometric encoders");
+
+  MAB_TRY(mab_posembed_resize(h->F("encoder.model.pos_embed"), cf.enc_pos_grid, D, p.h, p.w, p.pos, c.st));
+  // a3-a6 are per-view independent: p.Ve views per pass through one pass-sized set of activations, each
+  // pass writing its rows of the fused tokens (bf16, + fp32 for the fp32 head / the identity-embed stream)
+  const Plan whole = h->plan;
+  int rc = 0;
+  for (int v0 = 0; v0 < whole.V && rc == 0; v0 += whole.Ve) {
+    const int vc = whole.V - v0 < whole.Ve ? whole.V - v0 : whole.Ve;
+    mab_inputs sub = *in;
+    const long long px = (long long)whole.H * whole.W;
+    sub.views = vc;
+    sub.images = in->images + (long long)v0 * 3 * px;
+    if (in->ray_dirs) sub.ray_dirs = in->ray_dirs + (long long)v0 * px * 3;
+    if (in->depth_along_ray) sub.depth_along_ray = in->depth_along_ray + (long long)v0 * px;
+    if (in->cam_quats) sub.cam_quats = in->cam_quats + (long long)v0 * 4;
+    if (in->cam_trans) sub.cam_trans = in->cam_trans + (long long)v0 * 3;
+    if (in->ray_mask) sub.ray_mask = in->ray_mask + v0;
+    if (in->depth_mask) sub.depth_mask = in->depth_mask + v0;
+    if (in->cam_mask) sub.cam_mask = in->cam_mask + v0;
+    if (in->depth_metric_mask) sub.depth_metric_mask = in->depth_metric_mask + v0;
+    if (in->pose_metric_mask) sub.pose_metric_mask = in->pose_metric_mask + v0;
+    // the helpers read h->plan: present the pass as a scene of vc views whose outputs start at view v0
+    Plan& q = h->plan;
+    q = whole;
+    q.V = vc;
+    q.Lenc = (long long)vc * (whole.T + 1);
+    q.fused = whole.fused + (long long)v0 * whole.T * D;
+    if (whole.fused32) q.fused32 = whole.fused32 + (long long)v0 * whole.T * D;
+    if (identity_embed) q.ys = whole.ys + (long long)v0 * whole.T * D;
+    rc = encode_views(c, &sub, multimodal, identity_embed);
+  }
+  h->plan = whole;
+  if (rc) return rc;
   if (identity_embed) {
     // the fp32 fused tokens were written straight into the stream; the scale token joins them as is
     if (p.has_scale)

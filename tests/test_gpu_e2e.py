@@ -473,3 +473,30 @@ def test_infer_host_outputs_equals_device_outputs(model):
     assert all(torch.equal(a[0][k], keep[k]) for k in keep)
     b = model.infer([dict(v) for v in other], host_outputs=True, reuse_host_buffers=True, **kw)
     assert b[0]["pts3d"].data_ptr() == ptr_a and torch.equal(b[0]["pts3d_cam"], second[0]["pts3d_cam"])
+
+
+def test_encoder_chunking_does_not_change_outputs(model, synthetic_sd):
+    """mab_config.enc_chunk (views per encoder pass, SURVEY 8(f) many-view streaming): a workspace knob like
+    head_chunk -- every kernel of the encoder is per-view independent and accumulates in a fixed order, so
+    a multi-modal scene encoded 2 views at a time (3 passes, the last one ragged) equals the one-pass result
+    bit for bit; and 2000 views at 518x392 need < 80 GB of workspace on one GPU (60 MB per view without it)."""
+    import ctypes as C
+
+    from mapanything_b200 import MapAnything
+    from oracle import weights
+
+    views = weights.add_multimodal_inputs(weights.synthetic_views(5, 56, 84, seed=41), seed=42)
+    kw = dict(apply_confidence_mask=True, confidence_percentile=20)
+    want = model.infer([dict(v) for v in views], **kw)
+    m2 = MapAnything(device="cuda:0", head_chunk=2, enc_chunk=2)
+    m2.load_state_dict(synthetic_sd)
+    got = m2.infer([dict(v) for v in views], **kw)
+    torch.cuda.synchronize()
+    for g, w in zip(got, want):
+        for k in w:
+            assert torch.equal(g[k], w[k]), k
+    need = m2._lib.mab_workspace_bytes(model._handle, 2000, 2000, 392, 518)
+    m_one = MapAnything(device="cuda:0", enc_chunk=0)  # keep the object: its handle dies with it
+    one_pass = m2._lib.mab_workspace_bytes(m_one._handle, 2000, 2000, 392, 518)
+    print(f"workspace for 2000 views 518x392: {need / 2**30:.1f} GiB with enc_chunk=64, {one_pass / 2**30:.1f} GiB in one pass")
+    assert need < 80 * 2**30 < one_pass
