@@ -37,6 +37,9 @@ METRIC = "views/sec (518px, bf16)"
 UNIT = "views/s"
 
 
+print_line = print  # replaced in main(): the JSON line goes to the ORIGINAL stdout, everything else to stderr
+
+
 def flops_per_scene(n):
     """image-only algorithmic FLOPs of one scene of n views."""
     return (1369.1 * n + 39.57 * n * n) * 1e9
@@ -173,7 +176,7 @@ def reference_arm(args, rank, world):
     v = sample_views / dt
     sample = (f"the whole scene: {sample_views} views 518x392 per step" if sample_views == n_views else
               f"{sample_views} of the scene's {n_views} views 518x392 per step")
-    print(json.dumps({
+    print_line(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -182,7 +185,7 @@ def reference_arm(args, rank, world):
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                          "sample": sample + ", " + _kind_text(kind) + f", fp32 torch CPU, {cores} threads"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }), flush=True)
+    }))
 
 
 def cpu_and_gpu_baseline_legs(dev, budget_s=25.0):
@@ -245,6 +248,14 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries ONE JSON line.  Libraries write to file descriptor 1 behind Python's back (NCCL prints its
+    # version banner there whatever NCCL_DEBUG_FILE says): fd 1 is pointed at stderr for the whole run and
+    # the line goes out through a private duplicate of the original stdout.
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    global print_line
+    print_line = lambda text: (real_stdout.write(text + "\n"), real_stdout.flush())
     if args.impl == "reference":
         reference_arm(args, rank, world)
         return
@@ -478,7 +489,7 @@ def main():
             line["roofline"] = roof
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        print_line(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     if shard_par is not None and not shard_par["ok"]:

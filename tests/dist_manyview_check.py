@@ -64,9 +64,11 @@ def main():
         d = float((depth[g - lo].float() - depth[g + DISTINCT - lo].float()).abs().max())
         same_rank_max = max(same_rank_max, d)
         pairs += 1
-    # cross-rank copies: every rank contributes its first copy of distinct view 1 (a digest of 4096 pixels)
+    # cross-rank copies: every rank contributes its first copy of distinct view 1: a digest of 16384 pixels of
+    # the confidence map (NOT of the depth: infer() zeroes the masked pixels of the depth, so the ~0.5 % of
+    # pixels whose mask bit flips between two bf16 noise draws would count with their full magnitude)
     first = next(g for g in range(lo, hi) if g % DISTINCT == 1) if any(g % DISTINCT == 1 for g in range(lo, hi)) else None
-    dig = depth[first - lo, :4096].float().to(dev) if first is not None else torch.full((4096,), float("nan"), device=dev)
+    dig = conf[first - lo, :16384].float().to(dev) if first is not None else torch.full((16384,), float("nan"), device=dev)
     allv = [torch.empty_like(dig) for _ in range(world)]
     dist.all_gather(allv, dig)
     have = [t for t in allv if bool(torch.isfinite(t).all())]
