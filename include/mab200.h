@@ -69,6 +69,12 @@ typedef struct {
    * resident per view (about 35 MB per view at 518x392 instead of 60 MB).  Outputs do not depend on it.
    * <= 0 or >= the views held: one pass. */
   int enc_chunk;
+  /* Encoder lanes: 2 = the passes of the encoder alternate between TWO streams (the caller's and one the
+   * handle owns), each with its own pass-sized activations, so that the idle SMs of one lane's last wave
+   * and draining tiles could run the other lane's kernels; 0 / 1 = one stream (the Python mirror's
+   * default: measured on one box, 8 views, 21.76 / 21.86 ms with one lane against 21.82 / 21.92 ms with
+   * two -- the halves' own wave quantisation eats what the overlap buys).  Outputs do not depend on it. */
+  int enc_lanes;
 } mab_config;
 
 /* One scene, `views` views of H x W pixels held by this rank. */

@@ -12,7 +12,7 @@ class MabConfig(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("patch", "enc_dim", "enc_depth", "enc_heads", "enc_pos_grid",
                                        "aat_dim", "aat_depth", "aat_heads", "aat_tap0", "aat_tap1",
                                        "head_chunk", "aat_ref_view_pe", "aat_entropy_scaling", "aat_tap2", "aat_nonref_view_pe", "aat_all_global",
-                                       "head_tf32", "enc_chunk")]
+                                       "head_tf32", "enc_chunk", "enc_lanes")]
 
 
 class MabInputs(C.Structure):

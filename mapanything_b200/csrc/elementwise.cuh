@@ -403,7 +403,11 @@ __global__ void resize_bilinear_ac_kernel(const __nv_bfloat16* __restrict__ in, 
   if (out_relu) reinterpret_cast<uint4*>(out_relu)[i] = make_uint4(orl[0], orl[1], orl[2], orl[3]);
 }
 
-// the same on fp32 NHWC activations, 4 channels per thread (fp32 / TF32 dense head)
+// the same on fp32 NHWC activations (fp32 / TF32 dense head): thread = 4 channels of RESIZE_ROWS consecutive
+// output rows of one output column -- the column's x taps and weights are shared, and the 4 * RESIZE_ROWS
+// 16-byte loads are all issued before the first blend (the one-row version ran at 2.1 TB/s of stores:
+// latency-bound, 395 us for the 224x296 -> 392x518 resize of 8 views)
+constexpr int RESIZE_ROWS = 4;
 __global__ void resize_bilinear_ac_f32_kernel(const float* __restrict__ in, int views, int Hi, int Wi, int C,
                                               int Hv, int Wv, int Ho, int Wo, float* __restrict__ out,
                                               float* __restrict__ out_relu) {
@@ -411,26 +415,41 @@ __global__ void resize_bilinear_ac_f32_kernel(const float* __restrict__ in, int 
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= Wo * c4n) return;
   const int ox = idx / c4n, c4 = idx - ox * c4n;
-  const int oy = blockIdx.y, v = blockIdx.z;
+  const int oy0 = blockIdx.y * RESIZE_ROWS, v = blockIdx.z;
   const float ry = Hv > 1 ? float(Hi - 1) / float(Hv - 1) : 0.f;
   const float rx = Wv > 1 ? float(Wi - 1) / float(Wv - 1) : 0.f;
-  const float sy = ry * oy, sx = rx * ox;
-  const int y0 = min((int)sy, Hi - 1), x0 = min((int)sx, Wi - 1);
-  const int y1 = min(y0 + 1, Hi - 1), x1 = min(x0 + 1, Wi - 1);
-  const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
+  const float sx = rx * ox;
+  const int x0 = min((int)sx, Wi - 1), x1 = min(x0 + 1, Wi - 1);
+  const float lx = sx - x0, hx = 1.f - lx;
   const float4* base = reinterpret_cast<const float4*>(in) + (long long)v * Hi * Wi * c4n + c4;
-  const float4 a = base[((long long)y0 * Wi + x0) * c4n], b = base[((long long)y0 * Wi + x1) * c4n];
-  const float4 c = base[((long long)y1 * Wi + x0) * c4n], d = base[((long long)y1 * Wi + x1) * c4n];
-  float4 o;  // ATen: hy*(hx*a + lx*b) + ly*(hx*c + lx*d)
-  o.x = hy * (hx * a.x + lx * b.x) + ly * (hx * c.x + lx * d.x);
-  o.y = hy * (hx * a.y + lx * b.y) + ly * (hx * c.y + lx * d.y);
-  o.z = hy * (hx * a.z + lx * b.z) + ly * (hx * c.z + lx * d.z);
-  o.w = hy * (hx * a.w + lx * b.w) + ly * (hx * c.w + lx * d.w);
-  const long long i = (((long long)v * Ho + oy) * Wo + ox) * c4n + c4;
-  o = tf32_rn(o);  // operand of the next kind::tf32 contraction
-  if (out) reinterpret_cast<float4*>(out)[i] = o;
-  if (out_relu)
-    reinterpret_cast<float4*>(out_relu)[i] = make_float4(fmaxf(o.x, 0.f), fmaxf(o.y, 0.f), fmaxf(o.z, 0.f), fmaxf(o.w, 0.f));
+  float4 a[RESIZE_ROWS], b[RESIZE_ROWS], c[RESIZE_ROWS], d[RESIZE_ROWS];
+  float ly[RESIZE_ROWS];
+#pragma unroll
+  for (int r = 0; r < RESIZE_ROWS; ++r) {
+    const int oy = min(oy0 + r, Ho - 1);
+    const float sy = ry * oy;
+    const int y0 = min((int)sy, Hi - 1), y1 = min(y0 + 1, Hi - 1);
+    ly[r] = sy - y0;
+    a[r] = __ldg(base + ((long long)y0 * Wi + x0) * c4n); b[r] = __ldg(base + ((long long)y0 * Wi + x1) * c4n);
+    c[r] = __ldg(base + ((long long)y1 * Wi + x0) * c4n); d[r] = __ldg(base + ((long long)y1 * Wi + x1) * c4n);
+  }
+#pragma unroll
+  for (int r = 0; r < RESIZE_ROWS; ++r) {
+    const int oy = oy0 + r;
+    if (oy >= Ho) break;
+    const float hy = 1.f - ly[r];
+    float4 o;  // ATen: hy*(hx*a + lx*b) + ly*(hx*c + lx*d)
+    o.x = hy * (hx * a[r].x + lx * b[r].x) + ly[r] * (hx * c[r].x + lx * d[r].x);
+    o.y = hy * (hx * a[r].y + lx * b[r].y) + ly[r] * (hx * c[r].y + lx * d[r].y);
+    o.z = hy * (hx * a[r].z + lx * b[r].z) + ly[r] * (hx * c[r].z + lx * d[r].z);
+    o.w = hy * (hx * a[r].w + lx * b[r].w) + ly[r] * (hx * c[r].w + lx * d[r].w);
+    o = tf32_rn(o);  // operand of the next kind::tf32 contraction
+    const long long i = (((long long)v * Ho + oy) * Wo + ox) * c4n + c4;
+    if (out) __stcs(reinterpret_cast<float4*>(out) + i, o);   // streamed: read once by the next conv
+    if (out_relu)
+      __stcs(reinterpret_cast<float4*>(out_relu) + i,
+             make_float4(fmaxf(o.x, 0.f), fmaxf(o.y, 0.f), fmaxf(o.z, 0.f), fmaxf(o.w, 0.f)));
+  }
 }
 
 // ConvTranspose2d with kernel == stride (dpt.py:117-127,139-149) = GEMM + pixel shuffle.

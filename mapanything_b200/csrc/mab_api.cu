@@ -652,6 +652,13 @@ struct Bump {  // bump allocator over the caller's workspace (256-byte aligned)
 struct Plan {  // every workspace pointer of one forward
   int V = 0, Vtot = 0, H = 0, W = 0, h = 0, w = 0, T = 0;
   int Ve = 0;  // views per encoder pass (cfg.enc_chunk): the encoder's activations are sized for Ve views
+  // The encoder runs on `lanes` streams at once, each pass of Vl views on the lane whose turn it is, with
+  // its own activations: persistent GEMM / attention kernels leave SMs idle in their last wave (M = 8 views
+  // x 1037 rows is 33 CTA-pair tiles per column of tiles on 74 clusters: 89 % full) and while their last
+  // tiles drain; the other lane's kernels fill those SMs.
+  int lanes = 1, Vl = 0;
+  struct EncBufs { bf16* im2col; float* patch; float* xs; bf16* ln; bf16* qkv; bf16* att; bf16* hid;
+                   float* enc_out; float* geo_sum; float* geo_vec; float* geo_small; } lane[2];
   int has_scale = 0, has_ref = 0;
   long long Lenc = 0, L = 0;  // encoder rows V*(T+1); info-sharing rows V*T (+1)
   // encoder
@@ -682,6 +689,8 @@ struct mab_handle {
   std::map<std::string, float*> extra;        // derived fp32 tensors (tiled biases)
   std::vector<void*> owned;
   std::vector<int> view_pe_rows;               // mab_set_view_pe_rows: one table row per view of the shard
+  cudaStream_t lane_stream = nullptr;          // second encoder lane (the first is the caller's stream)
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   Plan plan;
 
   const float* F(const std::string& k) const {
@@ -716,21 +725,32 @@ void make_plan(const mab_handle* hd, int V, int Vtot, int H, int W, int has_scal
   // fp32 for the fp32 head), the info-sharing stream, its taps and the info-sharing activations, which
   // share the ln | qkv | att | hid buffers with the encoder (each sized for the larger of the two uses).
   p.Ve = (c.enc_chunk > 0 && c.enc_chunk < V) ? c.enc_chunk : V;
-  const long long VTe = (long long)p.Ve * p.T, Le = (long long)p.Ve * (p.T + 1);
+  p.lanes = (p.Ve >= 2 && c.enc_lanes == 2) ? 2 : 1;
+  p.Vl = (p.Ve + p.lanes - 1) / p.lanes;
+  const long long VTe = (long long)p.Vl * p.T, Le = (long long)p.Vl * (p.T + 1);
   auto mx = [](long long a, long long b2) { return a > b2 ? a : b2; };
-  p.im2col = b.take<bf16>(VTe * 640);
-  p.patch = b.take<float>(VTe * D);
   p.pos = b.take<float>((long long)(p.T + 1) * D);
-  p.xs = b.take<float>(Le * D);
-  p.ln = b.take<bf16>(mx(Le * D, (VT + 1) * A));
-  p.qkv = b.take<bf16>(mx(Le * 3 * D, (VT + 1) * 3 * A));
-  p.att = b.take<bf16>(mx(Le * D, (VT + 1) * A));
-  p.hid = b.take<bf16>(mx(Le * 4 * D, (VT + 1) * 4 * A));
-  p.enc_out = b.take<float>(VTe * D);
+  for (int l = 0; l < p.lanes; ++l) {
+    Plan::EncBufs& e = p.lane[l];
+    // lane 0's ln | qkv | att | hid also serve the info-sharing blocks (all local tokens at width A)
+    const long long rows_a = l == 0 ? VT + 1 : 0;
+    e.im2col = b.take<bf16>(VTe * 640);
+    e.patch = b.take<float>(VTe * D);
+    e.xs = b.take<float>(Le * D);
+    e.ln = b.take<bf16>(mx(Le * D, rows_a * A));
+    e.qkv = b.take<bf16>(mx(Le * 3 * D, rows_a * 3 * A));
+    e.att = b.take<bf16>(mx(Le * D, rows_a * A));
+    e.hid = b.take<bf16>(mx(Le * 4 * D, rows_a * 4 * A));
+    e.enc_out = b.take<float>(VTe * D);
+    e.geo_sum = b.take<float>(VTe * D);          // sum of the masked dense geometric features
+    e.geo_vec = b.take<float>((long long)p.Vl * D); // sum of the masked per-view (global) features
+    e.geo_small = b.take<float>((long long)p.Vl * 4096 + 64);  // MLP scratch + masks + scalar inputs
+  }
+  if (p.lanes == 1) p.lane[1] = p.lane[0];
+  p.im2col = p.lane[0].im2col; p.patch = p.lane[0].patch; p.xs = p.lane[0].xs; p.ln = p.lane[0].ln;
+  p.qkv = p.lane[0].qkv; p.att = p.lane[0].att; p.hid = p.lane[0].hid; p.enc_out = p.lane[0].enc_out;
+  p.geo_sum = p.lane[0].geo_sum; p.geo_vec = p.lane[0].geo_vec; p.geo_small = p.lane[0].geo_small;
   p.fused = b.take<bf16>((VT + 1) * D);
-  p.geo_sum = b.take<float>(VTe * D);          // sum of the masked dense geometric features
-  p.geo_vec = b.take<float>((long long)p.Ve * D); // sum of the masked per-view (global) features
-  p.geo_small = b.take<float>((long long)p.Ve * 4096 + 64);  // MLP scratch + masks + scalar inputs
   p.ys = b.take<float>((VT + 1) * A);
   p.view_rows = b.take<int>(V);  // view_pos_table row of every view (use_pe_for_non_reference_views)
   const bool tf = c.head_tf32 != 0;
@@ -803,6 +823,14 @@ extern "C" int mab_create(const mab_config* cfg, int device, mab_handle** out) {
   mab_handle* h = new mab_handle();
   h->cfg = *cfg;
   h->device = device;
+  // set-up time only: the second encoder lane's stream and the two events that fork / join it
+  cudaError_t e1 = cudaStreamCreateWithFlags(&h->lane_stream, cudaStreamNonBlocking);
+  cudaError_t e2 = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+  cudaError_t e3 = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
+  if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) {
+    delete h;
+    return fail((int)(e1 != cudaSuccess ? e1 : e2 != cudaSuccess ? e2 : e3), "could not create the encoder lane stream / events");
+  }
   *out = h;
   return 0;
 }
@@ -811,6 +839,9 @@ extern "C" int mab_destroy(mab_handle* h) {
   if (!h) return 0;
   for (auto& kv : h->raw) cudaFree(kv.second.p);
   for (void* p : h->owned) cudaFree(p);
+  if (h->lane_stream) cudaStreamDestroy(h->lane_stream);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   delete h;
   return 0;
 }
@@ -1074,7 +1105,7 @@ extern "C" int mab_debug_buffer(mab_handle* h, const char* name, void** ptr, lon
   const long long VT = (long long)p.V * p.T;
   const int D = h->cfg.enc_dim, A = h->cfg.aat_dim;
   const std::string n = name;
-  if (n == "enc_tokens") { *ptr = p.xs; *numel = (long long)p.Ve * (p.T + 1) * D; *dtype = MAB_F32; }  // last encoder pass
+  if (n == "enc_tokens") { *ptr = p.xs; *numel = (long long)p.Vl * (p.T + 1) * D; *dtype = MAB_F32; }  // lane 0, its last pass
   else if (n == "fused" && p.fused32) { *ptr = p.fused32; *numel = VT * D; *dtype = MAB_F32; }
   else if (n == "fused") { *ptr = p.fused; *numel = VT * D; *dtype = MAB_BF16; }
   else if (n == "aat_stream") { *ptr = p.ys; *numel = p.L * A; *dtype = MAB_F32; }
@@ -1189,8 +1220,8 @@ int head_resize(Ctx& c, const bf16* x, int batch, int Hi, int Wi, int C, int Hv,
 }
 int head_resize(Ctx& c, const float* x, int batch, int Hi, int Wi, int C, int Hv, int Wv, int Ho, int Wo, float* out) {
   MAB_ARG(batch > 0 && batch <= 65535 && Ho > 0 && Ho <= 65535 && Wo > 0 && C % 4 == 0, "resize: bad sizes");
-  const dim3 grid((Wo * (C / 4) + 255) / 256, Ho, batch);
-  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
+  const dim3 grid((Wo * (C / 4) + 255) / 256, (Ho + RESIZE_ROWS - 1) / RESIZE_ROWS, batch);
+  MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, (double)batch * C * 4.0 * ((double)Ho * Wo + (double)Hi * Wi), c.st,
              resize_bilinear_ac_f32_kernel<<<grid, 256, 0, c.st>>>(x, batch, Hi, Wi, C, Hv, Wv, Ho, Wo, out, nullptr));
   MAB_CUDA(cudaGetLastError());
   return 0;
@@ -1455,12 +1486,19 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
     return fail(-4, "geometric inputs given but the checkpoint has no geometric encoders");
 
   MAB_TRY(mab_posembed_resize(h->F("encoder.model.pos_embed"), cf.enc_pos_grid, D, p.h, p.w, p.pos, c.st));
-  // a3-a6 are per-view independent: p.Ve views per pass through one pass-sized set of activations, each
-  // pass writing its rows of the fused tokens (bf16, + fp32 for the fp32 head / the identity-embed stream)
+  // a3-a6 are per-view independent: passes of p.Vl views, alternating between the encoder lanes (streams),
+  // each pass writing its rows of the fused tokens (bf16, + fp32 for the fp32 head / identity-embed stream)
   const Plan whole = h->plan;
   int rc = 0;
-  for (int v0 = 0; v0 < whole.V && rc == 0; v0 += whole.Ve) {
-    const int vc = whole.V - v0 < whole.Ve ? whole.V - v0 : whole.Ve;
+  const bool two = whole.lanes == 2;
+  if (two) {  // fork: the second lane starts after everything already queued on the caller's stream
+    MAB_CUDA(cudaEventRecord(h->ev_fork, c.st));
+    MAB_CUDA(cudaStreamWaitEvent(h->lane_stream, h->ev_fork, 0));
+  }
+  int pass = 0;
+  for (int v0 = 0; v0 < whole.V && rc == 0; v0 += whole.Vl, ++pass) {
+    const int vc = whole.V - v0 < whole.Vl ? whole.V - v0 : whole.Vl;
+    const int l = two ? pass & 1 : 0;
     mab_inputs sub = *in;
     const long long px = (long long)whole.H * whole.W;
     sub.views = vc;
@@ -1474,15 +1512,25 @@ extern "C" int mab_stage_encode(mab_handle* h, const mab_inputs* in, int views_t
     if (in->cam_mask) sub.cam_mask = in->cam_mask + v0;
     if (in->depth_metric_mask) sub.depth_metric_mask = in->depth_metric_mask + v0;
     if (in->pose_metric_mask) sub.pose_metric_mask = in->pose_metric_mask + v0;
-    // the helpers read h->plan: present the pass as a scene of vc views whose outputs start at view v0
+    // the helpers read h->plan: present the pass as a scene of vc views on this lane's activations whose
+    // outputs start at view v0 (kernel arguments are captured at launch, so the plan may change under
+    // kernels that are still queued)
     Plan& q = h->plan;
     q = whole;
     q.V = vc;
     q.Lenc = (long long)vc * (whole.T + 1);
+    const Plan::EncBufs& e = whole.lane[l];
+    q.im2col = e.im2col; q.patch = e.patch; q.xs = e.xs; q.ln = e.ln; q.qkv = e.qkv; q.att = e.att; q.hid = e.hid;
+    q.enc_out = e.enc_out; q.geo_sum = e.geo_sum; q.geo_vec = e.geo_vec; q.geo_small = e.geo_small;
     q.fused = whole.fused + (long long)v0 * whole.T * D;
     if (whole.fused32) q.fused32 = whole.fused32 + (long long)v0 * whole.T * D;
     if (identity_embed) q.ys = whole.ys + (long long)v0 * whole.T * D;
-    rc = encode_views(c, &sub, multimodal, identity_embed);
+    Ctx cl{h, l == 0 ? c.st : h->lane_stream};
+    rc = encode_views(cl, &sub, multimodal, identity_embed);
+  }
+  if (two && rc == 0) {  // join
+    MAB_CUDA(cudaEventRecord(h->ev_join, h->lane_stream));
+    MAB_CUDA(cudaStreamWaitEvent(c.st, h->ev_join, 0));
   }
   h->plan = whole;
   if (rc) return rc;

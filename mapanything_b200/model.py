@@ -63,7 +63,7 @@ def default_config():
     return dict(patch=14, enc_dim=1024, enc_depth=24, enc_heads=16, enc_pos_grid=37, aat_dim=768,
                 aat_depth=24, aat_heads=12, aat_tap0=11, aat_tap1=17, head_chunk=8,
                 aat_ref_view_pe=1, aat_entropy_scaling=0, aat_tap2=0,
-                aat_nonref_view_pe=0, aat_all_global=0, head_tf32=1, enc_chunk=64)
+                aat_nonref_view_pe=0, aat_all_global=0, head_tf32=1, enc_chunk=64, enc_lanes=1)
 
 
 def head_ranges(V, stream_chunk, default_chunk):
@@ -112,7 +112,7 @@ class MapAnything(torch.nn.Module):
                  load_specific_pretrained_submodules: bool = False,
                  specific_pretrained_submodules: Optional[list] = None,
                  torch_hub_force_reload: bool = False, device="cuda", head_chunk: int = 8,
-                 head_precision: str = "tf32", enc_chunk: int = 64):
+                 head_precision: str = "tf32", enc_chunk: int = 64, enc_lanes: int = 1):
         """Reference constructor arguments (model.py:99-113) plus four of this implementation: `device`,
         `head_chunk` (views per dense-head pass; a workspace knob, results do not depend on it) and
         `enc_chunk` (views per encoder pass; a workspace knob like head_chunk: the encoder's activations are
@@ -164,6 +164,7 @@ class MapAnything(torch.nn.Module):
         cfg["head_chunk"] = int(head_chunk)
         cfg["head_tf32"] = int(head_precision == "tf32")
         cfg["enc_chunk"] = int(enc_chunk)
+        cfg["enc_lanes"] = int(os.environ.get("MAB_ENC_LANES", enc_lanes))  # env: A/B runs (profiles/)
         self.head_precision = head_precision
         self._cfg = _lib.MabConfig(**cfg)
         self._handle = C.c_void_p()
