@@ -382,7 +382,8 @@ def main():
         for _ in range(args.steps):
             step_resident()
         cats = {}
-        for cat, name in enumerate(["gemm", "conv3", "conv3_regress", "attention", "layernorm", "elementwise", "postprocess"]):
+        for cat, name in enumerate(["gemm", "conv3", "conv3_regress", "attention", "layernorm", "elementwise", "postprocess",
+                                    "gemm_tf32", "conv3_tf32"]):
             n, ms, fl, by = C.c_longlong(), C.c_double(), C.c_double(), C.c_double()
             _lib.check(lib.mab_prof_query(cat, C.byref(n), C.byref(ms), C.byref(fl), C.byref(by)))
             cats[name] = dict(launches=n.value // args.steps, ms=ms.value / args.steps, flops=fl.value / args.steps,
@@ -404,10 +405,11 @@ def main():
                        "attention": "attention_kernel (tcgen05 flash attention)",
                        "conv3": "gemm_kernel<MODE_CONV3> (tcgen05 implicit-GEMM 3x3 conv)"}[dom]
         # DRAM traffic per launch of that kernel class from the committed `ncu --set full` capture of the
-        # 8-view step (profiles/r1_traffic.json); only quoted for the workload it was captured on
+        # 8-view step of THIS round (profiles/r2_traffic.json, derived from the capture's summary CSV with the
+        # git head recorded); only quoted for the workload it was captured on
         traffic, traffic_src = None, None
         try:
-            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
                 tj = json.load(f)
             if n_views == VIEWS_PER_GPU and world == 1 and dom in tj:
                 traffic, traffic_src = tj[dom], tj["source"]

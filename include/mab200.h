@@ -199,7 +199,10 @@ int mab_stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out,
 /* Launch accounting for bench.py: kernels launched by this library since load, and an optional
  * per-launch CUDA-event profiler (events recorded on the launch stream around every kernel). */
 enum { MAB_CAT_GEMM = 0, MAB_CAT_CONV3 = 1, MAB_CAT_CONV3_REGRESS = 2, MAB_CAT_ATTENTION = 3,
-       MAB_CAT_LAYERNORM = 4, MAB_CAT_ELEMENTWISE = 5, MAB_CAT_POSTPROCESS = 6, MAB_CAT_COUNT = 7 };
+       MAB_CAT_LAYERNORM = 4, MAB_CAT_ELEMENTWISE = 5, MAB_CAT_POSTPROCESS = 6,
+       MAB_CAT_GEMM_TF32 = 7,  /* kind::tf32 linear layers (fp32 dense head 1x1 convs, geometric encoders) */
+       MAB_CAT_CONV3_TF32 = 8, /* kind::tf32 3x3 convolutions; MAB_CAT_CONV3_REGRESS is bf16 or tf32 by head_tf32 */
+       MAB_CAT_COUNT = 9 };
 /* K/V length up to which mab_attention uses the one-Q-tile kernel (two CTAs per SM) instead of the
  * two-Q-tile kernel; < 0 restores the default (6000).  Test hook: both kernels at small sizes. */
 int mab_set_attention_short_max(int kv_len);

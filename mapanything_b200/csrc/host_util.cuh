@@ -48,7 +48,7 @@ inline int fail(int code, const char* fmt, ...) {
 
 // ---- launch accounting + optional per-launch CUDA-event profiler (bench.py's roofline leg) -------
 enum { CAT_GEMM = 0, CAT_CONV3 = 1, CAT_CONV3_REGRESS = 2, CAT_ATTENTION = 3, CAT_LAYERNORM = 4,
-       CAT_ELEMENTWISE = 5, CAT_POSTPROCESS = 6, CAT_COUNT = 7 };
+       CAT_ELEMENTWISE = 5, CAT_POSTPROCESS = 6, CAT_GEMM_TF32 = 7, CAT_CONV3_TF32 = 8, CAT_COUNT = 9 };
 struct ProfRec { int cat; double flops, bytes; cudaEvent_t e0, e1; };
 struct ProfState {
   bool on = false;
@@ -238,12 +238,16 @@ inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const Gem
   if (groups <= 0) return 0;
   const int max_clusters = sm_count() / CL;
   const int grid = (groups < max_clusters ? groups : max_clusters) * CL;
+  // ALGORITHMIC FLOPs: the un-padded K of the layer (creal for a conv; shp.creal > 0 for a linear layer whose
+  // K is padded (patch embed 588 -> 640) or tripled (bf16x3 pose head: three bf16 products per fp32 product))
   double flops;
   if (MODE == MODE_CONV3)
     flops = 2.0 * shp.batch * shp.H * shp.W * (double)shp.N * 9.0 * shp.creal;
   else
-    flops = 2.0 * shp.M * (double)shp.N * shp.K;
-  const int cat = MODE == MODE_CONV3 ? (EPI == EPI_REGRESS ? CAT_CONV3_REGRESS : CAT_CONV3) : CAT_GEMM;
+    flops = 2.0 * shp.M * (double)shp.N * (shp.creal > 0 ? shp.creal : shp.K);
+  // kind::tf32 launches have their own categories: half the tensor rate, not comparable with the bf16 peak
+  const int cat = MODE == MODE_CONV3 ? (EPI == EPI_REGRESS ? CAT_CONV3_REGRESS : (TF ? CAT_CONV3_TF32 : CAT_CONV3))
+                                     : (TF ? CAT_GEMM_TF32 : CAT_GEMM);
   ProfScope ps(cat, flops, 0.0, st);
   MAB_CUDA(launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), SM::TOTAL, st, CL, tA, tB, shp, ep, rg));
   return 0;
@@ -251,11 +255,11 @@ inline int launch_gemm_t(const CUtensorMap& tA, const CUtensorMap& tB, const Gem
 
 // C[M,N] = epilogue(A[M,K] B[N,K]^T); lda/ldb row pitches in elements
 inline int launch_gemm(const void* A, long long lda, const void* B, long long ldb, int M, int N,
-                       int K, const GemmEpilogue& ep, cudaStream_t st) {
+                       int K, const GemmEpilogue& ep, cudaStream_t st, int k_algorithmic = 0) {
   MAB_ARG(M > 0 && N > 0 && K > 0, "empty GEMM");
   MAB_ARG(N % 4 == 0, "N must be a multiple of 4");
   CUtensorMap tA, tB;
-  GemmShape shp{M, N, K, 0, 0, 0, 0, 0};
+  GemmShape shp{M, N, K, 0, 0, 0, 0, k_algorithmic};
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM));
   if (N > 128) {

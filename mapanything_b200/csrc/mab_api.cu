@@ -1143,13 +1143,13 @@ struct Ctx {
   // y = epilogue(A[M,K] W[N,K]^T); W, bias looked up by reference key
   int linear(const void* A, int M, int K, long long lda, const std::string& wkey, int N,
              const float* bias, int act, const float* gamma, const float* res_f32, float* out_f32,
-             bf16* out_bf16, const bf16* res1 = nullptr, long long ldw = 0) {
+             bf16* out_bf16, const bf16* res1 = nullptr, long long ldw = 0, int k_algorithmic = 0) {
     const bf16* W = h->P(wkey);
     if (!W) return fail(-4, "weight %s was not packed", wkey.c_str());
     GemmEpilogue ep{};
     ep.bias = bias; ep.gamma = gamma; ep.res_f32 = res_f32; ep.out_f32 = out_f32;
     ep.out_bf16 = out_bf16; ep.res1 = res1; ep.ldo = N; ep.act = act;
-    return launch_gemm(A, lda, W, ldw > 0 ? ldw : K, M, N, K, ep, st);
+    return launch_gemm(A, lda, W, ldw > 0 ? ldw : K, M, N, K, ep, st, k_algorithmic);
   }
   // bf16x3 linear: A rows are [hi | lo | hi] (pitch 3K), W rows [hi | hi | lo]; the output is
   // written in the same split form (pitch 3N) so that layers chain; the residual is a split value
@@ -1160,7 +1160,7 @@ struct Ctx {
     GemmEpilogue ep{};
     ep.bias = bias; ep.act = act; ep.out_bf16 = out_split; ep.ldo = 3 * N; ep.split_n = N;
     ep.res1 = res_split; ep.res2 = res_split ? res_split + N : nullptr;
-    return launch_gemm(A, 3LL * K, W, 3LL * K, M, N, 3 * K, ep, st);
+    return launch_gemm(A, 3LL * K, W, 3LL * K, M, N, 3 * K, ep, st, K);
   }
   int conv3(const bf16* x, int batch, int H, int W, int C, const std::string& wkey, int Cout,
             const float* bias, int act, const bf16* res1, const bf16* res2, bf16* out, bf16* out_relu) {
@@ -1434,7 +1434,7 @@ static int encode_views(Ctx& c, const mab_inputs* in, bool multimodal, bool iden
                                                                       nullptr, 0, p.im2col, nullptr));
   MAB_TRY(c.linear(p.im2col, (int)VT, 640, 640, "encoder.model.patch_embed.proj.weight", D,
                    h->F("encoder.model.patch_embed.proj.bias"), ACT_NONE, nullptr, nullptr, p.patch,
-                   nullptr, nullptr, 640));
+                   nullptr, nullptr, 640, 588));
   MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, 0.0, c.st,
              assemble_tokens_kernel<<<ew_grid(p.Lenc * D / 4), 256, 0, c.st>>>(
       p.patch, h->F("encoder.model.cls_token"), p.pos, V, T, D, p.xs));

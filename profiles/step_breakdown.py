@@ -15,7 +15,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from mapanything_b200 import MapAnything, synthetic  # noqa: E402
 
-CATS = ["gemm", "conv3", "conv3_regress", "attention", "layernorm", "elementwise", "postprocess"]
+CATS = ["gemm", "conv3", "conv3_regress", "attention", "layernorm", "elementwise", "postprocess", "gemm_tf32",
+        "conv3_tf32"]
 
 
 def main():
