@@ -454,6 +454,31 @@ def main():
         if world == 8:
             c4 = fixed_leg(512, 2, 1)
 
+    # single GPU: the same step replayed from a CUDA graph (the forward is one fixed kernel sequence on one
+    # stream); reported next to `value`, not instead of it
+    graph_leg = None
+    if world == 1 and not args.views and not args.multimodal:
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                model.run_resident(dev_imgs, H_IMG, W_IMG)
+            ms_g = timed(g.replay, args.steps, 3)
+            graph_leg = {"ms_per_step": ms_g, "views_per_s": n_views / (ms_g * 1e-3),
+                         "what": "run_resident captured once with torch.cuda.graph and replayed"}
+            del g
+        except Exception as e:
+            graph_leg = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+
+    # the bf16 dense head (opt-in, head_precision="bf16"): bf16 operands where the reference runs fp32 / TF32
+    bf16_leg = None
+    if world == 1 and not args.views and not args.multimodal:
+        m16 = MapAnything(device=dev, head_chunk=8, head_precision="bf16")
+        m16.load_state_dict(synthetic.synthetic_state_dict())
+        ms16 = timed(lambda: m16.run_resident(dev_imgs, H_IMG, W_IMG), args.steps, 3)
+        bf16_leg = {"ms_per_step": ms16, "views_per_s": n_views / (ms16 * 1e-3),
+                    "what": "the same step with MapAnything(head_precision='bf16'); parity of that head: DESIGN.md section 5"}
+        del m16
+
     cpu = ref_gpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu, ref_gpu = cpu_and_gpu_baseline_legs(dev)
@@ -487,6 +512,11 @@ def main():
             line["c4_512"] = c4
         if ref_gpu is not None:
             line["reference_gpu"] = ref_gpu
+        if graph_leg is not None:
+            line["cuda_graph_replay"] = graph_leg
+        if bf16_leg is not None:
+            line["head_bf16"] = bf16_leg
+        line["config"]["head_precision"] = "tf32 (fp32 activations, TF32 contractions: the reference's precision for the dense head; model.py:1774)"
         if roof is not None:
             line["roofline"] = roof
         if cpu is not None:

@@ -27,7 +27,12 @@ constexpr int CONV_TW = 16;
 
 enum { MODE_GEMM = 0, MODE_CONV3 = 1 };
 enum { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2 };
-enum { EPI_GENERIC = 0, EPI_REGRESS = 1 };
+enum { EPI_GENERIC = 0, EPI_REGRESS = 1,
+       EPI_RESID = 2,    // in-place fp32 residual update only (proj / fc2 of every transformer block)
+       EPI_PLAIN = 3 };  // bias (+ GELU) -> bf16 only (qkv / fc1 of every transformer block)
+// EPI_RESID / EPI_PLAIN carry exactly the epilogue their layers need: 135 / ~150 registers and no spills,
+// where the generic kernel (every operand combination of the dense head and the tests behind a switch)
+// sits on the 168-register cap of a 10-warp CTA with 140-420 B of spills
 
 struct GemmEpilogue {
   const float* bias;             // [N] or null
@@ -143,7 +148,7 @@ __device__ __forceinline__ int epilogue_flags(const GemmEpilogue& ep) {
          (ep.res2_f32 ? EF_RES2F : 0) | (ep.out_relu_f32 ? EF_OUTRELUF : 0);
 }
 
-template <int F>
+template <int F, bool RED = false>
 __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, uint32_t t_row, float* stg,
                                                 int lane, int sub_r, int sub_c4, const long long (&ro)[8],
                                                 uint32_t row_mask, int c_begin, int c_end, int n0) {
@@ -163,15 +168,10 @@ __device__ __forceinline__ void epilogue_chunks(const GemmEpilogue& ep, int N, u
   // In-place fp32 residual (x += gamma * (A B^T + bias): out_f32 == res_f32 and nothing else written -- the
   // proj and fc2 GEMMs of every transformer block): the add is performed by the L2 with a fire-and-forget
   // vector reduction (red.global.add.v4.f32), so the epilogue never waits for a residual load.  One fp32 add
-  // per element either way: bit-identical.  Only these two instantiations carry the extra path (in the
-  // others the run-time test cost registers: fc1 62.9 -> 75.9 us).  profiles/r2_gemm_variants.txt:
-  // proj 23.5 -> 20.0 us, fc2 60.0 -> 56.9 us (encoder), 17.7 -> 15.2 / 35.3 -> 33.0 us (info sharing).
-#ifndef MAB_NO_EPI_RED
-  constexpr bool RED_CASE = F == (EF_OUTF32 | EF_RESF32 | EF_GAMMA) || F == (EF_OUTF32 | EF_RESF32);
-#else
-  constexpr bool RED_CASE = false;
-#endif
-  const bool red_inplace = RED_CASE && ep.out_f32 == ep.res_f32 && !ep.round_tf32;
+  // per element either way (not an accumulation: deterministic).  The path lives in its OWN kernel
+  // instantiation (EPI_RESID): inside the generic kernel its mere presence cost every other epilogue
+  // registers (in the step: fc1 67 -> 74 us, qkv 43.7 -> 45.4 us, while proj went 33.3 -> 27.5 us).
+  const bool red_inplace = RED;
 #pragma unroll 1
   for (int c0 = c_begin; c0 < c_end; c0 += 32) {
     const int ncol0 = n0 + c0;
@@ -529,7 +529,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int n0 = n_blk * BN;
 #define MAB_EPI_CASE(F) \
   case F: epilogue_chunks<F>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro, row_mask, c_begin, c_end, n0); break;
-      if constexpr (TF) {  // fp32 operands: geometric-input encoders and the fp32 / TF32 dense head
+      if constexpr (EPI == EPI_PLAIN) {  // the launcher guarantees: bf16 output only, bias, optional GELU
+        if (ep.act == ACT_GELU)
+          epilogue_chunks<EF_OUTBF16 | EF_GELU>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro,
+                                                                     row_mask, c_begin, c_end, n0);
+        else
+          epilogue_chunks<EF_OUTBF16>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro, row_mask,
+                                                           c_begin, c_end, n0);
+      } else if constexpr (EPI == EPI_RESID) {  // the launcher guarantees out_f32 == res_f32, fp32 only, no activation
+        if (ep.gamma)
+          epilogue_chunks<EF_OUTF32 | EF_RESF32 | EF_GAMMA, true>(ep, shp.N, t_row, stg, lane, sub_r,
+                                                                                sub_c4, ro, row_mask, c_begin, c_end, n0);
+        else
+          epilogue_chunks<EF_OUTF32 | EF_RESF32, true>(ep, shp.N, t_row, stg, lane, sub_r, sub_c4, ro,
+                                                                     row_mask, c_begin, c_end, n0);
+      } else if constexpr (TF) {  // fp32 operands: geometric-input encoders and the fp32 / TF32 dense head
         switch (epi_flags) {
           MAB_EPI_CASE(EF_OUTF32)
           MAB_EPI_CASE(EF_OUTF32 | EF_RELU)

@@ -262,6 +262,14 @@ inline int launch_gemm(const void* A, long long lda, const void* B, long long ld
   GemmShape shp{M, N, K, 0, 0, 0, 0, k_algorithmic};
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_2d(&tA, A, M, K, lda, GEMM_BM));
+  // x += gamma * (A W^T + b) in place and nothing else: the residual-update kernel (red.global.add epilogue)
+  const bool resid = ep.res_f32 && ep.out_f32 == ep.res_f32 && !ep.out_bf16 && !ep.out_relu && !ep.res1 &&
+                     !ep.res2 && !ep.res2_f32 && !ep.out_relu_f32 && ep.act == ACT_NONE && !ep.split_n &&
+                     !ep.act_post && !ep.round_tf32 && N > 128 && !getenv("MAB_NO_EPI_RED");
+  // bias (+ GELU) -> bf16 and nothing else: the plain kernel (qkv, fc1)
+  const bool plain = ep.out_bf16 && !ep.out_f32 && !ep.out_relu && !ep.res_f32 && !ep.res1 && !ep.res2 &&
+                     !ep.res2_f32 && !ep.out_relu_f32 && !ep.gamma && (ep.act == ACT_NONE || ep.act == ACT_GELU) &&
+                     !ep.split_n && !ep.act_post && !ep.round_tf32 && N > 128 && !getenv("MAB_NO_EPI_PLAIN");
   if (N > 128) {
     // tile width by wave quantisation: the persistent grid has sm_count/2 clusters, each 256 x BN
     // tile costs ~BN (x1.12 at BN = 192, measured: the B half-tile amortises less of the A traffic); e.g. the
@@ -274,9 +282,13 @@ inline int launch_gemm(const void* A, long long lda, const void* B, long long ld
     };
     if (cost(192, 1.12) < cost(256, 1.0)) {
       MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 192 / GEMM_CL));
+      if (resid) return launch_gemm_t<192, 6, MODE_GEMM, EPI_RESID, GEMM_CL>(tA, tB, shp, ep, rg, st);
+      if (plain) return launch_gemm_t<192, 6, MODE_GEMM, EPI_PLAIN, GEMM_CL>(tA, tB, shp, ep, rg, st);
       return launch_gemm_t<192, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
     }
     MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 256 / GEMM_CL));
+    if (resid) return launch_gemm_t<256, 6, MODE_GEMM, EPI_RESID, GEMM_CL>(tA, tB, shp, ep, rg, st);
+    if (plain) return launch_gemm_t<256, 6, MODE_GEMM, EPI_PLAIN, GEMM_CL>(tA, tB, shp, ep, rg, st);
     return launch_gemm_t<256, 6, MODE_GEMM, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
   }
   MAB_TRY(make_tmap_2d(&tB, B, N, K, ldb, 128 / GEMM_CL));

@@ -10,8 +10,8 @@ sys.path.insert(0, ROOT)
 from mapanything_b200 import build  # noqa: E402
 
 VARIANTS = {
-    "default": [],                                # red.add residual epilogue, ex2 + rcp GELU
-    "nored": ["MAB_NO_EPI_RED"],                  # fp32 residual through load / add / store (round 1)
+    "default": [],                                # lean EPI_PLAIN / EPI_RESID kernels (MAB_NO_EPI_RED=1 /
+                                                  # MAB_NO_EPI_PLAIN=1 in the environment route back to the generic one)
     "tanhgelu": ["MAB_GELU_TANH"],                # GELU through one tanh.approx (faster, less accurate: not used)
 }
 

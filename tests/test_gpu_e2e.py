@@ -508,3 +508,29 @@ def test_encoder_chunking_does_not_change_outputs(model, synthetic_sd):
     one_pass = m2._lib.mab_workspace_bytes(m_one._handle, 2000, 2000, 392, 518)
     print(f"workspace for 2000 views 518x392: {need / 2**30:.1f} GiB with enc_chunk=64, {one_pass / 2**30:.1f} GiB in one pass")
     assert need < 80 * 2**30 < one_pass
+
+
+def test_forward_is_cuda_graph_capturable(model):
+    """the forward + post-processing of a scene is a fixed kernel sequence on ONE stream
+    (no host synchronisation, no allocation inside the library), so it can be captured into a CUDA graph
+    and replayed: the replay on new images equals the eager call bit for bit."""
+    from oracle import weights
+
+    H, W = 70, 98
+    a = torch.cat([v["img"] for v in weights.synthetic_views(3, H, W, seed=51)], 0).cuda()
+    b = torch.cat([v["img"] for v in weights.synthetic_views(3, H, W, seed=52)], 0).cuda()
+    static_in = a.clone()
+    model.run_resident(static_in, H, W)          # warm-up: workspace and function attributes exist
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        outs, post = model.run_resident(static_in, H, W)
+    static_in.copy_(b)
+    g.replay()
+    torch.cuda.synchronize()
+    got = {k: t.clone() for k, t in list(outs.items()) + list(post.items())}
+    want_o, want_p = model.run_resident(b, H, W)
+    torch.cuda.synchronize()
+    for k, t in list(want_o.items()) + list(want_p.items()):
+        assert torch.equal(got[k], t), k
+    assert not torch.equal(got["pts3d"], model.run_resident(a, H, W)[0]["pts3d"])
