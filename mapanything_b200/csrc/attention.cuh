@@ -127,10 +127,14 @@ __device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
   return r;
 }
 
-template <int QT>
+// LEAN: no carried online-softmax state and no log-sum-exp output (every single-GPU launch of the path):
+// the carry prologue / epilogue and their live values are compiled out of that instantiation
+template <int QT, bool LEAN = false>
 __global__ void __launch_bounds__(AttCfg<QT>::THREADS, QT == 2 ? 1 : 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                 const __grid_constant__ CUtensorMap tmV, AttnParams p) {
+                 const __grid_constant__ CUtensorMap tmV, AttnParams p_in) {
+  AttnParams p = p_in;
+  if constexpr (LEAN) { p.carry_in = 0; p.carry_out = 0; p.lse = nullptr; p.carry_o = nullptr; p.carry_ml = nullptr; }
   constexpr int KS = AttCfg<QT>::STAGES;
   constexpr int POLY_MASK = QT == 2 ? ATT_POLY_MASK : ATT_POLY_MASK_SHORT;
   constexpr int CTRL = AttCfg<QT>::CTRL_WARPS;

@@ -400,23 +400,29 @@ inline int launch_attention(const void* q_src, long long q_rows_total, const voi
   p.carry_o = carry_o; p.carry_ml = carry_ml; p.carry_in = carry_in; p.carry_out = carry_out;
   static bool attr_done[MAB_MAX_DEVICES] = {false};
   if (!attr_done[current_device()]) {
-    MAB_CUDA(cudaFuncSetAttribute(attention_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    MAB_CUDA(cudaFuncSetAttribute(attention_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   AttCfg<2>::SMEM_BYTES));
-    MAB_CUDA(cudaFuncSetAttribute(attention_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    MAB_CUDA(cudaFuncSetAttribute(attention_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  AttCfg<1>::SMEM_BYTES));
+    MAB_CUDA(cudaFuncSetAttribute(attention_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   AttCfg<1>::SMEM_BYTES));
     attr_done[current_device()] = true;
   }
   ProfScope ps(CAT_ATTENTION, 4.0 * q_len * (double)kv_len * 64.0 * heads * num_seqs, 0.0, st);
+  static const bool no_lean = getenv("MAB_NO_ATT_LEAN") != nullptr;
+  // one-tile kernel only: the lean instantiation is 2.5 % faster there (465 vs 453 TFLOP/s on 8x16x1037), while
+  // the same change costs the two-tile kernel its schedule (821 -> 724 TFLOP/s at 66 305 tokens)
+  const bool lean = !carry_in && !carry_out && !lse && !no_lean;
   // short sequences (frame / encoder attention: 9 K/V tiles): one Q tile per CTA, two CTAs per SM;
   // long ones (global attention): two Q tiles per CTA sharing every K/V tile in shared memory
   if (kv_len <= att_short_max()) {
     dim3 grid((q_len + ATT_BQ - 1) / ATT_BQ, heads, num_seqs);
-    MAB_CUDA(launch_pdl(attention_kernel<1>, grid, dim3(AttCfg<1>::THREADS), AttCfg<1>::SMEM_BYTES, st, 1, tQ,
-                        tKV, tKV, p));
+    MAB_CUDA(launch_pdl(lean ? attention_kernel<1, true> : attention_kernel<1, false>, grid, dim3(AttCfg<1>::THREADS),
+                        AttCfg<1>::SMEM_BYTES, st, 1, tQ, tKV, tKV, p));
     return 0;
   }
   dim3 grid((q_len + ATT_QT * ATT_BQ - 1) / (ATT_QT * ATT_BQ), heads, num_seqs);
-  MAB_CUDA(launch_pdl(attention_kernel<2>, grid, dim3(AttCfg<2>::THREADS), AttCfg<2>::SMEM_BYTES, st, 1, tQ,
+  MAB_CUDA(launch_pdl(attention_kernel<2, false>, grid, dim3(AttCfg<2>::THREADS), AttCfg<2>::SMEM_BYTES, st, 1, tQ,
                       tKV, tKV, p));
   MAB_CUDA(cudaGetLastError());
   return 0;
