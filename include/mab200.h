@@ -196,6 +196,21 @@ int mab_stage_heads(mab_handle* h, const mab_inputs* in, mab_outputs* out,
 int mab_stage_heads_range(mab_handle* h, const mab_inputs* in, mab_outputs* out, int view_lo,
                           int view_hi, void* stream);
 
+/* The view-sharded forward as ONE call (SURVEY.md 8(b) `mab_set_comm`, 8(e)): no reference counterpart
+ * (the reference has no multi-GPU inference; its only NCCL use is training, train_tools.py:362-403).
+ * mab_set_comm: `nccl_comm` is the caller's ncclComm_t over the `world` ranks that share the scene (rank r
+ * holds the r-th block of parallel.shard_table), `nccl_library` the path of the libnccl.so.2 that created it
+ * (resolved with dlopen: the library has no link-time NCCL dependency).  The communicator stays the
+ * caller's.  mab_forward_sharded = mab_stage_encode, then per block qkv / attention / finish with the K|V
+ * rows of the global layers exchanged by grouped ncclSend / ncclRecv on a stream the handle owns (every
+ * rank attends to its own block while the blocks travel, carried online softmax), the metric scale
+ * broadcast from rank 0, and (with_heads != 0) the heads.  kv_all: caller-owned scratch of
+ * mab_kv_gather_bytes(views_total, H, W) bytes (the scene's K|V rows, bf16). */
+int mab_set_comm(mab_handle* h, void* nccl_comm, int rank, int world, const char* nccl_library);
+size_t mab_kv_gather_bytes(mab_handle* h, int views_total, int H, int W);
+int mab_forward_sharded(mab_handle* h, const mab_inputs* in, int views_total, mab_outputs* out, void* workspace,
+                        size_t workspace_bytes, void* kv_all, size_t kv_all_bytes, int with_heads, void* stream);
+
 /* Launch accounting for bench.py: kernels launched by this library since load, and an optional
  * per-launch CUDA-event profiler (events recorded on the launch stream around every kernel). */
 enum { MAB_CAT_GEMM = 0, MAB_CAT_CONV3 = 1, MAB_CAT_CONV3_REGRESS = 2, MAB_CAT_ATTENTION = 3,

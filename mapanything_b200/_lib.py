@@ -67,6 +67,10 @@ SYMBOLS = {
     "mab_stage_aat_finish": (_i, [_vp, _i, _vp]),
     "mab_stage_scale_head": (_i, [_vp, _vp, _vp]),
     "mab_stage_heads": (_i, [_vp, C.POINTER(MabInputs), C.POINTER(MabOutputs), _vp, _vp]),
+    "mab_set_comm": (_i, [_vp, _vp, _i, _i, C.c_char_p]),
+    "mab_kv_gather_bytes": (C.c_size_t, [_vp, _i, _i, _i]),
+    "mab_forward_sharded": (_i, [_vp, C.POINTER(MabInputs), _i, C.POINTER(MabOutputs), _vp, C.c_size_t, _vp,
+                                 C.c_size_t, _i, _vp]),
     "mab_rays_from_intrinsics": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "mab_normalize_rays": (_i, [_vp, C.c_longlong, _vp, _vp]),
     "mab_depth_z_to_along_ray": (_i, [_vp, _vp, C.c_longlong, _vp, _vp]),

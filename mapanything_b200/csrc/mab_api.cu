@@ -2,6 +2,8 @@
 // MapAnything inference hot path.  Part 1: weight packing kernels and the per-kernel entry points.
 #include "../../include/mab200.h"
 
+#include <dlfcn.h>
+
 #include <map>
 #include <mutex>
 #include <vector>
@@ -688,7 +690,20 @@ struct mab_handle {
   std::map<std::string, float*> packed32;     // fp32 (TF32) GEMM / conv operands, padded layouts
   std::map<std::string, float*> extra;        // derived fp32 tensors (tiled biases)
   std::vector<void*> owned;
+  std::vector<std::string> packed_keys;        // raw tensors that only fed a pack_* kernel: freed by finalize
   std::vector<int> view_pe_rows;               // mab_set_view_pe_rows: one table row per view of the shard
+  // view-sharded forward inside the library (mab_set_comm / mab_forward_sharded): NCCL entry points resolved
+  // with dlopen from the library the caller names (no link-time dependency), the caller's communicator
+  struct Nccl {
+    void* lib = nullptr; void* comm = nullptr; int rank = 0, world = 1;
+    int (*GroupStart)() = nullptr; int (*GroupEnd)() = nullptr;
+    int (*Send)(const void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+  } nccl;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_kv_ready = nullptr, ev_kv_done = nullptr;
   cudaStream_t lane_stream = nullptr;          // second encoder lane (the first is the caller's stream)
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   Plan plan;
@@ -839,6 +854,10 @@ extern "C" int mab_destroy(mab_handle* h) {
   if (!h) return 0;
   for (auto& kv : h->raw) cudaFree(kv.second.p);
   for (void* p : h->owned) cudaFree(p);
+  if (h->comm_stream) cudaStreamDestroy(h->comm_stream);
+  if (h->ev_kv_ready) cudaEventDestroy(h->ev_kv_ready);
+  if (h->ev_kv_done) cudaEventDestroy(h->ev_kv_done);
+  if (h->nccl.lib) dlclose(h->nccl.lib);   // the communicator stays the caller's
   if (h->lane_stream) cudaStreamDestroy(h->lane_stream);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -896,6 +915,7 @@ int pack_linear(mab_handle* h, const std::string& key, int ld_pad, cudaStream_t 
   pack_matrix_kernel<bf16><<<ew_grid((long long)rows * ld), 256, 0, st>>>(t.p, rows, cols, ld, out);
   MAB_CUDA(cudaGetLastError());
   h->packed[key] = out;
+  h->packed_keys.push_back(key);
   return 0;
 }
 
@@ -911,6 +931,7 @@ int pack_linear_split(mab_handle* h, const std::string& key, cudaStream_t st) {
   pack_matrix_split_kernel<<<ew_grid((long long)rows * cols), 256, 0, st>>>(t.p, rows, cols, out);
   MAB_CUDA(cudaGetLastError());
   h->packed[key] = out;
+  h->packed_keys.push_back(key);
   return 0;
 }
 
@@ -926,6 +947,7 @@ int pack_conv3(mab_handle* h, const std::string& key, cudaStream_t st) {
   pack_conv3_kernel<bf16><<<ew_grid((long long)Cout * 9 * Cpad), 256, 0, st>>>(t.p, Cout, Cin, Cpad, out);
   MAB_CUDA(cudaGetLastError());
   h->packed[key] = out;
+  h->packed_keys.push_back(key);
   return 0;
 }
 
@@ -943,6 +965,7 @@ int pack_linear_f32(mab_handle* h, const std::string& key, int ld_pad, cudaStrea
   pack_matrix_kernel<float><<<ew_grid((long long)rows * ld), 256, 0, st>>>(t.p, rows, cols, ld, out);
   MAB_CUDA(cudaGetLastError());
   h->packed32[key] = out;
+  h->packed_keys.push_back(key);
   return 0;
 }
 int pack_conv3_f32(mab_handle* h, const std::string& key, int cpad, cudaStream_t st) {
@@ -956,6 +979,7 @@ int pack_conv3_f32(mab_handle* h, const std::string& key, int cpad, cudaStream_t
   pack_conv3_kernel<float><<<ew_grid((long long)Cout * 9 * cpad), 256, 0, st>>>(t.p, Cout, Cin, cpad, out);
   MAB_CUDA(cudaGetLastError());
   h->packed32[key] = out;
+  h->packed_keys.push_back(key);
   return 0;
 }
 
@@ -979,6 +1003,7 @@ int pack_convT(mab_handle* h, const std::string& wkey, const std::string& bkey, 
   MAB_CUDA(cudaGetLastError());
   if (f32) h->packed32[wkey] = (float*)out;
   else h->packed[wkey] = (bf16*)out;
+  h->packed_keys.push_back(wkey);
   h->extra[bkey + ".tiled"] = bt;
   return 0;
 }
@@ -1093,6 +1118,16 @@ extern "C" int mab_finalize_weights(mab_handle* h, void* stream) {
     h->extra["pose_head.fc7.bias"] = b7;
   }
   MAB_CUDA(cudaStreamSynchronize(st));  // one-time setup, not on the inference path
+  // the fp32 staging copies of every packed GEMM / conv operand are dead now (> 2 GB for the production
+  // model); biases, norms, LayerScale vectors, tokens, tables and the small fp32 heads stay (read through F())
+  for (const std::string& k : h->packed_keys) {
+    auto it = h->raw.find(k);
+    if (it != h->raw.end() && it->second.p) {
+      cudaFree(it->second.p);
+      it->second.p = nullptr;
+    }
+  }
+  h->packed_keys.clear();
   h->finalized = true;
   return 0;
 }
@@ -1920,6 +1955,113 @@ extern "C" int mab_forward(mab_handle* h, const mab_inputs* in, mab_outputs* out
     MAB_TRY(mab_stage_aat_finish(h, l, stream));
   }
   return mab_stage_heads(h, in, out, nullptr, stream);
+}
+
+// ---- view-sharded forward as ONE call: the K|V exchange of the global layers issued from here ----------
+#define MAB_NCCL(expr)                                                                          \
+  do {                                                                                          \
+    int _r = (expr);                                                                            \
+    if (_r != 0)                                                                                \
+      return ::mab::fail(1000 + _r, "%s failed: %s", #expr,                                     \
+                         h->nccl.GetErrorString ? h->nccl.GetErrorString(_r) : "NCCL error");  \
+  } while (0)
+
+extern "C" int mab_set_comm(mab_handle* h, void* nccl_comm, int rank, int world, const char* nccl_library) {
+  MAB_ARG(h && nccl_comm && nccl_library, "null argument");
+  MAB_ARG(world >= 1 && rank >= 0 && rank < world, "bad rank / world");
+  MAB_CUDA(cudaSetDevice(h->device));
+  mab_handle::Nccl& n = h->nccl;
+  if (!n.lib) {
+    n.lib = dlopen(nccl_library, RTLD_NOW | RTLD_GLOBAL);
+    if (!n.lib) return fail(-6, "dlopen(%s) failed: %s", nccl_library, dlerror());
+  }
+  auto sym = [&](const char* name) { return dlsym(n.lib, name); };
+  n.GroupStart = reinterpret_cast<decltype(n.GroupStart)>(sym("ncclGroupStart"));
+  n.GroupEnd = reinterpret_cast<decltype(n.GroupEnd)>(sym("ncclGroupEnd"));
+  n.Send = reinterpret_cast<decltype(n.Send)>(sym("ncclSend"));
+  n.Recv = reinterpret_cast<decltype(n.Recv)>(sym("ncclRecv"));
+  n.Broadcast = reinterpret_cast<decltype(n.Broadcast)>(sym("ncclBroadcast"));
+  n.GetErrorString = reinterpret_cast<decltype(n.GetErrorString)>(sym("ncclGetErrorString"));
+  if (!n.GroupStart || !n.GroupEnd || !n.Send || !n.Recv || !n.Broadcast)
+    return fail(-6, "%s does not export the NCCL point-to-point API", nccl_library);
+  n.comm = nccl_comm; n.rank = rank; n.world = world;
+  if (!h->comm_stream) {  // set-up time: the exchange stream and its two events
+    MAB_CUDA(cudaStreamCreateWithFlags(&h->comm_stream, cudaStreamNonBlocking));
+    MAB_CUDA(cudaEventCreateWithFlags(&h->ev_kv_ready, cudaEventDisableTiming));
+    MAB_CUDA(cudaEventCreateWithFlags(&h->ev_kv_done, cudaEventDisableTiming));
+  }
+  return 0;
+}
+
+extern "C" size_t mab_kv_gather_bytes(mab_handle* h, int views_total, int H, int W) {
+  if (!h || views_total <= 0 || H % h->cfg.patch || W % h->cfg.patch) return 0;
+  const size_t T = (size_t)(H / h->cfg.patch) * (W / h->cfg.patch);
+  return ((size_t)views_total * T + 1) * 2 * h->cfg.aat_dim * sizeof(bf16);
+}
+
+extern "C" int mab_forward_sharded(mab_handle* h, const mab_inputs* in, int views_total, mab_outputs* out,
+                                   void* workspace, size_t workspace_bytes, void* kv_all, size_t kv_all_bytes,
+                                   int with_heads, void* stream) {
+  MAB_ARG(h && in && out && kv_all, "null argument");
+  mab_handle::Nccl& n = h->nccl;
+  MAB_ARG(n.comm, "mab_set_comm must be called first");
+  MAB_ARG(views_total >= n.world && in->views > 0, "every rank needs a view");
+  cudaStream_t st = (cudaStream_t)stream;
+  // the shard table of mapanything_b200.parallel.shard_table: contiguous blocks, earlier ranks take the extra view
+  const int base = views_total / n.world, extra = views_total % n.world;
+  MAB_ARG(in->views == base + (n.rank < extra ? 1 : 0), "in->views does not match the shard table");
+  const size_t T = (size_t)(in->H / h->cfg.patch) * (in->W / h->cfg.patch);
+  const size_t row_bytes = 2 * (size_t)h->cfg.aat_dim * sizeof(bf16);
+  std::vector<size_t> offs(n.world + 1, 0);  // byte offsets of the ranks' K|V blocks in kv_all
+  for (int r = 0; r < n.world; ++r)
+    offs[r + 1] = offs[r] + ((size_t)(base + (r < extra ? 1 : 0)) * T + (r == 0 ? 1 : 0)) * row_bytes;
+  MAB_ARG(kv_all_bytes >= offs[n.world], "kv_all too small (mab_kv_gather_bytes)");
+  uint8_t* kv = reinterpret_cast<uint8_t*>(kv_all);
+
+  MAB_TRY(mab_stage_encode(h, in, views_total, workspace, workspace_bytes, n.rank == 0 ? 3 : 0, stream));
+  for (int l = 0; l < h->cfg.aat_depth; ++l) {
+    MAB_TRY(mab_stage_aat_qkv(h, l, nullptr, nullptr, stream));
+    if (global_layer(h->cfg, l) && n.world > 1) {
+      // every rank exports its K|V rows, posts sends to / receives from all peers in one group on the
+      // exchange stream, attends to its own block while the blocks travel, then to the remote rows in at
+      // most two contiguous spans (before / after its own block); the online-softmax state is carried
+      MAB_TRY(mab_stage_aat_export_kv(h, kv + offs[n.rank], stream));
+      MAB_CUDA(cudaEventRecord(h->ev_kv_ready, st));
+      MAB_CUDA(cudaStreamWaitEvent(h->comm_stream, h->ev_kv_ready, 0));
+      MAB_NCCL(n.GroupStart());
+      for (int d = 1; d < n.world; ++d) {
+        const int dst = (n.rank + d) % n.world, src = (n.rank - d + n.world) % n.world;
+        MAB_NCCL(n.Send(kv + offs[n.rank], offs[n.rank + 1] - offs[n.rank], 0 /* ncclInt8 */, dst, n.comm, h->comm_stream));
+        MAB_NCCL(n.Recv(kv + offs[src], offs[src + 1] - offs[src], 0, src, n.comm, h->comm_stream));
+      }
+      MAB_NCCL(n.GroupEnd());
+      MAB_CUDA(cudaEventRecord(h->ev_kv_done, h->comm_stream));
+      const bool before = offs[n.rank] > 0, after = offs[n.rank + 1] < offs[n.world];
+      MAB_TRY(mab_stage_aat_attend(h, l, nullptr, 0, MAB_RING_FIRST | ((before || after) ? 0 : MAB_RING_LAST), stream));
+      MAB_CUDA(cudaStreamWaitEvent(st, h->ev_kv_done, 0));
+      if (before)
+        MAB_TRY(mab_stage_aat_attend_kv(h, l, kv, (int)(offs[n.rank] / row_bytes), after ? 0 : MAB_RING_LAST, stream));
+      if (after)
+        MAB_TRY(mab_stage_aat_attend_kv(h, l, kv + offs[n.rank + 1],
+                                        (int)((offs[n.world] - offs[n.rank + 1]) / row_bytes), MAB_RING_LAST, stream));
+    } else {
+      MAB_TRY(mab_stage_aat_attend(h, l, nullptr, 0, MAB_RING_FIRST | MAB_RING_LAST, stream));
+    }
+    MAB_TRY(mab_stage_aat_finish(h, l, stream));
+  }
+  // metric scale: computed by the rank that owns the scale token, broadcast to the others
+  if (n.rank == 0) MAB_TRY(mab_stage_scale_head(h, out->metric_scale, stream));
+  if (n.world > 1) {
+    // the next layer's exchange must not start before this broadcast is queued behind the last one: same
+    // communicator, one stream at a time -- the broadcast rides the exchange stream as well
+    MAB_CUDA(cudaEventRecord(h->ev_kv_ready, st));
+    MAB_CUDA(cudaStreamWaitEvent(h->comm_stream, h->ev_kv_ready, 0));
+    MAB_NCCL(n.Broadcast(out->metric_scale, out->metric_scale, 1, 7 /* ncclFloat32 */, 0, n.comm, h->comm_stream));
+    MAB_CUDA(cudaEventRecord(h->ev_kv_done, h->comm_stream));
+    MAB_CUDA(cudaStreamWaitEvent(st, h->ev_kv_done, 0));
+  }
+  if (with_heads) return mab_stage_heads(h, in, out, out->metric_scale, stream);
+  return 0;
 }
 
 // workspace: views*H*W*18 + views*8 + 512 bytes

@@ -177,6 +177,7 @@ class MapAnything(torch.nn.Module):
         self._copy_stream = None
         self._ring_bufs = None
         self._kv_all = None
+        self._comm = None   # (ncclComm_t, rank, world) given to the library for the one-call sharded forward
         if pretrained_checkpoint_path is not None:
             ckpt = torch.load(pretrained_checkpoint_path, map_location="cpu", weights_only=False)
             self.load_state_dict(ckpt["model"] if "model" in ckpt else ckpt)
@@ -331,7 +332,7 @@ class MapAnything(torch.nn.Module):
             imgs[i].copy_(v["img"][0], non_blocking=True)
         return imgs, H, W
 
-    def _pack_geometry(self, views, flags, H, W, view_lo=0, total_views=None):
+    def _pack_geometry(self, views, flags, H, W, view_lo=0, total_views=None, default_metric=True):
         """a1 + the host part of a6: pre-process the optional geometric inputs of this rank's views
         (inference.py:222-311) into the stacked device buffers `mab_inputs` takes, with the per-view
         availability masks of model.py:1336-1369 made deterministic by `flags`
@@ -344,7 +345,9 @@ class MapAnything(torch.nn.Module):
             return None
         rays = torch.zeros((V, H, W, 3), dtype=torch.float32, device=dev)
         depth = torch.zeros((V, H, W), dtype=torch.float32, device=dev)
-        has_ray, has_depth, has_cam, metric = [0] * V, [0] * V, [0] * V, [1] * V
+        # is_metric_scale: infer()'s pre-processing defaults it to True (inference.py:298-306); the raw
+        # forward() uses zeros when the key is absent (model.py:1044-1053)
+        has_ray, has_depth, has_cam, metric = [0] * V, [0] * V, [0] * V, [int(default_metric)] * V
         quats, trans = [None] * V, [None] * V
         npix = H * W
         with torch.cuda.device(dev):
@@ -557,6 +560,20 @@ class MapAnything(torch.nn.Module):
         if mode == "gather" and (self._kv_all is None or self._kv_all.shape[0] != sum(rows)):
             self._kv_all = torch.empty((sum(rows), 2 * self._cfg.aat_dim), dtype=torch.bfloat16,
                                        device=self._device)
+        if mode == "gather" and os.environ.get("MAB_EXCHANGE_HOST", "0") != "1":
+            # default: the whole sharded forward is ONE library call (mab_forward_sharded): the K|V exchange
+            # of the global layers is issued by the library on its own stream through an NCCL communicator
+            # created once for the ranks of the default group (MAB_EXCHANGE_HOST=1: the per-layer exchange
+            # sequenced from here through torch.distributed, the round-1 path)
+            if self._comm is None:
+                from . import nccl_comm
+                comm, r, w, path = nccl_comm.create(self._device)
+                _lib.check(lib.mab_set_comm(hd, comm, r, w, path.encode()), "mab_set_comm")
+                self._comm = (comm, r, w)
+            _lib.check(lib.mab_forward_sharded(hd, C.byref(inp), total, C.byref(ost), ws.data_ptr(), ws.numel(),
+                                               self._kv_all.data_ptr(), self._kv_all.numel() * 2, int(heads),
+                                               self._stream_ptr()), "mab_forward_sharded")
+            return
         if mode == "ring" and (self._ring_bufs is None or self._ring_bufs[0].shape[0] < max(rows)):
             self._ring_bufs = [torch.empty((max(rows), width), dtype=torch.bfloat16, device=self._device)
                                for _ in range(2)]
@@ -771,7 +788,10 @@ class MapAnything(torch.nn.Module):
             return [{k: torch.cat([per_scene[b][i][k] for b in range(B)], 0) for k in per_scene[0][i]}
                     for i in range(len(views))]
         imgs, H, W = self._pack_images(views)
-        geo = self._pack_geometry(views, dict(_ALL_INPUTS), H, W)
+        # the reference's forward() draws the per-sample input masks from geometric_input_config's
+        # probabilities (model.py:1305-1373); here every geometric input that is present is used, which is
+        # what infer() configures (model.py:2170-2197) -- training-time input dropout is out of scope
+        geo = self._pack_geometry(views, dict(_ALL_INPUTS), H, W, default_metric=False)
         outs = self._run_forward(imgs, H, W, geo=geo)
         return self._raw_dicts(outs, len(views))
 

@@ -118,7 +118,7 @@ SELF_CHECK_KEYS = ("pts3d", "pts3d_cam", "ray_directions", "depth_along_ray", "c
                    "cam_trans", "cam_quats", "metric_scaling_factor", "intrinsics")
 
 
-def sharded_vs_single(model, views, exchange=("gather", "ring"), infer_kwargs=None, group=None):
+def sharded_vs_single(model, views, exchange=("gather", "gather_host", "ring"), infer_kwargs=None, group=None):
     """Self-check of the view-sharded path on the GPUs of this job: every rank runs `views` (the WHOLE
     scene, a list of view dicts, identical on every rank) once on its own GPU and once view-sharded over
     the process group, per exchange schedule, and compares its shard of the sharded result with the
@@ -139,8 +139,12 @@ def sharded_vs_single(model, views, exchange=("gather", "ring"), infer_kwargs=No
     per_key, agree = {}, 1.0
     saved = os.environ.get("MAB_EXCHANGE")
     try:
+        saved_host = os.environ.get("MAB_EXCHANGE_HOST")
         for mode in exchange:
-            os.environ["MAB_EXCHANGE"] = mode
+            # "gather": the library's one-call sharded forward (mab_forward_sharded, NCCL issued in C);
+            # "gather_host" / "ring": the per-layer exchange sequenced from Python through torch.distributed
+            os.environ["MAB_EXCHANGE"] = "gather" if mode == "gather_host" else mode
+            os.environ["MAB_EXCHANGE_HOST"] = "1" if mode == "gather_host" else "0"
             mine = model.infer([dict(v) for v in views[lo:hi]], view_range=(lo, hi), total_views=n, **kw)
             for p, r in zip(mine, full[lo:hi]):
                 both = (p["mask"] & r["mask"]).double() if "mask" in p else None
@@ -153,10 +157,11 @@ def sharded_vs_single(model, views, exchange=("gather", "ring"), infer_kwargs=No
                 if "mask" in p:
                     agree = min(agree, float((p["mask"] == r["mask"]).float().mean()))
     finally:
-        if saved is None:
-            os.environ.pop("MAB_EXCHANGE", None)
-        else:
-            os.environ["MAB_EXCHANGE"] = saved
+        for name, val in (("MAB_EXCHANGE", saved), ("MAB_EXCHANGE_HOST", saved_host)):
+            if val is None:
+                os.environ.pop(name, None)
+            else:
+                os.environ[name] = val
     dev = full[0]["pts3d"].device
     t = torch.tensor([per_key[k] for k in SELF_CHECK_KEYS] + [-agree], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
