@@ -2,6 +2,7 @@
 declares (no compute call), and the host-side validation logic mirrors the reference."""
 import os
 import re
+import subprocess
 
 import pytest
 import torch
@@ -299,3 +300,34 @@ def test_production_config_is_accepted_and_other_heads_are_refused():
                         (("encoder_config", "data_norm_type"), "dust3r")):
         with pytest.raises(NotImplementedError):
             MapAnything(**variant(path, value))
+
+
+def test_nccl_library_is_found_and_exports_the_p2p_api():
+    """mab_set_comm resolves NCCL with dlopen from the path mapanything_b200.nccl_comm names: the library
+    torch ships must be there and export the calls mab_forward_sharded issues (no communicator is made)."""
+    import ctypes
+
+    from mapanything_b200 import nccl_comm
+
+    path = nccl_comm.nccl_library_path()
+    assert os.path.exists(path), path
+    lib = ctypes.CDLL(path)
+    for name in ("ncclGetUniqueId", "ncclCommInitRank", "ncclGroupStart", "ncclGroupEnd", "ncclSend", "ncclRecv",
+                 "ncclBroadcast", "ncclGetErrorString"):
+        assert hasattr(lib, name), name
+    assert ctypes.sizeof(nccl_comm._UniqueId) == 128
+
+
+def test_reference_tree_for_the_bench_legs():
+    """oracle/make_ref.py: where /root/reference is mounted the two packages are copied into the git-ignored
+    oracle/_ref/ (what travels to the GPU box); ref_root() names a tree that holds both packages."""
+    from oracle import make_ref
+
+    if not os.path.isdir("/root/reference/mapanything"):
+        pytest.skip("no reference mount here")
+    dst = make_ref.make()
+    assert dst and all(os.path.isdir(os.path.join(dst, p)) for p in make_ref.PACKAGES)
+    root = make_ref.ref_root()
+    assert root and os.path.isfile(os.path.join(root, "mapanything", "models", "mapanything", "model.py"))
+    tracked = subprocess.run(["git", "ls-files", "oracle/_ref"], capture_output=True, text=True, cwd=ROOT).stdout
+    assert tracked.strip() == "", "oracle/_ref must stay out of history"
