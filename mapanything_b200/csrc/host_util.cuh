@@ -303,7 +303,9 @@ inline int launch_conv3(const void* x, int batch, int H, int W, int C, const voi
   GemmShape shp{0, Cout, 9 * cblocks * 64, batch, H, W, cblocks, C};
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, C));
-  if (Cout > 128) {
+  const int m_pairs = (batch * ((W + CONV_TW - 1) / CONV_TW) * ((H + CONV_TH - 1) / CONV_TH) + GEMM_CL - 1) / GEMM_CL;
+  const bool narrow = m_pairs * ((Cout + 255) / 256) * 2 <= sm_count() / GEMM_CL;  // see launch_conv3_tf32
+  if (Cout > 128 && !narrow) {
     MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 64, 9LL * cblocks * 64, 256 / GEMM_CL));
     return launch_gemm_t<256, 6, MODE_CONV3, EPI_GENERIC, GEMM_CL>(tA, tB, shp, ep, rg, st);
   }
@@ -335,7 +337,11 @@ inline int launch_conv3_tf32(const float* x, int batch, int H, int W, int C, int
   GemmShape shp{0, Cout, 9 * cblocks * 32, batch, H, W, cblocks, Creal};
   RegressEpilogue rg{};
   MAB_TRY(make_tmap_nhwc(&tA, x, batch, H, W, C, true));
-  if (Cout <= 128) {
+  // small feature maps (28x37 and 14x19 levels of the DPT head at 8 views): 256-wide tiles would occupy
+  // fewer than half of the 74 clusters for the whole K loop; 128-wide tiles double the clusters at work
+  const int m_pairs = (batch * ((W + CONV_TW - 1) / CONV_TW) * ((H + CONV_TH - 1) / CONV_TH) + GEMM_CL - 1) / GEMM_CL;
+  const bool narrow = m_pairs * ((Cout + 255) / 256) * 2 <= sm_count() / GEMM_CL;
+  if (Cout <= 128 || narrow) {
     MAB_TRY(make_tmap_2d(&tB, w, Cout, 9LL * cblocks * 32, 9LL * cblocks * 32, 128 / GEMM_CL, true));
     return launch_gemm_t<128, 8, MODE_CONV3, EPI_GENERIC, GEMM_CL, 1>(tA, tB, shp, ep, rg, st);
   }
@@ -441,7 +447,15 @@ inline int launch_layernorm(const float* x, int rows_out, int C, int group_out, 
   const double bytes = (double)rows_out * C * (4.0 + (out_bf16 ? 2.0 : 0.0) + (out_f32 ? 4.0 : 0.0) +
                                                (out_mid ? 4.0 : 0.0) + (out_split ? 6.0 : 0.0));
   ProfScope ps(CAT_LAYERNORM, 0.0, bytes, st);
-  if (C == 768)
+  static const bool no_lean = getenv("MAB_NO_LN_LEAN") != nullptr;
+  const bool lean = ob && !out_f32 && !out_mid && !os && !w2 && group_out == group_in && skip == 0 && !no_lean;
+  if (lean && C == 768)
+    MAB_CUDA(launch_pdl(layernorm_kernel<6, true>, dim3(grid), dim3(block), 0, st, 1, x, rows_out, group_out,
+                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os, round_f32));
+  else if (lean && C == 1024)
+    MAB_CUDA(launch_pdl(layernorm_kernel<8, true>, dim3(grid), dim3(block), 0, st, 1, x, rows_out, group_out,
+                        group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os, round_f32));
+  else if (C == 768)
     MAB_CUDA(launch_pdl(layernorm_kernel<6>, dim3(grid), dim3(block), 0, st, 1, x, rows_out, group_out,
                         group_in, skip, w, b, w2, b2, eps, ob, out_f32, out_mid, os, round_f32));
   else if (C == 1024)
