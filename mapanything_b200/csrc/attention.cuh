@@ -40,15 +40,18 @@ constexpr int ATT_KV_STAGES = 4;
 #define ATT_TURN_LATE 1   // 1: the softmax turn barrier sits after the row max (0: before it)
 #endif
 // Which of the 16 element pairs of every 32 S columns take their exponentials from a polynomial on
-// the FMA pipe instead of the MUFU (bit k = pair k).  The exp pass is bound by the SM's 16 MUFU lanes;
-// measured (profiles/attn_variants.sh, 66 305 tokens): none 690, 4 adjacent pairs 812, 5 spread pairs
-// (0x1249) 836 TFLOP/s, 6 and more slower again (one warp per scheduler issues the whole pass, so the
-// extra FMA-pipe instructions must fit between its MUFU issues).
+// the FMA pipe instead of the MUFU (bit k = pair k).  Round 1 (one thread per row, exp-pass turns) was bound by
+// the SM's 16 MUFU lanes and gained 20 % from 5 spread pairs (0x1249).  With two threads per row and no turns
+// the kernels are bound by the TMEM read port instead (64 B/clk/SM) and the share no
+// longer matters: none / 2 / 5 of 16 pairs = 817.9 / 818.4 / 815.9 TFLOP/s at 66 305 tokens, 441 / 436 / 405 on
+// 8x16x1037 (profiles/r2_attn_variants.txt).  Default: none -- every exponential is the MUFU's ex2.approx,
+// fewer instructions per element (what counts under the 1000 W cap of the many-view regime), one
+// approximation less; the polynomial path stays selectable for experiments.
 #ifndef ATT_POLY_MASK
-#define ATT_POLY_MASK 0x1249   // long sequences (two Q tiles per CTA)
+#define ATT_POLY_MASK 0        // long sequences (two Q tiles per CTA)
 #endif
 #ifndef ATT_POLY_MASK_SHORT
-#define ATT_POLY_MASK_SHORT 0x0101   // short sequences (one Q tile per CTA, two CTAs per SM)
+#define ATT_POLY_MASK_SHORT 0  // short sequences (one Q tile per CTA, two CTAs per SM)
 #endif
 #ifndef ATT_NO_TURNS
 #define ATT_NO_TURNS 1   // measured with two threads per row (66 305 tokens): turns 686, no turns 816 TFLOP/s
