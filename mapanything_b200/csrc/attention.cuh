@@ -53,9 +53,6 @@ constexpr int ATT_KV_STAGES = 4;
 #ifndef ATT_POLY_MASK_SHORT
 #define ATT_POLY_MASK_SHORT 0  // short sequences (one Q tile per CTA, two CTAs per SM)
 #endif
-#ifndef ATT_PIPE
-#define ATT_PIPE 0   // two-tile kernel: S(j+1) is read from TMEM under the exponentials / P store of tile j
-#endif
 #ifndef ATT_NO_TURNS
 #define ATT_NO_TURNS 1   // measured with two threads per row (66 305 tokens): turns 686, no turns 816 TFLOP/s
 #endif
@@ -488,117 +485,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         l_run = fmaf(l_run, alpha, row_sum);
         m_ref = m_new;
       };
-      if constexpr (QT == 2 && ATT_PIPE && SPLIT == 2) {
-        // Long sequences, software-pipelined over the K/V tiles.  The loop is bound by the TMEM read port
-        // (64 B/clk/SM: a 128x128 fp32 S tile is 1024 clk of reads against 512 clk of tensor work), and a
-        // warp that loads its whole S row and only then computes leaves the port idle while it computes.
-        // Here the thread's 64 columns are two halves a | b: S_a(j+1) is read while the exponentials of
-        // b(j) run, S_b(j+1) while P(j) is stored and the row sums are folded.
-        uint32_t va[32], vb[32];
-        auto mask_half = [&](uint32_t* v, int valid_h) {  // columns >= valid_h of this half are padding
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (i >= valid_h) v[i] = 0xff800000u;
-        };
-        auto exp_half = [&](const uint32_t* v, uint32_t* pk, uint64_t sc2_, uint64_t nmb2_, uint64_t& sa, uint64_t& sb) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float x0, x1;
-            unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])), sc2_, nmb2_), x0, x1);
-            const float e0 = fast_exp2(x0), e1 = fast_exp2(x1);
-            if (i & 2) sb = add_f2(sb, pack_f2(e0, e1));
-            else sa = add_f2(sa, pack_f2(e0, e1));
-            pk[i >> 1] = cvt_bf16x2(e0, e1);
-          }
-        };
-        // prologue: S(0)
-        mbar_wait(&s_full[t], 0);
-        tc_fence_after();
-        MAB_TMEM_LD_32(ts, va);
-        MAB_TMEM_LD_32(ts + 32, vb);
-        tmem_wait_ld();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&s_free[t]);
-        for (int j = 0; j < nkv; ++j) {
-          const int valid = p.kv_len - j * ATT_BKV - hf * NC;
-          if (valid < NC) { mask_half(va, valid); mask_half(vb, valid - 32); }
-          // ---- row max of S(j), exchanged with the other half of the row ----
-          float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-#pragma unroll
-          for (int i = 0; i < 32; i += 8) {
-            mx0 = max3(mx0, __uint_as_float(va[i]), __uint_as_float(va[i + 1]));
-            mx1 = max3(mx1, __uint_as_float(va[i + 2]), __uint_as_float(va[i + 3]));
-            mx2 = max3(mx2, __uint_as_float(va[i + 4]), __uint_as_float(va[i + 5]));
-            mx3 = max3(mx3, __uint_as_float(va[i + 6]), __uint_as_float(va[i + 7]));
-            mx0 = max3(mx0, __uint_as_float(vb[i]), __uint_as_float(vb[i + 1]));
-            mx1 = max3(mx1, __uint_as_float(vb[i + 2]), __uint_as_float(vb[i + 3]));
-            mx2 = max3(mx2, __uint_as_float(vb[i + 4]), __uint_as_float(vb[i + 5]));
-            mx3 = max3(mx3, __uint_as_float(vb[i + 6]), __uint_as_float(vb[i + 7]));
-          }
-          float mx = fmaxf(max3(mx0, mx1, mx2), mx3);
-          *xslot(j & 1, hf) = mx;
-          bar_sync_named(pair_bar, 64);
-          mx = fmaxf(mx, *xslot(j & 1, hf ^ 1));
-          const bool grow_ref = (mx - m_ref) * sc > 8.0f;  // true on the first tile (m_ref = -inf)
-          const float m_new = grow_ref ? mx : m_ref;
-          const float alpha = grow_ref ? fast_exp2((m_ref - m_new) * sc) : 1.0f;
-          const bool rescale = __any_sync(0xffffffffu, grow_ref) && (j > 0 || p.carry_in);
-          const float nmb = -m_new * sc;
-          const uint64_t nmb2 = pack_f2(nmb, nmb);
-          uint64_t sum_a = pack_f2(0.f, 0.f), sum_b = sum_a;
-          const bool next = j + 1 < nkv;
-          // ---- half a: exponentials, then P_a(j) out (P_t and O_t are free once P_t(j-1) V has completed) ----
-          uint32_t pk[16];
-          exp_half(va, pk, sc2, nmb2, sum_a, sum_b);
-          if (j > 0) {
-            mbar_wait(&pv_done[t], (j - 1) & 1);
-            tc_fence_after();
-          }
-          if (rescale) {  // warp-uniform; rows that keep their reference multiply by 1
-            const uint64_t a2 = pack_f2(alpha, alpha);
-            uint32_t o[32];
-            MAB_TMEM_LD_32(to, o);
-            tmem_wait_ld();
-#pragma unroll
-            for (int d = 0; d < 32; d += 2) {
-              float y0, y1;
-              unpack_f2(fma_f2(pack_f2(__uint_as_float(o[d]), __uint_as_float(o[d + 1])), a2, pack_f2(0.f, 0.f)), y0, y1);
-              o[d] = __float_as_uint(y0); o[d + 1] = __float_as_uint(y1);
-            }
-            MAB_TMEM_ST_16(to, o);
-            MAB_TMEM_ST_16(to + 16, (o + 16));
-          }
-          MAB_TMEM_ST_16(tp, pk);
-          // ---- S_a(j+1) travels under the exponentials of half b ----
-          if (next) {
-            mbar_wait(&s_full[t], (j + 1) & 1);
-            tc_fence_after();
-            MAB_TMEM_LD_32(ts, va);
-          }
-          exp_half(vb, pk, sc2, nmb2, sum_a, sum_b);
-          MAB_TMEM_ST_16(tp + 16, pk);
-          if (next) {
-            tmem_wait_ld();            // S_a(j+1) is in registers
-            MAB_TMEM_LD_32(ts + 32, vb);  // S_b(j+1) travels under the store of P(j)
-          }
-          float s0, s1;
-          unpack_f2(add_f2(sum_a, sum_b), s0, s1);
-          const float row_sum = s0 + s1;
-          tmem_wait_st();
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&p_full[t]);
-          l_run = fmaf(l_run, alpha, row_sum);
-          m_ref = m_new;
-          if (next) {
-            tmem_wait_ld();            // S_b(j+1) is in registers: S_t may be overwritten by Q K^T(j+2)
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&s_free[t]);
-          }
-        }
-      } else if constexpr (QT == 2) {
+      if constexpr (QT == 2) {
         // long sequences: one instantiation, the (single) partial tile is masked at run time and goes
         // through the common pass -- a second copy of the body costs the hot loop its schedule
         // (measured 836 -> 740 TFLOP/s at 66 305 tokens)
