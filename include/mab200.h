@@ -292,6 +292,8 @@ typedef struct {
 } mab_image_plan;
 int mab_image_plan_make(int in_w, int in_h, int target_w, int target_h, mab_image_plan* plan);
 size_t mab_preprocess_workspace_bytes(const mab_image_plan* plan);
+/* The resampling coefficient tables of a plan are computed at its first use and kept in pinned host memory
+ * (one cudaHostAlloc per distinct plan), so every call is one asynchronous table upload + two kernels. */
 int mab_preprocess_image(const unsigned char* rgb, const mab_image_plan* plan, const float* mean_host,
                          const float* std_host, float* out, unsigned char* out_u8, void* workspace,
                          size_t workspace_bytes, void* stream);

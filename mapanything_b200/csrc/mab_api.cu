@@ -418,37 +418,58 @@ extern "C" int mab_preprocess_image(const unsigned char* rgb, const mab_image_pl
           p->crop_top + p->out_h <= p->resize_h, "crop outside the resized image");
   MAB_ARG(workspace_bytes >= mab_preprocess_workspace_bytes(p), "workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
-  std::vector<int> hb, hk, vb, vk;
-  // a pass is skipped when that dimension is unchanged (ImagingResample need_horizontal / need_vertical)
+  // The coefficient tables depend on the plan only: computed once per plan and kept in PINNED host memory
+  // (one cudaHostAlloc per distinct plan, at its first use), so that the uploads below are truly
+  // asynchronous on the caller's stream -- copies from pageable vectors stage synchronously.
+  struct Tables { int* pinned = nullptr; size_t nhb = 0, nhk = 0, nvb = 0, nvk = 0; int hks = 0, vks = 0, y0 = 0, y1 = 0; };
+  static std::map<std::vector<int>, Tables> cache;
+  static std::mutex cache_mu;
   const bool need_h = p->resize_w != p->in_w, need_v = p->resize_h != p->in_h;
-  int hks = 0, vks = 0;
-  if (need_h) hks = img_coeffs(p->in_w, p->resize_w, p->filter, p->crop_left, p->out_w, &hb, &hk);
-  else {  // identity taps: one coefficient of 1.0 per column
-    hks = 1; hb.resize((size_t)p->out_w * 2); hk.assign(p->out_w, 1 << IMG_PRECISION_BITS);
-    for (int x = 0; x < p->out_w; ++x) { hb[2 * x] = p->crop_left + x; hb[2 * x + 1] = 1; }
-  }
-  int y0 = p->crop_top, y1 = p->crop_top + p->out_h;  // source rows the vertical pass reads
-  if (need_v) {
-    vks = img_coeffs(p->in_h, p->resize_h, p->filter, p->crop_top, p->out_h, &vb, &vk);
-    y0 = vb[0]; y1 = vb[2 * (p->out_h - 1)] + vb[2 * (p->out_h - 1) + 1];
-    for (int y = 0; y < p->out_h; ++y) {  // bounds are monotone, but do not rely on it
-      if (vb[2 * y] < y0) y0 = vb[2 * y];
-      if (vb[2 * y] + vb[2 * y + 1] > y1) y1 = vb[2 * y] + vb[2 * y + 1];
+  Tables tb;
+  {
+    std::lock_guard<std::mutex> lock(cache_mu);
+    const std::vector<int> key = {p->in_w, p->in_h, p->resize_w, p->resize_h, p->filter, p->crop_left, p->crop_top,
+                                  p->out_w, p->out_h};
+    auto it = cache.find(key);
+    if (it == cache.end()) {
+      std::vector<int> hb, hk, vb, vk;
+      Tables t;
+      // a pass is skipped when that dimension is unchanged (ImagingResample need_horizontal / need_vertical)
+      if (need_h) t.hks = img_coeffs(p->in_w, p->resize_w, p->filter, p->crop_left, p->out_w, &hb, &hk);
+      else {  // identity taps: one coefficient of 1.0 per column
+        t.hks = 1; hb.resize((size_t)p->out_w * 2); hk.assign(p->out_w, 1 << IMG_PRECISION_BITS);
+        for (int x = 0; x < p->out_w; ++x) { hb[2 * x] = p->crop_left + x; hb[2 * x + 1] = 1; }
+      }
+      t.y0 = p->crop_top; t.y1 = p->crop_top + p->out_h;  // source rows the vertical pass reads
+      if (need_v) {
+        t.vks = img_coeffs(p->in_h, p->resize_h, p->filter, p->crop_top, p->out_h, &vb, &vk);
+        t.y0 = vb[0]; t.y1 = vb[2 * (p->out_h - 1)] + vb[2 * (p->out_h - 1) + 1];
+        for (int y = 0; y < p->out_h; ++y) {  // bounds are monotone, but do not rely on it
+          if (vb[2 * y] < t.y0) t.y0 = vb[2 * y];
+          if (vb[2 * y] + vb[2 * y + 1] > t.y1) t.y1 = vb[2 * y] + vb[2 * y + 1];
+        }
+      }
+      t.nhb = hb.size(); t.nhk = hk.size(); t.nvb = vb.size(); t.nvk = vk.size();
+      const size_t total = t.nhb + t.nhk + t.nvb + t.nvk;
+      MAB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&t.pinned), (total > 0 ? total : 1) * sizeof(int), cudaHostAllocPortable));
+      int* q = t.pinned;
+      memcpy(q, hb.data(), t.nhb * sizeof(int)); q += t.nhb;
+      memcpy(q, hk.data(), t.nhk * sizeof(int)); q += t.nhk;
+      memcpy(q, vb.data(), t.nvb * sizeof(int)); q += t.nvb;
+      memcpy(q, vk.data(), t.nvk * sizeof(int));
+      it = cache.emplace(key, t).first;
     }
+    tb = it->second;
   }
-  const int rows = y1 - y0;
+  const int hks = tb.hks, vks = tb.vks, y0 = tb.y0, rows = tb.y1 - tb.y0;
   uint8_t* w8 = reinterpret_cast<uint8_t*>(workspace);
   int* d_hb = reinterpret_cast<int*>(w8);
-  int* d_hk = d_hb + hb.size();
-  int* d_vb = d_hk + hk.size();
-  int* d_vk = d_vb + vb.size();
-  unsigned char* tmp = reinterpret_cast<unsigned char*>(d_vk + vk.size());
-  MAB_CUDA(cudaMemcpyAsync(d_hb, hb.data(), hb.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-  MAB_CUDA(cudaMemcpyAsync(d_hk, hk.data(), hk.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-  if (need_v) {
-    MAB_CUDA(cudaMemcpyAsync(d_vb, vb.data(), vb.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-    MAB_CUDA(cudaMemcpyAsync(d_vk, vk.data(), vk.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-  }
+  int* d_hk = d_hb + tb.nhb;
+  int* d_vb = d_hk + tb.nhk;
+  int* d_vk = d_vb + tb.nvb;
+  unsigned char* tmp = reinterpret_cast<unsigned char*>(d_vk + tb.nvk);
+  // one upload: hb | hk | vb | vk are contiguous on both sides
+  MAB_CUDA(cudaMemcpyAsync(d_hb, tb.pinned, (tb.nhb + tb.nhk + tb.nvb + tb.nvk) * sizeof(int), cudaMemcpyHostToDevice, st));
   const double in_bytes = (double)rows * p->in_w * 3, tmp_bytes = (double)rows * p->out_w * 3;
   dim3 gh((p->out_w + 127) / 128, rows), gv((p->out_w + 127) / 128, p->out_h);
   MAB_LAUNCH(CAT_ELEMENTWISE, 0.0, in_bytes + tmp_bytes, st,
