@@ -724,7 +724,7 @@ struct mab_handle {
     const char* (*GetErrorString)(int) = nullptr;
   } nccl;
   cudaStream_t comm_stream = nullptr;
-  cudaEvent_t ev_kv_ready = nullptr, ev_kv_done = nullptr;
+  cudaEvent_t ev_kv_ready = nullptr, ev_kv_done = nullptr, ev_kv_far = nullptr;
   cudaStream_t lane_stream = nullptr;          // second encoder lane (the first is the caller's stream)
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   Plan plan;
@@ -878,6 +878,7 @@ extern "C" int mab_destroy(mab_handle* h) {
   if (h->comm_stream) cudaStreamDestroy(h->comm_stream);
   if (h->ev_kv_ready) cudaEventDestroy(h->ev_kv_ready);
   if (h->ev_kv_done) cudaEventDestroy(h->ev_kv_done);
+  if (h->ev_kv_far) cudaEventDestroy(h->ev_kv_far);
   if (h->nccl.lib) dlclose(h->nccl.lib);   // the communicator stays the caller's
   if (h->lane_stream) cudaStreamDestroy(h->lane_stream);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
@@ -2010,6 +2011,7 @@ extern "C" int mab_set_comm(mab_handle* h, void* nccl_comm, int rank, int world,
     MAB_CUDA(cudaStreamCreateWithFlags(&h->comm_stream, cudaStreamNonBlocking));
     MAB_CUDA(cudaEventCreateWithFlags(&h->ev_kv_ready, cudaEventDisableTiming));
     MAB_CUDA(cudaEventCreateWithFlags(&h->ev_kv_done, cudaEventDisableTiming));
+    MAB_CUDA(cudaEventCreateWithFlags(&h->ev_kv_far, cudaEventDisableTiming));
   }
   return 0;
 }
@@ -2043,28 +2045,54 @@ extern "C" int mab_forward_sharded(mab_handle* h, const mab_inputs* in, int view
   for (int l = 0; l < h->cfg.aat_depth; ++l) {
     MAB_TRY(mab_stage_aat_qkv(h, l, nullptr, nullptr, stream));
     if (global_layer(h->cfg, l) && n.world > 1) {
-      // every rank exports its K|V rows, posts sends to / receives from all peers in one group on the
+      // Every rank exports its K|V rows, posts sends to / receives from all peers in ONE NCCL group on the
       // exchange stream, attends to its own block while the blocks travel, then to the remote rows in at
-      // most two contiguous spans (before / after its own block); the online-softmax state is carried
+      // most two contiguous spans (before / after its own block); the online-softmax state is carried.
+      // MAB_EXCHANGE_GROUPS=2 splits the exchange into a near group (ranks within world / 4) and a far group
+      // and attends to the near blocks while the far ones travel (up to four remote spans): measured at 4 GPUs,
+      // 32 views, 33.5 ms against 33.2 ms with one group -- the extra attention launches cost what the earlier
+      // start buys, so one group is the default.
+      static const bool one_group = !(getenv("MAB_EXCHANGE_GROUPS") && atoi(getenv("MAB_EXCHANGE_GROUPS")) == 2);
+      const int reach = one_group ? n.world : (n.world / 4 > 1 ? n.world / 4 : 1);
+      const int near_lo = n.rank - reach < 0 ? 0 : n.rank - reach;
+      const int near_hi = n.rank + reach > n.world - 1 ? n.world - 1 : n.rank + reach;  // inclusive
       MAB_TRY(mab_stage_aat_export_kv(h, kv + offs[n.rank], stream));
       MAB_CUDA(cudaEventRecord(h->ev_kv_ready, st));
       MAB_CUDA(cudaStreamWaitEvent(h->comm_stream, h->ev_kv_ready, 0));
-      MAB_NCCL(n.GroupStart());
-      for (int d = 1; d < n.world; ++d) {
-        const int dst = (n.rank + d) % n.world, src = (n.rank - d + n.world) % n.world;
-        MAB_NCCL(n.Send(kv + offs[n.rank], offs[n.rank + 1] - offs[n.rank], 0 /* ncclInt8 */, dst, n.comm, h->comm_stream));
-        MAB_NCCL(n.Recv(kv + offs[src], offs[src + 1] - offs[src], 0, src, n.comm, h->comm_stream));
-      }
-      MAB_NCCL(n.GroupEnd());
+      auto exchange = [&](int lo, int hi, bool inside) -> int {  // peers in [lo, hi] (inside) or outside it
+        bool any = false;
+        for (int r = 0; r < n.world; ++r) any |= r != n.rank && ((r >= lo && r <= hi) == inside);
+        if (!any) return 0;
+        MAB_NCCL(n.GroupStart());
+        for (int r = 0; r < n.world; ++r) {
+          if (r == n.rank || ((r >= lo && r <= hi) != inside)) continue;
+          MAB_NCCL(n.Send(kv + offs[n.rank], offs[n.rank + 1] - offs[n.rank], 0 /* ncclInt8 */, r, n.comm, h->comm_stream));
+          MAB_NCCL(n.Recv(kv + offs[r], offs[r + 1] - offs[r], 0, r, n.comm, h->comm_stream));
+        }
+        MAB_NCCL(n.GroupEnd());
+        return 0;
+      };
+      MAB_TRY(exchange(near_lo, near_hi, true));
       MAB_CUDA(cudaEventRecord(h->ev_kv_done, h->comm_stream));
-      const bool before = offs[n.rank] > 0, after = offs[n.rank + 1] < offs[n.world];
-      MAB_TRY(mab_stage_aat_attend(h, l, nullptr, 0, MAB_RING_FIRST | ((before || after) ? 0 : MAB_RING_LAST), stream));
-      MAB_CUDA(cudaStreamWaitEvent(st, h->ev_kv_done, 0));
-      if (before)
-        MAB_TRY(mab_stage_aat_attend_kv(h, l, kv, (int)(offs[n.rank] / row_bytes), after ? 0 : MAB_RING_LAST, stream));
-      if (after)
-        MAB_TRY(mab_stage_aat_attend_kv(h, l, kv + offs[n.rank + 1],
-                                        (int)((offs[n.world] - offs[n.rank + 1]) / row_bytes), MAB_RING_LAST, stream));
+      MAB_TRY(exchange(near_lo, near_hi, false));
+      MAB_CUDA(cudaEventRecord(h->ev_kv_far, h->comm_stream));
+      // remote spans in the order they become available: near-before, near-after, far-before, far-after
+      struct Span { size_t lo, hi; int ev; } spans[4] = {
+          {offs[near_lo], offs[n.rank], 0}, {offs[n.rank + 1], offs[near_hi + 1], 0},
+          {0, offs[near_lo], 1}, {offs[near_hi + 1], offs[n.world], 1}};
+      int last = -1;
+      for (int i = 0; i < 4; ++i) if (spans[i].hi > spans[i].lo) last = i;
+      MAB_TRY(mab_stage_aat_attend(h, l, nullptr, 0, MAB_RING_FIRST | (last < 0 ? MAB_RING_LAST : 0), stream));
+      int waited = -1;
+      for (int i = 0; i < 4; ++i) {
+        if (spans[i].hi <= spans[i].lo) continue;
+        if (spans[i].ev > waited) {
+          MAB_CUDA(cudaStreamWaitEvent(st, spans[i].ev == 0 ? h->ev_kv_done : h->ev_kv_far, 0));
+          waited = spans[i].ev;
+        }
+        MAB_TRY(mab_stage_aat_attend_kv(h, l, kv + spans[i].lo, (int)((spans[i].hi - spans[i].lo) / row_bytes),
+                                        i == last ? MAB_RING_LAST : 0, stream));
+      }
     } else {
       MAB_TRY(mab_stage_aat_attend(h, l, nullptr, 0, MAB_RING_FIRST | MAB_RING_LAST, stream));
     }
