@@ -72,3 +72,45 @@ def test_config2_32_views_multimodal(synthetic_sd):
 
     views = weights.add_multimodal_inputs(weights.synthetic_views(32, 392, 518, seed=1), seed=2)
     _assert_case(*_run_case("config2_32views_518x392_multimodal", views, synthetic_sd))
+
+
+def test_unit_gain_checkpoint_tracks_the_reference_bf16_path(monkeypatch):
+    """The parity checkpoints damp every residual branch (synthetic.BRANCH_GAIN = 0.1, as trained checkpoints'
+    LayerScale does) so that BASELINE.json's absolute tolerances mean something.  With the reference's OWN
+    initialiser scale (LayerScale gamma = 1, un-damped xavier branches) the 48-block trunk
+    amplifies bf16 rounding to ~1e-2 at the trunk outputs and > 1 deg at the pose in the reference's own
+    autocast path, so no absolute tolerance holds for either implementation.  What must still hold, and what
+    this records in the parity report: the CUDA path is no further from fp32 than a small multiple (5x, the
+    two paths carry independent noise draws) of the reference's own bf16 path, key by key."""
+    from mapanything_b200 import MapAnything, synthetic
+    from oracle import mapanything_oracle as orc
+    from tests import helpers
+
+    monkeypatch.setattr(synthetic, "BRANCH_GAIN", 1.0)
+    sd = synthetic.synthetic_state_dict()
+    monkeypatch.undo()
+    views = synthetic.synthetic_views(4, 392, 518, seed=1)
+    m = MapAnything(device="cuda:0", head_chunk=4)
+    m.load_state_dict(sd)
+    sd_cuda = {k: v.cuda() for k, v in sd.items()}
+    preds = m.infer(_to_cuda(views))
+    torch.cuda.synchronize()
+    with helpers.strict_fp32():
+        ref = orc.infer(sd_cuda, _to_cuda(views))
+    amp = orc.infer(sd_cuda, _to_cuda(views), amp=True)
+    entry = helpers.record_parity("unit_gain_checkpoint_4views_518x392", helpers.compare_pred_lists(preds, ref),
+                                  helpers.compare_pred_lists(amp, ref),
+                                  extra={"views": 4, "H": 392, "W": 518, "branch_gain": 1.0})
+    print("unit gain cuda     :", {k: round(v, 5) for k, v in entry["cuda"].items()})
+    print("unit gain ref bf16 :", {k: round(v, 5) for k, v in entry["ref_bf16"].items()})
+    bad = []
+    for k, v in entry["cuda"].items():
+        y = entry["ref_bf16"][k]
+        if k.endswith("_agree"):
+            if (1.0 - v) > max(1.0 - helpers.MIN_MASK_AGREE, 5.0 * (1.0 - y)):
+                bad.append((k, v, y))
+        elif v > max(TOL_POSE_DEG if k.endswith("_deg") else TOL_DENSE, 5.0 * y):
+            bad.append((k, v, y))
+    assert not bad, bad
+    del m
+    torch.cuda.empty_cache()
