@@ -74,6 +74,18 @@ def test_config2_32_views_multimodal(synthetic_sd):
     _assert_case(*_run_case("config2_32views_518x392_multimodal", views, synthetic_sd))
 
 
+def test_fixed_scene_64_views_518x392_image_only(synthetic_sd):
+    """The `fixed_scene` leg of every bench line (64 views, one scene: global attention over 66 305 tokens,
+    519 K/V tiles per query tile, the two-tile attention kernel) against the fp32 oracle on the same GPU."""
+    from oracle import weights
+
+    free, _ = torch.cuda.mem_get_info()
+    if free < 100 << 30:
+        pytest.skip("the fp32 oracle needs ~60 GB for 64 views")
+    views = weights.synthetic_views(64, 392, 518, seed=1)
+    _assert_case(*_run_case("fixed_scene_64views_518x392_image_only", views, synthetic_sd))
+
+
 def test_unit_gain_checkpoint_tracks_the_reference_bf16_path(monkeypatch):
     """The parity checkpoints damp every residual branch (synthetic.BRANCH_GAIN = 0.1, as trained checkpoints'
     LayerScale does) so that BASELINE.json's absolute tolerances mean something.  With the reference's OWN
