@@ -12,12 +12,13 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("n_views,H,W,mode", [(5, 70, 98, "img"), (4, 392, 518, "img"), (5, 70, 98, "mm"), (5, 70, 98, "viewpe")])
+@pytest.mark.parametrize("n_views,H,W,mode", [(5, 70, 98, "img"), (4, 392, 518, "img"), (5, 70, 98, "mm"), (5, 70, 98, "viewpe"),
+                                                 (48, 392, 518, "img")])
 def test_sharded_equals_single(n_views, H, W, mode):
     ngpu = torch.cuda.device_count()
     if ngpu < 2:
         pytest.skip("needs >= 2 GPUs")
-    world = 2 if n_views < 8 else min(ngpu, 4)
+    world = 2 if n_views < 8 else min(ngpu, 4)  # 48 views: 24 or 12 per rank, the two-tile attention kernel
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", "29731",
            os.path.join(ROOT, "tests", "dist_sharded_check.py"), str(n_views), str(H), str(W), mode]
