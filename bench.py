@@ -125,6 +125,27 @@ def _reference_runner():
             with contextlib.redirect_stdout(io.StringIO()):
                 return model.infer(vs, use_amp=amp, amp_dtype="bf16")
 
+        def forward_only(views, device):
+            """The reference's forward() alone, the way its infer() calls it (model.py:2304-2338): views on the
+            device, validated and pre-processed once outside the timed call, bf16 autocast."""
+            from mapanything.utils.inference import (preprocess_input_views_for_inference,
+                                                     validate_input_views_for_inference)
+            if state["dev"] != device:
+                model.to(device)
+                state["dev"] = device
+            vs = [{k: (t.to(device) if torch.is_tensor(t) else t) for k, t in v.items()} for v in views]
+            pv = preprocess_input_views_for_inference(validate_input_views_for_inference(vs))
+            model._configure_geometric_input_config(use_calibration=True, use_depth=True, use_pose=True,
+                                                    use_depth_scale=True, use_pose_scale=True)
+
+            def step():
+                with torch.inference_mode(), torch.autocast("cuda", enabled=True, dtype=torch.bfloat16), \
+                        contextlib.redirect_stdout(io.StringIO()):
+                    return model.forward(pv, memory_efficient_inference=False)
+
+            return step, model._restore_original_geometric_input_config
+
+        run.forward_only = forward_only
         return "reference", time.perf_counter() - t0, run
     from oracle import mapanything_oracle as orc
 
@@ -225,6 +246,26 @@ def cpu_and_gpu_baseline_legs(dev, budget_s=25.0):
         gpu = {"value": VIEWS_PER_GPU / dt_inf, "unit": UNIT, "ms_per_step": dt_inf * 1e3, "kind": kind,
                "what": "infer(use_amp=True, amp_dtype='bf16') of the 8-view scene on the same B200, inputs on the "
                        "device, wall clock incl. the reference's host-side numpy post-processing"}
+        if hasattr(run, "forward_only"):
+            # the reference's forward() alone (no post-processing): its eager library kernels against this
+            # repo's forward, CUDA events, 10 calls after 3 warm-ups
+            step, restore = run.forward_only(views, dname)
+            try:
+                for _ in range(3):
+                    step()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(10):
+                    step()
+                e1.record()
+                torch.cuda.synchronize()
+                ms_f = e0.elapsed_time(e1) / 10
+                gpu["forward_only"] = {"ms_per_step": ms_f, "views_per_s": VIEWS_PER_GPU / (ms_f * 1e-3),
+                                       "what": "the reference's forward() alone under bf16 autocast (eager PyTorch: "
+                                               "library SDPA / cuBLASLt / cuDNN), no post-processing, CUDA events"}
+            finally:
+                restore()
     except Exception as e:  # the baseline leg must never take the bench line down
         gpu = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
     return cpu, gpu
