@@ -17,7 +17,7 @@
 //   P_t(j) = exp2(...)      softmax warps: S row read ONCE into registers, bf16 P -> TMEM P_t
 //   O_t   += P_t(j) V_j     TS MMA 128x64x128 (A operand from TMEM, V MN-major from smem),
 //                           accumulated in TMEM over the whole K/V loop
-// TMEM reads are the scarce resource of the softmax (64-128 B/clk/SM): S is therefore loaded once
+// S is loaded from TMEM once
 // (128 registers per row) and O never leaves TMEM inside the loop.  The running max is only
 // advanced when a row's new maximum exceeds the reference by more than 2^8 (exp2 domain), so the
 // O rescale (TMEM load-scale-store by the row's own thread) is rare; P <= 256 stays exact enough
@@ -42,11 +42,13 @@ constexpr int ATT_KV_STAGES = 4;
 // Which of the 16 element pairs of every 32 S columns take their exponentials from a polynomial on
 // the FMA pipe instead of the MUFU (bit k = pair k).  Round 1 (one thread per row, exp-pass turns) was bound by
 // the SM's 16 MUFU lanes and gained 20 % from 5 spread pairs (0x1249).  With two threads per row and no turns
-// the kernels are bound by the TMEM read port instead (64 B/clk/SM) and the share no
-// longer matters: none / 2 / 5 of 16 pairs = 817.9 / 818.4 / 815.9 TFLOP/s at 66 305 tokens, 441 / 436 / 405 on
-// 8x16x1037 (profiles/r2_attn_variants.txt).  Default: none -- every exponential is the MUFU's ex2.approx,
-// fewer instructions per element (what counts under the 1000 W cap of the many-view regime), one
-// approximation less; the polynomial path stays selectable for experiments.
+// the share no longer matters: none / 2 / 5 of 16 pairs = 817.9 / 818.4 / 815.9 TFLOP/s at 66 305 tokens,
+// 441 / 436 / 405 on 8x16x1037 (profiles/r2_attn_variants.txt).  No single unit bounds the loop any more:
+// reading every S row from TMEM TWICE costs nothing (822 vs 821), dropping the row-max -> exp dependency and
+// the half-row exchange gains 1 %, dropping the exponentials altogether gives 1060 -- the softmax warps run
+// a latency-bound chain (ncu: issue slots 66 % busy, no pipe above 50 %).  Default: no polynomial -- every
+// exponential is the MUFU's ex2.approx, fewest instructions per element (what counts under the 1000 W cap
+// of the many-view regime), one approximation less; the polynomial path stays selectable for experiments.
 #ifndef ATT_POLY_MASK
 #define ATT_POLY_MASK 0        // long sequences (two Q tiles per CTA)
 #endif
@@ -345,6 +347,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 #pragma unroll
         for (int c = 0; c < NC; c += 32) MAB_TMEM_LD_32(ts + c, (v + c));
         tmem_wait_ld();
+#ifdef ATT_LD_TWICE   // experiment: the same S row read from TMEM a second time (is the loop bound by the TMEM read port?)
+#pragma unroll
+        for (int c = 0; c < NC; c += 32) MAB_TMEM_LD_32(ts + c, (v + c));
+        tmem_wait_ld();
+#endif
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&s_free[t]);
@@ -416,11 +423,15 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           for (int i = 0; i < NC; i += 2) {
             float x0, x1, e0, e1;
             unpack_f2(fma_f2(pack_f2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])), sc2, nmb2), x0, x1);
+#ifdef ATT_NO_EXP   // experiment (wrong results): no exponential at all -- is the loop bound by the softmax arithmetic?
+            e0 = x0; e1 = x1;
+#else
             if ((POLY_MASK >> ((i >> 1) & 15)) & 1) {
               exp2_poly2(x0, x1, e0, e1);
             } else {
               e0 = fast_exp2(x0); e1 = fast_exp2(x1);
             }
+#endif
             if (i & 2) sum_b = add_f2(sum_b, pack_f2(e0, e1));
             else sum_a = add_f2(sum_a, pack_f2(e0, e1));
             pk[i >> 1] = cvt_bf16x2(e0, e1);
