@@ -465,10 +465,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         if (take_turns && !(t == 1 && j == nkv - 1)) bar_arrive_named(1 + (t ^ 1), 2 * TILE_THREADS);
 #endif
         // ---- P_t and O_t are free once P_t(j-1) V has completed ----
+#ifndef ATT_NO_PV_WAIT   // experiment (race, wrong results): is the wait for P V(j-1) on the critical path?
         if (j > 0) {
           mbar_wait(&pv_done[t], (j - 1) & 1);
           tc_fence_after();
         }
+#endif
         if (rescale) {  // warp-uniform; rows that keep their reference multiply by 1
           const uint64_t a2 = pack_f2(alpha, alpha);
 #pragma unroll
