@@ -462,9 +462,12 @@ class MapAnything(torch.nn.Module):
         """One whole forward of this rank's views: returns the raw output tensors (views stacked).
 
         Single GPU (total_views == views): one `mab_forward` call.  View-sharded
-        (total_views > views, torch.distributed initialised, rank r holds views [view_lo, ...)): the
-        staged C ABI with ring global attention (parallel.ring_pass) and a broadcast of the metric
-        scale from the rank that owns the scale token."""
+        (total_views > views, torch.distributed initialised, rank r holds views [view_lo, ...)): one
+        `mab_forward_sharded` call -- the library exchanges the K|V rows of the global layers itself over
+        an NCCL communicator of its own (all-to-all gather overlapped with the local block) and broadcasts
+        the metric scale from the rank that owns the scale token; MAB_EXCHANGE=ring / MAB_EXCHANGE_HOST=1
+        select the per-layer schedules sequenced here through torch.distributed instead
+        (parallel.ring_pass / parallel.gather_pass over the staged C ABI)."""
         V = imgs.shape[0]
         total = int(total_views or V)
         with torch.cuda.device(self._device):
